@@ -1,0 +1,35 @@
+# Build of the B200-native library, the host driver and the test-side helpers.
+#   make            libnsgpu.so (sm_100a kernels + C ABI + host Grid/FluidSolver) and bin/main
+#   make oracle     CPU oracle (test infrastructure): oracle/libnsport.so, oracle/_ref/* when /root/reference exists
+#   make emul       tests/emul/libnsemul.so: host compile of the per-cell device functions, for the CPU-only tests
+NVCC ?= nvcc
+CXX = /usr/bin/g++
+PKG = navierstokessolver_b200
+CSRC = $(PKG)/csrc
+HOST = $(PKG)/host
+NVFLAGS = -std=c++17 -O3 -lineinfo -gencode arch=compute_100a,code=sm_100a -Xcompiler -fPIC
+CU_DEPS = $(wildcard $(CSRC)/*.cu $(CSRC)/*.cuh $(CSRC)/*.inl $(CSRC)/*.h) include/nsgpu.h
+HOST_SRC = $(wildcard $(HOST)/*.cpp)
+HOST_DEPS = $(wildcard $(HOST)/*.cpp $(HOST)/*.h)
+
+.PHONY: all oracle emul clean
+all: $(PKG)/libnsgpu.so bin/main
+
+$(PKG)/libnsgpu.so: $(CU_DEPS) $(HOST_DEPS)
+	$(NVCC) $(NVFLAGS) -shared $(CSRC)/nsgpu.cu $(HOST_SRC) -Iinclude -o $@ -lnccl
+
+bin/main: $(PKG)/libnsgpu.so $(HOST)/main/MAIN_Solver.cpp
+	@mkdir -p bin
+	$(CXX) -std=c++17 -O2 -Iinclude -I$(HOST) $(HOST)/main/MAIN_Solver.cpp -L$(PKG) -lnsgpu -Wl,-rpath,'$$ORIGIN/../$(PKG)' -o $@
+
+oracle:
+	$(MAKE) -C oracle port
+	if [ -d /root/reference/SRC ]; then $(MAKE) -C oracle ref; fi
+
+emul: tests/emul/libnsemul.so
+tests/emul/libnsemul.so: tests/emul/emul.cpp $(CSRC)/ns_cell.cuh $(CSRC)/ns_hostgeom.h include/nsgpu.h
+	$(CXX) -std=c++17 -O2 -fPIC -shared -Iinclude -I$(CSRC) tests/emul/emul.cpp -o $@
+
+clean:
+	rm -f $(PKG)/libnsgpu.so bin/main tests/emul/libnsemul.so
+	$(MAKE) -C oracle clean

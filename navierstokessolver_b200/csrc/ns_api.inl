@@ -1,0 +1,288 @@
+// ns_api.inl -- the extern "C" entry points declared in include/nsgpu.h.
+
+using namespace nsgpu;
+
+namespace nsgpu {
+
+static double** field_slot(nsgpu_ctx* ctx, int which) {
+  switch (which) {
+    case NSGPU_U: return &ctx->u;
+    case NSGPU_V: return &ctx->v;
+    case NSGPU_PHI: return &ctx->phi;
+    case NSGPU_RHS_U: return &ctx->rhs_u;
+    case NSGPU_RHS_V: return &ctx->rhs_v;
+    case NSGPU_RHS_PHI: return &ctx->rhs_phi;
+    case NSGPU_CONV_U0: return &ctx->conv_u;
+    case NSGPU_CONV_V0: return &ctx->conv_v;
+    case NSGPU_GRADPHI_X: return &ctx->gpx;
+    case NSGPU_GRADPHI_Y: return &ctx->gpy;
+    case NSGPU_USTAR: return &ctx->ustar;
+    case NSGPU_VSTAR: return &ctx->vstar;
+  }
+  return nullptr;
+}
+
+static int ensure_stage(nsgpu_ctx* ctx) {
+  if (ctx->h_stage) return 0;
+  NS_CUDA(cudaMallocHost((void**)&ctx->h_stage, ctx->levels[0].stride * sizeof(double)));
+  return 0;
+}
+
+// host compact-id order -> padded device layout
+static int upload_field(nsgpu_ctx* ctx, double* dev, const double* host) {
+  const Level& L = ctx->levels[0];
+  const LevelGeom& g = L.g;
+  NS_CUDA(cudaSetDevice(ctx->device));
+  if (ctx->rect) {
+    NS_CUDA(cudaMemcpy2DAsync(dev + cidx(g, 0, 0), (size_t)g.ld * sizeof(double), host, (size_t)g.ny * sizeof(double),
+                              (size_t)g.ny * sizeof(double), (size_t)g.nx, cudaMemcpyHostToDevice, ctx->stream));
+    NS_CUDA(cudaStreamSynchronize(ctx->stream));
+    return 0;
+  }
+  int rc = ensure_stage(ctx);
+  if (rc) return rc;
+  memset(ctx->h_stage, 0, L.stride * sizeof(double));
+  for (int i = 0; i < g.nx; i++)
+    for (int j = 0; j < g.ny; j++) {
+      const int32_t id = ctx->local_id[(size_t)i * g.ny + j];
+      if (id >= 0) ctx->h_stage[cidx(g, i, j)] = host[id];
+    }
+  NS_CUDA(cudaMemcpyAsync(dev, ctx->h_stage, L.stride * sizeof(double), cudaMemcpyHostToDevice, ctx->stream));
+  NS_CUDA(cudaStreamSynchronize(ctx->stream));
+  return 0;
+}
+
+static int download_field(nsgpu_ctx* ctx, const double* dev, double* host) {
+  const Level& L = ctx->levels[0];
+  const LevelGeom& g = L.g;
+  NS_CUDA(cudaSetDevice(ctx->device));
+  if (ctx->rect) {
+    NS_CUDA(cudaMemcpy2DAsync(host, (size_t)g.ny * sizeof(double), dev + cidx(g, 0, 0), (size_t)g.ld * sizeof(double),
+                              (size_t)g.ny * sizeof(double), (size_t)g.nx, cudaMemcpyDeviceToHost, ctx->stream));
+    NS_CUDA(cudaStreamSynchronize(ctx->stream));
+    return 0;
+  }
+  int rc = ensure_stage(ctx);
+  if (rc) return rc;
+  NS_CUDA(cudaMemcpyAsync(ctx->h_stage, dev, L.stride * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
+  NS_CUDA(cudaStreamSynchronize(ctx->stream));
+  for (int i = 0; i < g.nx; i++)
+    for (int j = 0; j < g.ny; j++) {
+      const int32_t id = ctx->local_id[(size_t)i * g.ny + j];
+      if (id >= 0) host[id] = ctx->h_stage[cidx(g, i, j)];
+    }
+  return 0;
+}
+
+static int sync_check(nsgpu_ctx* ctx) {
+  NS_CUDA(cudaStreamSynchronize(ctx->stream));
+  NS_CUDA(cudaGetLastError());
+  return 0;
+}
+
+static void fill_info(nsgpu_step_info* info, const SolveResult& ru, const SolveResult& rv, const SolveResult& rp) {
+  info->it_u = ru.cycles; info->it_v = rv.cycles; info->it_phi = rp.cycles;
+  info->res_u = ru.rel; info->res_v = rv.rel; info->res_phi = rp.rel;
+}
+
+}  // namespace nsgpu
+
+extern "C" {
+
+int nsgpu_nccl_unique_id(void* out128) {
+  ncclUniqueId id;
+  if (ncclGetUniqueId(&id) != ncclSuccess) return NSGPU_ERR_NCCL;
+  static_assert(sizeof(id) == 128, "ncclUniqueId is 128 bytes");
+  memcpy(out128, &id, sizeof id);
+  return 0;
+}
+
+int nsgpu_create(const nsgpu_grid* grid, const nsgpu_params* params, nsgpu_ctx** out) {
+  if (!out) return NSGPU_ERR_ARG;
+  *out = nullptr;
+  nsgpu_ctx* ctx = new nsgpu_ctx;
+  int rc = create_impl(ctx, grid, params);
+  if (rc) {
+    g_create_error = ctx->err;
+    destroy_ctx(ctx);
+    return rc;
+  }
+  *out = ctx;
+  return 0;
+}
+
+void nsgpu_destroy(nsgpu_ctx* ctx) { destroy_ctx(ctx); }
+
+const char* nsgpu_last_error(const nsgpu_ctx* ctx) { return ctx ? ctx->err.c_str() : g_create_error.c_str(); }
+
+int nsgpu_local_range(const nsgpu_ctx* ctx, int32_t* i0, int32_t* i1, int64_t* id0, int64_t* n_local) {
+  if (!ctx) return NSGPU_ERR_ARG;
+  if (i0) *i0 = ctx->i0;
+  if (i1) *i1 = ctx->i1;
+  if (id0) *id0 = ctx->id0;
+  if (n_local) *n_local = ctx->n_local;
+  return 0;
+}
+
+int nsgpu_num_levels(const nsgpu_ctx* ctx) { return ctx ? (int)ctx->levels.size() : 0; }
+int64_t nsgpu_kernel_launches(const nsgpu_ctx* ctx) { return ctx ? ctx->launches : 0; }
+int nsgpu_synchronize(nsgpu_ctx* ctx) { if (!ctx) return NSGPU_ERR_ARG; cudaSetDevice(ctx->device); return sync_check(ctx); }
+
+int nsgpu_get_array(nsgpu_ctx* ctx, int32_t which, double* out) {
+  if (!ctx || !out) return NSGPU_ERR_ARG;
+  double** s = field_slot(ctx, which);
+  if (!s) { ctx->err = "unknown array id"; return NSGPU_ERR_ARG; }
+  return download_field(ctx, *s, out);
+}
+int nsgpu_set_array(nsgpu_ctx* ctx, int32_t which, const double* in) {
+  if (!ctx || !in) return NSGPU_ERR_ARG;
+  double** s = field_slot(ctx, which);
+  if (!s) { ctx->err = "unknown array id"; return NSGPU_ERR_ARG; }
+  return upload_field(ctx, *s, in);
+}
+int nsgpu_get_fields(nsgpu_ctx* ctx, double* u, double* v, double* phi) {
+  int rc = 0;
+  if (u && (rc = nsgpu_get_array(ctx, NSGPU_U, u))) return rc;
+  if (v && (rc = nsgpu_get_array(ctx, NSGPU_V, v))) return rc;
+  if (phi && (rc = nsgpu_get_array(ctx, NSGPU_PHI, phi))) return rc;
+  return 0;
+}
+int nsgpu_set_fields(nsgpu_ctx* ctx, const double* u, const double* v, const double* phi) {
+  int rc = 0;
+  if (u && (rc = nsgpu_set_array(ctx, NSGPU_U, u))) return rc;
+  if (v && (rc = nsgpu_set_array(ctx, NSGPU_V, v))) return rc;
+  if (phi && (rc = nsgpu_set_array(ctx, NSGPU_PHI, phi))) return rc;
+  return 0;
+}
+
+int nsgpu_rhs_build(nsgpu_ctx* ctx) {
+  if (!ctx) return NSGPU_ERR_ARG;
+  cudaSetDevice(ctx->device);
+  int rc = phase_rhs(ctx);
+  return rc ? rc : sync_check(ctx);
+}
+
+int nsgpu_solve_velocity(nsgpu_ctx* ctx, nsgpu_step_info* info) {
+  if (!ctx) return NSGPU_ERR_ARG;
+  cudaSetDevice(ctx->device);
+  SolveResult ru, rv, rp;
+  int rc = phase_velocity(ctx, &ru, &rv);
+  if (rc) return rc;
+  if ((rc = sync_check(ctx))) return rc;
+  if (info) { memset(info, 0, sizeof *info); fill_info(info, ru, rv, rp); }
+  return (ru.converged && rv.converged) ? 0 : NSGPU_ERR_NOT_CONVERGED;
+}
+
+int nsgpu_div_rhs(nsgpu_ctx* ctx, int32_t remove_mean) {
+  if (!ctx) return NSGPU_ERR_ARG;
+  cudaSetDevice(ctx->device);
+  int rc = phase_div(ctx, remove_mean != 0);
+  return rc ? rc : sync_check(ctx);
+}
+
+int nsgpu_solve_phi(nsgpu_ctx* ctx, nsgpu_step_info* info) {
+  if (!ctx) return NSGPU_ERR_ARG;
+  cudaSetDevice(ctx->device);
+  SolveResult ru, rv, rp;
+  int rc = phase_phi(ctx, &rp);
+  if (rc) return rc;
+  if ((rc = sync_check(ctx))) return rc;
+  if (info) { memset(info, 0, sizeof *info); fill_info(info, ru, rv, rp); }
+  return rp.converged ? 0 : NSGPU_ERR_NOT_CONVERGED;
+}
+
+int nsgpu_correct(nsgpu_ctx* ctx, nsgpu_step_info* info) {
+  if (!ctx) return NSGPU_ERR_ARG;
+  cudaSetDevice(ctx->device);
+  double mm[4];
+  int rc = phase_correct(ctx, mm);
+  if (rc) return rc;
+  if (info) { memset(info, 0, sizeof *info); info->umin = mm[0]; info->umax = mm[1]; info->vmin = mm[2]; info->vmax = mm[3]; }
+  return 0;
+}
+
+int nsgpu_step(nsgpu_ctx* ctx, int32_t n_steps, nsgpu_step_info* last) {
+  if (!ctx || n_steps < 0) return NSGPU_ERR_ARG;
+  cudaSetDevice(ctx->device);
+  SolveResult ru, rv, rp;
+  double mm[4] = {0, 0, 0, 0};
+  const int64_t l0 = ctx->launches;
+  const double s0 = ctx->fine_sweeps_phi;
+  int status = 0, rc;
+  NS_CUDA(cudaEventRecord(ctx->ev0, ctx->stream));
+  for (int s = 0; s < n_steps; s++) {
+    if ((rc = phase_rhs(ctx))) return rc;
+    if ((rc = phase_velocity(ctx, &ru, &rv))) return rc;
+    if ((rc = phase_div(ctx, true))) return rc;
+    if ((rc = phase_phi(ctx, &rp))) return rc;
+    if ((rc = phase_correct(ctx, (s == n_steps - 1) ? mm : nullptr))) return rc;
+    if (!(ru.converged && rv.converged && rp.converged)) status = NSGPU_ERR_NOT_CONVERGED;   // silent in the reference
+  }
+  NS_CUDA(cudaEventRecord(ctx->ev1, ctx->stream));
+  if ((rc = sync_check(ctx))) return rc;
+  float ms = 0;
+  NS_CUDA(cudaEventElapsedTime(&ms, ctx->ev0, ctx->ev1));
+  if (n_steps > 0 && !(std::isfinite(mm[0]) && std::isfinite(mm[1]) && std::isfinite(mm[2]) && std::isfinite(mm[3]))) status = NSGPU_ERR_NAN;
+  if (last) {
+    memset(last, 0, sizeof *last);
+    fill_info(last, ru, rv, rp);
+    last->umin = mm[0]; last->umax = mm[1]; last->vmin = mm[2]; last->vmax = mm[3];
+    last->fine_sweeps = ctx->fine_sweeps_phi - s0;
+    last->ms_total = ms;
+    last->kernel_launches = (int32_t)(ctx->launches - l0);
+    last->status = status;
+  }
+  return status;
+}
+
+int nsgpu_poisson_sweeps(nsgpu_ctx* ctx, int32_t n_sweeps, double* residual_l2, float* ms) {
+  if (!ctx || n_sweeps < 0) return NSGPU_ERR_ARG;
+  cudaSetDevice(ctx->device);
+  const Level& L = ctx->levels[0];
+  int rc;
+  if ((rc = halo_exchange(ctx, L, ctx->rhs_phi, 1))) return rc;
+  NS_CUDA(cudaEventRecord(ctx->ev0, ctx->stream));
+  if ((rc = smooth(ctx, L, coef_phi(), &ctx->phi, &ctx->tmp, ctx->rhs_phi, n_sweeps))) return rc;
+  NS_CUDA(cudaEventRecord(ctx->ev1, ctx->stream));
+  if ((rc = sync_check(ctx))) return rc;
+  if (ms) NS_CUDA(cudaEventElapsedTime(ms, ctx->ev0, ctx->ev1));
+  if (residual_l2) {
+    double h;
+    if ((rc = residual_norm2(ctx, L, coef_phi(), ctx->phi, ctx->rhs_phi, ctx->d_scal + 24))) return rc;
+    if ((rc = read_scalars(ctx, ctx->d_scal + 24, 1, &h))) return rc;
+    *residual_l2 = std::sqrt(h);
+  }
+  return 0;
+}
+
+int nsgpu_apply_operator(nsgpu_ctx* ctx, int32_t op, const double* x, double* y) {
+  if (!ctx || !x || !y || (op != 0 && op != 1)) return NSGPU_ERR_ARG;
+  cudaSetDevice(ctx->device);
+  const Level& L = ctx->levels[0];
+  // scratch: the smoother's ping-pong partner holds x, rhs_phi's slot is NOT touched: use two lazily made arrays
+  static const int SCR = 2;
+  if (!ctx->kry[0]) for (int k = 0; k < SCR; k++) { int rc = dev_zeros(ctx, ctx->owned, L.stride, &ctx->kry[k]); if (rc) return rc; }
+  int rc;
+  if ((rc = upload_field(ctx, ctx->kry[0], x))) return rc;
+  if ((rc = apply_op(ctx, L, op == 0 ? coef_v(ctx) : coef_phi(), ctx->kry[0], ctx->kry[1], nullptr, nullptr))) return rc;
+  if ((rc = sync_check(ctx))) return rc;
+  return download_field(ctx, ctx->kry[1], y);
+}
+
+int nsgpu_pressure(nsgpu_ctx* ctx, double* pr, double* lap_phi) {
+  if (!ctx || !pr) return NSGPU_ERR_ARG;
+  cudaSetDevice(ctx->device);
+  const Level& L = ctx->levels[0];
+  if (!ctx->kry[0]) for (int k = 0; k < 2; k++) { int rc = dev_zeros(ctx, ctx->owned, L.stride, &ctx->kry[k]); if (rc) return rc; }
+  int rc;
+  if ((rc = apply_op(ctx, L, coef_phi(), ctx->phi, ctx->kry[1], nullptr, nullptr))) return rc;
+  if ((rc = sync_check(ctx))) return rc;
+  std::vector<double> lap((size_t)ctx->n_local), ph((size_t)ctx->n_local);
+  if ((rc = download_field(ctx, ctx->kry[1], lap.data()))) return rc;
+  if ((rc = download_field(ctx, ctx->phi, ph.data()))) return rc;
+  const double f = ctx->dt / (2.0 * ctx->re);
+  for (size_t k = 0; k < lap.size(); k++) { pr[k] = ph[k] - f * lap[k]; if (lap_phi) lap_phi[k] = lap[k]; }   // FS.cpp:579-581
+  return 0;
+}
+
+}  // extern "C"

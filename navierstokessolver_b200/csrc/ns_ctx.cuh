@@ -1,0 +1,67 @@
+// ns_ctx.cuh -- device-side state of one FluidSolver (host bookkeeping of libnsgpu.so).
+#pragma once
+#include <cuda_runtime.h>
+#include <nccl.h>
+#include <string>
+#include <vector>
+#include <cstdio>
+#include <cstring>
+#include <cmath>
+#include "../../include/nsgpu.h"
+#include "ns_kernels.cuh"
+#include "ns_hostgeom.h"
+
+namespace nsgpu {
+
+struct Level {
+  LevelGeom g{};
+  int cx = 1, cy = 1;        // coarsening factors towards the next (coarser) level
+  int gny = 0;
+  size_t stride = 0;         // doubles per field on this level: (nx + 2HX) * ld
+  double* x = nullptr;       // levels >= 1: correction, ping-pong partner, right-hand side
+  double* xt = nullptr;
+  double* b = nullptr;
+  std::vector<void*> owned;  // device allocations of this level (geometry arrays)
+  int coarse_sweeps = 0;     // only used on the coarsest level
+};
+
+struct SolveResult { int cycles = 0; double rel = 0.0; bool converged = false; };
+
+}  // namespace nsgpu
+
+struct nsgpu_ctx {
+  std::string err;
+  int device = 0, rank = 0, world = 1;
+  bool rect = true;
+  double dt = 0, re = 0;
+  double rtol_u = 1e-8, rtol_phi = 1e-8;
+  int max_cycles = 200, nu_pre = 2, nu_post = 2, solver = 0, use_graph = 0;
+  cudaStream_t stream = nullptr;
+  cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+  ncclComm_t comm = nullptr;
+
+  // global description
+  int gnx = 0, ny = 0;
+  int i0 = 0, i1 = 0;           // owned columns
+  int64_t id0 = 0, n_local = 0; // compact ids owned by this rank
+  int64_t n_cells_global = 0;
+  std::vector<int32_t> local_id;  // general domains: compact local id per (i - i0, j) or -1
+
+  std::vector<nsgpu::Level> levels;
+  nsgpu::EdgeDev* d_edges = nullptr;
+
+  // fine-level fields (each `stride` doubles)
+  double *u = nullptr, *v = nullptr, *phi = nullptr;
+  double *conv_u = nullptr, *conv_v = nullptr, *gpx = nullptr, *gpy = nullptr;
+  double *rhs_u = nullptr, *rhs_v = nullptr, *rhs_phi = nullptr, *ustar = nullptr, *vstar = nullptr;
+  double* tmp = nullptr;        // ping-pong partner of the fine-level smoother
+  double* kry[8] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};  // BiCGStab vectors (solver == 1)
+
+  nsgpu::Reducer red{};
+  double* d_scal = nullptr;     // device scalars (64 doubles)
+  double* h_scal = nullptr;     // pinned mirror
+  double* h_stage = nullptr;    // host staging for general-domain field transfers
+  int64_t launches = 0;
+  double fine_sweeps_phi = 0;
+  std::vector<void*> owned;
+};

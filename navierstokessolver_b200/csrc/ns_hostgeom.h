@@ -1,0 +1,265 @@
+// ns_hostgeom.h -- pure host C++ (no CUDA): turns the flattened Grid descriptor (include/nsgpu.h) into the per-level
+// coefficient tables, flag bytes and the coarsening plan the kernels consume.  Restates, matrix-free, what
+// ConstructGhostStencils / ConstructLHS set up in the reference (FS.cpp:84-164).
+#pragma once
+#include <algorithm>
+#include <cstdint>
+#include <cstdio>
+#include <string>
+#include <vector>
+#include "../../include/nsgpu.h"
+#include "ns_cell.cuh"
+
+namespace nsgpu {
+
+// One level over the GLOBAL domain.
+struct HostLevel {
+  int gnx = 0, ny = 0;
+  std::vector<double> hx, hy;
+  std::vector<uint8_t> flags;  // [gnx*ny], empty on the rectangle fast path
+};
+
+struct HostPlan {
+  bool rect = true;
+  uint8_t side_out[4] = {0, 0, 0, 0}, side_edge[4] = {0, 0, 0, 0};
+  std::vector<EdgeDev> edges;
+  std::vector<uint8_t> cedges0;       // [4*gnx*ny] edge ids, general domains only
+  std::vector<HostLevel> levels;
+  std::vector<int> lnx, lgi0, lcx, lcy;  // per level: local columns, global index of local column 0, coarsening factors
+  int64_t n_cells_global = 0;
+  int i0 = 0, i1 = 0;
+  int64_t id0 = 0, n_local = 0;
+  std::vector<int32_t> local_id;      // general domains: compact local id per (i - i0, j), -1 outside
+};
+
+// 1-D tables of one level for the local slab [gi0, gi0 + nx), indexed with the halo/padding offsets.
+struct GeomArrays {
+  int nx = 0, ny = 0, ld = 0, gi0 = 0, gnx = 0;
+  size_t stride = 0;
+  std::vector<double> hx, hy, rhx, rhy, rsx, rsy, bx, by;
+  std::vector<Pair> ax, ay;
+  std::vector<uint8_t> flags, cedges;  // padded layout; empty on the rectangle fast path
+};
+
+static inline double clamp_get(const std::vector<double>& a, int k) {
+  if (k < 0) k = 0;
+  if (k >= (int)a.size()) k = (int)a.size() - 1;
+  return a[k];
+}
+
+static inline void make_geom_arrays(const HostLevel& H, int gi0, int nx, const std::vector<uint8_t>* cedges_global, GeomArrays& A) {
+  const int ny = H.ny;
+  A.nx = nx; A.ny = ny; A.gi0 = gi0; A.gnx = H.gnx;
+  A.ld = ((ny + 3) / 4) * 4 + 2 * PJ;
+  A.stride = (size_t)(nx + 2 * HX) * A.ld;
+  const int nxa = nx + 2 * HX, nya = ny + 2 * PJ;
+  A.hx.resize(nxa); A.rhx.resize(nxa); A.rsx.resize(nxa); A.bx.resize(nxa); A.ax.resize(nxa);
+  A.hy.resize(nya); A.rhy.resize(nya); A.rsy.resize(nya); A.by.resize(nya); A.ay.resize(nya);
+  for (int a = 0; a < nxa; a++) {
+    const int ig = gi0 + a - HX;
+    const double h = clamp_get(H.hx, ig), hm = clamp_get(H.hx, ig - 1), hp = clamp_get(H.hx, ig + 1);
+    A.hx[a] = h; A.rhx[a] = 1.0 / h; A.rsx[a] = 1.0 / (h + hp);
+    A.ax[a].m = 2.0 / (h * (h + hm)); A.ax[a].p = 2.0 / (h * (h + hp));   // FS.cpp:119
+    A.bx[a] = 1.0 / (h * h);                                              // FS.cpp:125
+  }
+  for (int a = 0; a < nya; a++) {
+    const int jg = a - PJ;
+    const double h = clamp_get(H.hy, jg), hm = clamp_get(H.hy, jg - 1), hp = clamp_get(H.hy, jg + 1);
+    A.hy[a] = h; A.rhy[a] = 1.0 / h; A.rsy[a] = 1.0 / (h + hp);
+    A.ay[a].m = 2.0 / (h * (h + hm)); A.ay[a].p = 2.0 / (h * (h + hp));   // FS.cpp:120
+    A.by[a] = 1.0 / (h * h);                                              // FS.cpp:126
+  }
+  A.flags.clear(); A.cedges.clear();
+  if (!H.flags.empty()) {
+    A.flags.assign(A.stride, (uint8_t)F_OUTSIDE);
+    for (int a = 0; a < nxa; a++) {
+      const int ig = gi0 + a - HX;
+      if (ig < 0 || ig >= H.gnx) continue;
+      for (int j = 0; j < ny; j++) A.flags[(size_t)a * A.ld + j + PJ] = H.flags[(size_t)ig * ny + j];
+    }
+    if (cedges_global) {
+      A.cedges.assign(4 * A.stride, (uint8_t)0);
+      for (int a = 0; a < nxa; a++) {
+        const int ig = gi0 + a - HX;
+        if (ig < 0 || ig >= H.gnx) continue;
+        for (int j = 0; j < ny; j++)
+          for (int k = 0; k < 4; k++) A.cedges[4 * ((size_t)a * A.ld + j + PJ) + k] = (*cedges_global)[4 * ((size_t)ig * ny + j) + k];
+      }
+    }
+  }
+}
+
+// Fill a LevelGeom with pointers (host or device copies of the GeomArrays tables).
+static inline void geom_scalars(const GeomArrays& A, const HostPlan& P, LevelGeom& g) {
+  g.nx = A.nx; g.ny = A.ny; g.ld = A.ld; g.gi0 = A.gi0; g.gnx = A.gnx;
+  for (int k = 0; k < 4; k++) { g.side_out[k] = P.side_out[k]; g.side_edge[k] = P.side_edge[k]; }
+}
+
+static inline double mean_of(const std::vector<double>& a) {
+  double s = 0;
+  for (double x : a) s += x;
+  return s / (double)a.size();
+}
+
+// Validates the descriptor and builds edges, flags, the slab of `rank` and the multigrid coarsening plan.
+// Returns 0 or a negative nsgpu_status with `err` filled.
+static inline int make_host_plan(const nsgpu_grid* G, int rank, int world, int max_levels_in, HostPlan& P, std::string& err) {
+  if (!G) { err = "null grid"; return NSGPU_ERR_ARG; }
+  if (G->nx < 1 || G->ny < 1 || !G->hx || !G->hy) { err = "bad grid extents"; return NSGPU_ERR_ARG; }
+  if (G->n_edges < 1 || G->n_edges > 255 || !G->edge_nx || !G->edge_ny || !G->edge_bc_type || !G->edge_bc_info) {
+    err = "edge list missing (1..255 edges)"; return NSGPU_ERR_ARG;
+  }
+  if ((G->cell_id == nullptr) != (G->cell_edges == nullptr)) { err = "cell_id and cell_edges must both be given or both be NULL"; return NSGPU_ERR_ARG; }
+  if (world < 1 || rank < 0 || rank >= world) { err = "rank outside [0, world)"; return NSGPU_ERR_ARG; }
+  const int gnx = G->nx, ny = G->ny;
+
+  // ---- edges (ConstructGhostStencils, FS.cpp:84-103)
+  P.edges.assign(G->n_edges, EdgeDev{});
+  for (int e = 0; e < G->n_edges; e++) {
+    const int t = G->edge_bc_type[e];
+    EdgeDev& E = P.edges[e];
+    E.nx = G->edge_nx[e]; E.ny = G->edge_ny[e]; E.cu = 0; E.cv = 0; E.outflow = 0; E.pad = 0;
+    if ((E.nx != 0) == (E.ny != 0)) { err = "edge normal must be axis aligned"; return NSGPU_ERR_ARG; }
+    const double c = 2.0 * G->edge_bc_info[e];
+    if (t == 0) { if (E.nx == 0) E.cv = c; else E.cu = c; }          // uniform inlet: normal component (FS.cpp:89-92)
+    else if (t == 2) { if (E.nx != 0) E.cv = c; else E.cu = c; }     // wall: tangential component (FS.cpp:93-96)
+    else if (t == 4) { E.outflow = 1; }                              // zero-gradient outflow (FS.cpp:98-101)
+    else {
+      char buf[160];
+      snprintf(buf, sizeof buf, "edge %d: bcType %d is not implemented by the reference either (FS.cpp:86-101)", e, t);
+      err = buf; return NSGPU_ERR_BC;
+    }
+  }
+
+  // ---- domain shape
+  HostLevel H0;
+  H0.gnx = gnx; H0.ny = ny;
+  H0.hx.assign(G->hx, G->hx + gnx);
+  H0.hy.assign(G->hy, G->hy + ny);
+  for (double h : H0.hx) if (!(h > 0)) { err = "non-positive hx"; return NSGPU_ERR_ARG; }
+  for (double h : H0.hy) if (!(h > 0)) { err = "non-positive hy"; return NSGPU_ERR_ARG; }
+  bool full = true;
+  if (G->cell_id) for (size_t c = 0; c < (size_t)gnx * ny; c++) if (G->cell_id[c] < 0) { full = false; break; }
+  bool rect = full && G->n_edges == 4;
+  if (rect) {
+    int seen[4] = {0, 0, 0, 0};
+    for (int e = 0; e < 4; e++) {
+      int k = P.edges[e].nx == -1 ? 0 : P.edges[e].nx == 1 ? 1 : P.edges[e].ny == -1 ? 2 : 3;
+      seen[k]++; P.side_edge[k] = (uint8_t)e; P.side_out[k] = (uint8_t)P.edges[e].outflow;
+    }
+    for (int k = 0; k < 4; k++) if (seen[k] != 1) rect = false;
+  }
+  if (!rect && !G->cell_id) { err = "cell_id/cell_edges are required unless the domain is a rectangle with one edge per side"; return NSGPU_ERR_ARG; }
+  P.rect = rect;
+  if (!rect) { for (int k = 0; k < 4; k++) { P.side_out[k] = 0; P.side_edge[k] = 0; } }
+
+  const int dx[4] = {-1, 1, 0, 0}, dy[4] = {0, 0, -1, 1};
+  if (G->cell_id) {   // validate the tags even when the fast path will ignore them
+    std::vector<uint8_t> fl((size_t)gnx * ny, (uint8_t)F_OUTSIDE);
+    P.cedges0.assign((size_t)4 * gnx * ny, 0);
+    int64_t count = 0;
+    for (int i = 0; i < gnx; i++)
+      for (int j = 0; j < ny; j++) {
+        const size_t c = (size_t)i * ny + j;
+        if (G->cell_id[c] < 0) continue;
+        if (G->cell_id[c] != count) { err = "cell ids must be compact and ordered i-major (Grid.cpp:149-161)"; return NSGPU_ERR_ARG; }
+        count++;
+        unsigned f = 0;
+        for (int k = 0; k < 4; k++) {
+          const int in = i + dx[k], jn = j + dy[k];
+          const bool present = in >= 0 && in < gnx && jn >= 0 && jn < ny && G->cell_id[(size_t)in * ny + jn] >= 0;
+          const int e = G->cell_edges[4 * c + k];
+          if (present != (e < 0) || e >= G->n_edges) {
+            char buf[220];
+            snprintf(buf, sizeof buf, "cell (%d,%d) side %d: edge tag %d inconsistent with the neighbour cell (the reference would index out of bounds)", i, j, k, e);
+            err = buf; return NSGPU_ERR_ARG;
+          }
+          if (present) f |= (1u << k);
+          else { P.cedges0[4 * c + k] = (uint8_t)e; if (P.edges[e].outflow) f |= (16u << k); }
+        }
+        fl[c] = (uint8_t)f;
+      }
+    if (count != G->n_cells) { err = "n_cells does not match cell_id"; return NSGPU_ERR_ARG; }
+    P.n_cells_global = count;
+    if (!rect) H0.flags.swap(fl); else P.cedges0.clear();
+  } else {
+    if (G->n_cells != gnx * ny) { err = "n_cells does not match nx*ny"; return NSGPU_ERR_ARG; }
+    P.n_cells_global = (int64_t)gnx * ny;
+  }
+
+  // ---- slab of this rank
+  if (gnx % world != 0) { err = "nx must be divisible by the number of ranks"; return NSGPU_ERR_ARG; }
+  const int nxl = gnx / world;
+  if (world > 1 && nxl < 2) { err = "slab thinner than the 2-column halo"; return NSGPU_ERR_ARG; }
+  P.i0 = rank * nxl; P.i1 = P.i0 + nxl;
+  if (rect) { P.id0 = (int64_t)P.i0 * ny; P.n_local = (int64_t)nxl * ny; }
+  else {
+    P.local_id.assign((size_t)nxl * ny, -1);
+    int64_t before = 0, mine = 0;
+    for (int i = 0; i < gnx; i++)
+      for (int j = 0; j < ny; j++) {
+        if (G->cell_id[(size_t)i * ny + j] < 0) continue;
+        if (i < P.i0) before++;
+        else if (i < P.i1) P.local_id[(size_t)(i - P.i0) * ny + j] = (int32_t)mine++;
+      }
+    P.id0 = before; P.n_local = mine;
+  }
+
+  // ---- level hierarchy (rediscretisation: coarse h = sum of the children's h)
+  P.levels.clear();
+  P.levels.push_back(std::move(H0));
+  P.lnx.assign(1, nxl); P.lgi0.assign(1, P.i0); P.lcx.clear(); P.lcy.clear();
+  const int max_levels = max_levels_in > 0 ? max_levels_in : 64;
+  while ((int)P.levels.size() < max_levels) {
+    const HostLevel& F = P.levels.back();
+    const int nx_l = P.lnx.back();
+    const double mx = mean_of(F.hx), my = mean_of(F.hy);
+    const int min_nx = world > 1 ? 2 : 1;
+    const bool can_x = (nx_l % 2 == 0) && (nx_l / 2 >= min_nx) && (F.gnx / 2 >= 2);
+    const bool can_y = (F.ny % 2 == 0) && (F.ny / 2 >= 2);
+    // semi-coarsen only the strongly coupled (finer) direction while the cells are stretched
+    const bool want_x = mx <= 1.6 * my, want_y = my <= 1.6 * mx;
+    const int cx = (can_x && want_x) ? 2 : 1, cy = (can_y && want_y) ? 2 : 1;
+    if (cx == 1 && cy == 1) break;
+    HostLevel C;
+    C.gnx = F.gnx / cx; C.ny = F.ny / cy;
+    C.hx.resize(C.gnx); C.hy.resize(C.ny);
+    for (int I = 0; I < C.gnx; I++) { double s = 0; for (int d = 0; d < cx; d++) s += F.hx[I * cx + d]; C.hx[I] = s; }
+    for (int J = 0; J < C.ny; J++) { double s = 0; for (int d = 0; d < cy; d++) s += F.hy[J * cy + d]; C.hy[J] = s; }
+    if (!F.flags.empty()) {
+      std::vector<uint8_t> in((size_t)C.gnx * C.ny, 0), oc((size_t)C.gnx * C.ny, 0);
+      for (int I = 0; I < C.gnx; I++)
+        for (int J = 0; J < C.ny; J++)
+          for (int di = 0; di < cx; di++)
+            for (int dj = 0; dj < cy; dj++) {
+              const uint8_t f = F.flags[(size_t)(I * cx + di) * F.ny + J * cy + dj];
+              if (f != F_OUTSIDE) { in[(size_t)I * C.ny + J] = 1; oc[(size_t)I * C.ny + J] |= (f & 0xF0); }
+            }
+      C.flags.assign((size_t)C.gnx * C.ny, (uint8_t)F_OUTSIDE);
+      for (int I = 0; I < C.gnx; I++)
+        for (int J = 0; J < C.ny; J++) {
+          if (!in[(size_t)I * C.ny + J]) continue;
+          unsigned f = 0;
+          for (int k = 0; k < 4; k++) {
+            const int In = I + dx[k], Jn = J + dy[k];
+            const bool present = In >= 0 && In < C.gnx && Jn >= 0 && Jn < C.ny && in[(size_t)In * C.ny + Jn];
+            if (present) f |= (1u << k);
+            else if (oc[(size_t)I * C.ny + J] & (16u << k)) f |= (16u << k);
+          }
+          C.flags[(size_t)I * C.ny + J] = (uint8_t)f;
+        }
+    }
+    P.lcx.push_back(cx); P.lcy.push_back(cy);
+    P.lnx.push_back(nx_l / cx); P.lgi0.push_back(P.lgi0.back() / cx);
+    P.levels.push_back(std::move(C));
+  }
+  P.lcx.push_back(1); P.lcy.push_back(1);
+  return 0;
+}
+
+static inline int coarsest_sweeps(int gnx, int ny) {
+  int n = std::min(400, std::max(8, 2 * std::max(gnx, ny)));
+  return n + (n & 1);   // even: the ping-pong ends in the buffer it started from
+}
+
+}  // namespace nsgpu

@@ -1,0 +1,380 @@
+// ns_kernels.cuh -- sm_100a kernels of the time-step loop (fp64, HBM-bound stencils; no tensor cores).
+//
+//   k_smooth_rb        one full red-black Gauss-Seidel sweep in ONE pass over HBM: shared-memory tile with a
+//                      2-cell halo, red update on tile+1 ring, black update on the tile, out of place.
+//                      Algorithmic traffic 24 B per cell-update (read x, read b, write x).
+//   k_residual         r = b - A x and/or ||r||^2            (16-24 B/cell)
+//   k_restrict         coarse b = average of the children's residuals (fused residual + restriction)
+//   k_prolong_add      x_fine += x_coarse(parent)            (piecewise-constant prolongation)
+//   k_apply            y = A x (+ optional dots)
+//   k_rhs_build        ConstructRHS_V                        (64 B/cell)
+//   k_div_rhs          ConstructRHS_phi + block sums for MatNullSpaceRemove   (24 B/cell)
+//   k_correct          CorrectVelocities + GradP + VecMin/VecMax              (40+16 B/cell)
+// Reductions are two-stage and deterministic: warp shuffles -> one partial per block -> the last block to
+// finish adds the partials in a fixed order.
+#pragma once
+#include <cuda_runtime.h>
+#include "ns_cell.cuh"
+
+namespace nsgpu {
+
+constexpr int RED_MAX_BLOCKS = 1 << 16;
+
+struct Reducer {
+  double* partials;   // [NV * RED_MAX_BLOCKS]
+  unsigned* counter;  // zero between launches
+};
+
+struct OpSum { __device__ static double f(double a, double b) { return a + b; } __device__ static double id() { return 0.0; } };
+struct OpMax { __device__ static double f(double a, double b) { return fmax(a, b); } __device__ static double id() { return -1.79769313486231570e308; } };
+
+template <class OP>
+__device__ __forceinline__ double warp_red(double v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v = OP::f(v, __shfl_down_sync(0xffffffffu, v, o));
+  return v;
+}
+
+// Block-level then grid-level reduction of NV values held by every thread.  All threads of the block must call.
+template <int NV, class OP>
+__device__ void grid_reduce(double (&v)[NV], Reducer red, double* out) {
+  __shared__ double sm[NV][32];
+  __shared__ bool is_last;
+  const int tid = threadIdx.x + blockDim.x * (threadIdx.y + blockDim.y * threadIdx.z);
+  const int nth = blockDim.x * blockDim.y * blockDim.z;
+  const int lane = tid & 31, wid = tid >> 5, nw = (nth + 31) >> 5;
+#pragma unroll
+  for (int k = 0; k < NV; k++) {
+    double w = warp_red<OP>(v[k]);
+    if (lane == 0) sm[k][wid] = w;
+  }
+  __syncthreads();
+  const unsigned bid = blockIdx.x + gridDim.x * (blockIdx.y + gridDim.y * blockIdx.z);
+  const unsigned nb = gridDim.x * gridDim.y * gridDim.z;
+  if (wid == 0) {
+#pragma unroll
+    for (int k = 0; k < NV; k++) {
+      double w = (lane < nw) ? sm[k][lane] : OP::id();
+      w = warp_red<OP>(w);
+      if (lane == 0) red.partials[(size_t)k * RED_MAX_BLOCKS + bid] = w;
+    }
+    if (lane == 0) {
+      __threadfence();
+      unsigned t = atomicAdd(red.counter, 1u);
+      is_last = (t == nb - 1);
+    }
+  }
+  __syncthreads();
+  if (!is_last) return;
+  __threadfence();
+#pragma unroll
+  for (int k = 0; k < NV; k++) {
+    double w = OP::id();
+    for (unsigned b = tid; b < nb; b += nth) w = OP::f(w, __ldcg(&red.partials[(size_t)k * RED_MAX_BLOCKS + b]));
+    w = warp_red<OP>(w);
+    __syncthreads();
+    if (lane == 0) sm[k][wid] = w;
+    __syncthreads();
+    if (wid == 0) {
+      double z = (lane < nw) ? sm[k][lane] : OP::id();
+      z = warp_red<OP>(z);
+      if (lane == 0) out[k] = z;
+    }
+  }
+  if (tid == 0) *red.counter = 0u;
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// Fused red-black Gauss-Seidel sweep.  Colour of a cell = (global i + j) & 1, red = 0 first.
+// The outflow rows of L_phi use the previous sweep's value for their second inward cell (same colour).
+constexpr int SM_TI = 16, SM_TJ = 128, SM_THREADS = 256;
+
+template <int OP, bool RECT, bool XZERO>
+__global__ void __launch_bounds__(SM_THREADS)
+k_smooth_rb(LevelGeom g, const double* __restrict__ xin, const double* __restrict__ b, double* __restrict__ xout,
+            double alpha, double beta) {
+  constexpr int SI = SM_TI + 4, SJ = SM_TJ + 4;
+  __shared__ double s[SI][SJ];
+  const int tid = threadIdx.x;
+  const int i0 = blockIdx.y * SM_TI, j0 = blockIdx.x * SM_TJ;
+
+  // phase 1: tile + 2-cell halo -> shared memory (double2, 16-byte aligned since j0 - 2 + PJ is even)
+  if (XZERO) {
+    for (int q = tid; q < SI * SJ; q += SM_THREADS) (&s[0][0])[q] = 0.0;
+  } else {
+    for (int q = tid; q < SI * (SJ / 2); q += SM_THREADS) {
+      const int a = q / (SJ / 2), c = 2 * (q - a * (SJ / 2));
+      const int i = i0 - 2 + a, j = j0 - 2 + c;
+      double2 val = make_double2(0.0, 0.0);
+      if (i < g.nx + HX && j < g.ny + PJ) val = *reinterpret_cast<const double2*>(xin + cidx(g, i, j));
+      *reinterpret_cast<double2*>(&s[a][c]) = val;
+    }
+  }
+  __syncthreads();
+
+  // phase 2: red cells of the tile and of the one-cell ring around it
+  {
+    constexpr int PER = SM_TJ / 2 + 1;
+    for (int q = tid; q < (SM_TI + 2) * PER; q += SM_THREADS) {
+      const int a = 1 + q / PER, t = q % PER;
+      const int i = i0 - 2 + a;
+      const int par = (g.gi0 + i + j0) & 1;          // parity of the cell at c == 2
+      const int c = (par ? 1 : 2) + 2 * t;           // red: (gi + j) even
+      const int j = j0 - 2 + c;
+      if (i >= g.nx + 1 || j >= g.ny + 1) continue;
+      const unsigned f = cell_flags<RECT>(g, i, j);
+      if (f == F_OUTSIDE) continue;
+      const size_t id = cidx(g, i, j);
+      s[a][c] = relax_cell<OP>(g, f, i, j, s[a - 1][c], s[a + 1][c], s[a][c - 1], s[a][c + 1], xin + id, b[id], alpha, beta);
+    }
+  }
+  __syncthreads();
+
+  // phase 3: black cells of the tile
+  {
+    constexpr int PER = SM_TJ / 2;
+    for (int q = tid; q < SM_TI * PER; q += SM_THREADS) {
+      const int a = 2 + q / PER, t = q % PER;
+      const int i = i0 - 2 + a;
+      const int par = (g.gi0 + i + j0) & 1;
+      const int c = (par ? 2 : 3) + 2 * t;           // black: (gi + j) odd
+      const int j = j0 - 2 + c;
+      if (i >= g.nx || j >= g.ny) continue;
+      const unsigned f = cell_flags<RECT>(g, i, j);
+      if (f == F_OUTSIDE) continue;
+      const size_t id = cidx(g, i, j);
+      s[a][c] = relax_cell<OP>(g, f, i, j, s[a - 1][c], s[a + 1][c], s[a][c - 1], s[a][c + 1], xin + id, b[id], alpha, beta);
+    }
+  }
+  __syncthreads();
+
+  // phase 4: tile -> xout
+  for (int q = tid; q < SM_TI * (SM_TJ / 2); q += SM_THREADS) {
+    const int a = 2 + q / (SM_TJ / 2), c = 2 + 2 * (q % (SM_TJ / 2));
+    const int i = i0 - 2 + a, j = j0 - 2 + c;
+    if (i >= g.nx || j >= g.ny) continue;
+    if (j + 1 < g.ny) *reinterpret_cast<double2*>(xout + cidx(g, i, j)) = *reinterpret_cast<const double2*>(&s[a][c]);
+    else xout[cidx(g, i, j)] = s[a][c];
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// r = b - A x  (WRITE) and / or sum r^2 (NORM)
+template <int OP, bool RECT, bool WRITE, bool NORM>
+__global__ void __launch_bounds__(256)
+k_residual(LevelGeom g, const double* __restrict__ x, const double* __restrict__ b, double* __restrict__ r,
+           double alpha, double beta, Reducer red, double* out) {
+  const int j = blockIdx.x * blockDim.x + threadIdx.x;
+  double acc[1] = {0.0};
+  for (int i = blockIdx.y; i < g.nx; i += gridDim.y) {
+    if (j < g.ny) {
+      const unsigned f = cell_flags<RECT>(g, i, j);
+      if (f != F_OUTSIDE) {
+        const size_t id = cidx(g, i, j);
+        const double rv = b[id] - apply_cell<OP>(g, f, i, j, x + id, alpha, beta);
+        if (WRITE) r[id] = rv;
+        if (NORM) acc[0] += rv * rv;
+      }
+    }
+  }
+  if (NORM) grid_reduce<1, OpSum>(acc, red, out);
+}
+
+// y = A x, optionally with the dots (w, y) and (y, y)
+template <int OP, bool RECT, bool DOTS>
+__global__ void __launch_bounds__(256)
+k_apply(LevelGeom g, const double* __restrict__ x, double* __restrict__ y, const double* __restrict__ w,
+        double alpha, double beta, Reducer red, double* out) {
+  const int j = blockIdx.x * blockDim.x + threadIdx.x;
+  double acc[2] = {0.0, 0.0};
+  for (int i = blockIdx.y; i < g.nx; i += gridDim.y) {
+    if (j < g.ny) {
+      const unsigned f = cell_flags<RECT>(g, i, j);
+      if (f != F_OUTSIDE) {
+        const size_t id = cidx(g, i, j);
+        const double yv = apply_cell<OP>(g, f, i, j, x + id, alpha, beta);
+        y[id] = yv;
+        if (DOTS) { acc[0] += w[id] * yv; acc[1] += yv * yv; }
+      }
+    }
+  }
+  if (DOTS) grid_reduce<2, OpSum>(acc, red, out);
+}
+
+// coarse b = (1/(cx*cy)) * sum over children of (b - A x); one thread per coarse cell
+template <int OP, bool RECT>
+__global__ void __launch_bounds__(256)
+k_restrict(LevelGeom gf, LevelGeom gc, const double* __restrict__ x, const double* __restrict__ b,
+           double* __restrict__ bc, double alpha, double beta, int cx, int cy) {
+  const int J = blockIdx.x * blockDim.x + threadIdx.x;
+  const int I = blockIdx.y;
+  if (J >= gc.ny || I >= gc.nx) return;
+  double acc = 0.0;
+  for (int di = 0; di < cx; di++)
+    for (int dj = 0; dj < cy; dj++) {
+      const int i = I * cx + di, j = J * cy + dj;
+      const unsigned f = cell_flags<RECT>(gf, i, j);
+      if (f == F_OUTSIDE) continue;
+      const size_t id = cidx(gf, i, j);
+      acc += b[id] - apply_cell<OP>(gf, f, i, j, x + id, alpha, beta);
+    }
+  const unsigned fc = cell_flags<RECT>(gc, I, J);
+  bc[cidx(gc, I, J)] = (fc == F_OUTSIDE) ? 0.0 : acc / (double)(cx * cy);
+}
+
+// x_fine += x_coarse(parent); one thread per fine cell
+template <bool RECT>
+__global__ void __launch_bounds__(256)
+k_prolong_add(LevelGeom gf, LevelGeom gc, double* __restrict__ xf, const double* __restrict__ xc, int cx, int cy) {
+  const int j = blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= gf.ny) return;
+  for (int i = blockIdx.y; i < gf.nx; i += gridDim.y) {
+    if (cell_flags<RECT>(gf, i, j) == F_OUTSIDE) continue;
+    xf[cidx(gf, i, j)] += xc[cidx(gc, i / cx, j / cy)];
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// Time-step physics
+
+template <bool RECT>
+__global__ void __launch_bounds__(128)
+k_rhs_build(LevelGeom g, const EdgeDev* __restrict__ edges, StepConst sc, const double* __restrict__ u,
+            const double* __restrict__ v, double* __restrict__ nu0, double* __restrict__ nv0,
+            const double* __restrict__ gpx, const double* __restrict__ gpy, double* __restrict__ rhs_u,
+            double* __restrict__ rhs_v) {
+  const int j = blockIdx.x * blockDim.x + threadIdx.x;
+  const int i = blockIdx.y;
+  if (j >= g.ny || i >= g.nx) return;
+  if (cell_flags<RECT>(g, i, j) == F_OUTSIDE) return;
+  const size_t id = cidx(g, i, j);
+  RhsOut o = rhs_cell<RECT>(g, edges, sc, i, j, u + id, v + id, nu0[id], nv0[id], gpx + id, gpy + id);
+  rhs_u[id] = o.rhs_u;
+  rhs_v[id] = o.rhs_v;
+  nu0[id] = o.nu;
+  nv0[id] = o.nv;
+}
+
+template <bool RECT>
+__global__ void __launch_bounds__(256)
+k_div_rhs(LevelGeom g, const EdgeDev* __restrict__ edges, StepConst sc, const double* __restrict__ u,
+          const double* __restrict__ v, double* __restrict__ b, Reducer red, double* out) {
+  const int j = blockIdx.x * blockDim.x + threadIdx.x;
+  double acc[1] = {0.0};
+  for (int i = blockIdx.y; i < g.nx; i += gridDim.y) {
+    if (j < g.ny && cell_flags<RECT>(g, i, j) != F_OUTSIDE) {
+      const size_t id = cidx(g, i, j);
+      const double d = div_cell<RECT>(g, edges, sc, i, j, u + id, v + id);
+      b[id] = d;
+      acc[0] += d;
+    }
+  }
+  grid_reduce<1, OpSum>(acc, red, out);
+}
+
+// b -= *sum / n over fluid cells (MatNullSpaceRemove: plain arithmetic mean over ids, FS.cpp:550)
+template <bool RECT>
+__global__ void __launch_bounds__(256)
+k_sub_mean(LevelGeom g, double* __restrict__ b, const double* __restrict__ sum, double inv_n) {
+  const int j = blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= g.ny) return;
+  const double m = *sum * inv_n;
+  for (int i = blockIdx.y; i < g.nx; i += gridDim.y)
+    if (cell_flags<RECT>(g, i, j) != F_OUTSIDE) b[cidx(g, i, j)] -= m;
+}
+
+// out[0..3] = max(-u), max(u), max(-v), max(v)
+template <bool RECT>
+__global__ void __launch_bounds__(256)
+k_correct(LevelGeom g, StepConst sc, const double* __restrict__ phi, const double* __restrict__ us,
+          const double* __restrict__ vs, double* __restrict__ u, double* __restrict__ v, double* __restrict__ gpx,
+          double* __restrict__ gpy, Reducer red, double* out) {
+  const int j = blockIdx.x * blockDim.x + threadIdx.x;
+  double acc[4] = {OpMax::id(), OpMax::id(), OpMax::id(), OpMax::id()};
+  for (int i = blockIdx.y; i < g.nx; i += gridDim.y) {
+    if (j < g.ny) {
+      const unsigned f = cell_flags<RECT>(g, i, j);
+      if (f != F_OUTSIDE) {
+        const size_t id = cidx(g, i, j);
+        const UV gr = grad_cell(g, f, i, j, phi + id);
+        gpx[id] = gr.u;
+        gpy[id] = gr.v;
+        const double un = us[id] - sc.dt * gr.u, vn = vs[id] - sc.dt * gr.v;
+        u[id] = un;
+        v[id] = vn;
+        // NaN-propagating: fmax drops NaNs, so map a non-finite value to +inf on all four
+        const bool bad = !(isfinite(un) && isfinite(vn));
+        const double inf = 1.0 / 0.0;
+        acc[0] = fmax(acc[0], bad ? inf : -un);
+        acc[1] = fmax(acc[1], bad ? inf : un);
+        acc[2] = fmax(acc[2], bad ? inf : -vn);
+        acc[3] = fmax(acc[3], bad ? inf : vn);
+      }
+    }
+  }
+  grid_reduce<4, OpMax>(acc, red, out);
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// Contiguous vector kernels over the owned columns [HX*ld, (HX+nx)*ld): padding rows and masked cells hold 0
+// in every vector, so plain linear loops are exact.
+
+__global__ void __launch_bounds__(256) k_axpby(size_t n, double a, const double* __restrict__ x, double bb, double* __restrict__ y) {
+  for (size_t k = blockIdx.x * (size_t)blockDim.x + threadIdx.x; k < n; k += (size_t)gridDim.x * blockDim.x)
+    y[k] = a * x[k] + bb * y[k];
+}
+
+// scalars live on the device (sc[]) so the Krylov loop needs no host round trip between kernels
+// p = r + beta*(p - omega*v),  beta = (rho_new/rho_old)*(alpha/omega)
+__global__ void __launch_bounds__(256) k_bicg_p(size_t n, const double* __restrict__ r, double* __restrict__ p,
+                                                const double* __restrict__ v, const double* __restrict__ scal) {
+  const double beta = (scal[0] / scal[1]) * (scal[2] / scal[3]), omega = scal[3];
+  for (size_t k = blockIdx.x * (size_t)blockDim.x + threadIdx.x; k < n; k += (size_t)gridDim.x * blockDim.x)
+    p[k] = r[k] + beta * (p[k] - omega * v[k]);
+}
+// s = r - alpha*v ; out[0] = (s,s)
+__global__ void __launch_bounds__(256) k_bicg_s(size_t n, const double* __restrict__ r, const double* __restrict__ v,
+                                                double* __restrict__ s, const double* __restrict__ alpha_p, Reducer red, double* out) {
+  const double alpha = *alpha_p;
+  double acc[1] = {0.0};
+  for (size_t k = blockIdx.x * (size_t)blockDim.x + threadIdx.x; k < n; k += (size_t)gridDim.x * blockDim.x) {
+    const double sv = r[k] - alpha * v[k];
+    s[k] = sv;
+    acc[0] += sv * sv;
+  }
+  grid_reduce<1, OpSum>(acc, red, out);
+}
+// x += alpha*ph + omega*sh ; r = s - omega*t ; out = {(r,r), (r0,r)}
+__global__ void __launch_bounds__(256) k_bicg_xr(size_t n, double* __restrict__ x, const double* __restrict__ ph,
+                                                 const double* __restrict__ sh, double* __restrict__ r, const double* __restrict__ s,
+                                                 const double* __restrict__ t, const double* __restrict__ r0,
+                                                 const double* __restrict__ alpha_p, const double* __restrict__ omega_p,
+                                                 Reducer red, double* out) {
+  const double alpha = *alpha_p, omega = *omega_p;
+  double acc[2] = {0.0, 0.0};
+  for (size_t k = blockIdx.x * (size_t)blockDim.x + threadIdx.x; k < n; k += (size_t)gridDim.x * blockDim.x) {
+    x[k] += alpha * ph[k] + omega * sh[k];
+    const double rv = s[k] - omega * t[k];
+    r[k] = rv;
+    acc[0] += rv * rv;
+    acc[1] += r0[k] * rv;
+  }
+  grid_reduce<2, OpSum>(acc, red, out);
+}
+// out = {(a,b)}
+__global__ void __launch_bounds__(256) k_dot(size_t n, const double* __restrict__ a, const double* __restrict__ b, Reducer red, double* out) {
+  double acc[1] = {0.0};
+  for (size_t k = blockIdx.x * (size_t)blockDim.x + threadIdx.x; k < n; k += (size_t)gridDim.x * blockDim.x) acc[0] += a[k] * b[k];
+  grid_reduce<1, OpSum>(acc, red, out);
+}
+// out = {sum a}
+__global__ void __launch_bounds__(256) k_sum(size_t n, const double* __restrict__ a, Reducer red, double* out) {
+  double acc[1] = {0.0};
+  for (size_t k = blockIdx.x * (size_t)blockDim.x + threadIdx.x; k < n; k += (size_t)gridDim.x * blockDim.x) acc[0] += a[k];
+  grid_reduce<1, OpSum>(acc, red, out);
+}
+// tiny scalar kernels of the Krylov recurrences: dst = num/den
+__global__ void k_scalar_div(double* dst, const double* num, const double* den) { *dst = *num / *den; }
+__global__ void k_scalar_copy(double* dst, const double* src) { *dst = *src; }
+
+}  // namespace nsgpu

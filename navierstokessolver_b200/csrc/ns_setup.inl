@@ -1,0 +1,160 @@
+// ns_setup.inl -- nsgpu_create / nsgpu_destroy: slab descriptor, matrix-free operator coefficients and the
+// multigrid hierarchy.  Stands in for SolverInitialize + SolverSetup (reference FS.cpp:16-58, 84-164).
+
+namespace nsgpu {
+
+static thread_local std::string g_create_error;
+
+#define NS_CUDA(call)                                                                                   \
+  do {                                                                                                  \
+    cudaError_t e_ = (call);                                                                            \
+    if (e_ != cudaSuccess) {                                                                            \
+      char buf_[512];                                                                                   \
+      snprintf(buf_, sizeof buf_, "%s:%d: %s -> %s", __FILE__, __LINE__, #call, cudaGetErrorString(e_)); \
+      ctx->err = buf_;                                                                                  \
+      return NSGPU_ERR_CUDA;                                                                            \
+    }                                                                                                   \
+  } while (0)
+
+#define NS_NCCL(call)                                                                                   \
+  do {                                                                                                  \
+    ncclResult_t e_ = (call);                                                                           \
+    if (e_ != ncclSuccess) {                                                                            \
+      char buf_[512];                                                                                   \
+      snprintf(buf_, sizeof buf_, "%s:%d: %s -> %s", __FILE__, __LINE__, #call, ncclGetErrorString(e_)); \
+      ctx->err = buf_;                                                                                  \
+      return NSGPU_ERR_NCCL;                                                                            \
+    }                                                                                                   \
+  } while (0)
+
+template <class T>
+static int dev_upload(nsgpu_ctx* ctx, std::vector<void*>& owned, const std::vector<T>& h, const T** out) {
+  void* p = nullptr;
+  NS_CUDA(cudaMalloc(&p, std::max<size_t>(h.size() * sizeof(T), 16)));
+  owned.push_back(p);
+  if (!h.empty()) NS_CUDA(cudaMemcpy(p, h.data(), h.size() * sizeof(T), cudaMemcpyHostToDevice));
+  *out = (const T*)p;
+  return 0;
+}
+
+static int dev_zeros(nsgpu_ctx* ctx, std::vector<void*>& owned, size_t n_doubles, double** out) {
+  void* p = nullptr;
+  NS_CUDA(cudaMalloc(&p, n_doubles * sizeof(double)));
+  owned.push_back(p);
+  NS_CUDA(cudaMemset(p, 0, n_doubles * sizeof(double)));
+  *out = (double*)p;
+  return 0;
+}
+
+// Device copy of the tables of one level.
+static int build_level_geom(nsgpu_ctx* ctx, Level& L, const HostPlan& P, size_t l) {
+  GeomArrays A;
+  make_geom_arrays(P.levels[l], P.lgi0[l], P.lnx[l], (l == 0 && !P.rect) ? &P.cedges0 : nullptr, A);
+  LevelGeom& g = L.g;
+  geom_scalars(A, P, g);
+  L.gny = A.ny;
+  L.stride = A.stride;
+  int rc;
+  if ((rc = dev_upload(ctx, L.owned, A.hx, &g.hx))) return rc;
+  if ((rc = dev_upload(ctx, L.owned, A.hy, &g.hy))) return rc;
+  if ((rc = dev_upload(ctx, L.owned, A.rhx, &g.rhx))) return rc;
+  if ((rc = dev_upload(ctx, L.owned, A.rhy, &g.rhy))) return rc;
+  if ((rc = dev_upload(ctx, L.owned, A.rsx, &g.rsx))) return rc;
+  if ((rc = dev_upload(ctx, L.owned, A.rsy, &g.rsy))) return rc;
+  if ((rc = dev_upload(ctx, L.owned, A.ax, &g.ax))) return rc;
+  if ((rc = dev_upload(ctx, L.owned, A.ay, &g.ay))) return rc;
+  if ((rc = dev_upload(ctx, L.owned, A.bx, &g.bx))) return rc;
+  if ((rc = dev_upload(ctx, L.owned, A.by, &g.by))) return rc;
+  g.flags = nullptr;
+  g.cedges = nullptr;
+  if (!A.flags.empty() && (rc = dev_upload(ctx, L.owned, A.flags, &g.flags))) return rc;
+  if (!A.cedges.empty() && (rc = dev_upload(ctx, L.owned, A.cedges, &g.cedges))) return rc;
+  return 0;
+}
+
+static void destroy_ctx(nsgpu_ctx* ctx) {
+  if (!ctx) return;
+  cudaSetDevice(ctx->device);
+  if (ctx->stream) cudaStreamSynchronize(ctx->stream);
+  if (ctx->comm) ncclCommDestroy(ctx->comm);
+  for (auto& L : ctx->levels)
+    for (void* p : L.owned) cudaFree(p);
+  for (void* p : ctx->owned) cudaFree(p);
+  if (ctx->h_scal) cudaFreeHost(ctx->h_scal);
+  if (ctx->h_stage) cudaFreeHost(ctx->h_stage);
+  if (ctx->ev0) cudaEventDestroy(ctx->ev0);
+  if (ctx->ev1) cudaEventDestroy(ctx->ev1);
+  if (ctx->stream) cudaStreamDestroy(ctx->stream);
+  delete ctx;
+}
+
+static int create_impl(nsgpu_ctx* ctx, const nsgpu_grid* G, const nsgpu_params* P) {
+  if (!G || !P) { ctx->err = "null grid or params"; return NSGPU_ERR_ARG; }
+  if (!(P->dt > 0) || !(P->re > 0)) { ctx->err = "dt and re must be positive"; return NSGPU_ERR_ARG; }   // FS.cpp:17-28
+  ctx->dt = P->dt; ctx->re = P->re;
+  ctx->device = P->device; ctx->rank = P->rank; ctx->world = P->world > 0 ? P->world : 1;
+  ctx->rtol_u = P->rtol_u > 0 ? P->rtol_u : 1e-8;
+  ctx->rtol_phi = P->rtol_phi > 0 ? P->rtol_phi : 1e-8;
+  ctx->max_cycles = P->max_cycles > 0 ? P->max_cycles : 200;
+  ctx->nu_pre = P->nu_pre > 0 ? P->nu_pre : 2;
+  ctx->nu_post = P->nu_post > 0 ? P->nu_post : 2;
+  ctx->solver = P->solver;
+  ctx->use_graph = P->use_graph;
+  HostPlan plan;
+  {
+    int rc = make_host_plan(G, ctx->rank, ctx->world, P->max_levels, plan, ctx->err);
+    if (rc) return rc;
+  }
+  ctx->gnx = G->nx; ctx->ny = G->ny;
+  ctx->rect = plan.rect;
+  ctx->n_cells_global = plan.n_cells_global;
+  ctx->i0 = plan.i0; ctx->i1 = plan.i1; ctx->id0 = plan.id0; ctx->n_local = plan.n_local;
+  ctx->local_id = plan.local_id;
+
+  // ---- device
+  int ndev = 0;
+  NS_CUDA(cudaGetDeviceCount(&ndev));
+  if (ctx->device < 0 || ctx->device >= ndev) { ctx->err = "no such CUDA device"; return NSGPU_ERR_CUDA; }
+  NS_CUDA(cudaSetDevice(ctx->device));
+  NS_CUDA(cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking));
+  NS_CUDA(cudaEventCreate(&ctx->ev0));
+  NS_CUDA(cudaEventCreate(&ctx->ev1));
+  if (ctx->world > 1) {
+    if (!P->nccl_id) { ctx->err = "world > 1 needs params.nccl_id"; return NSGPU_ERR_ARG; }
+    ncclUniqueId id;
+    memcpy(&id, P->nccl_id, sizeof id);
+    NS_NCCL(ncclCommInitRank(&ctx->comm, ctx->world, id, ctx->rank));
+  }
+
+  // ---- level hierarchy
+  ctx->levels.resize(plan.levels.size());
+  for (size_t l = 0; l < plan.levels.size(); l++) {
+    Level& L = ctx->levels[l];
+    L.cx = plan.lcx[l]; L.cy = plan.lcy[l];
+    int rc = build_level_geom(ctx, L, plan, l);
+    if (rc) return rc;
+    if (l > 0) {
+      if ((rc = dev_zeros(ctx, L.owned, L.stride, &L.x))) return rc;
+      if ((rc = dev_zeros(ctx, L.owned, L.stride, &L.xt))) return rc;
+      if ((rc = dev_zeros(ctx, L.owned, L.stride, &L.b))) return rc;
+    }
+  }
+  ctx->levels.back().coarse_sweeps = coarsest_sweeps(ctx->levels.back().g.gnx, ctx->levels.back().gny);
+
+  // ---- fields
+  const size_t S = ctx->levels[0].stride;
+  double** fields[] = {&ctx->u, &ctx->v, &ctx->phi, &ctx->conv_u, &ctx->conv_v, &ctx->gpx, &ctx->gpy,
+                       &ctx->rhs_u, &ctx->rhs_v, &ctx->rhs_phi, &ctx->ustar, &ctx->vstar, &ctx->tmp};
+  for (double** f : fields) { int rc = dev_zeros(ctx, ctx->owned, S, f); if (rc) return rc; }
+  if (ctx->solver == 1)
+    for (int k = 0; k < 8; k++) { int rc = dev_zeros(ctx, ctx->owned, S, &ctx->kry[k]); if (rc) return rc; }
+  { const EdgeDev* p; int rc = dev_upload(ctx, ctx->owned, plan.edges, &p); if (rc) return rc; ctx->d_edges = const_cast<EdgeDev*>(p); }
+  { int rc = dev_zeros(ctx, ctx->owned, (size_t)4 * RED_MAX_BLOCKS, &ctx->red.partials); if (rc) return rc; }
+  { double* c; int rc = dev_zeros(ctx, ctx->owned, 2, &c); if (rc) return rc; ctx->red.counter = (unsigned*)c; }
+  { int rc = dev_zeros(ctx, ctx->owned, 64, &ctx->d_scal); if (rc) return rc; }
+  NS_CUDA(cudaMallocHost((void**)&ctx->h_scal, 64 * sizeof(double)));
+  NS_CUDA(cudaDeviceSynchronize());
+  return 0;
+}
+
+}  // namespace nsgpu

@@ -1,0 +1,302 @@
+// TEST INFRASTRUCTURE ONLY -- host compile of the per-cell DEVICE functions (csrc/ns_cell.cuh) and of the
+// host-side geometry / multigrid plan (csrc/ns_hostgeom.h), so that the CPU-only test run can check the very
+// arithmetic the sm_100a kernels execute against the oracle.  Nothing in navierstokessolver_b200/ or
+// libnsgpu.so links, loads or calls this file; it is not a fallback path.  The loops below mirror the kernel
+// launch structure of csrc/ns_solver.inl one to one (same red-black order, same restriction/prolongation).
+#include <cmath>
+#include <cstring>
+#include <vector>
+#include <string>
+#include "ns_hostgeom.h"
+
+using namespace nsgpu;
+
+namespace {
+
+struct ELevel {
+  GeomArrays A;
+  LevelGeom g;
+  int cx = 1, cy = 1;
+  std::vector<double> x, xt, b;
+};
+
+struct Emul {
+  HostPlan plan;
+  std::vector<ELevel> lv;
+  double dt, re;
+  int nu_pre = 2, nu_post = 2;
+  std::vector<double> f[13];   // NSGPU_* ids 0..11, 12 = tmp
+  std::string err;
+};
+
+void bind(ELevel& L, const HostPlan& P) {
+  geom_scalars(L.A, P, L.g);
+  L.g.hx = L.A.hx.data(); L.g.hy = L.A.hy.data(); L.g.rhx = L.A.rhx.data(); L.g.rhy = L.A.rhy.data();
+  L.g.rsx = L.A.rsx.data(); L.g.rsy = L.A.rsy.data(); L.g.ax = L.A.ax.data(); L.g.ay = L.A.ay.data();
+  L.g.bx = L.A.bx.data(); L.g.by = L.A.by.data();
+  L.g.flags = L.A.flags.empty() ? nullptr : L.A.flags.data();
+  L.g.cedges = L.A.cedges.empty() ? nullptr : L.A.cedges.data();
+}
+
+template <bool RECT> unsigned fl(const LevelGeom& g, int i, int j) { return cell_flags<RECT>(g, i, j); }
+
+struct Coef { int op; double alpha, beta; };
+
+template <int OP, bool RECT>
+void smoothphase_t(const LevelGeom& g, std::vector<double>& x, std::vector<double>& xt, const std::vector<double>& b, double alpha, double beta, int n) {
+  for (int s = 0; s < n; s++) {
+    xt = x;   // xin stays untouched: outflow rows read their second inward cell from it
+    for (int colour = 0; colour < 2; colour++)
+      for (int i = 0; i < g.nx; i++)
+        for (int j = 0; j < g.ny; j++) {
+          if (((g.gi0 + i + j) & 1) != colour) continue;
+          const unsigned f = fl<RECT>(g, i, j);
+          if (f == F_OUTSIDE) continue;
+          const size_t id = cidx(g, i, j);
+          xt[id] = relax_cell<OP>(g, f, i, j, xt[id - g.ld], xt[id + g.ld], xt[id - 1], xt[id + 1], x.data() + id, b[id], alpha, beta);
+        }
+    x.swap(xt);
+  }
+}
+void smooth(const Emul& E, const ELevel& L, Coef c, std::vector<double>& x, std::vector<double>& xt, const std::vector<double>& b, int n) {
+  if (c.op == 0) { if (E.plan.rect) smoothphase_t<0, true>(L.g, x, xt, b, c.alpha, c.beta, n); else smoothphase_t<0, false>(L.g, x, xt, b, c.alpha, c.beta, n); }
+  else { if (E.plan.rect) smoothphase_t<1, true>(L.g, x, xt, b, c.alpha, c.beta, n); else smoothphase_t<1, false>(L.g, x, xt, b, c.alpha, c.beta, n); }
+}
+
+template <int OP, bool RECT>
+double apply_at(const LevelGeom& g, int i, int j, const std::vector<double>& x, double alpha, double beta) {
+  return apply_cell<OP>(g, fl<RECT>(g, i, j), i, j, x.data() + cidx(g, i, j), alpha, beta);
+}
+double apply_any(const Emul& E, const LevelGeom& g, Coef c, int i, int j, const std::vector<double>& x) {
+  if (c.op == 0) return E.plan.rect ? apply_at<0, true>(g, i, j, x, c.alpha, c.beta) : apply_at<0, false>(g, i, j, x, c.alpha, c.beta);
+  return E.plan.rect ? apply_at<1, true>(g, i, j, x, c.alpha, c.beta) : apply_at<1, false>(g, i, j, x, c.alpha, c.beta);
+}
+unsigned flags_any(const Emul& E, const LevelGeom& g, int i, int j) { return E.plan.rect ? fl<true>(g, i, j) : fl<false>(g, i, j); }
+
+double resnorm2(const Emul& E, const ELevel& L, Coef c, const std::vector<double>& x, const std::vector<double>& b) {
+  double s = 0;
+  for (int i = 0; i < L.g.nx; i++)
+    for (int j = 0; j < L.g.ny; j++) {
+      if (flags_any(E, L.g, i, j) == F_OUTSIDE) continue;
+      const double r = b[cidx(L.g, i, j)] - apply_any(E, L.g, c, i, j, x);
+      s += r * r;
+    }
+  return s;
+}
+
+void vcycle(Emul& E, int l, Coef c, std::vector<double>& x, std::vector<double>& xt, const std::vector<double>& b) {
+  ELevel& L = E.lv[l];
+  if (l == (int)E.lv.size() - 1) {
+    smooth(E, L, c, x, xt, b, E.lv.size() == 1 ? E.nu_pre + E.nu_post : coarsest_sweeps(L.g.gnx, L.g.ny));
+    return;
+  }
+  ELevel& C = E.lv[l + 1];
+  smooth(E, L, c, x, xt, b, E.nu_pre);
+  for (int I = 0; I < C.g.nx; I++)
+    for (int J = 0; J < C.g.ny; J++) {
+      double acc = 0;
+      for (int di = 0; di < L.cx; di++)
+        for (int dj = 0; dj < L.cy; dj++) {
+          const int i = I * L.cx + di, j = J * L.cy + dj;
+          if (flags_any(E, L.g, i, j) == F_OUTSIDE) continue;
+          acc += b[cidx(L.g, i, j)] - apply_any(E, L.g, c, i, j, x);
+        }
+      C.b[cidx(C.g, I, J)] = flags_any(E, C.g, I, J) == F_OUTSIDE ? 0.0 : acc / (double)(L.cx * L.cy);
+    }
+  std::fill(C.x.begin(), C.x.end(), 0.0);
+  vcycle(E, l + 1, c, C.x, C.xt, C.b);
+  for (int i = 0; i < L.g.nx; i++)
+    for (int j = 0; j < L.g.ny; j++)
+      if (flags_any(E, L.g, i, j) != F_OUTSIDE) x[cidx(L.g, i, j)] += C.x[cidx(C.g, i / L.cx, j / L.cy)];
+  smooth(E, L, c, x, xt, b, E.nu_post);
+}
+
+int solve_mg(Emul& E, Coef c, std::vector<double>& x, const std::vector<double>& b, double rtol, int max_cycles, double* rel) {
+  ELevel& L = E.lv[0];
+  double bn = 0;
+  for (double v : b) bn += v * v;   // padding and masked cells hold zeros
+  bn = std::sqrt(bn);
+  double rn = std::sqrt(resnorm2(E, L, c, x, b));
+  int cycles = 0;
+  if (bn == 0) { std::fill(x.begin(), x.end(), 0.0); *rel = 0; return 0; }
+  while (rn > rtol * bn && cycles < max_cycles) {
+    vcycle(E, 0, c, x, E.f[12], b);
+    cycles++;
+    rn = std::sqrt(resnorm2(E, L, c, x, b));
+  }
+  *rel = rn / bn;
+  return cycles;
+}
+
+template <bool RECT>
+void rhsphase_t(Emul& E) {
+  const LevelGeom& g = E.lv[0].g;
+  const StepConst sc{E.dt, E.re};
+  std::vector<double> nu(E.f[NSGPU_CONV_U0]), nv(E.f[NSGPU_CONV_V0]);
+  for (int i = 0; i < g.nx; i++)
+    for (int j = 0; j < g.ny; j++) {
+      if (fl<RECT>(g, i, j) == F_OUTSIDE) continue;
+      const size_t id = cidx(g, i, j);
+      RhsOut o = rhs_cell<RECT>(g, E.plan.edges.data(), sc, i, j, E.f[NSGPU_U].data() + id, E.f[NSGPU_V].data() + id, nu[id], nv[id],
+                                E.f[NSGPU_GRADPHI_X].data() + id, E.f[NSGPU_GRADPHI_Y].data() + id);
+      E.f[NSGPU_RHS_U][id] = o.rhs_u; E.f[NSGPU_RHS_V][id] = o.rhs_v;
+      E.f[NSGPU_CONV_U0][id] = o.nu; E.f[NSGPU_CONV_V0][id] = o.nv;
+    }
+}
+template <bool RECT>
+void divphase_t(Emul& E, bool remove_mean) {
+  const LevelGeom& g = E.lv[0].g;
+  const StepConst sc{E.dt, E.re};
+  double sum = 0;
+  for (int i = 0; i < g.nx; i++)
+    for (int j = 0; j < g.ny; j++) {
+      if (fl<RECT>(g, i, j) == F_OUTSIDE) continue;
+      const size_t id = cidx(g, i, j);
+      const double d = div_cell<RECT>(g, E.plan.edges.data(), sc, i, j, E.f[NSGPU_USTAR].data() + id, E.f[NSGPU_VSTAR].data() + id);
+      E.f[NSGPU_RHS_PHI][id] = d;
+      sum += d;
+    }
+  if (remove_mean) {
+    const double m = sum / (double)E.plan.n_cells_global;
+    for (int i = 0; i < g.nx; i++)
+      for (int j = 0; j < g.ny; j++)
+        if (fl<RECT>(g, i, j) != F_OUTSIDE) E.f[NSGPU_RHS_PHI][cidx(g, i, j)] -= m;
+  }
+}
+template <bool RECT>
+void correctphase_t(Emul& E, double* mm) {
+  const LevelGeom& g = E.lv[0].g;
+  double umin = 1e300, umax = -1e300, vmin = 1e300, vmax = -1e300;
+  for (int i = 0; i < g.nx; i++)
+    for (int j = 0; j < g.ny; j++) {
+      const unsigned f = fl<RECT>(g, i, j);
+      if (f == F_OUTSIDE) continue;
+      const size_t id = cidx(g, i, j);
+      const UV gr = grad_cell(g, f, i, j, E.f[NSGPU_PHI].data() + id);
+      E.f[NSGPU_GRADPHI_X][id] = gr.u; E.f[NSGPU_GRADPHI_Y][id] = gr.v;
+      const double un = E.f[NSGPU_USTAR][id] - E.dt * gr.u, vn = E.f[NSGPU_VSTAR][id] - E.dt * gr.v;
+      E.f[NSGPU_U][id] = un; E.f[NSGPU_V][id] = vn;
+      umin = std::min(umin, un); umax = std::max(umax, un); vmin = std::min(vmin, vn); vmax = std::max(vmax, vn);
+    }
+  if (mm) { mm[0] = umin; mm[1] = umax; mm[2] = vmin; mm[3] = vmax; }
+}
+
+void phi_mean_zero(Emul& E) {
+  const LevelGeom& g = E.lv[0].g;
+  double s = 0;
+  for (double v : E.f[NSGPU_PHI]) s += v;
+  const double m = s / (double)E.plan.n_cells_global;
+  for (int i = 0; i < g.nx; i++)
+    for (int j = 0; j < g.ny; j++)
+      if (flags_any(E, g, i, j) != F_OUTSIDE) E.f[NSGPU_PHI][cidx(g, i, j)] -= m;
+}
+
+}  // namespace
+
+extern "C" {
+
+void* emul_create(const nsgpu_grid* G, double dt, double re, int nu_pre, int nu_post, int max_levels, char* errbuf, int errlen) {
+  Emul* E = new Emul;
+  E->dt = dt; E->re = re;
+  if (nu_pre > 0) E->nu_pre = nu_pre;
+  if (nu_post > 0) E->nu_post = nu_post;
+  int rc = make_host_plan(G, 0, 1, max_levels, E->plan, E->err);
+  if (rc) {
+    if (errbuf && errlen > 0) { strncpy(errbuf, E->err.c_str(), errlen - 1); errbuf[errlen - 1] = 0; }
+    delete E;
+    return nullptr;
+  }
+  E->lv.resize(E->plan.levels.size());
+  for (size_t l = 0; l < E->lv.size(); l++) {
+    ELevel& L = E->lv[l];
+    make_geom_arrays(E->plan.levels[l], E->plan.lgi0[l], E->plan.lnx[l], (l == 0 && !E->plan.rect) ? &E->plan.cedges0 : nullptr, L.A);
+    bind(L, E->plan);
+    L.cx = E->plan.lcx[l]; L.cy = E->plan.lcy[l];
+    if (l > 0) { L.x.assign(L.A.stride, 0.0); L.xt.assign(L.A.stride, 0.0); L.b.assign(L.A.stride, 0.0); }
+  }
+  for (auto& v : E->f) v.assign(E->lv[0].A.stride, 0.0);
+  return E;
+}
+void emul_destroy(void* h) { delete (Emul*)h; }
+int emul_rect(void* h) { return ((Emul*)h)->plan.rect ? 1 : 0; }
+int emul_num_levels(void* h) { return (int)((Emul*)h)->lv.size(); }
+long emul_n_local(void* h) { return (long)((Emul*)h)->plan.n_local; }
+void emul_level_shape(void* h, int l, int* gnx, int* ny, int* cx, int* cy) {
+  Emul* E = (Emul*)h; *gnx = E->lv[l].g.gnx; *ny = E->lv[l].g.ny; *cx = E->lv[l].cx; *cy = E->lv[l].cy;
+}
+
+void emul_set(void* h, int which, const double* in) {
+  Emul* E = (Emul*)h;
+  const LevelGeom& g = E->lv[0].g;
+  std::fill(E->f[which].begin(), E->f[which].end(), 0.0);
+  for (int i = 0; i < g.nx; i++)
+    for (int j = 0; j < g.ny; j++) {
+      const long id = E->plan.rect ? (long)i * g.ny + j : (long)E->plan.local_id[(size_t)i * g.ny + j];
+      if (id >= 0) E->f[which][cidx(g, i, j)] = in[id];
+    }
+}
+void emul_get(void* h, int which, double* out) {
+  Emul* E = (Emul*)h;
+  const LevelGeom& g = E->lv[0].g;
+  for (int i = 0; i < g.nx; i++)
+    for (int j = 0; j < g.ny; j++) {
+      const long id = E->plan.rect ? (long)i * g.ny + j : (long)E->plan.local_id[(size_t)i * g.ny + j];
+      if (id >= 0) out[id] = E->f[which][cidx(g, i, j)];
+    }
+}
+
+void emul_rhs_build(void* h) { Emul* E = (Emul*)h; if (E->plan.rect) rhsphase_t<true>(*E); else rhsphase_t<false>(*E); }
+void emul_div_rhs(void* h, int remove_mean) { Emul* E = (Emul*)h; if (E->plan.rect) divphase_t<true>(*E, remove_mean != 0); else divphase_t<false>(*E, remove_mean != 0); }
+void emul_correct(void* h, double* mm) { Emul* E = (Emul*)h; if (E->plan.rect) correctphase_t<true>(*E, mm); else correctphase_t<false>(*E, mm); }
+
+void emul_apply(void* h, int op, const double* x, double* y) {
+  Emul* E = (Emul*)h;
+  emul_set(h, 12, x);
+  const LevelGeom& g = E->lv[0].g;
+  Coef c = op == 0 ? Coef{0, 1.0, E->dt / (2.0 * E->re)} : Coef{1, 0.0, -1.0};
+  for (int i = 0; i < g.nx; i++)
+    for (int j = 0; j < g.ny; j++) {
+      const long id = E->plan.rect ? (long)i * g.ny + j : (long)E->plan.local_id[(size_t)i * g.ny + j];
+      if (id >= 0) y[id] = apply_any(*E, g, c, i, j, E->f[12]);
+    }
+}
+
+// which: 0 = u* from rhs_u (initial guess u), 1 = v*, 2 = phi (warm start)
+int emul_solve(void* h, int which, double rtol, int max_cycles, double* rel) {
+  Emul* E = (Emul*)h;
+  if (which == 2) {
+    int n = solve_mg(*E, Coef{1, 0.0, -1.0}, E->f[NSGPU_PHI], E->f[NSGPU_RHS_PHI], rtol, max_cycles, rel);
+    phi_mean_zero(*E);
+    return n;
+  }
+  const Coef c{0, 1.0, E->dt / (2.0 * E->re)};
+  if (which == 0) { E->f[NSGPU_USTAR] = E->f[NSGPU_U]; return solve_mg(*E, c, E->f[NSGPU_USTAR], E->f[NSGPU_RHS_U], rtol, max_cycles, rel); }
+  E->f[NSGPU_VSTAR] = E->f[NSGPU_V];
+  return solve_mg(*E, c, E->f[NSGPU_VSTAR], E->f[NSGPU_RHS_V], rtol, max_cycles, rel);
+}
+
+void emul_poisson_sweeps(void* h, int n, double* resid) {
+  Emul* E = (Emul*)h;
+  const Coef c{1, 0.0, -1.0};
+  smooth(*E, E->lv[0], c, E->f[NSGPU_PHI], E->f[12], E->f[NSGPU_RHS_PHI], n);
+  if (resid) *resid = std::sqrt(resnorm2(*E, E->lv[0], c, E->f[NSGPU_PHI], E->f[NSGPU_RHS_PHI]));
+}
+
+// n passes of the Solve() loop body (FS.cpp:546-557); returns the worst relative residual
+double emul_step(void* h, int n, double rtol, int max_cycles, double* mm, int* cycles3) {
+  Emul* E = (Emul*)h;
+  double worst = 0, rel;
+  for (int s = 0; s < n; s++) {
+    emul_rhs_build(h);
+    int cu = emul_solve(h, 0, rtol, max_cycles, &rel); worst = std::max(worst, rel);
+    int cv = emul_solve(h, 1, rtol, max_cycles, &rel); worst = std::max(worst, rel);
+    emul_div_rhs(h, 1);
+    int cp = emul_solve(h, 2, rtol, max_cycles, &rel); worst = std::max(worst, rel);
+    emul_correct(h, mm);
+    if (cycles3) { cycles3[0] = cu; cycles3[1] = cv; cycles3[2] = cp; }
+  }
+  (void)E;
+  return worst;
+}
+
+}  // extern "C"
