@@ -16,11 +16,11 @@ HOST_DEPS = $(wildcard $(HOST)/*.cpp $(HOST)/*.h)
 all: $(PKG)/libnsgpu.so bin/main
 
 $(PKG)/libnsgpu.so: $(CU_DEPS) $(HOST_DEPS)
-	$(NVCC) $(NVFLAGS) -shared $(CSRC)/nsgpu.cu $(HOST_SRC) -Iinclude -o $@ -lnccl
+	$(NVCC) $(NVFLAGS) -shared $(CSRC)/nsgpu.cu $(HOST_SRC) -Iinclude -I$(HOST) -o $@ -lnccl
 
-bin/main: $(PKG)/libnsgpu.so $(HOST)/main/MAIN_Solver.cpp
+bin/main: $(PKG)/libnsgpu.so $(HOST)/main/ns_main.cpp
 	@mkdir -p bin
-	$(CXX) -std=c++17 -O2 -Iinclude -I$(HOST) $(HOST)/main/MAIN_Solver.cpp -L$(PKG) -lnsgpu -Wl,-rpath,'$$ORIGIN/../$(PKG)' -o $@
+	$(CXX) -std=c++17 -O2 -Iinclude -I$(HOST) $(HOST)/main/ns_main.cpp -L$(PKG) -lnsgpu -Wl,-rpath,'$$ORIGIN/../$(PKG)' -o $@
 
 oracle:
 	$(MAKE) -C oracle port

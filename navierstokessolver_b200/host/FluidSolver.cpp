@@ -1,0 +1,206 @@
+// FluidSolver.cpp -- host driver of the GPU time-step loop; behaviour modelled on the reference's
+// FluidSolver (SRC/FluidSolver.cpp), implementation new.  What stays on the host: the simulation-file parser
+// (FS.cpp:626-669), parameter validation (FS.cpp:16-32), ghost-stencil bookkeeping on the borrowed Grid
+// (FS.cpp:84-103), the per-step stdout table (FS.cpp:559-560) and the CSV export (FS.cpp:569-615).
+// Everything numerical goes through include/nsgpu.h.
+#include "FluidSolver.h"
+
+#include <cmath>
+#include <cstdio>
+#include <cstdlib>
+#include <iostream>
+#include <sstream>
+
+double minmode(double a, double b) {   // FS.cpp:671-674 (kept as a free function of the public surface)
+  if (a * b > 0) return a * std::min(1.0, std::abs(b / a));
+  return 0;
+}
+
+FluidSolver::FluidSolver(char* fname, Grid* g) : grid(g) {
+  ifstream in{fname};
+  if (readSimulationFile(in) && checkParameters()) {
+    buildGhostStencils();
+    if (createDeviceSolver()) {
+      cout << "Solver Setup Complete!\n";
+      setup = true;
+    }
+  }
+  in.close();
+}
+
+FluidSolver::~FluidSolver() {
+  if (gpu) nsgpu_destroy(gpu);
+}
+
+// Keywords: BC { one "<type> [info]" line per edge }, dt, final_time, re, saveIter.  As in the reference every
+// item must be followed by more input (a number that ends exactly at end-of-file is rejected, FS.cpp:662).
+bool FluidSolver::readSimulationFile(ifstream& in) {
+  if (!in) { cout << "Simulation data file not found!\n"; return false; }
+  bool ok = true;
+  string key;
+  while (!in.eof()) {
+    in >> key;
+    if (in.eof()) break;
+    if (key == "BC") {
+      if ((in >> ws).get() != '{') { ok = false; break; }
+      size_t k = 0;
+      while (in.good()) {
+        if ((in >> ws).peek() == '}') {
+          if (k == grid->edges.size()) in.ignore(); else ok = false;
+          break;
+        }
+        string line;
+        getline(in, line);
+        if (in.eof() || k == grid->edges.size()) { ok = false; break; }
+        istringstream ls(line);
+        ls >> grid->edges[k].bcType >> grid->edges[k].bcInfo;   // a missing info keeps Edge's default 1.0
+        k++;
+      }
+      if (!ok) break;
+    }
+    else if (key == "dt") in >> dt;
+    else if (key == "final_time") in >> finalTime;
+    else if (key == "re") in >> re;
+    else if (key == "saveIter") in >> saveIter;
+    else { ok = false; break; }
+    if (!in.good()) { ok = false; break; }
+  }
+  if (!ok) cout << "Invalid data file format!\n";
+  return ok;
+}
+
+bool FluidSolver::checkParameters() {   // same order and messages as FS.cpp:17-32
+  if (dt <= 0) { cout << "Time step should be positive\n"; return false; }
+  if (dt > finalTime) { cout << "Time step should be less than final time!\n"; return false; }
+  if (re <= 0) { cout << "Reynolds number should be positive\n"; return false; }
+  if (saveIter <= 0) { cout << "saveIter must be greater than zero!\n"; return false; }
+  return true;
+}
+
+// The reference stores the ghost-cell closures on the Grid's edges (FS.cpp:84-103) where user code can see them;
+// the device builds its own copy from bcType / bcInfo, this one serves ExportData and API compatibility.
+void FluidSolver::buildGhostStencils() {
+  for (Edge& e : grid->edges) {
+    if (e.bcType <= WALL) {
+      Stencil vel, phi;
+      vel.weights = {-1}; vel.support = {{0, 0}};
+      phi.weights = {1};  phi.support = {{0, 0}};
+      const double c = 2 * e.bcInfo;
+      if (e.bcType == INLET_UNI) vel.constant = (e.nx == 0) ? vector<double>{0, c} : vector<double>{c, 0};
+      else if (e.bcType == WALL) vel.constant = (e.nx != 0) ? vector<double>{0, c} : vector<double>{c, 0};
+      e.ghost.push_back(vel);
+      e.ghost.push_back(phi);
+    } else if (e.bcType == NEUMANN) {
+      Stencil vel, phi;
+      vel.weights = {1}; vel.support = {{0, 0}}; vel.constant = {0, 0};
+      phi.weights = {2.5, -2.0, 0.5};
+      phi.support = {{0, 0}, {-e.nx, -e.ny}, {-2 * e.nx, -2 * e.ny}};
+      e.ghost.push_back(vel);
+      e.ghost.push_back(phi);
+    }
+  }
+}
+
+static int env_int(const char* name, int dflt) { const char* v = std::getenv(name); return v ? std::atoi(v) : dflt; }
+static double env_double(const char* name, double dflt) { const char* v = std::getenv(name); return v ? std::atof(v) : dflt; }
+
+bool FluidSolver::createDeviceSolver() {
+  const int nx = (int)grid->hx.size(), ny = (int)grid->hy.size();
+  vector<int32_t> ids((size_t)nx * ny), tags((size_t)nx * ny * 4);
+  for (int i = 0; i < nx; i++)
+    for (int j = 0; j < ny; j++) {
+      const Cell& c = grid->cells[i][j];
+      ids[(size_t)i * ny + j] = c.id;
+      for (int k = 0; k < 4; k++) tags[((size_t)i * ny + j) * 4 + k] = c.edges[k];
+    }
+  const int ne = (int)grid->edges.size();
+  vector<int32_t> enx(ne), eny(ne), etype(ne);
+  vector<double> einfo(ne);
+  for (int k = 0; k < ne; k++) {
+    enx[k] = grid->edges[k].nx; eny[k] = grid->edges[k].ny;
+    etype[k] = grid->edges[k].bcType; einfo[k] = grid->edges[k].bcInfo;
+  }
+  nsgpu_grid g{};
+  g.nx = nx; g.ny = ny; g.n_cells = grid->N;
+  g.hx = grid->hx.data(); g.hy = grid->hy.data();
+  g.cell_id = ids.data(); g.cell_edges = tags.data();
+  g.n_edges = ne; g.edge_nx = enx.data(); g.edge_ny = eny.data(); g.edge_bc_type = etype.data(); g.edge_bc_info = einfo.data();
+  nsgpu_params p{};
+  p.dt = dt; p.re = re;
+  p.device = env_int("NSGPU_DEVICE", 0);
+  p.rank = 0; p.world = 1;
+  p.rtol_u = env_double("NSGPU_RTOL_U", 1e-8);       // KSPSetTolerances(..., 1.e-8, ...) FS.cpp:68,80
+  p.rtol_phi = env_double("NSGPU_RTOL_PHI", 1e-8);
+  p.solver = env_int("NSGPU_SOLVER", grid->N == nx * ny ? 0 : 1);
+  p.max_cycles = env_int("NSGPU_MAX_CYCLES", 0);
+  int rc = nsgpu_create(&g, &p, &gpu);
+  if (rc != 0) {
+    cout << "GPU solver setup failed (" << rc << "): " << nsgpu_last_error(nullptr) << "\n";
+    gpu = nullptr;
+    return false;
+  }
+  return true;
+}
+
+// Same loop control as FS.cpp:536-567: iter starts at 1, the first step always runs, stop when dt*iter > finalTime.
+void FluidSolver::Solve() {
+  int iter = 1;
+  cout << "Initiating Solver..\n";
+  do {
+    nsgpu_step_info info;
+    int rc = nsgpu_step(gpu, 1, &info);
+    if (rc != 0 && rc != NSGPU_ERR_NOT_CONVERGED && rc != NSGPU_ERR_NAN) {
+      cout << "GPU time step failed (" << rc << "): " << nsgpu_last_error(gpu) << "\n";
+      return;
+    }
+    if ((iter - 1) % 10 == 0) printf("iter\tumin\t\tumax\t\tvmin\t\tvmax\n");
+    printf("%d\t%lf\t%lf\t%lf\t%lf\n", iter, info.umin, info.umax, info.vmin, info.vmax);
+    if (saveIter > 0 && iter % saveIter == 0) ExportData(iter);
+    iter++;
+  } while (dt * iter <= finalTime);
+  cout << "Solution Complete!\n";
+}
+
+double FluidSolver::ghostVelocity(const double* V, int i, int j, int e, int d) {   // EvaluateGhostStencil_V, FS.cpp:166-173
+  const Stencil& s = grid->edges[e].ghost[0];
+  double r = 0.0;
+  for (size_t l = 0; l < s.weights.size(); l++) r += s.weights[l] * V[grid->cells[i + s.support[l][0]][j + s.support[l][1]].id];
+  return r + s.constant[d];
+}
+
+double FluidSolver::ghostPhi(const double* P, int i, int j, int e) {                // EvaluateGhostStencil_P, FS.cpp:175-181
+  const Stencil& s = grid->edges[e].ghost[1];
+  double r = 0.0;
+  for (size_t l = 0; l < s.weights.size(); l++) r += s.weights[l] * P[grid->cells[i + s.support[l][0]][j + s.support[l][1]].id];
+  return r;
+}
+
+// FlowData_<iter>.csv: one row per cell centre followed by one row per adjacent boundary face (FS.cpp:588-605).
+void FluidSolver::ExportData(int iter) {
+  const size_t n = (size_t)grid->N;
+  vector<double> u(n), v(n), phi(n), pr(n), lap(n);
+  if (nsgpu_get_fields(gpu, u.data(), v.data(), phi.data()) != 0 || nsgpu_pressure(gpu, pr.data(), lap.data()) != 0) {
+    cout << "GPU export failed: " << nsgpu_last_error(gpu) << "\n";
+    return;
+  }
+  char name[255];
+  snprintf(name, sizeof name, "FlowData_%d.csv", iter);
+  ofstream out{name};
+  out << "Point_X,Point_Y,Point_Z,U,V,Pr\n";
+  const double half = dt / (2 * re);
+  for (size_t i = 0; i < grid->cells.size(); i++)
+    for (size_t j = 0; j < grid->cells[i].size(); j++) {
+      const Cell& c = grid->cells[i][j];
+      if (c.id < 0) continue;
+      out << c.x << "," << c.y << "," << 0.0 << "," << u[c.id] << "," << v[c.id] << "," << pr[c.id] << endl;
+      for (int k : c.edges) {
+        if (k < 0) continue;
+        const Edge& e = grid->edges[k];
+        out << c.x + e.nx * grid->hx[i] / 2 << "," << c.y + e.ny * grid->hy[j] / 2 << "," << 0.0 << ","
+            << 0.5 * (u[c.id] + ghostVelocity(u.data(), (int)i, (int)j, k, 0)) << ","
+            << 0.5 * (v[c.id] + ghostVelocity(v.data(), (int)i, (int)j, k, 1)) << ","
+            << 0.5 * (phi[c.id] + ghostPhi(phi.data(), (int)i, (int)j, k)) - half * lap[c.id] << endl;
+      }
+    }
+  out.close();
+}

@@ -1,0 +1,40 @@
+// FluidSolver.h -- host class with the public surface of the reference's FluidSolver (SRC/FluidSolver.h:20-61):
+//   FluidSolver(char* fname, Grid* grid);  bool setup;  void Solve();  double minmode(double, double);
+// The time-step loop itself (reference FS.cpp:536-567 and everything it calls) runs on the GPU behind the C ABI of
+// include/nsgpu.h; this class parses the simulation file, flattens the borrowed Grid into an nsgpu_grid, drives
+// nsgpu_step() and writes the same stdout lines and FlowData_<iter>.csv files as the reference.
+#ifndef NSB200_FLUIDSOLVER_H
+#define NSB200_FLUIDSOLVER_H
+
+#include "compat/petsc.h"   // the reference header pulls in petsc.h (FS.h:3); MAIN_Solver.cpp relies on it
+#include "Grid.h"
+#include "nsgpu.h"
+
+class FluidSolver {
+ private:
+  Grid* grid;                 // borrowed; its edges receive bcType / bcInfo / ghost stencils like in the reference
+  nsgpu_ctx* gpu = nullptr;   // device-resident prevField, RHS vectors, operators (FS.h:22-33)
+  double dt;                  // deliberately uninitialised when the file omits them, like FS.h:24-26
+  double finalTime;
+  double re;
+  int saveIter = 50;
+  bool readSimulationFile(ifstream& in);
+  bool checkParameters();
+  void buildGhostStencils();
+  bool createDeviceSolver();
+  double ghostVelocity(const double* V, int i, int j, int e, int d);
+  double ghostPhi(const double* P, int i, int j, int e);
+  void ExportData(int iter);
+
+ public:
+  bool setup = false;
+  FluidSolver(char* fname, Grid* grid);
+  ~FluidSolver();
+  void Solve();
+  // extras (not in the reference): number of steps Solve() will take, and access for tests
+  nsgpu_ctx* device() { return gpu; }
+};
+
+double minmode(double a, double b);
+
+#endif
