@@ -8,3 +8,4 @@ from .capi import (  # noqa: F401
     GpuFluidSolver, GridDesc, NsGpuError, lib, lib_path,
     U, V, PHI, RHS_U, RHS_V, RHS_PHI, CONV_U0, CONV_V0, GRADPHI_X, GRADPHI_Y, USTAR, VSTAR,
 )
+from .host import HostGrid, HostFluidSolver, load_case, minmode  # noqa: F401,E402

@@ -48,7 +48,18 @@ def _load():
     if not os.path.exists(lib_path):
         raise ImportError("libnsgpu.so is not built (run `make` or __graft_entry__.build()); "
                           "navierstokessolver_b200 has no CPU fallback")
-    L = C.CDLL(lib_path, mode=C.RTLD_GLOBAL)
+    # libnsgpu.so needs "libnccl.so.2".  torch bundles a newer NCCL under the same soname; load that copy first so
+    # that a later `import torch` in the same process (bench.py, torch.distributed plumbing) finds its own symbols.
+    import sys
+    for d in sys.path:
+        cand = os.path.join(d, "nvidia", "nccl", "lib", "libnccl.so.2")
+        if os.path.exists(cand):
+            try:
+                C.CDLL(cand, mode=C.RTLD_GLOBAL)
+                break
+            except OSError:
+                pass
+    L = C.CDLL(lib_path)
     P = C.c_void_p
     dp = C.POINTER(C.c_double)
     L.nsgpu_nccl_unique_id.argtypes = [C.c_void_p]

@@ -1,0 +1,223 @@
+"""CPU-side tests (no GPU): the oracle against itself and its invariants, the host Grid / parser against the reference's,
+the host emulation of the device functions against the oracle, and the C-ABI surface of libnsgpu.so."""
+import ctypes
+import os
+import re
+import subprocess
+
+import numpy as np
+import pytest
+
+import refapi
+from refapi import CASES, ROOT, U, V, PHI, RHS_U, RHS_V, RHS_PHI, CONV_U0, CONV_V0, GRADPHI_X, GRADPHI_Y, USTAR, VSTAR
+
+needs_ref = pytest.mark.skipif(not refapi.have_ref(), reason="oracle/_ref/libnsref.so not built")
+GRIDS = ["cavity_32.grid", "channel.grid", "step.grid"]
+
+
+def _rel(a, b):
+    return np.abs(a - b).max() / max(np.abs(b).max(), 1e-300)
+
+
+# ---------------------------------------------------------------------------------------------- C ABI surface
+def test_library_exports_every_declared_symbol():
+    hdr = open(os.path.join(ROOT, "include", "nsgpu.h")).read()
+    declared = set(re.findall(r"\b(nsgpu_[a-z_0-9]+)\s*\(", hdr))
+    assert len(declared) >= 20
+    lib = ctypes.CDLL(os.path.join(ROOT, "navierstokessolver_b200", "libnsgpu.so"))
+    for name in declared:
+        assert hasattr(lib, name), name
+    from navierstokessolver_b200 import capi
+    assert set(capi.EXPORTED) == declared
+
+
+def test_no_gpu_means_loud_failure_not_a_fallback():
+    import navierstokessolver_b200 as ns
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("a GPU is present")
+    with pytest.raises(ns.NsGpuError) as e:
+        ns.GpuFluidSolver(ns.GridDesc.cavity(16), 0.01, 100.0)
+    assert e.value.code == -3
+
+
+def test_product_never_touches_the_oracle():
+    bad = []
+    for d, _, files in os.walk(os.path.join(ROOT, "navierstokessolver_b200")):
+        for f in files:
+            if f.endswith((".py", ".cu", ".cuh", ".inl", ".h", ".cpp")):
+                txt = open(os.path.join(d, f)).read()
+                if re.search(r"oracle/|libnsref|libnsport|libnsemul|tests/emul", txt) and "TEST" not in f:
+                    if re.search(r"(#include|import|CDLL|dlopen).*(oracle|nsref|nsport|nsemul)", txt):
+                        bad.append(f)
+    assert not bad, bad
+
+
+# ---------------------------------------------------------------------------------------------- host Grid / parsers
+@needs_ref
+@pytest.mark.parametrize("grid", GRIDS + ["cavity_128.grid"])
+def test_host_grid_equals_reference_grid(grid, workdir):
+    import navierstokessolver_b200 as ns
+    L = refapi.ref_lib()
+    h = L.nsref_grid_create(f"{CASES}/{grid}".encode(), 1)
+    assert L.nsref_grid_setup(h)
+    ref_centres = open("CellCenters.csv").read()
+    nx, ny, ne = L.nsref_nx(h), L.nsref_ny(h), L.nsref_n_edges(h)
+    hx, hy = np.empty(nx), np.empty(ny)
+    ids, tags = np.empty(nx * ny, dtype=np.int32), np.empty(nx * ny * 4, dtype=np.int32)
+    dp, ip = refapi._dp, refapi._ip
+    L.nsref_grid_arrays(h, hx.ctypes.data_as(dp), hy.ctypes.data_as(dp), ids.ctypes.data_as(ip), tags.ctypes.data_as(ip), None, None)
+    enx, eny, et = (np.empty(ne, dtype=np.int32) for _ in range(3))
+    ei, loc = np.empty(ne), np.empty(3 * ne)
+    L.nsref_edges(h, enx.ctypes.data_as(ip), eny.ctypes.data_as(ip), et.ctypes.data_as(ip), ei.ctypes.data_as(dp), loc.ctypes.data_as(dp))
+    g = ns.HostGrid(f"{CASES}/{grid}")
+    assert g.setup and (g.N, g.nx, g.ny) == (L.nsref_n(h), nx, ny)
+    assert np.array_equal(g.hx, hx) and np.array_equal(g.hy, hy)          # bit-identical widths
+    assert np.array_equal(g.cell_id, ids) and np.array_equal(g.cell_edges, tags)
+    assert np.array_equal(g.edge_nx, enx) and np.array_equal(g.edge_ny, eny) and np.array_equal(g.edge_loc, loc)
+    assert np.array_equal(g.edge_type, et) and np.array_equal(g.edge_info, ei)   # defaults -1 / 1.0 (Grid.h:25-26)
+    assert open("CellCenters.csv").read() == ref_centres
+
+
+BAD_GRIDS = {
+    "counter_clockwise": "Vertices {\n0 0\n1 0\n1 1\n0 1\n}\nNx {\n0 1 8 -1\n}\nNy {\n0 1 8 -1\n}\n",
+    "diagonal_edge": "Vertices {\n0 0\n0 1\n1 1\n2 0\n}\nNx {\n0 2 8 -1\n}\nNy {\n0 1 8 -1\n}\n",
+    "unknown_keyword": "Vertices {\n0 0\n0 1\n1 1\n1 0\n}\nNz {\n0 1 8 -1\n}\n",
+    "no_brace": "Vertices\n0 0\n0 1\n1 1\n1 0\n}\n",
+    "ratio_zero": "Vertices {\n0 0\n0 1\n1 1\n1 0\n}\nNx {\n0 1 8 0\n}\nNy {\n0 1 8 -1\n}\n",
+    "auto_count": "Vertices {\n0 0\n0 1\n2 1\n2 0\n}\nNx {\n0 1 8 -1\n1 2 0 1.2\n}\nNy {\n0 1 0 -1\n}\n",
+}
+
+
+@needs_ref
+@pytest.mark.parametrize("name", sorted(BAD_GRIDS))
+def test_grid_parser_accepts_and_rejects_like_the_reference(name, workdir):
+    import navierstokessolver_b200 as ns
+    p = workdir / "g.grid"
+    p.write_text(BAD_GRIDS[name])
+    L = refapi.ref_lib()
+    h = L.nsref_grid_create(str(p).encode(), 1)
+    g = ns.HostGrid(str(p))
+    assert g.setup == bool(L.nsref_grid_setup(h))
+    if g.setup:
+        assert g.N == L.nsref_n(h) and g.nx == L.nsref_nx(h)
+
+
+def test_minmode_matches():
+    import navierstokessolver_b200 as ns
+    rng = np.random.default_rng(0)
+    for a, b in rng.standard_normal((200, 2)):
+        want = a * min(1.0, abs(b / a)) if a * b > 0 else 0.0      # FS.cpp:671-674
+        assert ns.minmode(a, b) == want
+        if refapi.have_ref():
+            assert refapi.ref_lib().nsref_minmode(a, b) == want
+
+
+# ---------------------------------------------------------------------------------------------- device arithmetic, on the host
+@needs_ref
+@pytest.mark.parametrize("grid,sim", [("cavity_32.grid", "cavity_re100.sim"), ("channel.grid", "channel.sim"), ("step.grid", "step.sim")])
+def test_device_functions_match_reference_phases(grid, sim, workdir):
+    """Tier A (1e-12): ns_cell.cuh compiled for the host vs the reference's ConstructRHS_V / ConstructRHS_phi /
+    CorrectVelocities and the matrices ConstructLHS assembles."""
+    ref = refapi.RefSolver(f"{CASES}/{grid}", f"{CASES}/{sim}")
+    em = refapi.Emul(dt=ref.dt, re=ref.re, **ref.desc_kwargs())
+    rng = np.random.default_rng(5)
+    for op in (0, 1):
+        x = rng.standard_normal(ref.n)
+        assert _rel(em.apply(op, x), ref.csr(op) @ x) <= 1e-12
+    assert abs(ref.csr(1).sum(axis=1)).max() < 1e-9 * abs(ref.csr(1)).max()     # zero row sums for every BC type
+    for k in (U, V, CONV_U0, CONV_V0, GRADPHI_X, GRADPHI_Y, PHI):
+        a = 0.3 * rng.standard_normal(ref.n)
+        ref.set(k, a)
+        em.set(k, a)
+    ref.construct_rhs_v()
+    em.rhs_build()
+    for k in (RHS_U, RHS_V, CONV_U0, CONV_V0):
+        assert _rel(em.get(k), ref.get(k)) <= 1e-12
+    for k in (USTAR, VSTAR):
+        a = rng.standard_normal(ref.n)
+        ref.set(k, a)
+        em.set(k, a)
+    ref.construct_rhs_phi()
+    ref.nullspace_remove()
+    em.div_rhs(True)
+    assert _rel(em.get(RHS_PHI), ref.get(RHS_PHI)) <= 1e-12
+    assert abs(em.get(RHS_PHI).sum()) < 1e-9 * np.abs(em.get(RHS_PHI)).sum()
+    ref.correct()
+    em.correct()
+    for k in (U, V, GRADPHI_X, GRADPHI_Y):
+        assert _rel(em.get(k), ref.get(k)) <= 1e-12
+
+
+@needs_ref
+def test_multigrid_algorithm_whole_steps_vs_reference(workdir):
+    """Tier B on the host emulation: the V-cycle solver (same loops as the kernels) vs the oracle in exact mode."""
+    ref = refapi.RefSolver(f"{CASES}/cavity_64.grid", f"{CASES}/cavity_re100.sim")
+    ref.set_rtol(1e-12)
+    em = refapi.Emul(dt=ref.dt, re=ref.re, **ref.desc_kwargs())
+    for s in range(4):
+        mm = ref.step(1)
+        me, worst, cyc = em.step(1, rtol=1e-10)
+        assert worst <= 1e-10 and max(cyc) <= 12
+        for k in (U, V, PHI):
+            assert _rel(em.get(k), ref.get(k)) <= 2e-9
+        assert np.allclose(me, mm, atol=1e-9, rtol=0)
+    assert abs(em.get(PHI).mean()) < 1e-12
+
+
+@needs_ref
+def test_oracle_noise_floor_and_invariants(workdir):
+    """oracle(rtol 1e-8, the reference's setting) vs oracle(1e-12): the reference's own solver noise floor."""
+    a = refapi.RefSolver(f"{CASES}/cavity_32.grid", f"{CASES}/cavity_re100.sim")
+    b = refapi.RefSolver(f"{CASES}/cavity_32.grid", f"{CASES}/cavity_re100.sim")
+    b.set_rtol(1e-12)
+    for _ in range(5):
+        a.step(1)
+        b.step(1)
+    for k in (U, V, PHI):
+        assert _rel(a.get(k), b.get(k)) < 1e-5
+    assert abs(b.get(PHI).mean()) < 1e-12 and abs(b.get(RHS_PHI).sum()) < 1e-9
+
+
+@needs_ref
+def test_zero_lid_oracle_stays_at_rest(workdir):
+    sim = workdir / "z.sim"
+    sim.write_text("BC {\n2 0\n2 0\n2 0\n2 0\n}\ndt 0.01\nfinal_time 1\nre 100\nsaveIter 50\n")
+    r = refapi.RefSolver(f"{CASES}/cavity_16.grid", str(sim))
+    assert not r.step(3).any() and not r.get(PHI).any()
+
+
+def test_golden_fixture_matches_oracle_or_emulation(workdir):
+    """tests/golden/cavity32_re100_5steps.npz was written by tests/golden/make_golden.py from the oracle in exact mode."""
+    z = np.load(os.path.join(ROOT, "tests", "golden", "cavity32_re100_5steps.npz"))
+    n = 32
+    em = refapi.Emul(np.full(n, 1.0 / n), np.full(n, 1.0 / n), [-1, 0, 1, 0], [0, 1, 0, -1], [2, 2, 2, 2], [0, 1.0, 0, 0], 0.005, 100.0)
+    em.step(5, rtol=1e-11)
+    for name, k in (("u", U), ("v", V), ("phi", PHI)):
+        assert _rel(em.get(k), z[name]) <= 1e-8
+    if refapi.have_ref():
+        r = refapi.RefSolver(f"{CASES}/cavity_32.grid", f"{CASES}/cavity_re100.sim")
+        r.set_rtol(1e-12)
+        r.step(5)
+        for name, k in (("u", U), ("v", V), ("phi", PHI)):
+            assert _rel(r.get(k), z[name]) <= 1e-9
+
+
+@needs_ref
+def test_reference_main_compiles_unmodified_against_host_headers(workdir):
+    """Drop-in check of the driver: the reference's own MAIN_Solver.cpp builds against host/FluidSolver.h + libnsgpu.so."""
+    src = "/root/reference/SRC/MAIN_Solver.cpp"
+    if not os.path.exists(src):
+        pytest.skip("reference sources not on this machine")
+    pkg = os.path.join(ROOT, "navierstokessolver_b200")
+    out = workdir / "main_ref_on_gpu"
+    # quoted includes look beside the source first, so build from a scratch copy (tmp dir, never the repository)
+    scratch = workdir / "MAIN_Solver.cpp"
+    scratch.write_bytes(open(src, "rb").read())
+    src = str(scratch)
+    cmd = ["/usr/bin/g++", "-std=c++17", "-I", os.path.join(pkg, "host"), "-I", os.path.join(ROOT, "include"), src, "-L", pkg, "-lnsgpu",
+           f"-Wl,-rpath,{pkg}", "-o", str(out)]
+    r = subprocess.run(cmd, capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    r = subprocess.run([str(out)], capture_output=True, text=True)
+    assert "Grid data file or simulation data file not provided!" in r.stdout
