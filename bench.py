@@ -1,0 +1,284 @@
+#!/usr/bin/env python3
+"""bench.py -- the time-step loop of the lid-driven cavity on N B200s (contract: see DESIGN.md "Measurement").
+
+  python bench.py --gpus N --steps K --warmup W            (N > 1: launched by torch.distributed.run, one rank per GPU)
+  python bench.py --impl reference --steps K --warmup W    (the reference's own CPU code on the host cores)
+
+A "step" is one pass of FluidSolver::Solve()'s loop body (reference FS.cpp:546-557): RHS build, two Helmholtz
+solves, divergence + mean removal, Poisson solve, projection, min/max -- every solve converged to a relative true
+residual of 1e-8 (the reference's KSP tolerance).  Workload at N = 1: lid-driven cavity, Re = 1000, 4096 x 4096 cells
+(BASELINE.json configs[2]); weak scaling: every GPU owns a 4096-column slab, the domain is (4096 N) x 4096.
+
+  value  = cells x time steps / second, state resident in HBM, device time (CUDA events on the solver's stream,
+           max over ranks), in Gcell-updates/s (one cell-update = one cell advanced one time step);
+           "timesteps_per_s" and "poisson_gcell_updates_per_s" (the fine-level red-black sweep alone) ride along.
+  e2e    = same metric through the C ABI with HOST buffers: every step uploads the full state (7 fields) from pinned
+           host memory, runs nsgpu_step(1) and downloads u, v, phi.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+METRIC = "timestep_gcell_updates_per_s"
+UNIT = "Gcell-updates/s"
+SWEEP_BYTES_PER_UPDATE = 24.0     # read phi, read b, write phi
+
+
+def measured_peak_gbs():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    except Exception:
+        return 6650.0, "fallback (B200_PROFILING.md, 6.65 TB/s)"
+
+
+class ClockSampler(threading.Thread):
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region."""
+    Q = "clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown," \
+        "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index, self.rows, self.stop_flag = index, [], False
+
+    def run(self):
+        while not self.stop_flag:
+            try:
+                out = subprocess.run(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits"],
+                                     capture_output=True, text=True, timeout=5).stdout.strip()
+                if out:
+                    self.rows.append([x.strip() for x in out.split(",")])
+            except Exception:
+                pass
+            time.sleep(0.1)
+
+    def summary(self):
+        self.stop_flag = True
+        self.join(timeout=6)
+        if not self.rows:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        sm = sorted(float(r[0]) for r in self.rows if r[0].replace(".", "").isdigit())
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = [n for k, n in enumerate(names) if any(len(r) > 2 + k and r[2 + k].lower().startswith("active") for r in self.rows)]
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": float(self.rows[0][1]), "reasons": reasons, "samples": len(self.rows)}
+
+
+def reference_arm(args, rank):
+    """The reference's own CPU implementation (unmodified sources + PETSc stand-in, oracle/_ref) on a bounded sample."""
+    if rank != 0:
+        return
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import tempfile
+    import refapi
+    n = args.ref_n
+    cases = os.path.join(ROOT, "cases")
+    os.chdir(tempfile.mkdtemp())
+    ref = refapi.RefSolver(f"{cases}/cavity_{n}.grid", f"{cases}/cavity_re1000_{n}.sim")
+    ref.step(args.warmup)
+    t0 = time.perf_counter()
+    ref.step(args.steps)
+    dt = time.perf_counter() - t0
+    value = n * n * args.steps / dt / 1e9
+    ph = ref.phase_seconds()
+    line = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": {"workload": "lid-driven cavity Re=1000 from rest, dt=0.25/n, bounded sample %dx%d of the 4096x4096 workload" % (n, n),
+                       "solver": "reference FluidSolver (unmodified) on the PETSc-subset stand-in: ILU(0)-GMRES(30) + ILU(0)-BiCGStab(2), rtol 1e-8"},
+            "timesteps_per_s": args.steps / dt,
+            "cpu_baseline": {"value": value, "unit": UNIT, "cores": 1, "kind": "reference",
+                             "sample": "%d steps of cavity %dx%d after %d warm-up steps; the reference is strictly serial (PETSC_COMM_SELF)" % (args.steps, n, n, args.warmup)},
+            "phase_seconds": dict(zip(["rhs", "helmholtz", "div", "poisson", "correct"], [float(x) for x in ph])),
+            "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line), flush=True)
+
+
+def cpu_baseline_sample(n=512, steps=2):
+    """Oracle (reference sources + PETSc stand-in) on the host cores, bounded sample; reported, not the target."""
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import tempfile
+    import refapi
+    cases = os.path.join(ROOT, "cases")
+    cwd = os.getcwd()
+    os.chdir(tempfile.mkdtemp())
+    try:
+        ref = refapi.RefSolver(f"{cases}/cavity_{n}.grid", f"{cases}/cavity_re1000_{n}.sim")
+        t0 = time.perf_counter()
+        ref.step(steps)
+        dt = time.perf_counter() - t0
+        its = ref.ksp_stats(1)["iterations_total"]
+    finally:
+        os.chdir(cwd)
+    return {"value": n * n * steps / dt / 1e9, "unit": UNIT, "cores": 1, "kind": "reference",
+            "sample": "first %d steps of cavity %dx%d Re=1000 from rest (%.1f s, %d BiCGStab(2) iterations); host has %d cores, the reference uses 1"
+                      % (steps, n, n, dt, its, os.cpu_count()),
+            "timesteps_per_s": steps / dt}
+
+
+def ours(args, rank, world, local_rank):
+    import numpy as np
+    import navierstokessolver_b200 as ns
+    from navierstokessolver_b200 import capi
+    import torch
+    import torch.distributed as dist
+
+    torch.cuda.set_device(local_rank)
+    nccl_id = None
+    if world > 1:
+        dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", local_rank))
+        box = [capi.nccl_unique_id() if rank == 0 else None]
+        dist.broadcast_object_list(box, src=0)
+        nccl_id = box[0]
+
+    ny, nxl = args.ny, args.nx_per_gpu
+    gnx = nxl * world
+    n = ny                                     # dt follows the cell size like the reference inputs: 0.25 * h
+    grid = ns.GridDesc.cavity(ny, nx=gnx, lx=gnx / float(ny))
+    s = ns.GpuFluidSolver(grid, 0.25 / n, args.re, device=local_rank, rank=rank, world=world, nccl_id=nccl_id,
+                          rtol_u=args.rtol, rtol_phi=args.rtol, solver=args.solver, use_graph=args.graph)
+    cells_local, cells_global = nxl * ny, gnx * ny
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(x):
+        if world == 1:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    # ---- the time-step loop, state resident
+    s.step(args.warmup)
+    barrier()
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    t0 = time.perf_counter()
+    info = s.step(args.steps)
+    s.synchronize()
+    wall = time.perf_counter() - t0
+    barrier()
+    clocks = sampler.summary()
+    ms = max_over_ranks(info.ms_total)
+    wall = max_over_ranks(wall)
+    value = cells_global * args.steps / (ms * 1e-3) / 1e9
+    launches = int(info.kernel_launches)
+    fine_sweeps = float(info.fine_sweeps)
+
+    # ---- the dominant kernel alone: fine-level red-black Poisson sweep (k_smooth_rb), CUDA events on its stream
+    s.poisson_sweeps(20, False)
+    best = None
+    for _ in range(5):
+        barrier()
+        _, sms = s.poisson_sweeps(args.sweeps, False)
+        sms = max_over_ranks(sms) / args.sweeps
+        best = sms if best is None else min(best, sms)
+    sweep_gcups = cells_global / (best * 1e-3) / 1e9
+    peak, peak_src = measured_peak_gbs()
+    achieved = cells_local * SWEEP_BYTES_PER_UPDATE / (best * 1e-3) / 1e9
+    traffic = None
+    tpath = os.path.join(ROOT, "profiles", "sweep_traffic.json")
+    if os.path.exists(tpath):
+        try:
+            traffic = json.load(open(tpath)).get("dram_bytes_per_launch")
+        except Exception:
+            traffic = None
+
+    # ---- end to end through the C ABI with host buffers (pinned), full state up, fields down, every step
+    fields_up = [ns.U, ns.V, ns.PHI, ns.CONV_U0, ns.CONV_V0, ns.GRADPHI_X, ns.GRADPHI_Y]
+    fields_down = [ns.U, ns.V, ns.PHI]
+    host = {k: torch.empty(s.n_local, dtype=torch.float64).pin_memory().numpy() for k in fields_up}
+    for k in fields_up:
+        host[k][:] = s.get(k)
+    e2e_steps = max(2, min(args.steps, 5))
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(e2e_steps):
+        for k in fields_up:
+            s.set(k, host[k])
+        s.step(1)
+        for k in fields_down:
+            capi.lib.nsgpu_get_array(s._h, k, capi._dp(host[k]))
+        # the remaining state (convective terms, grad phi) is produced on the device: fetch it for the next upload
+        for k in fields_up[3:]:
+            capi.lib.nsgpu_get_array(s._h, k, capi._dp(host[k]))
+    s.synchronize()
+    e2e_wall = max_over_ranks(time.perf_counter() - t0)
+    e2e_value = cells_global * e2e_steps / e2e_wall / 1e9
+    h2d = 8 * s.n_local * len(fields_up)
+    d2h = 8 * s.n_local * len(fields_up)
+
+    cpu = cpu_baseline_sample() if (rank == 0 and world == 1 and not args.no_cpu_baseline) else None
+
+    if rank == 0:
+        line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+                "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
+                "data": "synthetic",
+                "config": {"workload": "lid-driven cavity Re=%g from rest, %dx%d cells (%d columns per GPU), dt=0.25/%d" % (args.re, gnx, ny, nxl, n),
+                           "parallelism": "x-slabs, %d rank(s), NCCL halo exchange + scalar allreduce" % world,
+                           "solver": ("BiCGStab + V(2,2)" if args.solver else "multigrid V(2,2) iteration") + ", red-black GS smoother, rtol %g both solves" % args.rtol,
+                           "levels": s.num_levels, "cache": "inputs larger than L2 (13 resident fields x %.0f MB per GPU)" % (cells_local * 8 / 1e6)},
+                "timesteps_per_s": args.steps / (ms * 1e-3),
+                "poisson_gcell_updates_per_s": sweep_gcups,
+                "solver_iterations_last_step": {"u": info.it_u, "v": info.it_v, "phi": info.it_phi},
+                "residuals_last_step": {"u": info.res_u, "v": info.res_v, "phi": info.res_phi},
+                "fine_poisson_sweeps_per_step": fine_sweeps / args.steps,
+                "host_wall_ms_per_step": 1e3 * wall / args.steps,
+                "gpu_launches": launches,
+                "clocks": clocks,
+                "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "steps": e2e_steps,
+                        "ms_per_step": 1e3 * e2e_wall / e2e_steps},
+                "roofline": {"bound": "hbm", "kernel": "k_smooth_rb (fine-level fused red-black Poisson sweep)", "achieved": achieved, "peak": peak,
+                             "unit": "GB/s", "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
+                             "bytes_per_cell_update": SWEEP_BYTES_PER_UPDATE, "us_per_launch": best * 1e3,
+                             "cells_per_launch": cells_local, "timing": "CUDA events on the solver stream around %d back-to-back launches, best of 5" % args.sweeps},
+                "status": int(info.status)}
+        if cpu:
+            line["cpu_baseline"] = cpu
+        print(json.dumps(line), flush=True)
+    s.close()
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--ny", type=int, default=4096)
+    ap.add_argument("--nx-per-gpu", type=int, default=4096)
+    ap.add_argument("--re", type=float, default=1000.0)
+    ap.add_argument("--rtol", type=float, default=1e-8)
+    ap.add_argument("--solver", type=int, default=0)
+    ap.add_argument("--graph", type=int, default=0)
+    ap.add_argument("--sweeps", type=int, default=100)
+    ap.add_argument("--ref-n", type=int, default=256)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference":
+        reference_arm(args, rank)
+        return
+    if world != args.gpus:
+        if world == 1 and args.gpus > 1:
+            sys.exit("bench.py --gpus %d must be launched with torch.distributed.run --nproc-per-node %d" % (args.gpus, args.gpus))
+    ours(args, rank, world, local_rank)
+
+
+if __name__ == "__main__":
+    main()
