@@ -9,6 +9,7 @@
 #include <cmath>
 #include "../../include/nsgpu.h"
 #include "ns_kernels.cuh"
+#include "ns_march.cuh"
 #include "ns_hostgeom.h"
 
 namespace nsgpu {
@@ -23,6 +24,9 @@ struct Level {
   double* b = nullptr;
   std::vector<void*> owned;  // device allocations of this level (geometry arrays)
   int coarse_sweeps = 0;     // only used on the coarsest level
+  const double* mcx[2] = {nullptr, nullptr};   // folded coefficient tables of k_sweep_march, per operator
+  const double* mcy[2] = {nullptr, nullptr};
+  bool march_ok[2] = {false, false};
 };
 
 struct SolveResult { int cycles = 0; double rel = 0.0; bool converged = false; };
@@ -36,6 +40,7 @@ struct nsgpu_ctx {
   double dt = 0, re = 0;
   double rtol_u = 1e-8, rtol_phi = 1e-8;
   int max_cycles = 200, nu_pre = 2, nu_post = 2, solver = 0, use_graph = 0;
+  int march = 1, march_ri = 0;   // NSGPU_MARCH=0 forces the generic tile kernel; NSGPU_RI overrides the chunk length
   cudaStream_t stream = nullptr;
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;
   ncclComm_t comm = nullptr;

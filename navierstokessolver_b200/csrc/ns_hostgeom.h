@@ -39,6 +39,10 @@ struct GeomArrays {
   std::vector<double> hx, hy, rhx, rhy, rsx, rsy, bx, by;
   std::vector<Pair> ax, ay;
   std::vector<uint8_t> flags, cedges;  // padded layout; empty on the rectangle fast path
+  // rectangle fast path (k_sweep_march): per operator, 3 doubles per column / row with the boundary rows of
+  // LHS_V / LHS_phi and the scaling alpha, beta folded in:  x_new = (b + cw xW + ce xE + cs xS + cn xN) / (dx + dy)
+  std::vector<double> mcx[2], mcy[2];
+  bool march_ok[2] = {false, false};
 };
 
 static inline double clamp_get(const std::vector<double>& a, int k) {
@@ -93,6 +97,38 @@ static inline void make_geom_arrays(const HostLevel& H, int gi0, int nx, const s
 static inline void geom_scalars(const GeomArrays& A, const HostPlan& P, LevelGeom& g) {
   g.nx = A.nx; g.ny = A.ny; g.ld = A.ld; g.gi0 = A.gi0; g.gnx = A.gnx;
   for (int k = 0; k < 4; k++) { g.side_out[k] = P.side_out[k]; g.side_edge[k] = P.side_edge[k]; }
+}
+
+// Folded 1-D coefficient tables of the marching sweep (rectangles only).  op 0: A = I - beta L_V (velocity ghosts:
+// Dirichlet-type sides add 2/h^2 to the diagonal, outflow sides drop out, FS.cpp:88,99,147-164); op 1: A = L_phi
+// (Neumann sides drop out; the outflow rows of L_phi reach two cells inward and are not separable -> march_ok false).
+// Indices outside the global domain get cw = ce = 0 and a dummy diagonal part so that every lane computes finite values.
+static inline void make_march_coefs(const HostLevel& H, const HostPlan& P, double dt, double re, GeomArrays& A) {
+  if (!P.rect) return;
+  const int nxa = A.nx + 2 * HX, nya = A.ny + 2 * PJ;
+  for (int op = 0; op < 2; op++) {
+    const double alpha = op == 0 ? 1.0 : 0.0, beta = op == 0 ? dt / (2.0 * re) : -1.0;
+    const double dummy = op == 0 ? 1.0 : -1.0;
+    A.march_ok[op] = !(op == 1 && (P.side_out[0] || P.side_out[1] || P.side_out[2] || P.side_out[3]));
+    A.mcx[op].assign((size_t)3 * nxa, 0.0);
+    A.mcy[op].assign((size_t)3 * nya, 0.0);
+    for (int a = 0; a < nxa; a++) {
+      const int ig = A.gi0 + a - HX;
+      double cw = 0, ce = 0, d = 0;
+      if (ig < 0 || ig >= H.gnx) { A.mcx[op][3 * a + 2] = dummy; continue; }
+      if (ig > 0) { cw = beta * A.ax[a].m; d -= A.ax[a].m; } else if (op == 0 && !P.side_out[0]) d -= 2.0 * A.bx[a];
+      if (ig < H.gnx - 1) { ce = beta * A.ax[a].p; d -= A.ax[a].p; } else if (op == 0 && !P.side_out[1]) d -= 2.0 * A.bx[a];
+      A.mcx[op][3 * a] = cw; A.mcx[op][3 * a + 1] = ce; A.mcx[op][3 * a + 2] = 0.5 * alpha - beta * d;
+    }
+    for (int a = 0; a < nya; a++) {
+      const int jg = a - PJ;
+      double cs = 0, cn = 0, d = 0;
+      if (jg < 0 || jg >= H.ny) { A.mcy[op][3 * a + 2] = dummy; continue; }
+      if (jg > 0) { cs = beta * A.ay[a].m; d -= A.ay[a].m; } else if (op == 0 && !P.side_out[2]) d -= 2.0 * A.by[a];
+      if (jg < H.ny - 1) { cn = beta * A.ay[a].p; d -= A.ay[a].p; } else if (op == 0 && !P.side_out[3]) d -= 2.0 * A.by[a];
+      A.mcy[op][3 * a] = cs; A.mcy[op][3 * a + 1] = cn; A.mcy[op][3 * a + 2] = 0.5 * alpha - beta * d;
+    }
+  }
 }
 
 static inline double mean_of(const std::vector<double>& a) {

@@ -28,6 +28,10 @@ struct Reducer {
 struct OpSum { __device__ static double f(double a, double b) { return a + b; } __device__ static double id() { return 0.0; } };
 struct OpMax { __device__ static double f(double a, double b) { return fmax(a, b); } __device__ static double id() { return -1.79769313486231570e308; } };
 
+// blockIdx.y owns a contiguous run of columns, so the x-neighbour columns a block re-reads are still in its L1
+__device__ __forceinline__ int chunk_lo(int nx) { return (int)(((long long)nx * blockIdx.y) / gridDim.y); }
+__device__ __forceinline__ int chunk_hi(int nx) { return (int)(((long long)nx * (blockIdx.y + 1)) / gridDim.y); }
+
 template <class OP>
 __device__ __forceinline__ double warp_red(double v) {
 #pragma unroll
@@ -166,7 +170,7 @@ k_residual(LevelGeom g, const double* __restrict__ x, const double* __restrict__
            double alpha, double beta, Reducer red, double* out) {
   const int j = blockIdx.x * blockDim.x + threadIdx.x;
   double acc[1] = {0.0};
-  for (int i = blockIdx.y; i < g.nx; i += gridDim.y) {
+  for (int i = chunk_lo(g.nx), i_hi = chunk_hi(g.nx); i < i_hi; i++) {
     if (j < g.ny) {
       const unsigned f = cell_flags<RECT>(g, i, j);
       if (f != F_OUTSIDE) {
@@ -187,7 +191,7 @@ k_apply(LevelGeom g, const double* __restrict__ x, double* __restrict__ y, const
         double alpha, double beta, Reducer red, double* out) {
   const int j = blockIdx.x * blockDim.x + threadIdx.x;
   double acc[2] = {0.0, 0.0};
-  for (int i = blockIdx.y; i < g.nx; i += gridDim.y) {
+  for (int i = chunk_lo(g.nx), i_hi = chunk_hi(g.nx); i < i_hi; i++) {
     if (j < g.ny) {
       const unsigned f = cell_flags<RECT>(g, i, j);
       if (f != F_OUTSIDE) {
@@ -228,7 +232,7 @@ __global__ void __launch_bounds__(256)
 k_prolong_add(LevelGeom gf, LevelGeom gc, double* __restrict__ xf, const double* __restrict__ xc, int cx, int cy) {
   const int j = blockIdx.x * blockDim.x + threadIdx.x;
   if (j >= gf.ny) return;
-  for (int i = blockIdx.y; i < gf.nx; i += gridDim.y) {
+  for (int i = chunk_lo(gf.nx), i_hi = chunk_hi(gf.nx); i < i_hi; i++) {
     if (cell_flags<RECT>(gf, i, j) == F_OUTSIDE) continue;
     xf[cidx(gf, i, j)] += xc[cidx(gc, i / cx, j / cy)];
   }
@@ -261,7 +265,7 @@ k_div_rhs(LevelGeom g, const EdgeDev* __restrict__ edges, StepConst sc, const do
           const double* __restrict__ v, double* __restrict__ b, Reducer red, double* out) {
   const int j = blockIdx.x * blockDim.x + threadIdx.x;
   double acc[1] = {0.0};
-  for (int i = blockIdx.y; i < g.nx; i += gridDim.y) {
+  for (int i = chunk_lo(g.nx), i_hi = chunk_hi(g.nx); i < i_hi; i++) {
     if (j < g.ny && cell_flags<RECT>(g, i, j) != F_OUTSIDE) {
       const size_t id = cidx(g, i, j);
       const double d = div_cell<RECT>(g, edges, sc, i, j, u + id, v + id);
@@ -279,7 +283,7 @@ k_sub_mean(LevelGeom g, double* __restrict__ b, const double* __restrict__ sum, 
   const int j = blockIdx.x * blockDim.x + threadIdx.x;
   if (j >= g.ny) return;
   const double m = *sum * inv_n;
-  for (int i = blockIdx.y; i < g.nx; i += gridDim.y)
+  for (int i = chunk_lo(g.nx), i_hi = chunk_hi(g.nx); i < i_hi; i++)
     if (cell_flags<RECT>(g, i, j) != F_OUTSIDE) b[cidx(g, i, j)] -= m;
 }
 
@@ -291,7 +295,7 @@ k_correct(LevelGeom g, StepConst sc, const double* __restrict__ phi, const doubl
           double* __restrict__ gpy, Reducer red, double* out) {
   const int j = blockIdx.x * blockDim.x + threadIdx.x;
   double acc[4] = {OpMax::id(), OpMax::id(), OpMax::id(), OpMax::id()};
-  for (int i = blockIdx.y; i < g.nx; i += gridDim.y) {
+  for (int i = chunk_lo(g.nx), i_hi = chunk_hi(g.nx); i < i_hi; i++) {
     if (j < g.ny) {
       const unsigned f = cell_flags<RECT>(g, i, j);
       if (f != F_OUTSIDE) {

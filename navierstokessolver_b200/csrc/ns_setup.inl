@@ -50,6 +50,7 @@ static int dev_zeros(nsgpu_ctx* ctx, std::vector<void*>& owned, size_t n_doubles
 static int build_level_geom(nsgpu_ctx* ctx, Level& L, const HostPlan& P, size_t l) {
   GeomArrays A;
   make_geom_arrays(P.levels[l], P.lgi0[l], P.lnx[l], (l == 0 && !P.rect) ? &P.cedges0 : nullptr, A);
+  make_march_coefs(P.levels[l], P, ctx->dt, ctx->re, A);
   LevelGeom& g = L.g;
   geom_scalars(A, P, g);
   L.gny = A.ny;
@@ -65,6 +66,13 @@ static int build_level_geom(nsgpu_ctx* ctx, Level& L, const HostPlan& P, size_t 
   if ((rc = dev_upload(ctx, L.owned, A.ay, &g.ay))) return rc;
   if ((rc = dev_upload(ctx, L.owned, A.bx, &g.bx))) return rc;
   if ((rc = dev_upload(ctx, L.owned, A.by, &g.by))) return rc;
+  for (int op = 0; op < 2; op++) {
+    L.march_ok[op] = A.march_ok[op];
+    if (!A.mcx[op].empty()) {
+      if ((rc = dev_upload(ctx, L.owned, A.mcx[op], &L.mcx[op]))) return rc;
+      if ((rc = dev_upload(ctx, L.owned, A.mcy[op], &L.mcy[op]))) return rc;
+    }
+  }
   g.flags = nullptr;
   g.cedges = nullptr;
   if (!A.flags.empty() && (rc = dev_upload(ctx, L.owned, A.flags, &g.flags))) return rc;
@@ -100,6 +108,8 @@ static int create_impl(nsgpu_ctx* ctx, const nsgpu_grid* G, const nsgpu_params* 
   ctx->nu_post = P->nu_post > 0 ? P->nu_post : 2;
   ctx->solver = P->solver;
   ctx->use_graph = P->use_graph;
+  if (const char* e = getenv("NSGPU_MARCH")) ctx->march = atoi(e);
+  if (const char* e = getenv("NSGPU_RI")) ctx->march_ri = atoi(e);
   HostPlan plan;
   {
     int rc = make_host_plan(G, ctx->rank, ctx->world, P->max_levels, plan, ctx->err);

@@ -28,7 +28,7 @@ static inline OpCoef coef_phi() { return OpCoef{1, 0.0, -1.0}; }                
 #define NS_DISPATCH_RECT(rect, CALL) \
   do { if (rect) { CALL(true); } else { CALL(false); } } while (0)
 
-static inline dim3 grid_cols(const LevelGeom& g, int threads, int max_blocks = RED_MAX_BLOCKS) {
+static inline dim3 grid_cols(const LevelGeom& g, int threads, int max_blocks = 148 * 16) {
   unsigned gx = (unsigned)((g.ny + threads - 1) / threads);
   unsigned gy = (unsigned)std::max(1, std::min(g.nx, max_blocks / (int)gx));
   return dim3(gx, gy, 1);
@@ -59,11 +59,30 @@ static int allreduce(nsgpu_ctx* ctx, double* d, int n, ncclRedOp_t op) {
 }
 
 // n sweeps of red-black Gauss-Seidel on level L; *x is the current iterate, *xt its ping-pong partner.
+static inline int march_chunk(const nsgpu_ctx* ctx, const Level& L, int uj) {
+  if (ctx->march_ri > 0) return std::min(ctx->march_ri, L.g.nx);
+  // enough warps for ~2 waves of 148 SMs x 24 resident warps, chunks no shorter than 8 columns
+  const int wj = (L.g.ny + uj - 1) / uj;
+  const int chunks = std::max(1, (2 * 148 * 24 + wj - 1) / wj);
+  return std::min(L.g.nx, std::max(8, (L.g.nx + chunks - 1) / chunks));
+}
+
 static int smooth(nsgpu_ctx* ctx, const Level& L, OpCoef c, double** x, double** xt, const double* b, int n) {
   const dim3 grid((L.g.ny + SM_TJ - 1) / SM_TJ, (L.g.nx + SM_TI - 1) / SM_TI);
+  const bool march = ctx->march && ctx->rect && L.march_ok[c.op];
   for (int s = 0; s < n; s++) {
     int rc = halo_exchange(ctx, L, *x, 2);
     if (rc) return rc;
+    if (march) {
+      constexpr int UJ = 60;
+      const int ri = march_chunk(ctx, L, UJ);
+      const dim3 mg(((L.g.ny + UJ - 1) / UJ + MARCH_WARPS - 1) / MARCH_WARPS, (L.g.nx + ri - 1) / ri);
+      const size_t sh = (size_t)3 * (ri + 3 * 2) * sizeof(double);
+      k_sweep_march<1><<<mg, MARCH_THREADS, sh, ctx->stream>>>(L.g, L.mcx[c.op], L.mcy[c.op], *x, b, *xt, ri);
+      NS_LAUNCH_CHECK();
+      std::swap(*x, *xt);
+      continue;
+    }
 #define CALL(OP, RECT) k_smooth_rb<OP, RECT, false><<<grid, SM_THREADS, 0, ctx->stream>>>(L.g, *x, b, *xt, c.alpha, c.beta)
     NS_DISPATCH_OP_RECT(c.op, ctx->rect, CALL);
 #undef CALL
