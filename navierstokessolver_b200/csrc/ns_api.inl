@@ -169,6 +169,7 @@ int nsgpu_solve_velocity(nsgpu_ctx* ctx, nsgpu_step_info* info) {
   int rc = phase_velocity(ctx, &ru, &rv);
   if (rc) return rc;
   if ((rc = sync_check(ctx))) return rc;
+  finish_results(ctx, &ru, &rv, nullptr);
   if (info) { memset(info, 0, sizeof *info); fill_info(info, ru, rv, rp); }
   return (ru.converged && rv.converged) ? 0 : NSGPU_ERR_NOT_CONVERGED;
 }
@@ -187,6 +188,7 @@ int nsgpu_solve_phi(nsgpu_ctx* ctx, nsgpu_step_info* info) {
   int rc = phase_phi(ctx, &rp);
   if (rc) return rc;
   if ((rc = sync_check(ctx))) return rc;
+  finish_results(ctx, nullptr, nullptr, &rp);
   if (info) { memset(info, 0, sizeof *info); fill_info(info, ru, rv, rp); }
   return rp.converged ? 0 : NSGPU_ERR_NOT_CONVERGED;
 }
@@ -216,10 +218,16 @@ int nsgpu_step(nsgpu_ctx* ctx, int32_t n_steps, nsgpu_step_info* last) {
     if ((rc = phase_div(ctx, true))) return rc;
     if ((rc = phase_phi(ctx, &rp))) return rc;
     if ((rc = phase_correct(ctx, (s == n_steps - 1) ? mm : nullptr))) return rc;
-    if (!(ru.converged && rv.converged && rp.converged)) status = NSGPU_ERR_NOT_CONVERGED;   // silent in the reference
+    if (!((ru.pending || ru.converged) && (rv.pending || rv.converged) && (rp.pending || rp.converged))) status = NSGPU_ERR_NOT_CONVERGED;   // silent in the reference
   }
   NS_CUDA(cudaEventRecord(ctx->ev1, ctx->stream));
   if ((rc = sync_check(ctx))) return rc;
+  if (n_steps > 0) {
+    const bool pend[3] = {ru.pending, rv.pending, rp.pending};
+    finish_results(ctx, &ru, &rv, &rp);
+    for (int k = 0; k < 3; k++)   // device-controlled solves count their failures on the device, over all the steps of this call
+      if (pend[k]) { if (ctx->h_ctl[k].fails != ctx->seen_fails[k]) status = NSGPU_ERR_NOT_CONVERGED; ctx->seen_fails[k] = ctx->h_ctl[k].fails; }
+  }
   float ms = 0;
   NS_CUDA(cudaEventElapsedTime(&ms, ctx->ev0, ctx->ev1));
   if (n_steps > 0 && !(std::isfinite(mm[0]) && std::isfinite(mm[1]) && std::isfinite(mm[2]) && std::isfinite(mm[3]))) status = NSGPU_ERR_NAN;

@@ -3,9 +3,10 @@
 // Device data layout (all fields, every multigrid level):
 //   value(i, j) lives at  (i + HX) * ld + (j + PJ),   i in [-HX, nx + HX),  j in [-PJ, ny + PJ)
 //   i = local x index inside this rank's slab (outer, like the reference's cells[i][j]), j = y (inner,
-//   unit stride: the reference's id = i*ny + j, Grid.cpp:149-161).  HX = 2 halo columns on each side hold
-//   the neighbour slab's cells (or nothing at a domain boundary); PJ = 4 padding rows keep every
-//   radius-2 read in bounds and every column 32-byte aligned (ld is a multiple of 4).
+//   unit stride: the reference's id = i*ny + j, Grid.cpp:149-161).  HX = 6 halo columns on each side hold
+//   the neighbour slab's cells (or zeros at a domain boundary): wide enough for two fused sweeps plus the
+//   fused residual (5 columns, ns_march.cuh); PJ = 8 padding rows keep every strip-halo read in bounds and
+//   every column 32-byte aligned (ld is a multiple of 4).
 //
 // The functions here are the matrix-free restatement of the reference's operators and per-cell physics:
 //   row_eval      rows of LHS_V / LHS_phi            FS.cpp:105-164 (ConstructLHS, AddGhostStencils)
@@ -26,8 +27,9 @@
 
 namespace nsgpu {
 
-constexpr int HX = 2;
-constexpr int PJ = 4;
+constexpr int HX = 6;
+constexpr int PJ = 8;
+constexpr int SLACK_COLS = 8;   // allocated (zero) columns behind the last halo column: the marching kernel prefetches past its chunk
 
 // per-cell flag byte: bits 0-3 = neighbour W,E,S,N is a fluid cell; bits 4-7 = that side is an outflow
 // (bcType 4) edge, meaningful only where the neighbour is absent; 0xFF = cell outside the domain.

@@ -29,7 +29,16 @@ struct Level {
   bool march_ok[2] = {false, false};
 };
 
-struct SolveResult { int cycles = 0; double rel = 0.0; bool converged = false; };
+struct SolveResult { int cycles = 0; double rel = 0.0; bool converged = false; bool pending = false; };
+
+// One linear solve as a CUDA graph: head (|b|^2, first residual) -> WHILE(not converged){ V-cycle } -> tail.
+struct SolveGraph {
+  cudaGraph_t graph = nullptr;
+  cudaGraphExec_t exec = nullptr;
+  const double *x = nullptr, *xt = nullptr, *b = nullptr;   // buffers the graph was built for
+  double rtol = 0;
+  int launches_fixed = 0, launches_body = 0;                 // kernels outside / inside the loop body
+};
 
 }  // namespace nsgpu
 
@@ -40,7 +49,7 @@ struct nsgpu_ctx {
   double dt = 0, re = 0;
   double rtol_u = 1e-8, rtol_phi = 1e-8;
   int max_cycles = 200, nu_pre = 2, nu_post = 2, solver = 0, use_graph = 0;
-  int march = 1, march_ri = 0;   // NSGPU_MARCH=0 forces the generic tile kernel; NSGPU_RI overrides the chunk length
+  int march = 1, march_ri = 0, march_pf = 3, march_wps = 24;   // NSGPU_MARCH=0 forces the generic tile kernel; NSGPU_RI overrides the chunk length
   cudaStream_t stream = nullptr;
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;
   ncclComm_t comm = nullptr;
@@ -66,6 +75,13 @@ struct nsgpu_ctx {
   double* d_scal = nullptr;     // device scalars (64 doubles)
   double* h_scal = nullptr;     // pinned mirror
   double* h_stage = nullptr;    // host staging for general-domain field transfers
+  // device-resident convergence control, one block per solve slot (0 = u, 1 = v, 2 = phi)
+  nsgpu::SolveCtl* d_ctl = nullptr;
+  nsgpu::SolveCtl* h_ctl = nullptr;       // pinned mirror
+  int seen_cycles[3] = {0, 0, 0}, seen_fails[3] = {0, 0, 0};
+  nsgpu::SolveGraph sgraph[3];
+  int graph_cycles_pending[3] = {0, 0, 0};
+  bool capturing = false;
   int64_t launches = 0;
   double fine_sweeps_phi = 0;
   std::vector<void*> owned;

@@ -55,7 +55,7 @@ static inline void make_geom_arrays(const HostLevel& H, int gi0, int nx, const s
   const int ny = H.ny;
   A.nx = nx; A.ny = ny; A.gi0 = gi0; A.gnx = H.gnx;
   A.ld = ((ny + 3) / 4) * 4 + 2 * PJ;
-  A.stride = (size_t)(nx + 2 * HX) * A.ld;
+  A.stride = (size_t)(nx + 2 * HX + SLACK_COLS) * A.ld;
   const int nxa = nx + 2 * HX, nya = ny + 2 * PJ;
   A.hx.resize(nxa); A.rhx.resize(nxa); A.rsx.resize(nxa); A.bx.resize(nxa); A.ax.resize(nxa);
   A.hy.resize(nya); A.rhy.resize(nya); A.rsy.resize(nya); A.by.resize(nya); A.ay.resize(nya);

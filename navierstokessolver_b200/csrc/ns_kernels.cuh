@@ -40,8 +40,11 @@ __device__ __forceinline__ double warp_red(double v) {
 }
 
 // Block-level then grid-level reduction of NV values held by every thread.  All threads of the block must call.
-template <int NV, class OP>
-__device__ void grid_reduce(double (&v)[NV], Reducer red, double* out) {
+struct NoEpilogue { __device__ void operator()(const double*) const {} };
+
+// `epi(out)` runs once, in the thread that wrote the results, after they are in place.
+template <int NV, class OP, class EPI = NoEpilogue>
+__device__ void grid_reduce(double (&v)[NV], Reducer red, double* out, EPI epi = EPI()) {
   __shared__ double sm[NV][32];
   __shared__ bool is_last;
   const int tid = threadIdx.x + blockDim.x * (threadIdx.y + blockDim.y * threadIdx.z);
@@ -85,7 +88,47 @@ __device__ void grid_reduce(double (&v)[NV], Reducer red, double* out) {
       if (lane == 0) out[k] = z;
     }
   }
-  if (tid == 0) *red.counter = 0u;
+  if (tid == 0) { *red.counter = 0u; epi(out); }
+}
+
+// Convergence control block of one linear solve, resident on the device (one per solve slot).
+struct SolveCtl {
+  double bn2;        // |b|^2
+  double rn2;        // |b - A x|^2 after the last cycle
+  double tol2;       // rtol^2
+  int cycles, max_cycles;
+  int go;            // loop condition computed by the last residual reduction
+  int zero_rhs;      // b == 0: the solution is x = 0 (k_zero_if)
+  int total_cycles;  // cumulative over the life of the context (never reset on the device)
+  int fails;         // cumulative number of solves that stopped at max_cycles above the tolerance
+  unsigned long long handle;   // cudaGraphConditionalHandle of the WHILE node (0: none)
+};
+
+struct CtlEpilogue {
+  SolveCtl* c;
+  __device__ void operator()(const double* out) const {
+    if (!c) return;
+    const double rn2 = out[0];
+    c->rn2 = rn2;
+    c->cycles += 1;
+    if (c->cycles > 0) c->total_cycles += 1;
+    const bool zero = !(c->bn2 > 0.0);
+    c->zero_rhs = zero ? 1 : 0;
+    const bool go = !zero && (rn2 > c->tol2 * c->bn2) && (c->cycles < c->max_cycles) && (rn2 == rn2);
+    c->go = go ? 1 : 0;
+    if (!go && !zero && !(rn2 <= c->tol2 * c->bn2)) c->fails += 1;
+    if (c->handle) cudaGraphSetConditional((cudaGraphConditionalHandle)c->handle, go ? 1u : 0u);
+  }
+};
+
+// ctl <- start of a solve: cycles = -1 (the first residual reduction brings it to 0)
+__global__ void k_ctl_init(SolveCtl* c, double tol2, int max_cycles, unsigned long long handle) {
+  c->tol2 = tol2; c->max_cycles = max_cycles; c->cycles = -1; c->go = 0; c->zero_rhs = 0; c->handle = handle; c->rn2 = 0.0;
+}
+// x <- 0 when the right-hand side was identically zero (KSPSolve returns x = 0 for b = 0)
+__global__ void __launch_bounds__(256) k_zero_if(size_t n, double* __restrict__ x, const SolveCtl* __restrict__ c) {
+  if (!c->zero_rhs) return;
+  for (size_t k = blockIdx.x * (size_t)blockDim.x + threadIdx.x; k < n; k += (size_t)gridDim.x * blockDim.x) x[k] = 0.0;
 }
 
 // ---------------------------------------------------------------------------------------------------------
@@ -167,7 +210,7 @@ k_smooth_rb(LevelGeom g, const double* __restrict__ xin, const double* __restric
 template <int OP, bool RECT, bool WRITE, bool NORM>
 __global__ void __launch_bounds__(256)
 k_residual(LevelGeom g, const double* __restrict__ x, const double* __restrict__ b, double* __restrict__ r,
-           double alpha, double beta, Reducer red, double* out) {
+           double alpha, double beta, Reducer red, double* out, SolveCtl* ctl) {
   const int j = blockIdx.x * blockDim.x + threadIdx.x;
   double acc[1] = {0.0};
   for (int i = chunk_lo(g.nx), i_hi = chunk_hi(g.nx); i < i_hi; i++) {
@@ -181,7 +224,7 @@ k_residual(LevelGeom g, const double* __restrict__ x, const double* __restrict__
       }
     }
   }
-  if (NORM) grid_reduce<1, OpSum>(acc, red, out);
+  if (NORM) grid_reduce<1, OpSum>(acc, red, out, CtlEpilogue{ctl});
 }
 
 // y = A x, optionally with the dots (w, y) and (y, y)

@@ -1,20 +1,24 @@
-// ns_march.cuh -- the fine-level hot kernel: NSW fused red-black Gauss-Seidel sweeps in ONE pass over HBM,
-// register-marching along x (the outer index), rectangle fast path.
+// ns_march.cuh -- the hot kernel of both linear solves: NSW fused red-black Gauss-Seidel sweeps in ONE pass over
+// HBM, register-marching along x (the outer index), with the neighbouring multigrid transfers fused in:
+//   PROLONG   the coarse-grid correction is added while the column is loaded      (x <- x + P xc)
+//   RES == 1  the residual of the smoothed iterate is restricted to the coarse rhs (bc <- R (b - A x))
+//   RES == 2  the squared residual norm of the smoothed iterate is reduced         (out <- |b - A x|^2)
+// so that one V(2,2) cycle touches every level exactly twice.  Rectangle fast path (1-D folded coefficients).
 //
 // Replaces the inner iterations of KSPSolve(phiSolver) / KSPSolve(uSolver) (reference FS.cpp:547-551) on the
-// operators ConstructLHS assembles (FS.cpp:105-145); identical arithmetic order to k_smooth_rb (red = (gi + j)
-// even first, then black, out of place), with the division replaced by a reciprocal good to 1 ulp.
+// operators ConstructLHS assembles (FS.cpp:105-145); same arithmetic order as k_smooth_rb (red = (gi + j) even
+// first, then black, out of place), with the division replaced by a reciprocal good to 1 ulp.
 //
 // Mapping.  Memory is y-fastest (id = i*ny + j, Grid.cpp:149-161).  A warp owns a strip of 64 consecutive j
-// (lane l holds the pair j0 = strip - L + 2l, j0 + 1 as one double2: one red and one black cell of every
+// (lane l holds the pair j0 = strip - HJ + 2l, j0 + 1 as one double2: one red and one black cell of every
 // column) and marches over the columns i of its chunk.  Per column it issues one 16-byte load of x and of b
-// per lane (512 contiguous bytes per warp), keeps the 2*NSW + 2 most recent columns in registers, and applies
-// the 2*NSW half-sweeps as a software pipeline: when column n arrives, half-sweep s updates column n - 1 - s.
-// y-neighbours come from the partner cell of the pair or from the adjacent lane (one shuffle per half-sweep),
-// x-neighbours from the register ring.  L = 2*NSW halo cells on each side of the strip are recomputed
-// (60 of 64 lanes useful for NSW = 1, 56 for NSW = 2); chunks overlap by 2L columns.  No shared-memory tile, no
-// block barrier inside the march: warps are independent, which is what hides the HBM latency.
-// Algorithmic traffic: 24 B per cell per launch (read x, read b, write x) for NSW cell-updates.
+// per lane (512 contiguous bytes per warp), keeps the most recent columns in registers, and applies the 2*NSW
+// half-sweeps as a software pipeline: when column n arrives, half-sweep s updates column n - 1 - s; with RES
+// the residual of column n - 2*NSW - 1 follows.  y-neighbours come from the partner cell of the pair or from
+// the adjacent lane (one shuffle per half-sweep), x-neighbours from the register ring.  The halo cells on each
+// side of the strip (2*NSW, two more with RES) are recomputed, chunks overlap by twice that many columns.
+// No shared-memory tile and no block barrier inside the march: warps are independent, which is what hides the
+// HBM latency.  Algorithmic traffic: 24 B per cell per launch (read x, read b, write x) for NSW cell-updates.
 #pragma once
 #include <cuda_runtime.h>
 #include "ns_cell.cuh"
@@ -23,7 +27,11 @@ namespace nsgpu {
 
 constexpr int MARCH_WARPS = 4;                 // warps per CTA (adjacent strips)
 constexpr int MARCH_THREADS = 32 * MARCH_WARPS;
-constexpr int MARCH_PF = 2;                    // columns prefetched ahead in registers
+constexpr int MARCH_PF = 3;                    // default number of columns prefetched ahead in registers
+
+__host__ __device__ constexpr int march_halo(int nsw, int res) { return 2 * nsw + (res ? 2 : 0); }      // cells, y
+__host__ __device__ constexpr int march_lead(int nsw, int res) { return 2 * nsw + (res ? 1 : 0); }      // columns, x
+__host__ __device__ constexpr int march_uj(int nsw, int res) { return 64 - 2 * march_halo(nsw, res); }  // useful j per warp
 
 // reciprocal to ~1 ulp: MUFU.RCP64H seed (>= 20 bits) + two Newton steps
 __device__ __forceinline__ double fast_rcp(double d) {
@@ -37,10 +45,11 @@ __device__ __forceinline__ double fast_rcp(double d) {
 
 struct ColConst { double csa, cna, dya, csb, cnb, dyb; };   // y-coefficients of the lane's two cells
 
-// one half-sweep on column `c` (current state), neighbours cm (i-1) and cp (i+1); ta: the updated cell is .x
+// one half-sweep on column `c` (current state), neighbours cm (i-1) and cp (i+1); TA: the updated cell is .x
+template <bool TA>
 __device__ __forceinline__ void half_update(double2& c, const double2& cm, const double2& cp, const double2& bb,
-                                            bool ta, double cw, double ce, double dx, const ColConst& k) {
-  if (ta) {
+                                            double cw, double ce, double dx, const ColConst& k) {
+  if (TA) {
     const double S = __shfl_up_sync(0xffffffffu, c.y, 1), N = c.y;
     double v = fma(cw, cm.x, bb.x);
     v = fma(ce, cp.x, v);
@@ -57,18 +66,139 @@ __device__ __forceinline__ void half_update(double2& c, const double2& cm, const
   }
 }
 
-template <int NSW>
+// residual b - A x of both cells of the pair:  A x = (dx + dy) x_c - (cw xW + ce xE + cs xS + cn xN)
+__device__ __forceinline__ double2 pair_residual(const double2& c, const double2& cm, const double2& cp, const double2& bb,
+                                                 double cw, double ce, double dx, const ColConst& k) {
+  const double Sa = __shfl_up_sync(0xffffffffu, c.y, 1), Nb = __shfl_down_sync(0xffffffffu, c.x, 1);
+  double2 r;
+  double v = fma(cw, cm.x, bb.x);
+  v = fma(ce, cp.x, v);
+  v = fma(k.csa, Sa, v);
+  v = fma(k.cna, c.y, v);
+  r.x = fma(-(dx + k.dya), c.x, v);
+  v = fma(cw, cm.y, bb.y);
+  v = fma(ce, cp.y, v);
+  v = fma(k.csb, c.x, v);
+  v = fma(k.cnb, Nb, v);
+  r.y = fma(-(dx + k.dyb), c.y, v);
+  return r;
+}
+
+struct MarchXfer {
+  const double* xc;   // PROLONG: coarse correction (level l+1 layout)
+  int ldc, pcx, pcy;
+  double* bc;         // RES == 1: coarse right-hand side (level l+1 layout)
+  int ldbc, rcx, rcy;
+  double rscale;      // 1 / (rcx * rcy)
+  Reducer red;        // RES == 2
+  double* out;
+  SolveCtl* ctl;      // RES == 2: optional convergence epilogue
+};
+
+// Per-thread state of the march: one ring of columns (PF prefetched ones ahead of the K being worked on) and
+// running pointers (one add per column instead of a 64-bit multiply per access).
+template <int NSW, bool PROLONG, int RES, int PF>
+struct Marcher {
+  static constexpr int L = 2 * NSW;                 // half-sweep stages
+  static constexpr int K = L + 2 + (RES ? 1 : 0);   // columns being worked on
+  static constexpr int RL = K + PF;                 // ring length
+  double2 X[RL], Bq[RL];                            // X[PF + q]: column n - q;  X[PF - 1 - p]: column n + 1 + p
+  ColConst k;
+  const double* cc;                                 // shared memory: (cw, ce, dx) of column n
+  const double* __restrict__ px;                    // next column to prefetch (nullptr: zero initial guess)
+  const double* __restrict__ pb;
+  double* __restrict__ po;                          // column n - L of xout
+  double* __restrict__ pbc;                         // RES == 1: next coarse column to emit
+  const double* __restrict__ pxc;                   // PROLONG: coarse column base + row offset
+  int ld, ny, j0, ib, ie;
+  bool useful, jstore2, jstore1;
+  MarchXfer xf;
+  double2 racc;
+  double acc;
+
+  // Unconditional loads (no branch, so they can be scheduled early).  Lanes past the column end read the zero
+  // padding (their row offset is clamped); columns past the chunk exist (SLACK_COLS extra columns are allocated
+  // behind every field) and only feed pipeline stages whose results are never stored.
+  __device__ __forceinline__ void load_col(int n, double2& vx, double2& vb) {
+    vx = make_double2(0.0, 0.0);
+    if (px) { vx = *reinterpret_cast<const double2*>(px); px += ld; }
+    vb = *reinterpret_cast<const double2*>(pb);
+    pb += ld;
+    if (PROLONG) {
+      const int ic = (xf.pcx == 2 ? ((n + 2 * HX) >> 1) : n + HX);
+      const double* pc = pxc + (size_t)ic * xf.ldc;
+      if (xf.pcy == 2) { const double c0 = *pc; vx.x += c0; vx.y += c0; }
+      else { const double2 c2 = *reinterpret_cast<const double2*>(pc); vx.x += c2.x; vx.y += c2.y; }
+    }
+  }
+
+  // column n enters the pipeline; TA: this step's half-sweeps all update the .x cell (they do: the colour of
+  // half-sweep s on column n - 1 - s depends on n only)
+  template <bool TA>
+  __device__ __forceinline__ void step(int n) {
+#pragma unroll
+    for (int q = RL - 1; q > 0; q--) { X[q] = X[q - 1]; Bq[q] = Bq[q - 1]; }
+    load_col(n + PF, X[0], Bq[0]);
+#pragma unroll
+    for (int s = 0; s < L; s++) {
+      const double* c3 = cc - 3 * (1 + s);
+      half_update<TA>(X[PF + s + 1], X[PF + s + 2], X[PF + s], Bq[PF + s + 1], c3[0], c3[1], c3[2], k);
+    }
+    const int rs = n - L;                              // this column is final
+    if ((unsigned)(rs - ib) < (unsigned)(ie - ib)) {
+      if (jstore2) *reinterpret_cast<double2*>(po) = X[PF + L];
+      else if (jstore1) *po = X[PF + L].x;
+    }
+    po += ld;
+    if (RES) {
+      const int rr = n - L - 1;                        // its x-neighbours n - L - 2 and n - L are final
+      const double* c3 = cc - 3 * (L + 1);
+      const double2 res = pair_residual(X[PF + L + 1], X[PF + L + 2], X[PF + L], Bq[PF + L + 1], c3[0], c3[1], c3[2], k);
+      if ((unsigned)(rr - ib) < (unsigned)(ie - ib)) {
+        if (RES == 2) {
+          acc += (jstore2 || jstore1 ? res.x * res.x : 0.0) + (jstore2 ? res.y * res.y : 0.0);   // branch-free
+        } else {
+          // chunks start on even columns, so a coarse pair never straddles two chunks
+          double2 t = res;
+          bool emit = true;
+          if (xf.rcx == 2) {
+            if (rr & 1) { t.x += racc.x; t.y += racc.y; }
+            else { racc = res; emit = false; }
+          }
+          if (emit) {
+            if (xf.rcy == 2) {
+              if (useful && j0 < ny) *pbc = (t.x + t.y) * xf.rscale;
+            } else {
+              if (jstore2) *reinterpret_cast<double2*>(pbc) = make_double2(t.x * xf.rscale, t.y * xf.rscale);
+              else if (jstore1) *pbc = t.x * xf.rscale;
+            }
+            pbc += xf.ldbc;
+          }
+        }
+      }
+    }
+    cc += 3;
+  }
+};
+
+template <int NSW, bool PROLONG, int RES, int PF>
 __global__ void __launch_bounds__(MARCH_THREADS)
-k_sweep_march(LevelGeom g, const double* __restrict__ mcx, const double* __restrict__ mcy,
-              const double* __restrict__ xin, const double* __restrict__ b, double* __restrict__ xout, int RI) {
-  constexpr int L = 2 * NSW;        // halo cells per side == pipeline lead in columns
-  constexpr int K = 2 * NSW + 2;    // columns held in registers
-  constexpr int UJ = 64 - 2 * L;    // useful rows per warp strip
-  extern __shared__ double s_c[];   // (cw, ce, dx) of columns [r0, r0 + nrows)
+k_march(LevelGeom g, const double* __restrict__ mcx, const double* __restrict__ mcy, const double* __restrict__ xin,
+        const double* __restrict__ b, double* __restrict__ xout, int RI, MarchXfer xf) {
+  using M = Marcher<NSW, PROLONG, RES, PF>;
+  constexpr int L = M::L;
+  constexpr int HJ = march_halo(NSW, RES);   // halo cells per side of the strip
+  constexpr int LL = march_lead(NSW, RES);   // halo columns per side of the chunk
+  constexpr int UJ = 64 - 2 * HJ;
+  constexpr int HL = HJ / 2;                 // halo lanes per side
+  extern __shared__ double s_c[];            // (cw, ce, dx) of columns [r0, r0 + nrows)
   const int lane = threadIdx.x & 31;
   const int wj = blockIdx.x * MARCH_WARPS + (threadIdx.x >> 5);
   const int ib = blockIdx.y * RI, ie = min(ib + RI, g.nx);
-  const int r0 = ib - 2 * L, nrows = ie + L - r0;
+  const int nbeg = ib - LL, nend = ie + LL;  // columns needed: [nbeg, nend) inside [-HX + 1, nx + HX)
+  // start on a column whose half-sweeps update the .x cells: (gi0 + n0 - 1) even; n0 >= -HX
+  const int n0 = nbeg - ((g.gi0 + nbeg - 1) & 1);
+  const int r0 = n0 - 1 - L - (RES ? 1 : 0), nrows = nend + 1 - r0;
   for (int q = threadIdx.x; q < nrows; q += MARCH_THREADS) {
     const int a = min(max(r0 + q + HX, 0), g.nx + 2 * HX - 1);
     s_c[3 * q] = mcx[3 * a];
@@ -76,79 +206,45 @@ k_sweep_march(LevelGeom g, const double* __restrict__ mcx, const double* __restr
     s_c[3 * q + 2] = mcx[3 * a + 2];
   }
   __syncthreads();
-  if (wj * UJ >= g.ny) return;
 
-  const int j0 = wj * UJ - L + 2 * lane;                     // even
-  const bool jload = (j0 + 1 < g.ny + PJ);                   // pair inside the padded column (j0 >= -L >= -PJ)
-  ColConst k;
+  // warps past the last strip run with every predicate false (no divergent exit: the shuffles stay convergent)
+  M m;
+  m.xf = xf;
+  m.ld = g.ld; m.ny = g.ny; m.ib = ib; m.ie = ie;
+  m.j0 = wj * UJ - HJ + 2 * lane;                            // even, >= -HJ >= -PJ
+  const int jl = min(m.j0, g.ny + PJ - 2);                   // lanes past the column end: its last (zero) pair
   {
-    const int a = min(j0 + PJ, g.ny + 2 * PJ - 2);           // clamped entries are outside the domain: cs = cn = 0
-    k.csa = mcy[3 * a]; k.cna = mcy[3 * a + 1]; k.dya = mcy[3 * a + 2];
-    k.csb = mcy[3 * a + 3]; k.cnb = mcy[3 * a + 4]; k.dyb = mcy[3 * a + 5];
+    const int a = jl + PJ;                                   // entries outside the domain have cs = cn = 0
+    m.k.csa = mcy[3 * a]; m.k.cna = mcy[3 * a + 1]; m.k.dya = mcy[3 * a + 2];
+    m.k.csb = mcy[3 * a + 3]; m.k.cnb = mcy[3 * a + 4]; m.k.dyb = mcy[3 * a + 5];
   }
-  const size_t joff = (size_t)(j0 + PJ);
-  const int ld = g.ld;
-  const bool jstore2 = lane >= NSW && lane < 32 - NSW && (j0 + 1 < g.ny);
-  const bool jstore1 = lane >= NSW && lane < 32 - NSW && (j0 < g.ny) && !jstore2;
+  const size_t joff = (size_t)(jl + PJ);
+  m.useful = lane >= HL && lane < 32 - HL;
+  m.jstore2 = m.useful && (m.j0 + 1 < g.ny);
+  m.jstore1 = m.useful && (m.j0 < g.ny) && !m.jstore2;
+  m.cc = s_c + 3 * (n0 - r0);
+  m.px = xin ? xin + (size_t)(n0 + HX) * g.ld + joff : nullptr;
+  m.pb = b + (size_t)(n0 + HX) * g.ld + joff;
+  m.po = xout + (size_t)(n0 - L + HX) * g.ld + joff;        // only dereferenced inside [ib, ie)
+  m.pbc = nullptr;
+  if (RES == 1) m.pbc = xf.bc + (size_t)((xf.rcx == 2 ? (ib >> 1) : ib) + HX) * xf.ldbc + (xf.rcy == 2 ? (size_t)((m.j0 >> 1) + PJ) : joff);
+  m.pxc = nullptr;
+  if (PROLONG) m.pxc = xf.xc + (size_t)((xf.pcy == 2 ? ((jl + 2 * PJ) >> 1) - PJ : jl) + PJ);
+  m.racc = make_double2(0.0, 0.0);
+  m.acc = 0.0;
+#pragma unroll
+  for (int q = 0; q < M::RL; q++) { m.X[q] = make_double2(0.0, 0.0); m.Bq[q] = make_double2(0.0, 0.0); }
+#pragma unroll
+  for (int p = 0; p < PF; p++) m.load_col(n0 + p, m.X[PF - 1 - p], m.Bq[PF - 1 - p]);
 
-  double2 R[K], B[K - 1];           // R[q]: column n - q; B[q]: right-hand side of column n - 1 - q ... see below
-#pragma unroll
-  for (int q = 0; q < K; q++) R[q] = make_double2(0.0, 0.0);
-#pragma unroll
-  for (int q = 0; q < K - 1; q++) B[q] = make_double2(0.0, 0.0);
-
-  const int nbeg = ib - L, nend = ie + L;                    // columns loaded: [nbeg, nend) within [-HX, nx + HX)
-  double2 px[MARCH_PF], pb[MARCH_PF];
-#pragma unroll
-  for (int q = 0; q < MARCH_PF; q++) {
-    px[q] = make_double2(0.0, 0.0);
-    pb[q] = make_double2(0.0, 0.0);
-    const int n = nbeg + q;
-    if (jload && n < nend) {
-      const size_t o = (size_t)(n + HX) * ld + joff;
-      px[q] = *reinterpret_cast<const double2*>(xin + o);
-      pb[q] = *reinterpret_cast<const double2*>(b + o);
-    }
+#pragma unroll 2
+  for (int n = n0; n < nend; n += 2) {
+    m.template step<true>(n);
+    m.template step<false>(n + 1);
   }
-
-  const int par0 = g.gi0 & 1;
-#pragma unroll(K)
-  for (int n = nbeg; n < nend; n++) {
-    // rotate the rings and take the prefetched column
-#pragma unroll
-    for (int q = K - 1; q > 0; q--) R[q] = R[q - 1];
-#pragma unroll
-    for (int q = K - 2; q > 0; q--) B[q] = B[q - 1];
-    R[0] = px[0];
-    B[0] = pb[0];                    // B[q] = b of column n - q
-#pragma unroll
-    for (int q = 0; q < MARCH_PF - 1; q++) { px[q] = px[q + 1]; pb[q] = pb[q + 1]; }
-    {
-      const int m = n + MARCH_PF;
-      double2 vx = make_double2(0.0, 0.0), vb = vx;
-      if (jload && m < nend) {
-        const size_t o = (size_t)(m + HX) * ld + joff;
-        vx = *reinterpret_cast<const double2*>(xin + o);
-        vb = *reinterpret_cast<const double2*>(b + o);
-      }
-      px[MARCH_PF - 1] = vx;
-      pb[MARCH_PF - 1] = vb;
-    }
-    // half-sweep s (colour s & 1) on column r = n - 1 - s
-#pragma unroll
-    for (int s = 0; s < 2 * NSW; s++) {
-      const int r = n - 1 - s;
-      const double* cc = s_c + 3 * (r - r0);
-      const bool ta = (((par0 + r + s) & 1) == 0);           // colour s&1 sits on .x when (gi + j0 + colour) is even
-      half_update(R[s + 1], R[s + 2], R[s], B[s + 1], ta, cc[0], cc[1], cc[2], k);
-    }
-    // column n - L is final
-    const int rs = n - L;
-    if (rs >= ib && rs < ie) {
-      double* o = xout + (size_t)(rs + HX) * ld + joff;
-      if (jstore2) *reinterpret_cast<double2*>(o) = R[L];
-      else if (jstore1) *o = R[L].x;
-    }
+  if (RES == 2) {
+    double acc[1] = {m.acc};
+    grid_reduce<1, OpSum>(acc, xf.red, xf.out, CtlEpilogue{xf.ctl});
   }
 }
 

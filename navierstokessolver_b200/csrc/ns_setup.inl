@@ -88,7 +88,9 @@ static void destroy_ctx(nsgpu_ctx* ctx) {
   for (auto& L : ctx->levels)
     for (void* p : L.owned) cudaFree(p);
   for (void* p : ctx->owned) cudaFree(p);
+  for (auto& sg : ctx->sgraph) { if (sg.exec) cudaGraphExecDestroy(sg.exec); if (sg.graph) cudaGraphDestroy(sg.graph); }
   if (ctx->h_scal) cudaFreeHost(ctx->h_scal);
+  if (ctx->h_ctl) cudaFreeHost(ctx->h_ctl);
   if (ctx->h_stage) cudaFreeHost(ctx->h_stage);
   if (ctx->ev0) cudaEventDestroy(ctx->ev0);
   if (ctx->ev1) cudaEventDestroy(ctx->ev1);
@@ -110,6 +112,9 @@ static int create_impl(nsgpu_ctx* ctx, const nsgpu_grid* G, const nsgpu_params* 
   ctx->use_graph = P->use_graph;
   if (const char* e = getenv("NSGPU_MARCH")) ctx->march = atoi(e);
   if (const char* e = getenv("NSGPU_RI")) ctx->march_ri = atoi(e);
+  if (const char* e = getenv("NSGPU_PF")) ctx->march_pf = atoi(e);
+  if (const char* e = getenv("NSGPU_WARPS_PER_SM")) ctx->march_wps = std::max(1, atoi(e));
+  if (const char* e = getenv("NSGPU_GRAPH")) ctx->use_graph = atoi(e);
   HostPlan plan;
   {
     int rc = make_host_plan(G, ctx->rank, ctx->world, P->max_levels, plan, ctx->err);
@@ -163,6 +168,9 @@ static int create_impl(nsgpu_ctx* ctx, const nsgpu_grid* G, const nsgpu_params* 
   { double* c; int rc = dev_zeros(ctx, ctx->owned, 2, &c); if (rc) return rc; ctx->red.counter = (unsigned*)c; }
   { int rc = dev_zeros(ctx, ctx->owned, 64, &ctx->d_scal); if (rc) return rc; }
   NS_CUDA(cudaMallocHost((void**)&ctx->h_scal, 64 * sizeof(double)));
+  { void* p = nullptr; NS_CUDA(cudaMalloc(&p, 3 * sizeof(SolveCtl))); ctx->owned.push_back(p); NS_CUDA(cudaMemset(p, 0, 3 * sizeof(SolveCtl))); ctx->d_ctl = (SolveCtl*)p; }
+  NS_CUDA(cudaMallocHost((void**)&ctx->h_ctl, 3 * sizeof(SolveCtl)));
+  memset(ctx->h_ctl, 0, 3 * sizeof(SolveCtl));
   NS_CUDA(cudaDeviceSynchronize());
   return 0;
 }

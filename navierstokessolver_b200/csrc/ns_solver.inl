@@ -58,31 +58,116 @@ static int allreduce(nsgpu_ctx* ctx, double* d, int n, ncclRedOp_t op) {
   return 0;
 }
 
-// n sweeps of red-black Gauss-Seidel on level L; *x is the current iterate, *xt its ping-pong partner.
-static inline int march_chunk(const nsgpu_ctx* ctx, const Level& L, int uj) {
-  if (ctx->march_ri > 0) return std::min(ctx->march_ri, L.g.nx);
-  // enough warps for ~2 waves of 148 SMs x 24 resident warps, chunks no shorter than 8 columns
-  const int wj = (L.g.ny + uj - 1) / uj;
-  const int chunks = std::max(1, (2 * 148 * 24 + wj - 1) / wj);
-  return std::min(L.g.nx, std::max(8, (L.g.nx + chunks - 1) / chunks));
+// ---------------------------------------------------------------------------------------------------------
+// Fused marching passes (rectangle fast path, ns_march.cuh)
+
+static inline bool march_level_ok(const nsgpu_ctx* ctx, const Level& L, OpCoef c) {
+  // with several ranks the 5-column halo of a fused pass has to come from ONE neighbour
+  return ctx->march && ctx->rect && L.march_ok[c.op] && (ctx->world == 1 || L.g.nx >= HX);
 }
 
+static inline int march_chunk(const nsgpu_ctx* ctx, const Level& L, int uj, int lead) {
+  int ri;
+  if (ctx->march_ri > 0) ri = ctx->march_ri;
+  else {
+    // enough warps for every SM (NSGPU_WARPS_PER_SM, default 24) even on the small levels, where the march is
+    // latency-bound and short chunks (more warps) beat the cost of the 2*lead overlap columns
+    const int wj = (L.g.ny + uj - 1) / uj;
+    const int chunks = std::max(1, (148 * ctx->march_wps + wj - 1) / wj);
+    ri = std::max(4, (L.g.nx + chunks - 1) / chunks);
+  }
+  ri = std::min(ri, L.g.nx);
+  ri += ri & 1;   // even: a coarse pair of columns never straddles two chunks
+  const int gx = ((L.g.ny + uj - 1) / uj + MARCH_WARPS - 1) / MARCH_WARPS;
+  while ((long long)gx * ((L.g.nx + ri - 1) / ri) > RED_MAX_BLOCKS) ri *= 2;
+  return ri;
+}
+
+// One pass: xout <- NSW red-black sweeps of (xin [+ P xc]) on level L; optional fused restriction / residual norm.
+//   xin == nullptr: zero initial guess;  Cp/xc: prolong from;  Cr: restrict the residual to Cr->b;  norm_out/ctl: |r|^2
+static int march_pass(nsgpu_ctx* ctx, const Level& L, OpCoef c, int nsw, double* xin, const double* b, double* xout,
+                      const Level* Cp, double* xc, const Level* Cr, double* norm_out, SolveCtl* ctl) {
+  const int res = Cr ? 1 : (norm_out ? 2 : 0);
+  const int lead = march_lead(nsw, res);
+  int rc;
+  if (xin && (rc = halo_exchange(ctx, L, xin, lead))) return rc;
+  if (Cp && (rc = halo_exchange(ctx, *Cp, xc, (lead + 1) / 2 + 1))) return rc;
+  MarchXfer xf{};
+  if (Cp) { xf.xc = xc; xf.ldc = Cp->g.ld; xf.pcx = L.cx; xf.pcy = L.cy; }
+  if (Cr) { xf.bc = Cr->b; xf.ldbc = Cr->g.ld; xf.rcx = L.cx; xf.rcy = L.cy; xf.rscale = 1.0 / (double)(L.cx * L.cy); }
+  if (res == 2) { xf.red = ctx->red; xf.out = norm_out; xf.ctl = ctl; }
+  const int uj = march_uj(nsw, res);
+  const int ri = march_chunk(ctx, L, uj, lead);
+  const dim3 grid(((L.g.ny + uj - 1) / uj + MARCH_WARPS - 1) / MARCH_WARPS, (L.g.nx + ri - 1) / ri);
+  const size_t sh = (size_t)3 * (ri + 2 * lead + 2 * nsw + 8) * sizeof(double);   // >= nrows of k_march
+  const double *mx = L.mcx[c.op], *my = L.mcy[c.op];
+#define NS_MARCH(NSW, PRO, RES, PF) k_march<NSW, PRO, RES, PF><<<grid, MARCH_THREADS, sh, ctx->stream>>>(L.g, mx, my, xin, b, xout, ri, xf)
+#define NS_MARCH_RES(NSW, PRO) do { if (res == 0) NS_MARCH(NSW, PRO, 0, MARCH_PF); else if (res == 1) NS_MARCH(NSW, PRO, 1, MARCH_PF); else NS_MARCH(NSW, PRO, 2, MARCH_PF); } while (0)
+  if (nsw == 1 && !Cp && res == 0 && ctx->march_pf != MARCH_PF) {   // prefetch-depth experiments on the plain sweep
+    switch (ctx->march_pf) {
+      case 2: NS_MARCH(1, false, 0, 2); break;
+      case 4: NS_MARCH(1, false, 0, 4); break;
+      case 6: NS_MARCH(1, false, 0, 6); break;
+      default: NS_MARCH(1, false, 0, MARCH_PF); break;
+    }
+  } else if (nsw == 1) { if (Cp) NS_MARCH_RES(1, true); else NS_MARCH_RES(1, false); }
+  else { if (Cp) NS_MARCH_RES(2, true); else NS_MARCH_RES(2, false); }
+#undef NS_MARCH_RES
+#undef NS_MARCH
+  NS_LAUNCH_CHECK();
+  if (Cr && (rc = halo_exchange(ctx, *Cr, Cr->b, std::min(HX, Cr->g.nx)))) return rc;
+  return 0;
+}
+
+// `n` sweeps as passes of two (and one single if n is odd).  first_* apply to the first pass, last_* to the last.
+static int march_sweeps(nsgpu_ctx* ctx, const Level& L, OpCoef c, int n, double** x, double** xt, const double* b, bool xzero,
+                        const Level* Cp, double* xc, const Level* Cr, double* norm_out, SolveCtl* ctl) {
+  for (int k = 0; k < n;) {
+    const int nsw = (n - k >= 2) ? 2 : 1;
+    const bool first = k == 0, last = k + nsw >= n;
+    int rc = march_pass(ctx, L, c, nsw, (xzero && first) ? nullptr : *x, b, *xt, first ? Cp : nullptr, first ? xc : nullptr,
+                        last ? Cr : nullptr, last ? norm_out : nullptr, last ? ctl : nullptr);
+    if (rc) return rc;
+    std::swap(*x, *xt);
+    k += nsw;
+  }
+  return 0;
+}
+
+// One V(nu_pre, nu_post) cycle with every transfer fused into a smoothing pass: two passes per level.
+static int vcycle_fused(nsgpu_ctx* ctx, int l, OpCoef c, double** x, double** xt, const double* b, bool xzero, double* norm_out,
+                        SolveCtl* ctl) {
+  Level& L = ctx->levels[l];
+  if (l == (int)ctx->levels.size() - 1) {
+    const int n = ctx->levels.size() == 1 ? ctx->nu_pre + ctx->nu_post : L.coarse_sweeps;
+    return march_sweeps(ctx, L, c, n, x, xt, b, xzero, nullptr, nullptr, nullptr, norm_out, ctl);
+  }
+  Level& C = ctx->levels[l + 1];
+  int rc;
+  if ((rc = march_sweeps(ctx, L, c, ctx->nu_pre, x, xt, b, xzero, nullptr, nullptr, &C, nullptr, nullptr))) return rc;
+  double *cx = C.x, *cxt = C.xt;
+  if ((rc = vcycle_fused(ctx, l + 1, c, &cx, &cxt, C.b, true, nullptr, nullptr))) return rc;
+  C.x = cx; C.xt = cxt;
+  return march_sweeps(ctx, L, c, ctx->nu_post, x, xt, b, false, &C, C.x, nullptr, norm_out, ctl);
+}
+
+static inline bool all_levels_march(const nsgpu_ctx* ctx, OpCoef c) {
+  for (const Level& L : ctx->levels) if (!march_level_ok(ctx, L, c)) return false;
+  return true;
+}
+
+// n sweeps of red-black Gauss-Seidel on level L; *x is the current iterate, *xt its ping-pong partner.
 static int smooth(nsgpu_ctx* ctx, const Level& L, OpCoef c, double** x, double** xt, const double* b, int n) {
   const dim3 grid((L.g.ny + SM_TJ - 1) / SM_TJ, (L.g.nx + SM_TI - 1) / SM_TI);
-  const bool march = ctx->march && ctx->rect && L.march_ok[c.op];
   for (int s = 0; s < n; s++) {
-    int rc = halo_exchange(ctx, L, *x, 2);
-    if (rc) return rc;
-    if (march) {
-      constexpr int UJ = 60;
-      const int ri = march_chunk(ctx, L, UJ);
-      const dim3 mg(((L.g.ny + UJ - 1) / UJ + MARCH_WARPS - 1) / MARCH_WARPS, (L.g.nx + ri - 1) / ri);
-      const size_t sh = (size_t)3 * (ri + 3 * 2) * sizeof(double);
-      k_sweep_march<1><<<mg, MARCH_THREADS, sh, ctx->stream>>>(L.g, L.mcx[c.op], L.mcy[c.op], *x, b, *xt, ri);
-      NS_LAUNCH_CHECK();
+    if (march_level_ok(ctx, L, c)) {   // plain single sweep through the marching kernel: 24 B per cell-update
+      int rc = march_pass(ctx, L, c, 1, *x, b, *xt, nullptr, nullptr, nullptr, nullptr, nullptr);
+      if (rc) return rc;
       std::swap(*x, *xt);
       continue;
     }
+    int rc = halo_exchange(ctx, L, *x, 2);
+    if (rc) return rc;
 #define CALL(OP, RECT) k_smooth_rb<OP, RECT, false><<<grid, SM_THREADS, 0, ctx->stream>>>(L.g, *x, b, *xt, c.alpha, c.beta)
     NS_DISPATCH_OP_RECT(c.op, ctx->rect, CALL);
 #undef CALL
@@ -93,11 +178,11 @@ static int smooth(nsgpu_ctx* ctx, const Level& L, OpCoef c, double** x, double**
 }
 
 // d_out[0] = ||b - A x||^2 over the local slab (all-reduced over ranks)
-static int residual_norm2(nsgpu_ctx* ctx, const Level& L, OpCoef c, double* x, const double* b, double* d_out) {
+static int residual_norm2(nsgpu_ctx* ctx, const Level& L, OpCoef c, double* x, const double* b, double* d_out, SolveCtl* ctl = nullptr) {
   int rc = halo_exchange(ctx, L, x, 2);
   if (rc) return rc;
   const dim3 grid = grid_cols(L.g, 256);
-#define CALL(OP, RECT) k_residual<OP, RECT, false, true><<<grid, 256, 0, ctx->stream>>>(L.g, x, b, nullptr, c.alpha, c.beta, ctx->red, d_out)
+#define CALL(OP, RECT) k_residual<OP, RECT, false, true><<<grid, 256, 0, ctx->stream>>>(L.g, x, b, nullptr, c.alpha, c.beta, ctx->red, d_out, ctl)
   NS_DISPATCH_OP_RECT(c.op, ctx->rect, CALL);
 #undef CALL
   NS_LAUNCH_CHECK();
@@ -108,7 +193,7 @@ static int residual_vec(nsgpu_ctx* ctx, const Level& L, OpCoef c, double* x, con
   int rc = halo_exchange(ctx, L, x, 2);
   if (rc) return rc;
   const dim3 grid = grid_cols(L.g, 256);
-#define CALL(OP, RECT) k_residual<OP, RECT, true, true><<<grid, 256, 0, ctx->stream>>>(L.g, x, b, r, c.alpha, c.beta, ctx->red, d_norm2)
+#define CALL(OP, RECT) k_residual<OP, RECT, true, true><<<grid, 256, 0, ctx->stream>>>(L.g, x, b, r, c.alpha, c.beta, ctx->red, d_norm2, nullptr)
   NS_DISPATCH_OP_RECT(c.op, ctx->rect, CALL);
 #undef CALL
   NS_LAUNCH_CHECK();
@@ -187,6 +272,16 @@ static int norm2_vec(nsgpu_ctx* ctx, const Level& L, const double* a, double* d_
   return allreduce(ctx, d_out, 1, ncclSum);
 }
 
+// V-cycle for the host-driven solvers: fused marching passes where every level supports them, generic kernels otherwise.
+static int vcycle_any(nsgpu_ctx* ctx, OpCoef c, double** x, double** xt, const double* b, bool xzero) {
+  if (all_levels_march(ctx, c)) return vcycle_fused(ctx, 0, c, x, xt, b, xzero, nullptr, nullptr);
+  if (xzero) {
+    cudaError_t e = cudaMemsetAsync(*x, 0, ctx->levels[0].stride * sizeof(double), ctx->stream);
+    if (e != cudaSuccess) { ctx->err = cudaGetErrorString(e); return NSGPU_ERR_CUDA; }
+  }
+  return vcycle(ctx, 0, c, x, xt, b);
+}
+
 // Stationary multigrid iteration: x <- x + V(b - A x) until ||b - A x|| <= rtol ||b||.
 static int solve_mg(nsgpu_ctx* ctx, OpCoef c, double** x, double** xt, const double* b, double rtol, SolveResult* out) {
   const Level& L = ctx->levels[0];
@@ -204,7 +299,7 @@ static int solve_mg(nsgpu_ctx* ctx, OpCoef c, double** x, double** xt, const dou
     return 0;
   }
   while (rn > rtol * bn && out->cycles < ctx->max_cycles) {
-    if ((rc = vcycle(ctx, 0, c, x, xt, b))) return rc;
+    if ((rc = vcycle_any(ctx, c, x, xt, b, false))) return rc;
     out->cycles++;
     if ((rc = residual_norm2(ctx, L, c, *x, b, ctx->d_scal + 1))) return rc;
     if ((rc = read_scalars(ctx, ctx->d_scal + 1, 1, h))) return rc;
@@ -249,8 +344,7 @@ static int solve_bicgstab(nsgpu_ctx* ctx, OpCoef c, double** xp, double** xtp, c
     k_bicg_p<<<blocks, 256, 0, ctx->stream>>>(n, r + off, p + off, v + off, S);
     NS_LAUNCH_CHECK();
     // ph = M^-1 p
-    cudaMemsetAsync(ph, 0, L.stride * sizeof(double), ctx->stream);
-    { double *a = ph, *bq = tmpA; if ((rc = vcycle(ctx, 0, c, &a, &bq, p))) return rc; ph = a; tmpA = bq; }
+    { double *a = ph, *bq = tmpA; if ((rc = vcycle_any(ctx, c, &a, &bq, p, true))) return rc; ph = a; tmpA = bq; }
     if ((rc = apply_op(ctx, L, c, ph, v, r0, S + 4))) return rc;
     k_scalar_div<<<1, 1, 0, ctx->stream>>>(S + 2, S + 0, S + 4);   // alpha = rho / (r0, v)
     NS_LAUNCH_CHECK();
@@ -258,8 +352,7 @@ static int solve_bicgstab(nsgpu_ctx* ctx, OpCoef c, double** xp, double** xtp, c
     NS_LAUNCH_CHECK();
     if ((rc = allreduce(ctx, S + 8, 1, ncclSum))) return rc;
     // sh = M^-1 s
-    cudaMemsetAsync(sh, 0, L.stride * sizeof(double), ctx->stream);
-    { double *a = sh, *bq = tmpA; if ((rc = vcycle(ctx, 0, c, &a, &bq, s))) return rc; sh = a; tmpA = bq; }
+    { double *a = sh, *bq = tmpA; if ((rc = vcycle_any(ctx, c, &a, &bq, s, true))) return rc; sh = a; tmpA = bq; }
     if ((rc = apply_op(ctx, L, c, sh, t, s, S + 6))) return rc;
     k_scalar_div<<<1, 1, 0, ctx->stream>>>(S + 3, S + 6, S + 7);   // omega = (t,s)/(t,t)
     NS_LAUNCH_CHECK();
@@ -286,9 +379,161 @@ static int solve_bicgstab(nsgpu_ctx* ctx, OpCoef c, double** xp, double** xtp, c
   return 0;
 }
 
-static int solve(nsgpu_ctx* ctx, OpCoef c, double** x, const double* b, double rtol, SolveResult* out) {
+// ---------------------------------------------------------------------------------------------------------
+// Device-controlled multigrid solve (one rank, rectangle): the stopping test runs in the epilogue of the
+// residual reductions (CtlEpilogue), so the host never has to look at a residual between cycles.
+
+static int solve_head(nsgpu_ctx* ctx, int slot, OpCoef c, double* x, const double* b, double rtol, unsigned long long handle) {
+  const Level& L = ctx->levels[0];
+  SolveCtl* ctl = ctx->d_ctl + slot;
+  k_ctl_init<<<1, 1, 0, ctx->stream>>>(ctl, rtol * rtol, ctx->max_cycles, handle);
+  NS_LAUNCH_CHECK();
+  int rc;
+  if ((rc = norm2_vec(ctx, L, b, &ctl->bn2))) return rc;
+  return residual_norm2(ctx, L, c, x, b, &ctl->rn2, ctl);
+}
+
+static int solve_tail(nsgpu_ctx* ctx, int slot, double* x) {
+  const Level& L = ctx->levels[0];
+  k_zero_if<<<148 * 4, 256, 0, ctx->stream>>>(L.stride, x, ctx->d_ctl + slot);
+  NS_LAUNCH_CHECK();
+  cudaError_t e = cudaMemcpyAsync(ctx->h_ctl + slot, ctx->d_ctl + slot, sizeof(SolveCtl), cudaMemcpyDeviceToHost, ctx->stream);
+  if (e != cudaSuccess) { ctx->err = std::string("ctl readback: ") + cudaGetErrorString(e); return NSGPU_ERR_CUDA; }
+  return 0;
+}
+
+#define NS_GRAPH_TRY(call)                                                                          \
+  do {                                                                                              \
+    cudaError_t e_ = (call);                                                                        \
+    if (e_ != cudaSuccess) {                                                                        \
+      fprintf(stderr, "nsgpu: %s -> %s; falling back to direct launches\n", #call, cudaGetErrorString(e_)); \
+      cudaGetLastError();                                                                           \
+      return 1;                                                                                     \
+    }                                                                                               \
+  } while (0)
+
+// Builds head -> WHILE(go){ V-cycle + residual norm } -> tail for (x, xt, b).  Returns 0 ok, 1 unsupported, < 0 error.
+static int build_solve_graph(nsgpu_ctx* ctx, int slot, OpCoef c, double* x, double* xt, const double* b, double rtol) {
+  SolveGraph& G = ctx->sgraph[slot];
+  if (G.exec) { cudaGraphExecDestroy(G.exec); G.exec = nullptr; }
+  if (G.graph) { cudaGraphDestroy(G.graph); G.graph = nullptr; }
+  const cudaStreamCaptureMode mode = cudaStreamCaptureModeThreadLocal;
+  NS_GRAPH_TRY(cudaGraphCreate(&G.graph, 0));
+  cudaGraphConditionalHandle handle;
+  NS_GRAPH_TRY(cudaGraphConditionalHandleCreate(&handle, G.graph, 0, cudaGraphCondAssignDefault));
+  const int64_t l0 = ctx->launches;
+  int rc;
+  // head
+  NS_GRAPH_TRY(cudaStreamBeginCaptureToGraph(ctx->stream, G.graph, nullptr, nullptr, 0, mode));
+  rc = solve_head(ctx, slot, c, x, b, rtol, (unsigned long long)handle);
+  cudaStreamCaptureStatus st;
+  const cudaGraphNode_t* deps = nullptr;
+  size_t ndeps = 0;
+  cudaGraph_t gcap = nullptr;
+  cudaError_t e = cudaStreamGetCaptureInfo(ctx->stream, &st, nullptr, &gcap, &deps, &ndeps);
+  std::vector<cudaGraphNode_t> leaf(deps, deps + (e == cudaSuccess ? ndeps : 0));
+  cudaGraph_t gout = nullptr;
+  cudaError_t e2 = cudaStreamEndCapture(ctx->stream, &gout);
+  if (rc) return rc;
+  NS_GRAPH_TRY(e);
+  NS_GRAPH_TRY(e2);
+  const int64_t l1 = ctx->launches;
+  // the loop
+  cudaGraphNodeParams p = {cudaGraphNodeTypeConditional};
+  p.type = cudaGraphNodeTypeConditional;
+  p.conditional.handle = handle;
+  p.conditional.type = cudaGraphCondTypeWhile;
+  p.conditional.size = 1;
+  cudaGraphNode_t loop;
+  NS_GRAPH_TRY(cudaGraphAddNode(&loop, G.graph, leaf.data(), leaf.size(), &p));
+  cudaGraph_t body = p.conditional.phGraph_out[0];
+  NS_GRAPH_TRY(cudaStreamBeginCaptureToGraph(ctx->stream, body, nullptr, nullptr, 0, mode));
+  double *xa = x, *xb = xt;
+  rc = vcycle_fused(ctx, 0, c, &xa, &xb, b, false, &ctx->d_ctl[slot].rn2, ctx->d_ctl + slot);
+  e2 = cudaStreamEndCapture(ctx->stream, &gout);
+  if (rc) return rc;
+  NS_GRAPH_TRY(e2);
+  if (xa != x) { fprintf(stderr, "nsgpu: V-cycle does not return to its buffer (odd number of passes); no graph\n"); return 1; }
+  const int64_t l2 = ctx->launches;
+  // tail
+  NS_GRAPH_TRY(cudaStreamBeginCaptureToGraph(ctx->stream, G.graph, &loop, nullptr, 1, mode));
+  rc = solve_tail(ctx, slot, x);
+  e2 = cudaStreamEndCapture(ctx->stream, &gout);
+  if (rc) return rc;
+  NS_GRAPH_TRY(e2);
+  const int64_t l3 = ctx->launches;
+  NS_GRAPH_TRY(cudaGraphInstantiate(&G.exec, G.graph, 0));
+  ctx->launches = l0;   // capture is not execution
+  G.launches_fixed = (int)((l1 - l0) + (l3 - l2));
+  G.launches_body = (int)(l2 - l1);
+  G.x = x; G.xt = xt; G.b = b; G.rtol = rtol;
+  return 0;
+}
+
+// Issues the whole solve on the stream; results land in h_ctl[slot] (decode_solve after a synchronize).
+static int solve_mg_dev(nsgpu_ctx* ctx, int slot, OpCoef c, double** x, double** xt, const double* b, double rtol) {
+  int rc;
+  if (ctx->use_graph) {
+    SolveGraph& G = ctx->sgraph[slot];
+    if (!G.exec || G.x != *x || G.xt != *xt || G.b != b || G.rtol != rtol) {
+      rc = build_solve_graph(ctx, slot, c, *x, *xt, b, rtol);
+      if (rc < 0) return rc;
+      if (rc > 0) {
+        cudaStreamCaptureStatus st = cudaStreamCaptureStatusNone;
+        cudaStreamIsCapturing(ctx->stream, &st);
+        if (st != cudaStreamCaptureStatusNone) { cudaGraph_t g = nullptr; cudaStreamEndCapture(ctx->stream, &g); }
+        cudaGetLastError();
+        ctx->use_graph = 0;
+      }
+    }
+    if (ctx->use_graph) {
+      cudaError_t e = cudaGraphLaunch(G.exec, ctx->stream);
+      if (e != cudaSuccess) { ctx->err = std::string("cudaGraphLaunch: ") + cudaGetErrorString(e); return NSGPU_ERR_CUDA; }
+      ctx->launches += G.launches_fixed;
+      ctx->graph_cycles_pending[slot] += 1;
+      return 0;
+    }
+  }
+  if ((rc = solve_head(ctx, slot, c, *x, b, rtol, 0ull))) return rc;
+  for (;;) {
+    cudaError_t e = cudaMemcpyAsync(ctx->h_ctl + slot, ctx->d_ctl + slot, sizeof(SolveCtl), cudaMemcpyDeviceToHost, ctx->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+    if (e != cudaSuccess) { ctx->err = std::string("ctl readback: ") + cudaGetErrorString(e); return NSGPU_ERR_CUDA; }
+    if (!ctx->h_ctl[slot].go) break;
+    if ((rc = vcycle_fused(ctx, 0, c, x, xt, b, false, &ctx->d_ctl[slot].rn2, ctx->d_ctl + slot))) return rc;
+  }
+  return solve_tail(ctx, slot, *x);
+}
+
+// After a stream synchronize: turn h_ctl[slot] into a SolveResult and book the loop-body launches of graph solves.
+static void decode_solve(nsgpu_ctx* ctx, int slot, SolveResult* out) {
+  const SolveCtl& h = ctx->h_ctl[slot];
+  out->cycles = h.cycles;
+  out->rel = h.bn2 > 0 ? std::sqrt(h.rn2 / h.bn2) : 0.0;
+  out->converged = !(h.bn2 > 0) || h.rn2 <= h.tol2 * h.bn2;
+  const int new_cycles = h.total_cycles - ctx->seen_cycles[slot];
+  if (ctx->graph_cycles_pending[slot]) {
+    ctx->launches += (int64_t)new_cycles * ctx->sgraph[slot].launches_body;
+    ctx->graph_cycles_pending[slot] = 0;
+  }
+  if (slot == 2) ctx->fine_sweeps_phi += (double)new_cycles * (ctx->nu_pre + ctx->nu_post);
+  ctx->seen_cycles[slot] = h.total_cycles;
+}
+
+static inline bool dev_solve_ok(const nsgpu_ctx* ctx, OpCoef c) { return ctx->solver == 0 && ctx->world == 1 && all_levels_march(ctx, c); }
+
+// slot: 0 = u, 1 = v, 2 = phi.  On the device-controlled path the result is pending until finish_results().
+static int solve(nsgpu_ctx* ctx, int slot, OpCoef c, double** x, const double* b, double rtol, SolveResult* out) {
+  if (dev_solve_ok(ctx, c)) { out->pending = true; return solve_mg_dev(ctx, slot, c, x, &ctx->tmp, b, rtol); }
+  out->pending = false;
   if (ctx->solver == 1) return solve_bicgstab(ctx, c, x, &ctx->tmp, b, rtol, out);
   return solve_mg(ctx, c, x, &ctx->tmp, b, rtol, out);
+}
+
+static void finish_results(nsgpu_ctx* ctx, SolveResult* ru, SolveResult* rv, SolveResult* rp) {
+  SolveResult* r[3] = {ru, rv, rp};
+  for (int k = 0; k < 3; k++)
+    if (r[k] && r[k]->pending) { decode_solve(ctx, k, r[k]); r[k]->pending = false; }
 }
 
 // ---------------------------------------------------------------------------------------------------------
@@ -317,8 +562,8 @@ static int phase_velocity(nsgpu_ctx* ctx, SolveResult* ru, SolveResult* rv) {   
   int rc;
   if ((rc = halo_exchange(ctx, L, ctx->rhs_u, 1))) return rc;
   if ((rc = halo_exchange(ctx, L, ctx->rhs_v, 1))) return rc;
-  if ((rc = solve(ctx, coef_v(ctx), &ctx->ustar, ctx->rhs_u, ctx->rtol_u, ru))) return rc;
-  if ((rc = solve(ctx, coef_v(ctx), &ctx->vstar, ctx->rhs_v, ctx->rtol_u, rv))) return rc;
+  if ((rc = solve(ctx, 0, coef_v(ctx), &ctx->ustar, ctx->rhs_u, ctx->rtol_u, ru))) return rc;
+  if ((rc = solve(ctx, 1, coef_v(ctx), &ctx->vstar, ctx->rhs_v, ctx->rtol_u, rv))) return rc;
   return 0;
 }
 
@@ -350,8 +595,8 @@ static int phase_phi(nsgpu_ctx* ctx, SolveResult* rp) {   // FS.cpp:551, warm st
   if ((rc = halo_exchange(ctx, L, ctx->rhs_phi, 1))) return rc;
   const int64_t before = ctx->launches;
   (void)before;
-  if ((rc = solve(ctx, coef_phi(), &ctx->phi, ctx->rhs_phi, ctx->rtol_phi, rp))) return rc;
-  ctx->fine_sweeps_phi += (double)rp->cycles * (ctx->nu_pre + ctx->nu_post) * (ctx->solver == 1 ? 2 : 1);
+  if ((rc = solve(ctx, 2, coef_phi(), &ctx->phi, ctx->rhs_phi, ctx->rtol_phi, rp))) return rc;
+  if (!rp->pending) ctx->fine_sweeps_phi += (double)rp->cycles * (ctx->nu_pre + ctx->nu_post) * (ctx->solver == 1 ? 2 : 1);
   // pin mean(phi) = 0: the reference projects the constant out of every Krylov update (MatSetNullSpace, FS.cpp:143)
   {
     const size_t n = (size_t)L.g.nx * L.g.ld;
