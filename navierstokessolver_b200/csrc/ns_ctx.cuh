@@ -10,6 +10,7 @@
 #include "../../include/nsgpu.h"
 #include "ns_kernels.cuh"
 #include "ns_march.cuh"
+#include "ns_tail.cuh"
 #include "ns_hostgeom.h"
 
 namespace nsgpu {
@@ -49,7 +50,7 @@ struct nsgpu_ctx {
   double dt = 0, re = 0;
   double rtol_u = 1e-8, rtol_phi = 1e-8;
   int max_cycles = 200, nu_pre = 2, nu_post = 2, solver = 0, use_graph = 0;
-  int march = 1, march_ri = 0, march_pf = 3, march_wps = 24;   // NSGPU_MARCH=0 forces the generic tile kernel; NSGPU_RI overrides the chunk length
+  int march = 1, march_ri = 0, march_pf = 6, march_wps = 24;   // NSGPU_MARCH=0 forces the generic tile kernel; NSGPU_RI overrides the chunk length
   cudaStream_t stream = nullptr;
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;
   ncclComm_t comm = nullptr;
@@ -82,6 +83,9 @@ struct nsgpu_ctx {
   nsgpu::SolveGraph sgraph[3];
   int graph_cycles_pending[3] = {0, 0, 0};
   bool capturing = false;
+  // coarse tail (ns_tail.cuh): levels >= tail_start run in one single-CTA kernel; 0 = no tail
+  int tail_start = 0, use_tail = 1;
+  nsgpu::TailDesc tail[2];
   int64_t launches = 0;
   double fine_sweeps_phi = 0;
   std::vector<void*> owned;

@@ -156,6 +156,41 @@ static int create_impl(nsgpu_ctx* ctx, const nsgpu_grid* G, const nsgpu_params* 
   }
   ctx->levels.back().coarse_sweeps = coarsest_sweeps(ctx->levels.back().g.gnx, ctx->levels.back().gny);
 
+  // ---- coarse tail: every level of at most TAIL_MAX_CELLS cells (never level 0) in one single-CTA kernel
+  if (const char* e = getenv("NSGPU_TAIL")) ctx->use_tail = atoi(e);
+  ctx->tail_start = 0;
+  if (ctx->use_tail && ctx->world == 1 && ctx->rect) {
+    const int nl = (int)ctx->levels.size();
+    int ts = 0;
+    for (int l = 1; l < nl; l++)
+      if ((long long)ctx->levels[l].g.nx * ctx->levels[l].g.ny <= TAIL_MAX_CELLS) { ts = l; break; }
+    if (ts > 0 && nl - ts <= TAIL_MAX_LEVELS) {
+      for (int op = 0; op < 2; op++) {
+        TailDesc& T = ctx->tail[op];
+        T.nlev = nl - ts; T.nu_pre = ctx->nu_pre; T.nu_post = ctx->nu_post;
+        T.coarse_sweeps = ctx->levels.back().coarse_sweeps; T.gi0 = 0;
+        int off = 0;
+        for (int k = 0; k < T.nlev; k++) {
+          const Level& L = ctx->levels[ts + k];
+          TailLevel& t = T.lv[k];
+          t.nx = L.g.nx; t.ny = L.g.ny; t.cx = L.cx; t.cy = L.cy; t.ld = L.g.ld;
+          t.mcx = L.mcx[op]; t.mcy = L.mcy[op];
+          const int cells = (t.nx + 2) * (t.ny + 2);
+          t.xoff = off; off += cells;
+          t.boff = off; off += cells;
+          t.sxoff = off; off += 3 * t.nx;
+          t.syoff = off; off += 3 * t.ny;
+        }
+        T.smem_doubles = off;
+      }
+      const size_t bytes = (size_t)ctx->tail[0].smem_doubles * sizeof(double);
+      if (bytes <= 200 * 1024) {
+        NS_CUDA(cudaFuncSetAttribute(k_coarse_tail, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
+        ctx->tail_start = ts;
+      }
+    }
+  }
+
   // ---- fields
   const size_t S = ctx->levels[0].stride;
   double** fields[] = {&ctx->u, &ctx->v, &ctx->phi, &ctx->conv_u, &ctx->conv_v, &ctx->gpx, &ctx->gpy,

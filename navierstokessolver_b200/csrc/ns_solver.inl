@@ -66,19 +66,37 @@ static inline bool march_level_ok(const nsgpu_ctx* ctx, const Level& L, OpCoef c
   return ctx->march && ctx->rect && L.march_ok[c.op] && (ctx->world == 1 || L.g.nx >= HX);
 }
 
-static inline int march_chunk(const nsgpu_ctx* ctx, const Level& L, int uj, int lead) {
-  int ri;
-  if (ctx->march_ri > 0) ri = ctx->march_ri;
-  else {
-    // enough warps for every SM (NSGPU_WARPS_PER_SM, default 24) even on the small levels, where the march is
-    // latency-bound and short chunks (more warps) beat the cost of the 2*lead overlap columns
-    const int wj = (L.g.ny + uj - 1) / uj;
-    const int chunks = std::max(1, (148 * ctx->march_wps + wj - 1) / wj);
-    ri = std::max(4, (L.g.nx + chunks - 1) / chunks);
-  }
-  ri = std::min(ri, L.g.nx);
-  ri += ri & 1;   // even: a coarse pair of columns never straddles two chunks
+typedef void (*MarchKernel)(LevelGeom, const double*, const double*, const double*, const double*, double*, int, MarchXfer);
+
+// CTAs of `kern` that fit on the GPU at once (one wave), cached per kernel
+static int march_wave(MarchKernel kern) {
+  static std::vector<std::pair<MarchKernel, int>> cache;
+  for (auto& e : cache) if (e.first == kern) return e.second;
+  int per_sm = 0, dev = 0, sms = 148;
+  cudaGetDevice(&dev);
+  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, MARCH_THREADS, 4096) != cudaSuccess || per_sm < 1) per_sm = 2;
+  cache.push_back({kern, per_sm * sms});
+  return per_sm * sms;
+}
+
+// Chunk length (columns per CTA).  Every warp marches `ri + ovh` columns and the CTAs run in ceil(ctas / wave) waves
+// of equal work, so the estimated time is waves * (ri + ovh): exact multiples of a wave win on the big levels, the
+// shortest chunks (most warps) on the small, latency-bound ones.
+static inline int march_chunk(const nsgpu_ctx* ctx, const Level& L, int uj, int ovh, int wave) {
   const int gx = ((L.g.ny + uj - 1) / uj + MARCH_WARPS - 1) / MARCH_WARPS;
+  int ri = 0;
+  if (ctx->march_ri > 0) ri = std::min(ctx->march_ri + (ctx->march_ri & 1), L.g.nx + (L.g.nx & 1));
+  else {
+    long long best = -1;
+    const int hi = std::min(L.g.nx + (L.g.nx & 1), 1024);
+    for (int r = 4; r <= hi; r += 2) {
+      const long long ctas = (long long)gx * ((L.g.nx + r - 1) / r);
+      const long long cost = ((ctas + wave - 1) / wave) * (r + ovh);
+      if (best < 0 || cost < best) { best = cost; ri = r; }
+    }
+    if (ri == 0) ri = 4;
+  }
   while ((long long)gx * ((L.g.nx + ri - 1) / ri) > RED_MAX_BLOCKS) ri *= 2;
   return ri;
 }
@@ -97,23 +115,24 @@ static int march_pass(nsgpu_ctx* ctx, const Level& L, OpCoef c, int nsw, double*
   if (Cr) { xf.bc = Cr->b; xf.ldbc = Cr->g.ld; xf.rcx = L.cx; xf.rcy = L.cy; xf.rscale = 1.0 / (double)(L.cx * L.cy); }
   if (res == 2) { xf.red = ctx->red; xf.out = norm_out; xf.ctl = ctl; }
   const int uj = march_uj(nsw, res);
-  const int ri = march_chunk(ctx, L, uj, lead);
-  const dim3 grid(((L.g.ny + uj - 1) / uj + MARCH_WARPS - 1) / MARCH_WARPS, (L.g.nx + ri - 1) / ri);
-  const size_t sh = (size_t)3 * (ri + 2 * lead + 2 * nsw + 8) * sizeof(double);   // >= nrows of k_march
-  const double *mx = L.mcx[c.op], *my = L.mcy[c.op];
-#define NS_MARCH(NSW, PRO, RES, PF) k_march<NSW, PRO, RES, PF><<<grid, MARCH_THREADS, sh, ctx->stream>>>(L.g, mx, my, xin, b, xout, ri, xf)
+  MarchKernel kern = nullptr;
+#define NS_MARCH(NSW, PRO, RES, PF) kern = k_march<NSW, PRO, RES, PF>
 #define NS_MARCH_RES(NSW, PRO) do { if (res == 0) NS_MARCH(NSW, PRO, 0, MARCH_PF); else if (res == 1) NS_MARCH(NSW, PRO, 1, MARCH_PF); else NS_MARCH(NSW, PRO, 2, MARCH_PF); } while (0)
-  if (nsw == 1 && !Cp && res == 0 && ctx->march_pf != MARCH_PF) {   // prefetch-depth experiments on the plain sweep
+  if (nsw == 1 && !Cp && res == 0) {   // the plain sweep has its own prefetch depth
     switch (ctx->march_pf) {
       case 2: NS_MARCH(1, false, 0, 2); break;
+      case 3: NS_MARCH(1, false, 0, 3); break;
       case 4: NS_MARCH(1, false, 0, 4); break;
-      case 6: NS_MARCH(1, false, 0, 6); break;
-      default: NS_MARCH(1, false, 0, MARCH_PF); break;
+      default: NS_MARCH(1, false, 0, 6); break;
     }
   } else if (nsw == 1) { if (Cp) NS_MARCH_RES(1, true); else NS_MARCH_RES(1, false); }
   else { if (Cp) NS_MARCH_RES(2, true); else NS_MARCH_RES(2, false); }
 #undef NS_MARCH_RES
 #undef NS_MARCH
+  const int ri = march_chunk(ctx, L, uj, 2 * lead + 2 * nsw + 2, march_wave(kern));
+  const dim3 grid(((L.g.ny + uj - 1) / uj + MARCH_WARPS - 1) / MARCH_WARPS, (L.g.nx + ri - 1) / ri);
+  const size_t sh = (size_t)3 * (ri + 2 * lead + 2 * nsw + 8) * sizeof(double);   // >= nrows of k_march
+  kern<<<grid, MARCH_THREADS, sh, ctx->stream>>>(L.g, L.mcx[c.op], L.mcy[c.op], xin, b, xout, ri, xf);
   NS_LAUNCH_CHECK();
   if (Cr && (rc = halo_exchange(ctx, *Cr, Cr->b, std::min(HX, Cr->g.nx)))) return rc;
   return 0;
@@ -138,6 +157,12 @@ static int march_sweeps(nsgpu_ctx* ctx, const Level& L, OpCoef c, int n, double*
 static int vcycle_fused(nsgpu_ctx* ctx, int l, OpCoef c, double** x, double** xt, const double* b, bool xzero, double* norm_out,
                         SolveCtl* ctl) {
   Level& L = ctx->levels[l];
+  if (ctx->tail_start > 0 && l == ctx->tail_start && L.march_ok[c.op]) {   // the rest of the cycle in one single-CTA kernel
+    const TailDesc& T = ctx->tail[c.op];
+    k_coarse_tail<<<1, TAIL_THREADS, (size_t)T.smem_doubles * sizeof(double), ctx->stream>>>(T, b, *x);
+    NS_LAUNCH_CHECK();
+    return 0;
+  }
   if (l == (int)ctx->levels.size() - 1) {
     const int n = ctx->levels.size() == 1 ? ctx->nu_pre + ctx->nu_post : L.coarse_sweeps;
     return march_sweeps(ctx, L, c, n, x, xt, b, xzero, nullptr, nullptr, nullptr, norm_out, ctl);
