@@ -85,6 +85,7 @@ struct nsgpu_ctx {
   bool capturing = false;
   // coarse tail (ns_tail.cuh): levels >= tail_start run in one single-CTA kernel; 0 = no tail
   int tail_start = 0, use_tail = 1;
+  double vel_rho = 0.0, vel_omega = 0.0;   // Jacobi radius bound of LHS_V; SOR factor (0: velocity solves use multigrid)
   nsgpu::TailDesc tail[2];
   int64_t launches = 0;
   double fine_sweeps_phi = 0;

@@ -46,23 +46,26 @@ __device__ __forceinline__ double fast_rcp(double d) {
 struct ColConst { double csa, cna, dya, csb, cnb, dyb; };   // y-coefficients of the lane's two cells
 
 // one half-sweep on column `c` (current state), neighbours cm (i-1) and cp (i+1); TA: the updated cell is .x
-template <bool TA>
+// SOR: over-relaxed update x <- x + omega (x_gs - x) (red-black SOR, used for the diagonally dominant LHS_V)
+template <bool TA, bool SOR>
 __device__ __forceinline__ void half_update(double2& c, const double2& cm, const double2& cp, const double2& bb,
-                                            double cw, double ce, double dx, const ColConst& k) {
+                                            double cw, double ce, double dx, const ColConst& k, double omega) {
   if (TA) {
     const double S = __shfl_up_sync(0xffffffffu, c.y, 1), N = c.y;
     double v = fma(cw, cm.x, bb.x);
     v = fma(ce, cp.x, v);
     v = fma(k.csa, S, v);
     v = fma(k.cna, N, v);
-    c.x = v * fast_rcp(dx + k.dya);
+    if (SOR) c.x = fma(omega, fma(v, fast_rcp(dx + k.dya), -c.x), c.x);
+    else c.x = v * fast_rcp(dx + k.dya);
   } else {
     const double S = c.x, N = __shfl_down_sync(0xffffffffu, c.x, 1);
     double v = fma(cw, cm.y, bb.y);
     v = fma(ce, cp.y, v);
     v = fma(k.csb, S, v);
     v = fma(k.cnb, N, v);
-    c.y = v * fast_rcp(dx + k.dyb);
+    if (SOR) c.y = fma(omega, fma(v, fast_rcp(dx + k.dyb), -c.y), c.y);
+    else c.y = v * fast_rcp(dx + k.dyb);
   }
 }
 
@@ -90,6 +93,7 @@ struct MarchXfer {
   double* bc;         // RES == 1: coarse right-hand side (level l+1 layout)
   int ldbc, rcx, rcy;
   double rscale;      // 1 / (rcx * rcy)
+  double omega;       // SOR relaxation factor
   Reducer red;        // RES == 2
   double* out;
   SolveCtl* ctl;      // RES == 2: optional convergence epilogue
@@ -97,7 +101,7 @@ struct MarchXfer {
 
 // Per-thread state of the march: one ring of columns (PF prefetched ones ahead of the K being worked on) and
 // running pointers (one add per column instead of a 64-bit multiply per access).
-template <int NSW, bool PROLONG, int RES, int PF>
+template <int NSW, bool PROLONG, int RES, int PF, bool SOR>
 struct Marcher {
   static constexpr int L = 2 * NSW;                 // half-sweep stages
   static constexpr int K = L + 2 + (RES ? 1 : 0);   // columns being worked on
@@ -142,7 +146,7 @@ struct Marcher {
 #pragma unroll
     for (int s = 0; s < L; s++) {
       const double* c3 = cc - 3 * (1 + s);
-      half_update<TA>(X[PF + s + 1], X[PF + s + 2], X[PF + s], Bq[PF + s + 1], c3[0], c3[1], c3[2], k);
+      half_update<TA, SOR>(X[PF + s + 1], X[PF + s + 2], X[PF + s], Bq[PF + s + 1], c3[0], c3[1], c3[2], k, xf.omega);
     }
     const int rs = n - L;                              // this column is final
     if ((unsigned)(rs - ib) < (unsigned)(ie - ib)) {
@@ -181,11 +185,11 @@ struct Marcher {
   }
 };
 
-template <int NSW, bool PROLONG, int RES, int PF>
+template <int NSW, bool PROLONG, int RES, int PF, bool SOR = false>
 __global__ void __launch_bounds__(MARCH_THREADS)
 k_march(LevelGeom g, const double* __restrict__ mcx, const double* __restrict__ mcy, const double* __restrict__ xin,
         const double* __restrict__ b, double* __restrict__ xout, int RI, MarchXfer xf) {
-  using M = Marcher<NSW, PROLONG, RES, PF>;
+  using M = Marcher<NSW, PROLONG, RES, PF, SOR>;
   constexpr int L = M::L;
   constexpr int HJ = march_halo(NSW, RES);   // halo cells per side of the strip
   constexpr int LL = march_lead(NSW, RES);   // halo columns per side of the chunk

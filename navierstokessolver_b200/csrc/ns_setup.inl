@@ -66,6 +66,17 @@ static int build_level_geom(nsgpu_ctx* ctx, Level& L, const HostPlan& P, size_t 
   if ((rc = dev_upload(ctx, L.owned, A.ay, &g.ay))) return rc;
   if ((rc = dev_upload(ctx, L.owned, A.bx, &g.bx))) return rc;
   if ((rc = dev_upload(ctx, L.owned, A.by, &g.by))) return rc;
+  if (l == 0 && !A.mcx[0].empty()) {
+    // Jacobi spectral-radius bound of LHS_V, max over cells of sum|off-diagonal| / diagonal (distinct columns x distinct rows)
+    std::vector<std::pair<double, double>> ux, uy;
+    for (int a = HX; a < HX + A.nx; a++) ux.push_back({std::fabs(A.mcx[0][3 * a]) + std::fabs(A.mcx[0][3 * a + 1]), A.mcx[0][3 * a + 2]});
+    for (int a = PJ; a < PJ + A.ny; a++) uy.push_back({std::fabs(A.mcy[0][3 * a]) + std::fabs(A.mcy[0][3 * a + 1]), A.mcy[0][3 * a + 2]});
+    std::sort(ux.begin(), ux.end()); ux.erase(std::unique(ux.begin(), ux.end()), ux.end());
+    std::sort(uy.begin(), uy.end()); uy.erase(std::unique(uy.begin(), uy.end()), uy.end());
+    double rho = 0;
+    for (auto& p : ux) for (auto& q : uy) rho = std::max(rho, (p.first + q.first) / (p.second + q.second));
+    ctx->vel_rho = rho;
+  }
   for (int op = 0; op < 2; op++) {
     L.march_ok[op] = A.march_ok[op];
     if (!A.mcx[op].empty()) {
@@ -155,6 +166,21 @@ static int create_impl(nsgpu_ctx* ctx, const nsgpu_grid* G, const nsgpu_params* 
     }
   }
   ctx->levels.back().coarse_sweeps = coarsest_sweeps(ctx->levels.back().g.gnx, ctx->levels.back().gny);
+
+  // ---- velocity solves: LHS_V = I - dt/(2Re) L is diagonally dominant; when red-black SOR with the optimal factor
+  // reaches rtol in a few sweeps it beats multigrid (no coarse levels, every pass is a fused double sweep)
+  ctx->vel_omega = 0.0;
+  {
+    int mode = 2;   // 0 = multigrid, 1 = SOR, 2 = auto
+    if (const char* e = getenv("NSGPU_VEL_SOLVER")) mode = !strcmp(e, "mg") ? 0 : !strcmp(e, "sor") ? 1 : 2;
+    if (P->reserved[0] == 1) mode = 0; else if (P->reserved[0] == 2) mode = 1;
+    const double rho = ctx->vel_rho;
+    if (mode != 0 && ctx->world == 1 && ctx->rect && ctx->solver == 0 && rho > 0 && rho < 1) {
+      const double omega = 2.0 / (1.0 + std::sqrt(1.0 - rho * rho));
+      const double sweeps = std::log(ctx->rtol_u) / std::log(std::max(omega - 1.0, 1e-3));
+      if (mode == 1 || sweeps <= 28.0) ctx->vel_omega = omega;
+    }
+  }
 
   // ---- coarse tail: every level of at most TAIL_MAX_CELLS cells (never level 0) in one single-CTA kernel
   if (const char* e = getenv("NSGPU_TAIL")) ctx->use_tail = atoi(e);

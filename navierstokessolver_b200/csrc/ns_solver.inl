@@ -104,7 +104,7 @@ static inline int march_chunk(const nsgpu_ctx* ctx, const Level& L, int uj, int 
 // One pass: xout <- NSW red-black sweeps of (xin [+ P xc]) on level L; optional fused restriction / residual norm.
 //   xin == nullptr: zero initial guess;  Cp/xc: prolong from;  Cr: restrict the residual to Cr->b;  norm_out/ctl: |r|^2
 static int march_pass(nsgpu_ctx* ctx, const Level& L, OpCoef c, int nsw, double* xin, const double* b, double* xout,
-                      const Level* Cp, double* xc, const Level* Cr, double* norm_out, SolveCtl* ctl) {
+                      const Level* Cp, double* xc, const Level* Cr, double* norm_out, SolveCtl* ctl, double omega = 0.0) {
   const int res = Cr ? 1 : (norm_out ? 2 : 0);
   const int lead = march_lead(nsw, res);
   int rc;
@@ -114,11 +114,15 @@ static int march_pass(nsgpu_ctx* ctx, const Level& L, OpCoef c, int nsw, double*
   if (Cp) { xf.xc = xc; xf.ldc = Cp->g.ld; xf.pcx = L.cx; xf.pcy = L.cy; }
   if (Cr) { xf.bc = Cr->b; xf.ldbc = Cr->g.ld; xf.rcx = L.cx; xf.rcy = L.cy; xf.rscale = 1.0 / (double)(L.cx * L.cy); }
   if (res == 2) { xf.red = ctx->red; xf.out = norm_out; xf.ctl = ctl; }
+  xf.omega = omega;
   const int uj = march_uj(nsw, res);
   MarchKernel kern = nullptr;
 #define NS_MARCH(NSW, PRO, RES, PF) kern = k_march<NSW, PRO, RES, PF>
 #define NS_MARCH_RES(NSW, PRO) do { if (res == 0) NS_MARCH(NSW, PRO, 0, MARCH_PF); else if (res == 1) NS_MARCH(NSW, PRO, 1, MARCH_PF); else NS_MARCH(NSW, PRO, 2, MARCH_PF); } while (0)
-  if (nsw == 1 && !Cp && res == 0) {   // the plain sweep has its own prefetch depth
+  if (omega > 0.0) {                   // red-black SOR double sweep (velocity solves)
+    if (nsw != 2 || Cp || res == 1) { ctx->err = "SOR passes are double sweeps without transfers"; return NSGPU_ERR_ARG; }
+    if (res == 0) kern = k_march<2, false, 0, MARCH_PF, true>; else kern = k_march<2, false, 2, MARCH_PF, true>;
+  } else if (nsw == 1 && !Cp && res == 0) {   // the plain sweep has its own prefetch depth
     switch (ctx->march_pf) {
       case 2: NS_MARCH(1, false, 0, 2); break;
       case 3: NS_MARCH(1, false, 0, 3); break;
@@ -408,6 +412,23 @@ static int solve_bicgstab(nsgpu_ctx* ctx, OpCoef c, double** xp, double** xtp, c
 // Device-controlled multigrid solve (one rank, rectangle): the stopping test runs in the epilogue of the
 // residual reductions (CtlEpilogue), so the host never has to look at a residual between cycles.
 
+// One iteration of a device-controlled solve: a V-cycle, or (velocity, SOR mode) four over-relaxed sweeps; the last
+// pass reduces the residual norm and its epilogue updates the control block.
+static int solve_body(nsgpu_ctx* ctx, int slot, OpCoef c, double** x, double** xt, const double* b) {
+  SolveCtl* ctl = ctx->d_ctl + slot;
+  if (c.op == 0 && ctx->vel_omega > 0.0) {
+    const Level& L = ctx->levels[0];
+    int rc = march_pass(ctx, L, c, 2, *x, b, *xt, nullptr, nullptr, nullptr, nullptr, nullptr, ctx->vel_omega);
+    if (rc) return rc;
+    std::swap(*x, *xt);
+    rc = march_pass(ctx, L, c, 2, *x, b, *xt, nullptr, nullptr, nullptr, &ctl->rn2, ctl, ctx->vel_omega);
+    if (rc) return rc;
+    std::swap(*x, *xt);
+    return 0;
+  }
+  return vcycle_fused(ctx, 0, c, x, xt, b, false, &ctl->rn2, ctl);
+}
+
 static int solve_head(nsgpu_ctx* ctx, int slot, OpCoef c, double* x, const double* b, double rtol, unsigned long long handle) {
   const Level& L = ctx->levels[0];
   SolveCtl* ctl = ctx->d_ctl + slot;
@@ -474,7 +495,7 @@ static int build_solve_graph(nsgpu_ctx* ctx, int slot, OpCoef c, double* x, doub
   cudaGraph_t body = p.conditional.phGraph_out[0];
   NS_GRAPH_TRY(cudaStreamBeginCaptureToGraph(ctx->stream, body, nullptr, nullptr, 0, mode));
   double *xa = x, *xb = xt;
-  rc = vcycle_fused(ctx, 0, c, &xa, &xb, b, false, &ctx->d_ctl[slot].rn2, ctx->d_ctl + slot);
+  rc = solve_body(ctx, slot, c, &xa, &xb, b);
   e2 = cudaStreamEndCapture(ctx->stream, &gout);
   if (rc) return rc;
   NS_GRAPH_TRY(e2);
@@ -525,7 +546,7 @@ static int solve_mg_dev(nsgpu_ctx* ctx, int slot, OpCoef c, double** x, double**
     if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
     if (e != cudaSuccess) { ctx->err = std::string("ctl readback: ") + cudaGetErrorString(e); return NSGPU_ERR_CUDA; }
     if (!ctx->h_ctl[slot].go) break;
-    if ((rc = vcycle_fused(ctx, 0, c, x, xt, b, false, &ctx->d_ctl[slot].rn2, ctx->d_ctl + slot))) return rc;
+    if ((rc = solve_body(ctx, slot, c, x, xt, b))) return rc;
   }
   return solve_tail(ctx, slot, *x);
 }
@@ -545,7 +566,11 @@ static void decode_solve(nsgpu_ctx* ctx, int slot, SolveResult* out) {
   ctx->seen_cycles[slot] = h.total_cycles;
 }
 
-static inline bool dev_solve_ok(const nsgpu_ctx* ctx, OpCoef c) { return ctx->solver == 0 && ctx->world == 1 && all_levels_march(ctx, c); }
+static inline bool dev_solve_ok(const nsgpu_ctx* ctx, OpCoef c) {
+  if (ctx->solver != 0 || ctx->world != 1) return false;
+  if (c.op == 0 && ctx->vel_omega > 0.0) return march_level_ok(ctx, ctx->levels[0], c);
+  return all_levels_march(ctx, c);
+}
 
 // slot: 0 = u, 1 = v, 2 = phi.  On the device-controlled path the result is pending until finish_results().
 static int solve(nsgpu_ctx* ctx, int slot, OpCoef c, double** x, const double* b, double rtol, SolveResult* out) {

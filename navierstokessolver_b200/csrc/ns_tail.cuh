@@ -38,11 +38,11 @@ __device__ void tail_smooth(const TailDesc& d, const TailLevel& L, double* sm, i
   const double* b = sm + L.boff;
   const double* sx = sm + L.sxoff;
   const double* sy = sm + L.syoff;
-  const int n = L.nx * L.ny, p = L.ny + 2;
+  const int hny = (L.ny + 1) >> 1, n = L.nx * hny, p = L.ny + 2;
   for (int h = 0; h < 2 * sweeps; h++) {
-    for (int c = threadIdx.x; c < n; c += TAIL_THREADS) {
-      const int i = c / L.ny, j = c - i * L.ny;
-      if (((d.gi0 + i + j + h) & 1) == 0) {
+    for (int c = threadIdx.x; c < n; c += TAIL_THREADS) {   // only the cells of this half-sweep's colour
+      const int i = c / hny, j = 2 * (c - i * hny) + ((d.gi0 + i + h) & 1);
+      if (j < L.ny) {
         const int q = tidx(L, i, j);
         double v = fma(sx[3 * i], x[q - p], b[q]);
         v = fma(sx[3 * i + 1], x[q + p], v);
