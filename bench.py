@@ -142,7 +142,7 @@ def ours(args, rank, world, local_rank):
     n = ny                                     # dt follows the cell size like the reference inputs: 0.25 * h
     grid = ns.GridDesc.cavity(ny, nx=gnx, lx=gnx / float(ny))
     s = ns.GpuFluidSolver(grid, 0.25 / n, args.re, device=local_rank, rank=rank, world=world, nccl_id=nccl_id,
-                          rtol_u=args.rtol, rtol_phi=args.rtol, solver=args.solver, use_graph=args.graph)
+                          rtol_u=args.rtol, rtol_phi=args.rtol, solver=args.solver, use_graph=0 if args.graph else -1)
     cells_local, cells_global = nxl * ny, gnx * ny
 
     def barrier():
@@ -175,7 +175,7 @@ def ours(args, rank, world, local_rank):
     launches = int(info.kernel_launches)
     fine_sweeps = float(info.fine_sweeps)
 
-    # ---- the dominant kernel alone: fine-level red-black Poisson sweep (k_smooth_rb), CUDA events on its stream
+    # ---- the dominant kernel alone: fine-level red-black Poisson sweep (k_march<1,false,0>), CUDA events on its stream
     s.poisson_sweeps(20, False)
     best = None
     for _ in range(5):
@@ -226,7 +226,8 @@ def ours(args, rank, world, local_rank):
                 "data": "synthetic",
                 "config": {"workload": "lid-driven cavity Re=%g from rest, %dx%d cells (%d columns per GPU), dt=0.25/%d" % (args.re, gnx, ny, nxl, n),
                            "parallelism": "x-slabs, %d rank(s), NCCL halo exchange + scalar allreduce" % world,
-                           "solver": ("BiCGStab + V(2,2)" if args.solver else "multigrid V(2,2) iteration") + ", red-black GS smoother, rtol %g both solves" % args.rtol,
+                           "solver": ("BiCGStab + V(2,2)" if args.solver else "phi: multigrid V(2,2), fused red-black GS passes; u*, v*: red-black SOR or multigrid (auto)")
+                                     + ", true-residual rtol %g all solves, %s" % (args.rtol, "one CUDA graph per solve (device-side WHILE)" if args.graph else "direct launches"),
                            "levels": s.num_levels, "cache": "inputs larger than L2 (13 resident fields x %.0f MB per GPU)" % (cells_local * 8 / 1e6)},
                 "timesteps_per_s": args.steps / (ms * 1e-3),
                 "poisson_gcell_updates_per_s": sweep_gcups,
@@ -238,7 +239,7 @@ def ours(args, rank, world, local_rank):
                 "clocks": clocks,
                 "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "steps": e2e_steps,
                         "ms_per_step": 1e3 * e2e_wall / e2e_steps},
-                "roofline": {"bound": "hbm", "kernel": "k_smooth_rb (fine-level fused red-black Poisson sweep)", "achieved": achieved, "peak": peak,
+                "roofline": {"bound": "hbm", "kernel": "k_march<1,false,0> (fine-level fused red-black Poisson sweep, register-marching)", "achieved": achieved, "peak": peak,
                              "unit": "GB/s", "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
                              "bytes_per_cell_update": SWEEP_BYTES_PER_UPDATE, "us_per_launch": best * 1e3,
                              "cells_per_launch": cells_local, "timing": "CUDA events on the solver stream around %d back-to-back launches, best of 5" % args.sweeps},
@@ -262,7 +263,7 @@ def main():
     ap.add_argument("--re", type=float, default=1000.0)
     ap.add_argument("--rtol", type=float, default=1e-8)
     ap.add_argument("--solver", type=int, default=0)
-    ap.add_argument("--graph", type=int, default=0)
+    ap.add_argument("--graph", type=int, default=1)
     ap.add_argument("--sweeps", type=int, default=100)
     ap.add_argument("--ref-n", type=int, default=256)
     ap.add_argument("--no-cpu-baseline", action="store_true")

@@ -63,9 +63,11 @@ typedef struct {
   int32_t max_cycles;        /* per linear solve; <= 0 selects 200                              */
   int32_t nu_pre, nu_post;   /* multigrid smoothing sweeps; <= 0 selects 2                      */
   int32_t solver;            /* 0 = multigrid iteration, 1 = BiCGStab preconditioned by one V-cycle */
-  int32_t use_graph;         /* 1 = replay the V-cycle from a CUDA graph                        */
+  int32_t use_graph;         /* >= 0: each linear solve is one CUDA graph (head -> WHILE(not converged){cycle}) with the */
+                             /* stopping test on the device; < 0: direct launches, one host read per cycle             */
   int32_t max_levels;        /* <= 0: coarsen as far as the grid allows                          */
-  int32_t reserved[7];
+  int32_t vel_solver;        /* LHS_V solves: 0 = auto, 1 = multigrid, 2 = red-black SOR (optimal factor)            */
+  int32_t reserved[6];
 } nsgpu_params;
 
 typedef struct {

@@ -30,7 +30,7 @@ class _Params(C.Structure):
     _fields_ = [("dt", C.c_double), ("re", C.c_double), ("device", C.c_int32), ("rank", C.c_int32),
                 ("world", C.c_int32), ("nccl_id", C.c_void_p), ("rtol_u", C.c_double), ("rtol_phi", C.c_double),
                 ("max_cycles", C.c_int32), ("nu_pre", C.c_int32), ("nu_post", C.c_int32), ("solver", C.c_int32),
-                ("use_graph", C.c_int32), ("max_levels", C.c_int32), ("reserved", C.c_int32 * 7)]
+                ("use_graph", C.c_int32), ("max_levels", C.c_int32), ("vel_solver", C.c_int32), ("reserved", C.c_int32 * 6)]
 
 
 class StepInfo(C.Structure):
@@ -153,7 +153,7 @@ class GpuFluidSolver:
     """One nsgpu_ctx: the device-resident state of a FluidSolver (FS.h:20-59)."""
 
     def __init__(self, grid, dt, re, device=0, rank=0, world=1, nccl_id=None, rtol_u=0.0, rtol_phi=0.0, max_cycles=0,
-                 nu_pre=0, nu_post=0, solver=0, use_graph=0, max_levels=0):
+                 nu_pre=0, nu_post=0, solver=0, use_graph=0, max_levels=0, vel_solver=0):
         self.grid = grid
         self._g = grid.c_struct()
         p = _Params()
@@ -162,6 +162,7 @@ class GpuFluidSolver:
         p.nccl_id = C.cast(self._nccl, C.c_void_p) if self._nccl is not None else None
         p.rtol_u, p.rtol_phi, p.max_cycles = rtol_u, rtol_phi, max_cycles
         p.nu_pre, p.nu_post, p.solver, p.use_graph, p.max_levels = nu_pre, nu_post, solver, use_graph, max_levels
+        p.vel_solver = vel_solver
         self._h = C.c_void_p()
         rc = lib.nsgpu_create(C.byref(self._g), C.byref(p), C.byref(self._h))
         if rc:

@@ -120,7 +120,7 @@ static int create_impl(nsgpu_ctx* ctx, const nsgpu_grid* G, const nsgpu_params* 
   ctx->nu_pre = P->nu_pre > 0 ? P->nu_pre : 2;
   ctx->nu_post = P->nu_post > 0 ? P->nu_post : 2;
   ctx->solver = P->solver;
-  ctx->use_graph = P->use_graph;
+  ctx->use_graph = P->use_graph < 0 ? 0 : 1;
   if (const char* e = getenv("NSGPU_MARCH")) ctx->march = atoi(e);
   if (const char* e = getenv("NSGPU_RI")) ctx->march_ri = atoi(e);
   if (const char* e = getenv("NSGPU_PF")) ctx->march_pf = atoi(e);
@@ -173,7 +173,7 @@ static int create_impl(nsgpu_ctx* ctx, const nsgpu_grid* G, const nsgpu_params* 
   {
     int mode = 2;   // 0 = multigrid, 1 = SOR, 2 = auto
     if (const char* e = getenv("NSGPU_VEL_SOLVER")) mode = !strcmp(e, "mg") ? 0 : !strcmp(e, "sor") ? 1 : 2;
-    if (P->reserved[0] == 1) mode = 0; else if (P->reserved[0] == 2) mode = 1;
+    if (P->vel_solver == 1) mode = 0; else if (P->vel_solver == 2) mode = 1;
     const double rho = ctx->vel_rho;
     if (mode != 0 && ctx->world == 1 && ctx->rect && ctx->solver == 0 && rho > 0 && rho < 1) {
       const double omega = 2.0 / (1.0 + std::sqrt(1.0 - rho * rho));
