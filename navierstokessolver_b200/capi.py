@@ -172,7 +172,7 @@ class GpuFluidSolver:
         self.i0, self.i1, self.id0, self.n_local = i0.value, i1.value, id0.value, n.value
 
     def close(self):
-        if getattr(self, "_h", None):
+        if getattr(self, "_h", None) and lib is not None:   # `lib` is already gone at interpreter shutdown
             lib.nsgpu_destroy(self._h)
             self._h = None
 

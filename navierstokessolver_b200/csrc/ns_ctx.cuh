@@ -25,6 +25,7 @@ struct Level {
   double* b = nullptr;
   std::vector<void*> owned;  // device allocations of this level (geometry arrays)
   int coarse_sweeps = 0;     // only used on the coarsest level
+  bool replicated = false;   // several ranks: every rank holds the whole level (coarse tail), no halo exchange
   const double* mcx[2] = {nullptr, nullptr};   // folded coefficient tables of k_sweep_march, per operator
   const double* mcy[2] = {nullptr, nullptr};
   bool march_ok[2] = {false, false};

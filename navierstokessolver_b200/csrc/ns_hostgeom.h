@@ -26,6 +26,7 @@ struct HostPlan {
   std::vector<uint8_t> cedges0;       // [4*gnx*ny] edge ids, general domains only
   std::vector<HostLevel> levels;
   std::vector<int> lnx, lgi0, lcx, lcy;  // per level: local columns, global index of local column 0, coarsening factors
+  int rep_start = 0;                     // several ranks: levels >= rep_start are REPLICATED (every rank holds the whole level); 0 = none
   int64_t n_cells_global = 0;
   int i0 = 0, i1 = 0;
   int64_t id0 = 0, n_local = 0;
@@ -250,7 +251,12 @@ static inline int make_host_plan(const nsgpu_grid* G, int rank, int world, int m
     const HostLevel& F = P.levels.back();
     const int nx_l = P.lnx.back();
     const double mx = mean_of(F.hx), my = mean_of(F.hy);
-    const int min_nx = world > 1 ? 2 : 1;
+    // Several ranks on a plain rectangle: slabs keep at least HX columns (the fused marching passes take their whole
+    // halo from ONE neighbour); as soon as a level is small enough for the single-CTA coarse tail it is replicated on
+    // every rank (all-gather of its right-hand side), so the coarse part of the cycle needs no communication at all.
+    const bool fast = rect && world > 1 && !(P.side_out[0] || P.side_out[1] || P.side_out[2] || P.side_out[3]);
+    const bool replicated = P.rep_start > 0;
+    const int min_nx = world == 1 || replicated ? 1 : (fast ? HX : 2);
     const bool can_x = (nx_l % 2 == 0) && (nx_l / 2 >= min_nx) && (F.gnx / 2 >= 2);
     const bool can_y = (F.ny % 2 == 0) && (F.ny / 2 >= 2);
     // semi-coarsen only the strongly coupled (finer) direction while the cells are stretched
@@ -286,7 +292,9 @@ static inline int make_host_plan(const nsgpu_grid* G, int rank, int world, int m
         }
     }
     P.lcx.push_back(cx); P.lcy.push_back(cy);
-    P.lnx.push_back(nx_l / cx); P.lgi0.push_back(P.lgi0.back() / cx);
+    if (fast && !replicated && (long long)C.gnx * C.ny <= 4096) P.rep_start = (int)P.levels.size();   // TAIL_MAX_CELLS
+    if (P.rep_start > 0) { P.lnx.push_back(C.gnx); P.lgi0.push_back(0); }
+    else { P.lnx.push_back(nx_l / cx); P.lgi0.push_back(P.lgi0.back() / cx); }
     P.levels.push_back(std::move(C));
   }
   P.lcx.push_back(1); P.lcy.push_back(1);

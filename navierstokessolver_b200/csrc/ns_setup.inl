@@ -157,6 +157,7 @@ static int create_impl(nsgpu_ctx* ctx, const nsgpu_grid* G, const nsgpu_params* 
   for (size_t l = 0; l < plan.levels.size(); l++) {
     Level& L = ctx->levels[l];
     L.cx = plan.lcx[l]; L.cy = plan.lcy[l];
+    L.replicated = plan.rep_start > 0 && (int)l >= plan.rep_start;
     int rc = build_level_geom(ctx, L, plan, l);
     if (rc) return rc;
     if (l > 0) {
@@ -175,7 +176,7 @@ static int create_impl(nsgpu_ctx* ctx, const nsgpu_grid* G, const nsgpu_params* 
     if (const char* e = getenv("NSGPU_VEL_SOLVER")) mode = !strcmp(e, "mg") ? 0 : !strcmp(e, "sor") ? 1 : 2;
     if (P->vel_solver == 1) mode = 0; else if (P->vel_solver == 2) mode = 1;
     const double rho = ctx->vel_rho;
-    if (mode != 0 && ctx->world == 1 && ctx->rect && ctx->solver == 0 && rho > 0 && rho < 1) {
+    if (mode != 0 && ctx->rect && ctx->solver == 0 && rho > 0 && rho < 1) {
       const double omega = 2.0 / (1.0 + std::sqrt(1.0 - rho * rho));
       const double sweeps = std::log(ctx->rtol_u) / std::log(std::max(omega - 1.0, 1e-3));
       if (mode == 1 || sweeps <= 28.0) ctx->vel_omega = omega;
@@ -185,11 +186,12 @@ static int create_impl(nsgpu_ctx* ctx, const nsgpu_grid* G, const nsgpu_params* 
   // ---- coarse tail: every level of at most TAIL_MAX_CELLS cells (never level 0) in one single-CTA kernel
   if (const char* e = getenv("NSGPU_TAIL")) ctx->use_tail = atoi(e);
   ctx->tail_start = 0;
-  if (ctx->use_tail && ctx->world == 1 && ctx->rect) {
+  if ((ctx->use_tail || plan.rep_start > 0) && (ctx->world == 1 || plan.rep_start > 0) && ctx->rect) {
     const int nl = (int)ctx->levels.size();
     int ts = 0;
     for (int l = 1; l < nl; l++)
-      if ((long long)ctx->levels[l].g.nx * ctx->levels[l].g.ny <= TAIL_MAX_CELLS) { ts = l; break; }
+      if ((long long)ctx->levels[l].g.gnx * ctx->levels[l].g.ny <= TAIL_MAX_CELLS) { ts = l; break; }
+    if (plan.rep_start > 0 && ts != plan.rep_start) { ctx->err = "internal: replicated levels do not start at the coarse tail"; return NSGPU_ERR_ARG; }
     if (ts > 0 && nl - ts <= TAIL_MAX_LEVELS) {
       for (int op = 0; op < 2; op++) {
         TailDesc& T = ctx->tail[op];
@@ -210,6 +212,7 @@ static int create_impl(nsgpu_ctx* ctx, const nsgpu_grid* G, const nsgpu_params* 
         T.smem_doubles = off;
       }
       const size_t bytes = (size_t)ctx->tail[0].smem_doubles * sizeof(double);
+      if (plan.rep_start > 0 && (bytes > 200 * 1024 || nl - ts > TAIL_MAX_LEVELS)) { ctx->err = "internal: coarse tail does not fit"; return NSGPU_ERR_ARG; }
       if (bytes <= 200 * 1024) {
         NS_CUDA(cudaFuncSetAttribute(k_coarse_tail, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
         ctx->tail_start = ts;

@@ -36,7 +36,8 @@ static inline dim3 grid_cols(const LevelGeom& g, int threads, int max_blocks = 1
 
 // One-column-block halo exchange with the x-neighbours: `width` columns, contiguous (width * ld doubles).
 static int halo_exchange(nsgpu_ctx* ctx, const Level& L, double* f, int width) {
-  if (ctx->world == 1) return 0;
+  if (ctx->world == 1 || L.replicated) return 0;
+  width = std::min(width, std::min(HX, L.g.nx));
   const size_t n = (size_t)width * L.g.ld;
   const int nx = L.g.nx;
   NS_NCCL(ncclGroupStart());
@@ -63,7 +64,7 @@ static int allreduce(nsgpu_ctx* ctx, double* d, int n, ncclRedOp_t op) {
 
 static inline bool march_level_ok(const nsgpu_ctx* ctx, const Level& L, OpCoef c) {
   // with several ranks the 5-column halo of a fused pass has to come from ONE neighbour
-  return ctx->march && ctx->rect && L.march_ok[c.op] && (ctx->world == 1 || L.g.nx >= HX);
+  return ctx->march && ctx->rect && L.march_ok[c.op] && (ctx->world == 1 || L.replicated || L.g.nx >= HX);
 }
 
 typedef void (*MarchKernel)(LevelGeom, const double*, const double*, const double*, const double*, double*, int, MarchXfer);
@@ -111,8 +112,11 @@ static int march_pass(nsgpu_ctx* ctx, const Level& L, OpCoef c, int nsw, double*
   if (xin && (rc = halo_exchange(ctx, L, xin, lead))) return rc;
   if (Cp && (rc = halo_exchange(ctx, *Cp, xc, (lead + 1) / 2 + 1))) return rc;
   MarchXfer xf{};
-  if (Cp) { xf.xc = xc; xf.ldc = Cp->g.ld; xf.pcx = L.cx; xf.pcy = L.cy; }
-  if (Cr) { xf.bc = Cr->b; xf.ldbc = Cr->g.ld; xf.rcx = L.cx; xf.rcy = L.cy; xf.rscale = 1.0 / (double)(L.cx * L.cy); }
+  // a replicated coarse level holds the whole domain: this rank's part starts at its global coarse column
+  const size_t rep_off_p = (Cp && Cp->replicated && !L.replicated) ? (size_t)(L.g.gi0 / L.cx) * Cp->g.ld : 0;
+  const size_t rep_off_r = (Cr && Cr->replicated && !L.replicated) ? (size_t)(L.g.gi0 / L.cx) * Cr->g.ld : 0;
+  if (Cp) { xf.xc = xc + rep_off_p; xf.ldc = Cp->g.ld; xf.pcx = L.cx; xf.pcy = L.cy; }
+  if (Cr) { xf.bc = Cr->b + rep_off_r; xf.ldbc = Cr->g.ld; xf.rcx = L.cx; xf.rcy = L.cy; xf.rscale = 1.0 / (double)(L.cx * L.cy); }
   if (res == 2) { xf.red = ctx->red; xf.out = norm_out; xf.ctl = ctl; }
   xf.omega = omega;
   const int uj = march_uj(nsw, res);
@@ -138,7 +142,11 @@ static int march_pass(nsgpu_ctx* ctx, const Level& L, OpCoef c, int nsw, double*
   const size_t sh = (size_t)3 * (ri + 2 * lead + 2 * nsw + 8) * sizeof(double);   // >= nrows of k_march
   kern<<<grid, MARCH_THREADS, sh, ctx->stream>>>(L.g, L.mcx[c.op], L.mcy[c.op], xin, b, xout, ri, xf);
   NS_LAUNCH_CHECK();
-  if (Cr && (rc = halo_exchange(ctx, *Cr, Cr->b, std::min(HX, Cr->g.nx)))) return rc;
+  if (Cr && Cr->replicated && !L.replicated && ctx->world > 1) {
+    // every rank contributes its slab of the coarse right-hand side; in place: the slabs are contiguous column ranges
+    const size_t count = (size_t)(L.g.nx / L.cx) * Cr->g.ld;
+    NS_NCCL(ncclAllGather(Cr->b + (size_t)HX * Cr->g.ld + rep_off_r, Cr->b + (size_t)HX * Cr->g.ld, count, ncclDouble, ctx->comm, ctx->stream));
+  } else if (Cr && (rc = halo_exchange(ctx, *Cr, Cr->b, HX - 1))) return rc;
   return 0;
 }
 
@@ -182,6 +190,7 @@ static int vcycle_fused(nsgpu_ctx* ctx, int l, OpCoef c, double** x, double** xt
 
 static inline bool all_levels_march(const nsgpu_ctx* ctx, OpCoef c) {
   for (const Level& L : ctx->levels) if (!march_level_ok(ctx, L, c)) return false;
+  if (ctx->world > 1 && ctx->levels.size() > 1 && ctx->tail_start == 0) return false;   // slabs thinner than HX below
   return true;
 }
 
@@ -327,10 +336,24 @@ static int solve_mg(nsgpu_ctx* ctx, OpCoef c, double** x, double** xt, const dou
     out->rel = 0; out->converged = true;
     return 0;
   }
+  // several ranks on a rectangle: the same fused passes as the device-controlled path, the residual norm comes out of
+  // the last pass and is all-reduced; the host reads one scalar per cycle
+  const bool sor = c.op == 0 && ctx->vel_omega > 0.0 && march_level_ok(ctx, L, c);
+  const bool fused = sor || all_levels_march(ctx, c);
   while (rn > rtol * bn && out->cycles < ctx->max_cycles) {
-    if ((rc = vcycle_any(ctx, c, x, xt, b, false))) return rc;
+    if (sor) {
+      if ((rc = march_pass(ctx, L, c, 2, *x, b, *xt, nullptr, nullptr, nullptr, nullptr, nullptr, ctx->vel_omega))) return rc;
+      std::swap(*x, *xt);
+      if ((rc = march_pass(ctx, L, c, 2, *x, b, *xt, nullptr, nullptr, nullptr, ctx->d_scal + 1, nullptr, ctx->vel_omega))) return rc;
+      std::swap(*x, *xt);
+    } else if (fused) {
+      if ((rc = vcycle_fused(ctx, 0, c, x, xt, b, false, ctx->d_scal + 1, nullptr))) return rc;
+    } else {
+      if ((rc = vcycle_any(ctx, c, x, xt, b, false))) return rc;
+    }
     out->cycles++;
-    if ((rc = residual_norm2(ctx, L, c, *x, b, ctx->d_scal + 1))) return rc;
+    if (fused) { if ((rc = allreduce(ctx, ctx->d_scal + 1, 1, ncclSum))) return rc; }
+    else if ((rc = residual_norm2(ctx, L, c, *x, b, ctx->d_scal + 1))) return rc;
     if ((rc = read_scalars(ctx, ctx->d_scal + 1, 1, h))) return rc;
     rn = std::sqrt(h[0]);
     if (!(rn == rn)) break;
@@ -610,8 +633,8 @@ static int phase_velocity(nsgpu_ctx* ctx, SolveResult* ru, SolveResult* rv) {   
   cudaMemcpyAsync(ctx->ustar, ctx->u, L.stride * sizeof(double), cudaMemcpyDeviceToDevice, ctx->stream);
   cudaMemcpyAsync(ctx->vstar, ctx->v, L.stride * sizeof(double), cudaMemcpyDeviceToDevice, ctx->stream);
   int rc;
-  if ((rc = halo_exchange(ctx, L, ctx->rhs_u, 1))) return rc;
-  if ((rc = halo_exchange(ctx, L, ctx->rhs_v, 1))) return rc;
+  if ((rc = halo_exchange(ctx, L, ctx->rhs_u, HX - 1))) return rc;   // the fused passes recompute up to 4 halo columns
+  if ((rc = halo_exchange(ctx, L, ctx->rhs_v, HX - 1))) return rc;
   if ((rc = solve(ctx, 0, coef_v(ctx), &ctx->ustar, ctx->rhs_u, ctx->rtol_u, ru))) return rc;
   if ((rc = solve(ctx, 1, coef_v(ctx), &ctx->vstar, ctx->rhs_v, ctx->rtol_u, rv))) return rc;
   return 0;
@@ -642,7 +665,7 @@ static int phase_div(nsgpu_ctx* ctx, bool remove_mean) {   // FS.cpp:549-550
 static int phase_phi(nsgpu_ctx* ctx, SolveResult* rp) {   // FS.cpp:551, warm start from phi^n (FS.cpp:54)
   const Level& L = ctx->levels[0];
   int rc;
-  if ((rc = halo_exchange(ctx, L, ctx->rhs_phi, 1))) return rc;
+  if ((rc = halo_exchange(ctx, L, ctx->rhs_phi, HX - 1))) return rc;
   const int64_t before = ctx->launches;
   (void)before;
   if ((rc = solve(ctx, 2, coef_phi(), &ctx->phi, ctx->rhs_phi, ctx->rtol_phi, rp))) return rc;
