@@ -195,12 +195,17 @@ void phi_mean_zero(Emul& E) {
 
 extern "C" {
 
+void* emul_create_rank(const nsgpu_grid* G, double dt, double re, int nu_pre, int nu_post, int max_levels, int rank, int world, char* errbuf, int errlen);
 void* emul_create(const nsgpu_grid* G, double dt, double re, int nu_pre, int nu_post, int max_levels, char* errbuf, int errlen) {
+  return emul_create_rank(G, dt, re, nu_pre, nu_post, max_levels, 0, 1, errbuf, errlen);
+}
+// x-slab `rank` of `world` (the host plan libnsgpu.so uses for several GPUs)
+void* emul_create_rank(const nsgpu_grid* G, double dt, double re, int nu_pre, int nu_post, int max_levels, int rank, int world, char* errbuf, int errlen) {
   Emul* E = new Emul;
   E->dt = dt; E->re = re;
   if (nu_pre > 0) E->nu_pre = nu_pre;
   if (nu_post > 0) E->nu_post = nu_post;
-  int rc = make_host_plan(G, 0, 1, max_levels, E->plan, E->err);
+  int rc = make_host_plan(G, rank, world, max_levels, E->plan, E->err);
   if (rc) {
     if (errbuf && errlen > 0) { strncpy(errbuf, E->err.c_str(), errlen - 1); errbuf[errlen - 1] = 0; }
     delete E;
@@ -273,6 +278,45 @@ int emul_solve(void* h, int which, double rtol, int max_cycles, double* rel) {
   if (which == 0) { E->f[NSGPU_USTAR] = E->f[NSGPU_U]; return solve_mg(*E, c, E->f[NSGPU_USTAR], E->f[NSGPU_RHS_U], rtol, max_cycles, rel); }
   E->f[NSGPU_VSTAR] = E->f[NSGPU_V];
   return solve_mg(*E, c, E->f[NSGPU_VSTAR], E->f[NSGPU_RHS_V], rtol, max_cycles, rel);
+}
+
+// slab plan: out = {i0, i1, id0, n_local, n_levels, rep_start}; per level lnx[l], lgi0[l]
+void emul_plan_info(void* h, long* out, int* lnx, int* lgi0) {
+  Emul* E = (Emul*)h;
+  out[0] = E->plan.i0; out[1] = E->plan.i1; out[2] = (long)E->plan.id0; out[3] = (long)E->plan.n_local;
+  out[4] = (long)E->plan.levels.size(); out[5] = E->plan.rep_start;
+  for (size_t l = 0; l < E->plan.levels.size(); l++) { lnx[l] = E->plan.lnx[l]; lgi0[l] = E->plan.lgi0[l]; }
+}
+int emul_ld(void* h) { return ((Emul*)h)->lv[0].g.ld; }
+// `width` owned columns next to side 0 (left) / 1 (right) -> out[width * ld]
+void emul_halo_pack(void* h, int which, int side, int width, double* out) {
+  Emul* E = (Emul*)h;
+  const LevelGeom& g = E->lv[0].g;
+  const size_t first = side == 0 ? (size_t)HX * g.ld : (size_t)(HX + g.nx - width) * g.ld;
+  std::copy(E->f[which].begin() + first, E->f[which].begin() + first + (size_t)width * g.ld, out);
+}
+// in[width * ld] -> the halo columns on that side
+void emul_halo_unpack(void* h, int which, int side, int width, const double* in) {
+  Emul* E = (Emul*)h;
+  const LevelGeom& g = E->lv[0].g;
+  const size_t first = side == 0 ? (size_t)(HX - width) * g.ld : (size_t)(HX + g.nx) * g.ld;
+  std::copy(in, in + (size_t)width * g.ld, E->f[which].begin() + first);
+}
+// one colour of a red-black Gauss-Seidel sweep of L_phi on the slab, in place (halo columns are read, never written)
+void emul_phi_half_sweep(void* h, int colour) {
+  Emul* E = (Emul*)h;
+  const LevelGeom& g = E->lv[0].g;
+  std::vector<double>& x = E->f[NSGPU_PHI];
+  const std::vector<double>& b = E->f[NSGPU_RHS_PHI];
+  for (int i = 0; i < g.nx; i++)
+    for (int j = 0; j < g.ny; j++) {
+      if (((g.gi0 + i + j) & 1) != colour) continue;
+      const unsigned f = flags_any(*E, g, i, j);
+      if (f == F_OUTSIDE) continue;
+      const size_t id = cidx(g, i, j);
+      x[id] = E->plan.rect ? relax_cell<1>(g, f, i, j, x[id - g.ld], x[id + g.ld], x[id - 1], x[id + 1], x.data() + id, b[id], 0.0, -1.0)
+                           : relax_cell<1>(g, f, i, j, x[id - g.ld], x[id + g.ld], x[id - 1], x[id + 1], x.data() + id, b[id], 0.0, -1.0);
+    }
 }
 
 void emul_poisson_sweeps(void* h, int n, double* resid) {

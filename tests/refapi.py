@@ -149,6 +149,13 @@ def emul_lib():
         L = C.CDLL(EMUL_SO)
         L.emul_create.restype = C.c_void_p
         L.emul_create.argtypes = [C.POINTER(_Grid), C.c_double, C.c_double, C.c_int, C.c_int, C.c_int, C.c_char_p, C.c_int]
+        L.emul_create_rank.restype = C.c_void_p
+        L.emul_create_rank.argtypes = [C.POINTER(_Grid), C.c_double, C.c_double, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_char_p, C.c_int]
+        L.emul_plan_info.argtypes = [C.c_void_p, C.POINTER(C.c_long), _ip, _ip]
+        L.emul_ld.argtypes = [C.c_void_p]
+        L.emul_halo_pack.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, _dp]
+        L.emul_halo_unpack.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, _dp]
+        L.emul_phi_half_sweep.argtypes = [C.c_void_p, C.c_int]
         L.emul_destroy.argtypes = [C.c_void_p]
         L.emul_rect.argtypes = [C.c_void_p]
         L.emul_num_levels.argtypes = [C.c_void_p]
@@ -173,7 +180,7 @@ class Emul:
     """Host execution of the device functions (tests only)."""
 
     def __init__(self, hx, hy, edge_nx, edge_ny, edge_bc_type, edge_bc_info, dt, re, cell_id=None, cell_edges=None, n_cells=None,
-                 nu_pre=2, nu_post=2, max_levels=0):
+                 nu_pre=2, nu_post=2, max_levels=0, rank=0, world=1):
         L = emul_lib()
         self._keep = [np.ascontiguousarray(hx, dtype=np.float64), np.ascontiguousarray(hy, dtype=np.float64),
                       np.ascontiguousarray(edge_nx, dtype=np.int32), np.ascontiguousarray(edge_ny, dtype=np.int32),
@@ -193,13 +200,35 @@ class Emul:
         else:
             g.n_cells = g.nx * g.ny
         err = C.create_string_buffer(512)
-        self.h = L.emul_create(C.byref(g), dt, re, nu_pre, nu_post, max_levels, err, 512)
+        self.h = L.emul_create_rank(C.byref(g), dt, re, nu_pre, nu_post, max_levels, rank, world, err, 512)
         if not self.h:
             raise RuntimeError(err.value.decode())
         self.L = L
         self.n = L.emul_n_local(self.h)
         self.rect = bool(L.emul_rect(self.h))
         self.num_levels = L.emul_num_levels(self.h)
+
+    def plan_info(self):
+        """Slab plan of this rank: dict(i0, i1, id0, n_local, n_levels, rep_start, lnx, lgi0)."""
+        out = (C.c_long * 6)()
+        lnx, lgi0 = (C.c_int * 64)(), (C.c_int * 64)()
+        self.L.emul_plan_info(self.h, out, lnx, lgi0)
+        n = int(out[4])
+        return dict(i0=int(out[0]), i1=int(out[1]), id0=int(out[2]), n_local=int(out[3]), n_levels=n, rep_start=int(out[5]),
+                    lnx=[int(lnx[k]) for k in range(n)], lgi0=[int(lgi0[k]) for k in range(n)])
+
+    def halo_pack(self, which, side, width):
+        out = np.empty(width * self.L.emul_ld(self.h))
+        self.L.emul_halo_pack(self.h, which, side, width, out.ctypes.data_as(_dp))
+        return out
+
+    def halo_unpack(self, which, side, width, data):
+        data = np.ascontiguousarray(data, dtype=np.float64)
+        assert data.size == width * self.L.emul_ld(self.h)
+        self.L.emul_halo_unpack(self.h, which, side, width, data.ctypes.data_as(_dp))
+
+    def phi_half_sweep(self, colour):
+        self.L.emul_phi_half_sweep(self.h, colour)
 
     def level_shapes(self):
         out = []

@@ -120,3 +120,63 @@ def test_unimplemented_bc_types_are_refused():
     with pytest.raises(ns.NsGpuError) as e:
         ns.GpuFluidSolver(g, 0.01, 100.0)
     assert e.value.code == -2
+
+
+@pytest.mark.parametrize("n,sim", [(128, "cavity_re1000_128.sim"), (256, "cavity_re1000_256.sim")])
+def test_graph_solves_equal_direct_launches(n, sim, workdir):
+    """One CUDA graph per solve (device-side WHILE) against plain launches with a host read per cycle: same kernels,
+    same order -> identical fields and iteration counts."""
+    ref = refapi.RefSolver(f"{CASES}/cavity_{n}.grid", f"{CASES}/{sim}")
+    a = _gpu(ref, use_graph=0)
+    b = _gpu(ref, use_graph=-1)
+    ia, ib = a.step(4), b.step(4)
+    assert (ia.it_u, ia.it_v, ia.it_phi) == (ib.it_u, ib.it_v, ib.it_phi)
+    assert ia.status == 0 and ib.status == 0
+    for k in (U, V, PHI):
+        assert np.array_equal(a.get(k), b.get(k)), k
+    assert ia.kernel_launches == ib.kernel_launches
+
+
+def test_velocity_sor_and_multigrid_agree(workdir):
+    """u*, v* from red-black SOR (optimal factor) and from multigrid: two converged solvers of the same LHS_V systems."""
+    ref = refapi.RefSolver(f"{CASES}/cavity_128.grid", f"{CASES}/cavity_re1000_128.sim")
+    ref.set_rtol(1e-12)
+    ref.step(3)
+    for vs in (1, 2):
+        g = _gpu(ref, rtol_u=1e-10, rtol_phi=1e-10, vel_solver=vs)
+        info = g.step(3)
+        assert info.status == 0
+        for k in (U, V, PHI):
+            assert _rel(g.get(k), ref.get(k)) <= 2e-8, (vs, k)
+
+
+def test_large_rectangle_invariants(workdir):
+    """BASELINE size class (2048^2): properties that need no oracle -- mean(phi) = 0, the fused sweep reduces the
+    residual monotonically, min/max bounded by the lid speed, every solve converged."""
+    import navierstokessolver_b200 as ns
+    n = 2048
+    g = ns.GpuFluidSolver(ns.GridDesc.cavity(n), 0.25 / n, 1000.0)
+    info = g.step(3)
+    assert info.status == 0 and max(info.res_u, info.res_v, info.res_phi) <= 1e-8
+    assert -1.0 <= info.umin <= 0.0 < info.umax <= 1.0 + 1e-12
+    phi = g.get(PHI)
+    assert abs(phi.mean()) <= 1e-12 * np.abs(phi).max()
+    rng = np.random.default_rng(2)
+    b = rng.uniform(-1, 1, n * n)
+    b -= b.mean()
+    g.set(RHS_PHI, b)
+    g.set(PHI, np.zeros(n * n))
+    r = [g.poisson_sweeps(k)[0] for k in (1, 1, 2, 4)]
+    assert all(r[k + 1] < r[k] for k in range(3))
+
+
+def test_two_gpus_equal_one_gpu(workdir):
+    """x-slab decomposition over NCCL against the single-GPU run (needs 2 visible GPUs; tools/mgpu_check.py)."""
+    import subprocess
+    import sys
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    out = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr", "127.0.0.1",
+                          "--master-port", "29533", f"{refapi.ROOT}/tools/mgpu_check.py", "256", "128", "4"], capture_output=True, text=True, timeout=600)
+    assert out.returncode == 0, out.stdout[-2000:] + out.stderr[-2000:]
