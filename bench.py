@@ -173,6 +173,7 @@ def ours(args, rank, world, local_rank):
     wall = max_over_ranks(wall)
     value = cells_global * args.steps / (ms * 1e-3) / 1e9
     launches = int(info.kernel_launches)
+    phase_ms = s.phase_ms()
     fine_sweeps = float(info.fine_sweeps)
 
     # ---- the dominant kernel alone: fine-level red-black Poisson sweep (k_march<1,false,0>), CUDA events on its stream
@@ -235,6 +236,7 @@ def ours(args, rank, world, local_rank):
                 "residuals_last_step": {"u": info.res_u, "v": info.res_v, "phi": info.res_phi},
                 "fine_poisson_sweeps_per_step": fine_sweeps / args.steps,
                 "host_wall_ms_per_step": 1e3 * wall / args.steps,
+                "phase_ms_last_step": dict(zip(["rhs_build", "velocity_solves", "div_rhs", "phi_solve", "correct"], phase_ms)),
                 "gpu_launches": launches,
                 "clocks": clocks,
                 "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "steps": e2e_steps,

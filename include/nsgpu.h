@@ -129,6 +129,9 @@ int nsgpu_set_fields(nsgpu_ctx* ctx, const double* u, const double* v, const dou
 
 /* introspection for benchmarks and tests */
 int nsgpu_num_levels(const nsgpu_ctx* ctx);
+/* device milliseconds of the five phases of the last time step run by nsgpu_step: ConstructRHS_V, the two velocity
+ * solves, ConstructRHS_phi + mean removal, the phi solve, CorrectVelocities + min/max (FS.cpp:546-557) */
+int nsgpu_phase_ms(const nsgpu_ctx* ctx, float* out5);
 int64_t nsgpu_kernel_launches(const nsgpu_ctx* ctx);   /* total kernels launched by this ctx so far */
 int nsgpu_synchronize(nsgpu_ctx* ctx);
 

@@ -70,6 +70,7 @@ def _load():
     L.nsgpu_last_error.restype = C.c_char_p
     L.nsgpu_local_range.argtypes = [P, C.POINTER(C.c_int32), C.POINTER(C.c_int32), C.POINTER(C.c_int64), C.POINTER(C.c_int64)]
     L.nsgpu_step.argtypes = [P, C.c_int32, C.POINTER(StepInfo)]
+    L.nsgpu_phase_ms.argtypes = [P, C.POINTER(C.c_float)]
     L.nsgpu_rhs_build.argtypes = [P]
     L.nsgpu_solve_velocity.argtypes = [P, C.POINTER(StepInfo)]
     L.nsgpu_div_rhs.argtypes = [P, C.c_int32]
@@ -95,7 +96,7 @@ EXPORTED = ["nsgpu_nccl_unique_id", "nsgpu_create", "nsgpu_destroy", "nsgpu_last
             "nsgpu_step", "nsgpu_rhs_build", "nsgpu_solve_velocity", "nsgpu_div_rhs", "nsgpu_solve_phi",
             "nsgpu_correct", "nsgpu_poisson_sweeps", "nsgpu_apply_operator", "nsgpu_pressure", "nsgpu_get_array",
             "nsgpu_set_array", "nsgpu_get_fields", "nsgpu_set_fields", "nsgpu_num_levels", "nsgpu_kernel_launches",
-            "nsgpu_synchronize"]
+            "nsgpu_synchronize", "nsgpu_phase_ms"]
 
 
 def _dp(a):
@@ -242,6 +243,12 @@ class GpuFluidSolver:
     @property
     def kernel_launches(self):
         return lib.nsgpu_kernel_launches(self._h)
+
+    def phase_ms(self):
+        """device ms of (rhs build, velocity solves, div + mean, phi solve, correct + min/max) in the last step run"""
+        out = (C.c_float * 5)()
+        self._chk(lib.nsgpu_phase_ms(self._h, out))
+        return [float(x) for x in out]
 
     def synchronize(self):
         self._chk(lib.nsgpu_synchronize(self._h))

@@ -30,6 +30,7 @@ static int ensure_stage(nsgpu_ctx* ctx) {
 
 // host compact-id order -> padded device layout
 static int upload_field(nsgpu_ctx* ctx, double* dev, const double* host) {
+  ctx->halo_w.clear();
   const Level& L = ctx->levels[0];
   const LevelGeom& g = L.g;
   NS_CUDA(cudaSetDevice(ctx->device));
@@ -124,6 +125,11 @@ int nsgpu_local_range(const nsgpu_ctx* ctx, int32_t* i0, int32_t* i1, int64_t* i
   return 0;
 }
 
+int nsgpu_phase_ms(const nsgpu_ctx* ctx, float* out5) {
+  if (!ctx || !out5) return NSGPU_ERR_ARG;
+  for (int k = 0; k < 5; k++) out5[k] = ctx->phase_ms[k];
+  return 0;
+}
 int nsgpu_num_levels(const nsgpu_ctx* ctx) { return ctx ? (int)ctx->levels.size() : 0; }
 int64_t nsgpu_kernel_launches(const nsgpu_ctx* ctx) { return ctx ? ctx->launches : 0; }
 int nsgpu_synchronize(nsgpu_ctx* ctx) { if (!ctx) return NSGPU_ERR_ARG; cudaSetDevice(ctx->device); return sync_check(ctx); }
@@ -213,11 +219,18 @@ int nsgpu_step(nsgpu_ctx* ctx, int32_t n_steps, nsgpu_step_info* last) {
   int status = 0, rc;
   NS_CUDA(cudaEventRecord(ctx->ev0, ctx->stream));
   for (int s = 0; s < n_steps; s++) {
+    const bool last = s == n_steps - 1;   // the last step of the call carries the phase timers (events are free)
+    if (last) cudaEventRecord(ctx->evp[0], ctx->stream);
     if ((rc = phase_rhs(ctx))) return rc;
+    if (last) cudaEventRecord(ctx->evp[1], ctx->stream);
     if ((rc = phase_velocity(ctx, &ru, &rv))) return rc;
+    if (last) cudaEventRecord(ctx->evp[2], ctx->stream);
     if ((rc = phase_div(ctx, true))) return rc;
+    if (last) cudaEventRecord(ctx->evp[3], ctx->stream);
     if ((rc = phase_phi(ctx, &rp))) return rc;
-    if ((rc = phase_correct(ctx, (s == n_steps - 1) ? mm : nullptr))) return rc;
+    if (last) cudaEventRecord(ctx->evp[4], ctx->stream);
+    if ((rc = phase_correct(ctx, last ? mm : nullptr))) return rc;
+    if (last) cudaEventRecord(ctx->evp[5], ctx->stream);
     if (!((ru.pending || ru.converged) && (rv.pending || rv.converged) && (rp.pending || rp.converged))) status = NSGPU_ERR_NOT_CONVERGED;   // silent in the reference
   }
   NS_CUDA(cudaEventRecord(ctx->ev1, ctx->stream));
@@ -230,6 +243,12 @@ int nsgpu_step(nsgpu_ctx* ctx, int32_t n_steps, nsgpu_step_info* last) {
   }
   float ms = 0;
   NS_CUDA(cudaEventElapsedTime(&ms, ctx->ev0, ctx->ev1));
+  if (n_steps > 0) for (int k = 0; k < 5; k++) cudaEventElapsedTime(&ctx->phase_ms[k], ctx->evp[k], ctx->evp[k + 1]);
+  if (ctx->world > 1 && ctx->use_p2p) {
+    int flag = 0;
+    NS_CUDA(cudaMemcpy(&flag, ctx->d_errflag, sizeof(int), cudaMemcpyDeviceToHost));
+    if (flag) { ctx->err = "a marching pass timed out waiting for a neighbour's halo push"; return NSGPU_ERR_NCCL; }
+  }
   if (n_steps > 0 && !(std::isfinite(mm[0]) && std::isfinite(mm[1]) && std::isfinite(mm[2]) && std::isfinite(mm[3]))) status = NSGPU_ERR_NAN;
   if (last) {
     memset(last, 0, sizeof *last);
@@ -248,6 +267,7 @@ int nsgpu_poisson_sweeps(nsgpu_ctx* ctx, int32_t n_sweeps, double* residual_l2, 
   cudaSetDevice(ctx->device);
   const Level& L = ctx->levels[0];
   int rc;
+  ctx->halo_w.clear();
   if ((rc = halo_exchange(ctx, L, ctx->rhs_phi, 1))) return rc;
   NS_CUDA(cudaEventRecord(ctx->ev0, ctx->stream));
   if ((rc = smooth(ctx, L, coef_phi(), &ctx->phi, &ctx->tmp, ctx->rhs_phi, n_sweeps))) return rc;

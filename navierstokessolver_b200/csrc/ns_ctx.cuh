@@ -4,6 +4,7 @@
 #include <nccl.h>
 #include <string>
 #include <vector>
+#include <unordered_map>
 #include <cstdio>
 #include <cstring>
 #include <cmath>
@@ -54,6 +55,8 @@ struct nsgpu_ctx {
   int march = 1, march_ri = 0, march_pf = 6, march_wps = 24;   // NSGPU_MARCH=0 forces the generic tile kernel; NSGPU_RI overrides the chunk length
   cudaStream_t stream = nullptr;
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+  cudaEvent_t evp[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};   // phase boundaries of the last step of a call
+  float phase_ms[5] = {0, 0, 0, 0, 0};
   ncclComm_t comm = nullptr;
 
   // global description
@@ -84,6 +87,16 @@ struct nsgpu_ctx {
   nsgpu::SolveGraph sgraph[3];
   int graph_cycles_pending[3] = {0, 0, 0};
   bool capturing = false;
+  // several ranks: every buffer a marching pass writes lives in one arena, mapped by the two neighbours through CUDA IPC,
+  // so that the pass can store its boundary columns straight into their halo columns (ns_march.cuh)
+  char* arena = nullptr;                 // device allocation (owned)
+  size_t arena_bytes = 0, arena_used = 0;
+  char *peerL = nullptr, *peerR = nullptr;       // the neighbours' arenas in this process' address space
+  unsigned long long* arrivals = nullptr;        // [0] pushes arrived from the left neighbour, [1] from the right (in the arena)
+  int* d_errflag = nullptr;
+  unsigned long long sent_left = 0, sent_right = 0;   // CTA signals every rank has sent towards its left / right neighbour so far
+  int use_p2p = 1;
+  std::unordered_map<const double*, int> halo_w; // valid halo width of a buffer since its last write
   // coarse tail (ns_tail.cuh): levels >= tail_start run in one single-CTA kernel; 0 = no tail
   int tail_start = 0, use_tail = 1;
   double vel_rho = 0.0, vel_omega = 0.0;   // Jacobi radius bound of LHS_V; SOR factor (0: velocity solves use multigrid)

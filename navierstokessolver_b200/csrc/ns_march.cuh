@@ -97,11 +97,33 @@ struct MarchXfer {
   Reducer red;        // RES == 2
   double* out;
   SolveCtl* ctl;      // RES == 2: optional convergence epilogue
+  // Several ranks (x-slabs, one process per GPU): the CTAs of the first / last chunk also store the outermost `pushw`
+  // columns they produce straight into the neighbour's halo columns (peer memory over NVLink) and then bump the
+  // neighbour's arrival counter; before reading their own halo columns they wait until the neighbours' earlier
+  // pushes have arrived.  Offsets are in doubles: local cell -> the same cell seen from the neighbour's halo.
+  long long dL, dR;                          // xout  (0: no neighbour on that side / no push)
+  long long dbL, dbR;                        // coarse right-hand side (RES == 1)
+  int pushw, nxc;                            // columns pushed per side; coarse columns of this slab
+  unsigned long long *sigL, *sigR;           // neighbours' arrival counters (peer-mapped)
+  const unsigned long long *waitL, *waitR;   // this rank's arrival counters
+  unsigned long long needL, needR;           // pushes that must have arrived (from the left / right) before halo columns are read
+  int zone;                                  // chunks starting within `zone` columns of a slab end push, signal and wait
+  int* errflag;                              // set when a wait times out (instead of hanging the GPU)
 };
+
+__device__ __forceinline__ void wait_arrivals(const unsigned long long* p, unsigned long long need, int* err) {
+  const long long t0 = clock64();
+  for (;;) {
+    unsigned long long v;
+    asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+    if (v >= need) break;
+    if (clock64() - t0 > 6000000000LL) { *err = 1; break; }   // ~3 s: report, do not hang
+  }
+}
 
 // Per-thread state of the march: one ring of columns (PF prefetched ones ahead of the K being worked on) and
 // running pointers (one add per column instead of a 64-bit multiply per access).
-template <int NSW, bool PROLONG, int RES, int PF, bool SOR>
+template <int NSW, bool PROLONG, int RES, int PF, bool SOR, bool PUSH>
 struct Marcher {
   static constexpr int L = 2 * NSW;                 // half-sweep stages
   static constexpr int K = L + 2 + (RES ? 1 : 0);   // columns being worked on
@@ -114,8 +136,8 @@ struct Marcher {
   double* __restrict__ po;                          // column n - L of xout
   double* __restrict__ pbc;                         // RES == 1: next coarse column to emit
   const double* __restrict__ pxc;                   // PROLONG: coarse column base + row offset
-  int ld, ny, j0, ib, ie;
-  bool useful, jstore2, jstore1;
+  int ld, ny, j0, ib, ie, nxl;
+  bool useful, jstore2, jstore1, pushL, pushR;
   MarchXfer xf;
   double2 racc;
   double acc;
@@ -152,6 +174,14 @@ struct Marcher {
     if ((unsigned)(rs - ib) < (unsigned)(ie - ib)) {
       if (jstore2) *reinterpret_cast<double2*>(po) = X[PF + L];
       else if (jstore1) *po = X[PF + L].x;
+      if (PUSH && pushL && rs < xf.pushw) {                    // first columns of the slab -> left neighbour's right halo
+        if (jstore2) *reinterpret_cast<double2*>(po + xf.dL) = X[PF + L];
+        else if (jstore1) po[xf.dL] = X[PF + L].x;
+      }
+      if (PUSH && pushR && rs >= nxl - xf.pushw) {             // last columns -> right neighbour's left halo
+        if (jstore2) *reinterpret_cast<double2*>(po + xf.dR) = X[PF + L];
+        else if (jstore1) po[xf.dR] = X[PF + L].x;
+      }
     }
     po += ld;
     if (RES) {
@@ -170,11 +200,26 @@ struct Marcher {
             else { racc = res; emit = false; }
           }
           if (emit) {
+            const int I = xf.rcx == 2 ? (rr >> 1) : rr;   // coarse column of this slab
+            const bool pl = PUSH && pushL && xf.dbL != 0 && I < xf.pushw, pr = PUSH && pushR && xf.dbR != 0 && I >= xf.nxc - xf.pushw;
             if (xf.rcy == 2) {
-              if (useful && j0 < ny) *pbc = (t.x + t.y) * xf.rscale;
+              if (useful && j0 < ny) {
+                const double v = (t.x + t.y) * xf.rscale;
+                *pbc = v;
+                if (pl) pbc[xf.dbL] = v;
+                if (pr) pbc[xf.dbR] = v;
+              }
             } else {
-              if (jstore2) *reinterpret_cast<double2*>(pbc) = make_double2(t.x * xf.rscale, t.y * xf.rscale);
-              else if (jstore1) *pbc = t.x * xf.rscale;
+              const double2 v = make_double2(t.x * xf.rscale, t.y * xf.rscale);
+              if (jstore2) {
+                *reinterpret_cast<double2*>(pbc) = v;
+                if (pl) *reinterpret_cast<double2*>(pbc + xf.dbL) = v;
+                if (pr) *reinterpret_cast<double2*>(pbc + xf.dbR) = v;
+              } else if (jstore1) {
+                *pbc = v.x;
+                if (pl) pbc[xf.dbL] = v.x;
+                if (pr) pbc[xf.dbR] = v.x;
+              }
             }
             pbc += xf.ldbc;
           }
@@ -185,11 +230,11 @@ struct Marcher {
   }
 };
 
-template <int NSW, bool PROLONG, int RES, int PF, bool SOR = false>
+template <int NSW, bool PROLONG, int RES, int PF, bool SOR = false, bool PUSH = false>
 __global__ void __launch_bounds__(MARCH_THREADS)
 k_march(LevelGeom g, const double* __restrict__ mcx, const double* __restrict__ mcy, const double* __restrict__ xin,
         const double* __restrict__ b, double* __restrict__ xout, int RI, MarchXfer xf) {
-  using M = Marcher<NSW, PROLONG, RES, PF, SOR>;
+  using M = Marcher<NSW, PROLONG, RES, PF, SOR, PUSH>;
   constexpr int L = M::L;
   constexpr int HJ = march_halo(NSW, RES);   // halo cells per side of the strip
   constexpr int LL = march_lead(NSW, RES);   // halo columns per side of the chunk
@@ -209,14 +254,20 @@ k_march(LevelGeom g, const double* __restrict__ mcx, const double* __restrict__ 
     s_c[3 * q + 1] = mcx[3 * a + 1];
     s_c[3 * q + 2] = mcx[3 * a + 2];
   }
+  if (PUSH && xf.zone && threadIdx.x == 0) {   // halo columns of this chunk come from a neighbour's push
+    if (ib < xf.zone && xf.waitL && xf.needL) wait_arrivals(xf.waitL, xf.needL, xf.errflag);
+    if (ie > g.nx - xf.zone && xf.waitR && xf.needR) wait_arrivals(xf.waitR, xf.needR, xf.errflag);
+  }
   __syncthreads();
 
   // warps past the last strip run with every predicate false (no divergent exit: the shuffles stay convergent)
   M m;
   m.xf = xf;
-  m.ld = g.ld; m.ny = g.ny; m.ib = ib; m.ie = ie;
+  m.ld = g.ld; m.ny = g.ny; m.ib = ib; m.ie = ie; m.nxl = g.nx;
+  m.pushL = PUSH && xf.dL != 0 && ib < xf.zone;
+  m.pushR = PUSH && xf.dR != 0 && ie > g.nx - xf.zone;
   m.j0 = wj * UJ - HJ + 2 * lane;                            // even, >= -HJ >= -PJ
-  const int jl = min(m.j0, g.ny + PJ - 2);                   // lanes past the column end: its last (zero) pair
+  const int jl = min(m.j0, (g.ny + PJ - 2) & ~1);            // lanes past the column end: an even (16-byte aligned) zero pair
   {
     const int a = jl + PJ;                                   // entries outside the domain have cs = cn = 0
     m.k.csa = mcy[3 * a]; m.k.cna = mcy[3 * a + 1]; m.k.dya = mcy[3 * a + 2];
@@ -245,6 +296,15 @@ k_march(LevelGeom g, const double* __restrict__ mcx, const double* __restrict__ 
   for (int n = n0; n < nend; n += 2) {
     m.template step<true>(n);
     m.template step<false>(n + 1);
+  }
+  if (PUSH && (xf.sigL || xf.sigR)) {   // pushed columns are visible system-wide before the neighbour is told
+    __threadfence_system();
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      __threadfence_system();
+      if (ib < xf.zone && xf.sigL) atomicAdd_system(xf.sigL, 1ull);
+      if (ie > g.nx - xf.zone && xf.sigR) atomicAdd_system(xf.sigR, 1ull);
+    }
   }
   if (RES == 2) {
     double acc[1] = {m.acc};

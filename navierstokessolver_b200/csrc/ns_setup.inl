@@ -38,6 +38,12 @@ static int dev_upload(nsgpu_ctx* ctx, std::vector<void*>& owned, const std::vect
 }
 
 static int dev_zeros(nsgpu_ctx* ctx, std::vector<void*>& owned, size_t n_doubles, double** out) {
+  const size_t bytes = (n_doubles * sizeof(double) + 255) & ~(size_t)255;
+  if (ctx->arena && ctx->arena_used + bytes <= ctx->arena_bytes) {   // peer-visible arena (already zeroed)
+    *out = (double*)(ctx->arena + ctx->arena_used);
+    ctx->arena_used += bytes;
+    return 0;
+  }
   void* p = nullptr;
   NS_CUDA(cudaMalloc(&p, n_doubles * sizeof(double)));
   owned.push_back(p);
@@ -95,7 +101,10 @@ static void destroy_ctx(nsgpu_ctx* ctx) {
   if (!ctx) return;
   cudaSetDevice(ctx->device);
   if (ctx->stream) cudaStreamSynchronize(ctx->stream);
+  if (ctx->peerL) cudaIpcCloseMemHandle(ctx->peerL);
+  if (ctx->peerR) cudaIpcCloseMemHandle(ctx->peerR);
   if (ctx->comm) ncclCommDestroy(ctx->comm);
+  if (ctx->arena) cudaFree(ctx->arena);
   for (auto& L : ctx->levels)
     for (void* p : L.owned) cudaFree(p);
   for (void* p : ctx->owned) cudaFree(p);
@@ -105,6 +114,7 @@ static void destroy_ctx(nsgpu_ctx* ctx) {
   if (ctx->h_stage) cudaFreeHost(ctx->h_stage);
   if (ctx->ev0) cudaEventDestroy(ctx->ev0);
   if (ctx->ev1) cudaEventDestroy(ctx->ev1);
+  for (auto& e : ctx->evp) if (e) cudaEventDestroy(e);
   if (ctx->stream) cudaStreamDestroy(ctx->stream);
   delete ctx;
 }
@@ -145,12 +155,62 @@ static int create_impl(nsgpu_ctx* ctx, const nsgpu_grid* G, const nsgpu_params* 
   NS_CUDA(cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking));
   NS_CUDA(cudaEventCreate(&ctx->ev0));
   NS_CUDA(cudaEventCreate(&ctx->ev1));
+  for (auto& e : ctx->evp) NS_CUDA(cudaEventCreate(&e));
   if (ctx->world > 1) {
     if (!P->nccl_id) { ctx->err = "world > 1 needs params.nccl_id"; return NSGPU_ERR_ARG; }
     ncclUniqueId id;
     memcpy(&id, P->nccl_id, sizeof id);
     NS_NCCL(ncclCommInitRank(&ctx->comm, ctx->world, id, ctx->rank));
   }
+
+  // ---- several ranks: one arena for everything the marching passes write, opened by both neighbours (CUDA IPC)
+  if (const char* e = getenv("NSGPU_P2P")) ctx->use_p2p = atoi(e);
+  if (ctx->world > 1 && ctx->use_p2p && plan.rect) {
+    size_t doubles = 0;
+    for (size_t l = 0; l < plan.levels.size(); l++) {
+      const size_t ld = ((plan.levels[l].ny + 3) / 4) * 4 + 2 * PJ;
+      const size_t stride = (size_t)(plan.lnx[l] + 2 * HX + SLACK_COLS) * ld + 32;
+      doubles += (l == 0 ? 13 + (ctx->solver == 1 ? 8 : 0) : 3) * stride;
+    }
+    ctx->arena_bytes = doubles * sizeof(double) + (1 << 20);
+    NS_CUDA(cudaMalloc((void**)&ctx->arena, ctx->arena_bytes));
+    NS_CUDA(cudaMemset(ctx->arena, 0, ctx->arena_bytes));
+    ctx->arrivals = (unsigned long long*)ctx->arena;    // first 256 bytes: arrival counters
+    ctx->arena_used = 256;
+    // exchange the IPC handles through the communicator that exists anyway
+    cudaIpcMemHandle_t mine;
+    NS_CUDA(cudaIpcGetMemHandle(&mine, ctx->arena));
+    static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle size");
+    char* d_h = nullptr;
+    NS_CUDA(cudaMalloc((void**)&d_h, 64 * (size_t)ctx->world));
+    NS_CUDA(cudaMemcpy(d_h + 64 * (size_t)ctx->rank, &mine, 64, cudaMemcpyHostToDevice));
+    NS_NCCL(ncclAllGather(d_h + 64 * (size_t)ctx->rank, d_h, 64, ncclChar, ctx->comm, ctx->stream));
+    NS_CUDA(cudaStreamSynchronize(ctx->stream));
+    std::vector<cudaIpcMemHandle_t> all(ctx->world);
+    NS_CUDA(cudaMemcpy(all.data(), d_h, 64 * (size_t)ctx->world, cudaMemcpyDeviceToHost));
+    cudaFree(d_h);
+    bool ok = true;
+    if (ctx->rank > 0 && cudaIpcOpenMemHandle((void**)&ctx->peerL, all[ctx->rank - 1], cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) ok = false;
+    if (ctx->rank < ctx->world - 1 && cudaIpcOpenMemHandle((void**)&ctx->peerR, all[ctx->rank + 1], cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) ok = false;
+    // every rank must agree, or the halo protocols would differ: all-reduce the outcome
+    int* d_ok = nullptr;
+    NS_CUDA(cudaMalloc((void**)&d_ok, sizeof(int)));
+    const int okv = ok ? 1 : 0;
+    NS_CUDA(cudaMemcpy(d_ok, &okv, sizeof(int), cudaMemcpyHostToDevice));
+    NS_NCCL(ncclAllReduce(d_ok, d_ok, 1, ncclInt, ncclMin, ctx->comm, ctx->stream));
+    NS_CUDA(cudaStreamSynchronize(ctx->stream));
+    int all_ok = 0;
+    NS_CUDA(cudaMemcpy(&all_ok, d_ok, sizeof(int), cudaMemcpyDeviceToHost));
+    cudaFree(d_ok);
+    cudaGetLastError();
+    if (!all_ok) {
+      fprintf(stderr, "nsgpu: CUDA IPC mapping of the neighbour slabs failed; halo columns go through NCCL\n");
+      if (ctx->peerL) cudaIpcCloseMemHandle(ctx->peerL);
+      if (ctx->peerR) cudaIpcCloseMemHandle(ctx->peerR);
+      ctx->peerL = ctx->peerR = nullptr;
+      ctx->use_p2p = 0;
+    }
+  } else ctx->use_p2p = 0;
 
   // ---- level hierarchy
   ctx->levels.resize(plan.levels.size());
@@ -231,6 +291,7 @@ static int create_impl(nsgpu_ctx* ctx, const nsgpu_grid* G, const nsgpu_params* 
   { int rc = dev_zeros(ctx, ctx->owned, (size_t)4 * RED_MAX_BLOCKS, &ctx->red.partials); if (rc) return rc; }
   { double* c; int rc = dev_zeros(ctx, ctx->owned, 2, &c); if (rc) return rc; ctx->red.counter = (unsigned*)c; }
   { int rc = dev_zeros(ctx, ctx->owned, 64, &ctx->d_scal); if (rc) return rc; }
+  ctx->d_errflag = (int*)(ctx->d_scal + 48);
   NS_CUDA(cudaMallocHost((void**)&ctx->h_scal, 64 * sizeof(double)));
   { void* p = nullptr; NS_CUDA(cudaMalloc(&p, 3 * sizeof(SolveCtl))); ctx->owned.push_back(p); NS_CUDA(cudaMemset(p, 0, 3 * sizeof(SolveCtl))); ctx->d_ctl = (SolveCtl*)p; }
   NS_CUDA(cudaMallocHost((void**)&ctx->h_ctl, 3 * sizeof(SolveCtl)));

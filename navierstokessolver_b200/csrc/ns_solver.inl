@@ -35,9 +35,15 @@ static inline dim3 grid_cols(const LevelGeom& g, int threads, int max_blocks = 1
 }
 
 // One-column-block halo exchange with the x-neighbours: `width` columns, contiguous (width * ld doubles).
-static int halo_exchange(nsgpu_ctx* ctx, const Level& L, double* f, int width) {
+// march_consumer: the reader is a marching pass, which waits for the neighbours' pushes itself -- if the buffer's halo
+// was filled by a pushing pass (ctx->halo_w) there is nothing to send.
+static int halo_exchange(nsgpu_ctx* ctx, const Level& L, double* f, int width, bool march_consumer = false) {
   if (ctx->world == 1 || L.replicated) return 0;
   width = std::min(width, std::min(HX, L.g.nx));
+  if (march_consumer) {
+    auto it = ctx->halo_w.find(f);
+    if (it != ctx->halo_w.end() && it->second >= width) return 0;
+  }
   const size_t n = (size_t)width * L.g.ld;
   const int nx = L.g.nx;
   NS_NCCL(ncclGroupStart());
@@ -109,8 +115,8 @@ static int march_pass(nsgpu_ctx* ctx, const Level& L, OpCoef c, int nsw, double*
   const int res = Cr ? 1 : (norm_out ? 2 : 0);
   const int lead = march_lead(nsw, res);
   int rc;
-  if (xin && (rc = halo_exchange(ctx, L, xin, lead))) return rc;
-  if (Cp && (rc = halo_exchange(ctx, *Cp, xc, (lead + 1) / 2 + 1))) return rc;
+  if (xin && (rc = halo_exchange(ctx, L, xin, lead, true))) return rc;
+  if (Cp && (rc = halo_exchange(ctx, *Cp, xc, (lead + 1) / 2 + 1, true))) return rc;
   MarchXfer xf{};
   // a replicated coarse level holds the whole domain: this rank's part starts at its global coarse column
   const size_t rep_off_p = (Cp && Cp->replicated && !L.replicated) ? (size_t)(L.g.gi0 / L.cx) * Cp->g.ld : 0;
@@ -120,18 +126,23 @@ static int march_pass(nsgpu_ctx* ctx, const Level& L, OpCoef c, int nsw, double*
   if (res == 2) { xf.red = ctx->red; xf.out = norm_out; xf.ctl = ctl; }
   xf.omega = omega;
   const int uj = march_uj(nsw, res);
+  // several ranks: push the boundary columns into the neighbours' halos from inside the pass (peer memory over NVLink)
+  const bool push = ctx->world > 1 && ctx->use_p2p && ctx->arena && !L.replicated && (ctx->peerL || ctx->peerR);
+  const bool push_b = push && Cr && !Cr->replicated;
   MarchKernel kern = nullptr;
-#define NS_MARCH(NSW, PRO, RES, PF) kern = k_march<NSW, PRO, RES, PF>
+#define NS_MARCH(NSW, PRO, RES, PF) do { if (push) kern = k_march<NSW, PRO, RES, PF, false, true>; else kern = k_march<NSW, PRO, RES, PF, false, false>; } while (0)
 #define NS_MARCH_RES(NSW, PRO) do { if (res == 0) NS_MARCH(NSW, PRO, 0, MARCH_PF); else if (res == 1) NS_MARCH(NSW, PRO, 1, MARCH_PF); else NS_MARCH(NSW, PRO, 2, MARCH_PF); } while (0)
   if (omega > 0.0) {                   // red-black SOR double sweep (velocity solves)
     if (nsw != 2 || Cp || res == 1) { ctx->err = "SOR passes are double sweeps without transfers"; return NSGPU_ERR_ARG; }
-    if (res == 0) kern = k_march<2, false, 0, MARCH_PF, true>; else kern = k_march<2, false, 2, MARCH_PF, true>;
+    if (res == 0) kern = push ? k_march<2, false, 0, MARCH_PF, true, true> : k_march<2, false, 0, MARCH_PF, true, false>;
+    else kern = push ? k_march<2, false, 2, MARCH_PF, true, true> : k_march<2, false, 2, MARCH_PF, true, false>;
   } else if (nsw == 1 && !Cp && res == 0) {   // the plain sweep has its own prefetch depth
-    switch (ctx->march_pf) {
-      case 2: NS_MARCH(1, false, 0, 2); break;
-      case 3: NS_MARCH(1, false, 0, 3); break;
-      case 4: NS_MARCH(1, false, 0, 4); break;
-      default: NS_MARCH(1, false, 0, 6); break;
+    if (push) kern = k_march<1, false, 0, 6, false, true>;
+    else switch (ctx->march_pf) {
+      case 2: kern = k_march<1, false, 0, 2, false, false>; break;
+      case 3: kern = k_march<1, false, 0, 3, false, false>; break;
+      case 4: kern = k_march<1, false, 0, 4, false, false>; break;
+      default: kern = k_march<1, false, 0, 6, false, false>; break;
     }
   } else if (nsw == 1) { if (Cp) NS_MARCH_RES(1, true); else NS_MARCH_RES(1, false); }
   else { if (Cp) NS_MARCH_RES(2, true); else NS_MARCH_RES(2, false); }
@@ -140,13 +151,45 @@ static int march_pass(nsgpu_ctx* ctx, const Level& L, OpCoef c, int nsw, double*
   const int ri = march_chunk(ctx, L, uj, 2 * lead + 2 * nsw + 2, march_wave(kern));
   const dim3 grid(((L.g.ny + uj - 1) / uj + MARCH_WARPS - 1) / MARCH_WARPS, (L.g.nx + ri - 1) / ri);
   const size_t sh = (size_t)3 * (ri + 2 * lead + 2 * nsw + 8) * sizeof(double);   // >= nrows of k_march
+  if (push) {
+    const long long offL = ctx->peerL ? (long long)((ctx->peerL - ctx->arena) / (ptrdiff_t)sizeof(double)) : 0;
+    const long long offR = ctx->peerR ? (long long)((ctx->peerR - ctx->arena) / (ptrdiff_t)sizeof(double)) : 0;
+    xf.pushw = std::min(HX - 1, L.g.nx);
+    xf.dL = ctx->peerL ? offL + (long long)L.g.nx * L.g.ld : 0;
+    xf.dR = ctx->peerR ? offR - (long long)L.g.nx * L.g.ld : 0;
+    if (push_b) {
+      xf.nxc = Cr->g.nx;
+      xf.dbL = ctx->peerL ? offL + (long long)Cr->g.nx * Cr->g.ld : 0;
+      xf.dbR = ctx->peerR ? offR - (long long)Cr->g.nx * Cr->g.ld : 0;
+    }
+    xf.sigL = ctx->peerL ? (unsigned long long*)ctx->peerL + 1 : nullptr;   // the left neighbour's "arrived from the right"
+    xf.sigR = ctx->peerR ? (unsigned long long*)ctx->peerR + 0 : nullptr;   // the right neighbour's "arrived from the left"
+    xf.waitL = ctx->peerL ? ctx->arrivals + 0 : nullptr;
+    xf.waitR = ctx->peerR ? ctx->arrivals + 1 : nullptr;
+    // what arrives from the left neighbour is what every rank sends rightwards, and vice versa
+    xf.needL = ctx->sent_right;
+    xf.needR = ctx->sent_left;
+    xf.zone = xf.pushw * (push_b ? L.cx : 1);
+    xf.errflag = ctx->d_errflag;
+  }
   kern<<<grid, MARCH_THREADS, sh, ctx->stream>>>(L.g, L.mcx[c.op], L.mcy[c.op], xin, b, xout, ri, xf);
+  if (push) {
+    // chunks that start inside the left zone / end inside the right zone signal once per CTA
+    const int gy = (int)grid.y, zone = std::min(xf.zone, L.g.nx);
+    ctx->sent_left += (unsigned long long)grid.x * ((zone + ri - 1) / ri);
+    ctx->sent_right += (unsigned long long)grid.x * (gy - (L.g.nx - zone) / ri);
+    ctx->halo_w[xout] = xf.pushw;
+    if (push_b) ctx->halo_w[Cr->b] = xf.pushw;
+  } else {
+    ctx->halo_w.erase(xout);
+    if (Cr) ctx->halo_w.erase(Cr->b);
+  }
   NS_LAUNCH_CHECK();
   if (Cr && Cr->replicated && !L.replicated && ctx->world > 1) {
     // every rank contributes its slab of the coarse right-hand side; in place: the slabs are contiguous column ranges
     const size_t count = (size_t)(L.g.nx / L.cx) * Cr->g.ld;
     NS_NCCL(ncclAllGather(Cr->b + (size_t)HX * Cr->g.ld + rep_off_r, Cr->b + (size_t)HX * Cr->g.ld, count, ncclDouble, ctx->comm, ctx->stream));
-  } else if (Cr && (rc = halo_exchange(ctx, *Cr, Cr->b, HX - 1))) return rc;
+  } else if (Cr && (rc = halo_exchange(ctx, *Cr, Cr->b, HX - 1, true))) return rc;
   return 0;
 }
 
@@ -206,6 +249,7 @@ static int smooth(nsgpu_ctx* ctx, const Level& L, OpCoef c, double** x, double**
     }
     int rc = halo_exchange(ctx, L, *x, 2);
     if (rc) return rc;
+    ctx->halo_w.clear();
 #define CALL(OP, RECT) k_smooth_rb<OP, RECT, false><<<grid, SM_THREADS, 0, ctx->stream>>>(L.g, *x, b, *xt, c.alpha, c.beta)
     NS_DISPATCH_OP_RECT(c.op, ctx->rect, CALL);
 #undef CALL
@@ -464,6 +508,7 @@ static int solve_head(nsgpu_ctx* ctx, int slot, OpCoef c, double* x, const doubl
 
 static int solve_tail(nsgpu_ctx* ctx, int slot, double* x) {
   const Level& L = ctx->levels[0];
+  ctx->halo_w.erase(x);
   k_zero_if<<<148 * 4, 256, 0, ctx->stream>>>(L.stride, x, ctx->d_ctl + slot);
   NS_LAUNCH_CHECK();
   cudaError_t e = cudaMemcpyAsync(ctx->h_ctl + slot, ctx->d_ctl + slot, sizeof(SolveCtl), cudaMemcpyDeviceToHost, ctx->stream);
@@ -613,6 +658,7 @@ static void finish_results(nsgpu_ctx* ctx, SolveResult* ru, SolveResult* rv, Sol
 // Phases of one time step
 
 static int phase_rhs(nsgpu_ctx* ctx) {   // ConstructRHS_V, FS.cpp:546
+  ctx->halo_w.clear();   // every field may have been rewritten by a non-marching kernel since
   const Level& L = ctx->levels[0];
   int rc;
   if ((rc = halo_exchange(ctx, L, ctx->u, 2))) return rc;
@@ -628,6 +674,7 @@ static int phase_rhs(nsgpu_ctx* ctx) {   // ConstructRHS_V, FS.cpp:546
 }
 
 static int phase_velocity(nsgpu_ctx* ctx, SolveResult* ru, SolveResult* rv) {   // FS.cpp:547-548
+  ctx->halo_w.clear();   // every field may have been rewritten by a non-marching kernel since
   const Level& L = ctx->levels[0];
   // initial guess u^n (the reference starts from zero; the converged u* is the same to tolerance)
   cudaMemcpyAsync(ctx->ustar, ctx->u, L.stride * sizeof(double), cudaMemcpyDeviceToDevice, ctx->stream);
@@ -641,6 +688,7 @@ static int phase_velocity(nsgpu_ctx* ctx, SolveResult* ru, SolveResult* rv) {   
 }
 
 static int phase_div(nsgpu_ctx* ctx, bool remove_mean) {   // FS.cpp:549-550
+  ctx->halo_w.clear();   // every field may have been rewritten by a non-marching kernel since
   const Level& L = ctx->levels[0];
   int rc;
   if ((rc = halo_exchange(ctx, L, ctx->ustar, 1))) return rc;
@@ -663,6 +711,7 @@ static int phase_div(nsgpu_ctx* ctx, bool remove_mean) {   // FS.cpp:549-550
 }
 
 static int phase_phi(nsgpu_ctx* ctx, SolveResult* rp) {   // FS.cpp:551, warm start from phi^n (FS.cpp:54)
+  ctx->halo_w.clear();   // every field may have been rewritten by a non-marching kernel since
   const Level& L = ctx->levels[0];
   int rc;
   if ((rc = halo_exchange(ctx, L, ctx->rhs_phi, HX - 1))) return rc;
@@ -674,6 +723,7 @@ static int phase_phi(nsgpu_ctx* ctx, SolveResult* rp) {   // FS.cpp:551, warm st
   {
     const size_t n = (size_t)L.g.nx * L.g.ld;
     const int blocks = (int)std::min<size_t>((n + 255) / 256, 148 * 8);
+    ctx->halo_w.clear();
     k_sum<<<blocks, 256, 0, ctx->stream>>>(n, ctx->phi + (size_t)HX * L.g.ld, ctx->red, ctx->d_scal + 17);
     NS_LAUNCH_CHECK();
     if ((rc = allreduce(ctx, ctx->d_scal + 17, 1, ncclSum))) return rc;
@@ -688,6 +738,7 @@ static int phase_phi(nsgpu_ctx* ctx, SolveResult* rp) {   // FS.cpp:551, warm st
 }
 
 static int phase_correct(nsgpu_ctx* ctx, double mm[4]) {   // FS.cpp:552-557
+  ctx->halo_w.clear();   // every field may have been rewritten by a non-marching kernel since
   const Level& L = ctx->levels[0];
   int rc;
   if ((rc = halo_exchange(ctx, L, ctx->phi, 2))) return rc;

@@ -71,6 +71,19 @@ def test_solver_free_phases(grid, sim, workdir):
     assert (info.umin, info.umax, info.vmin, info.vmax) == (u.min(), u.max(), v.min(), v.max())
 
 
+def test_whole_steps_odd_sizes_against_emulation(workdir):
+    """130 x 65-type levels (odd row counts, semi-coarsening): fused V-cycle against the host emulation of the same solver."""
+    import navierstokessolver_b200 as ns
+    g = ns.GridDesc.cavity(130, nx=96)
+    gpu = ns.GpuFluidSolver(g, 0.002, 100.0, rtol_u=1e-11, rtol_phi=1e-11)
+    em = refapi.Emul(g.hx, g.hy, g.edge_nx, g.edge_ny, g.edge_bc_type, g.edge_bc_info, 0.002, 100.0)
+    info = gpu.step(3)
+    em.step(3, rtol=1e-12)
+    assert info.status == 0
+    for k in (U, V, PHI):
+        assert _rel(gpu.get(k), em.get(k)) <= 2e-8, k
+
+
 @pytest.mark.parametrize("n,sim,solver", [(64, "cavity_re100.sim", 0), (64, "cavity_re100.sim", 1), (128, "cavity_re1000_128.sim", 0)])
 def test_whole_steps_cavity(n, sim, solver, workdir):
     ref = refapi.RefSolver(f"{CASES}/cavity_{n}.grid", f"{CASES}/{sim}")
@@ -85,12 +98,12 @@ def test_whole_steps_cavity(n, sim, solver, workdir):
         assert np.allclose([info.umin, info.umax, info.vmin, info.vmax], mm, rtol=0, atol=1e-8)
 
 
-def test_fused_sweep_equals_emulated_red_black(workdir):
-    """k_smooth_rb (tile + halo, one HBM pass) against the plain two-colour loops of tests/emul."""
-    n = 200   # not a multiple of the tile
+@pytest.mark.parametrize("n,nx", [(200, 72), (130, 96), (65, 33)])
+def test_fused_sweep_equals_emulated_red_black(n, nx, workdir):
+    """The marching sweep (one HBM pass) against the plain two-colour loops of tests/emul; ragged and odd sizes."""
     rng = np.random.default_rng(3)
     import navierstokessolver_b200 as ns
-    g = ns.GridDesc.cavity(n, nx=72)
+    g = ns.GridDesc.cavity(n, nx=nx)
     gpu = ns.GpuFluidSolver(g, 0.01, 100.0)
     em = refapi.Emul(g.hx, g.hy, g.edge_nx, g.edge_ny, g.edge_bc_type, g.edge_bc_info, 0.01, 100.0)
     b = rng.uniform(-1, 1, g.n_cells)
