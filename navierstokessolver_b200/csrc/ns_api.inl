@@ -112,7 +112,16 @@ int nsgpu_create(const nsgpu_grid* grid, const nsgpu_params* params, nsgpu_ctx**
   return 0;
 }
 
-void nsgpu_destroy(nsgpu_ctx* ctx) { destroy_ctx(ctx); }
+void nsgpu_destroy(nsgpu_ctx* ctx) {
+  if (ctx && ctx->trace && !ctx->trace_acc.empty()) {
+    std::vector<std::pair<int, std::pair<double, long>>> rows(ctx->trace_acc.begin(), ctx->trace_acc.end());
+    std::sort(rows.begin(), rows.end(), [](const auto& a, const auto& b) { return a.first < b.first; });
+    for (auto& r : rows)
+      fprintf(stderr, "nsgpu trace rank %d key %6d  n %6ld  avg %9.2f us  total %9.3f ms\n", ctx->rank, r.first, r.second.second,
+              1e3 * r.second.first / (double)r.second.second, r.second.first);
+  }
+  destroy_ctx(ctx);
+}
 
 const char* nsgpu_last_error(const nsgpu_ctx* ctx) { return ctx ? ctx->err.c_str() : g_create_error.c_str(); }
 
@@ -235,6 +244,7 @@ int nsgpu_step(nsgpu_ctx* ctx, int32_t n_steps, nsgpu_step_info* last) {
   }
   NS_CUDA(cudaEventRecord(ctx->ev1, ctx->stream));
   if ((rc = sync_check(ctx))) return rc;
+  trace_collect(ctx);
   if (n_steps > 0) {
     const bool pend[3] = {ru.pending, rv.pending, rp.pending};
     finish_results(ctx, &ru, &rv, &rp);

@@ -86,15 +86,22 @@ struct nsgpu_ctx {
   int seen_cycles[3] = {0, 0, 0}, seen_fails[3] = {0, 0, 0};
   nsgpu::SolveGraph sgraph[3];
   int graph_cycles_pending[3] = {0, 0, 0};
-  bool capturing = false;
   // several ranks: every buffer a marching pass writes lives in one arena, mapped by the two neighbours through CUDA IPC,
   // so that the pass can store its boundary columns straight into their halo columns (ns_march.cuh)
   char* arena = nullptr;                 // device allocation (owned)
   size_t arena_bytes = 0, arena_used = 0;
-  char *peerL = nullptr, *peerR = nullptr;       // the neighbours' arenas in this process' address space
-  unsigned long long* arrivals = nullptr;        // [0] pushes arrived from the left neighbour, [1] from the right (in the arena)
+  char* peers[nsgpu::MAX_RANKS] = {};                   // every other rank's arena in this process' address space (CUDA IPC)
+  char *peerL = nullptr, *peerR = nullptr;       // the neighbours' (aliases into peers[])
+  nsgpu::PeerTable* d_pt = nullptr;                     // device copy of the peer map (nullptr: one rank, or NCCL-only exchange)
+  bool capturing = false, capture_nccl = false;  // a solve graph is being captured / an NCCL call was issued meanwhile
+  // NSGPU_TRACE=1 (direct launches): CUDA events around every marching pass / coarse tail, table on stderr at destroy
+  struct TraceEv { cudaEvent_t a, b; int key; };
+  int trace = 0;
+  std::vector<TraceEv> trace_ev;
+  std::unordered_map<int, std::pair<double, long>> trace_acc;
+  int march_rb = 12;                             // width of the short boundary chunks of pushing passes (NSGPU_RB, 0 = off)
+  unsigned last_gather_ctas = 0;                 // CTAs of the last restriction pass that gathered onto the replicated level
   int* d_errflag = nullptr;
-  unsigned long long sent_left = 0, sent_right = 0;   // CTA signals every rank has sent towards its left / right neighbour so far
   int use_p2p = 1;
   std::unordered_map<const double*, int> halo_w; // valid halo width of a buffer since its last write
   // coarse tail (ns_tail.cuh): levels >= tail_start run in one single-CTA kernel; 0 = no tail

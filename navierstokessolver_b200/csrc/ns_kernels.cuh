@@ -104,11 +104,73 @@ struct SolveCtl {
   unsigned long long handle;   // cudaGraphConditionalHandle of the WHILE node (0: none)
 };
 
+// ---------------------------------------------------------------------------------------------------------
+// Several ranks (one process per GPU): every rank's arena is mapped into every other rank's address space (CUDA IPC).
+// The first words of an arena are its control header; off[r] is the distance, in 8-byte words, from this rank's
+// arena to rank r's, so `local_pointer + off[r]` is the same object on rank r.
+constexpr int MAX_RANKS = 8;
+enum : int { HDR_ARR_L = 0, HDR_ARR_R = 1, HDR_TAIL_ARR = 2, HDR_SENT_L = 3, HDR_SENT_R = 4, HDR_TICKET = 5, HDR_TAIL_NEED = 6,
+             HDR_XSEQ = 7, HDR_XSLOTS = 16, HDR_WORDS = 512 };
+struct PeerTable {
+  int world, rank;
+  long long off[MAX_RANKS];
+  unsigned long long* hdr;   // this rank's header
+  int* err;                  // set when a wait times out (instead of hanging the GPU)
+};
+
+__device__ __forceinline__ unsigned long long ld_acquire_sys(const unsigned long long* p) {
+  unsigned long long v;
+  asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+  return v;
+}
+// spin until *p >= need (exact == false) or *p == need (exact == true); gives up after ~3 s and raises the error flag
+__device__ __forceinline__ void wait_word(const unsigned long long* p, unsigned long long need, bool exact, int* err) {
+  const long long t0 = clock64();
+  for (;;) {
+    const unsigned long long v = ld_acquire_sys(p);
+    if (exact ? v == need : v >= need) break;
+    if (clock64() - t0 > 6000000000LL) { *err = 1; break; }
+  }
+}
+
+// Sum of one double over all ranks, called by ONE thread per rank; every rank adds the contributions in rank order,
+// so all ranks get the same bits.  Four slot buffers: a rank can be at most one reduction ahead of the slowest one.
+__device__ inline double xreduce_sum(const PeerTable* pt, double mine) {
+  unsigned long long* hdr = pt->hdr;
+  const unsigned long long s = hdr[HDR_XSEQ] + 1;
+  hdr[HDR_XSEQ] = s;
+  const int buf = (int)(s & 3);
+  unsigned long long* my_slot = hdr + HDR_XSLOTS + 2 * (buf * MAX_RANKS + pt->rank);
+  for (int r = 0; r < pt->world; r++) reinterpret_cast<double*>(my_slot + pt->off[r])[0] = mine;
+  __threadfence_system();
+  for (int r = 0; r < pt->world; r++) {
+    unsigned long long* q = my_slot + pt->off[r] + 1;
+    asm volatile("st.release.sys.global.u64 [%0], %1;" :: "l"(q), "l"(s) : "memory");
+  }
+  double sum = 0.0;
+  for (int r = 0; r < pt->world; r++) {
+    const unsigned long long* q = hdr + HDR_XSLOTS + 2 * (buf * MAX_RANKS + r);
+    wait_word(q + 1, s, true, pt->err);
+    sum += reinterpret_cast<const volatile double*>(q)[0];
+  }
+  return sum;
+}
+
+struct SumEpilogue {   // out[0] <- sum over ranks
+  const PeerTable* pt;
+  double* out_w;
+  __device__ void operator()(const double* out) const { if (pt) out_w[0] = xreduce_sum(pt, out[0]); }
+};
+
 struct CtlEpilogue {
   SolveCtl* c;
+  const PeerTable* pt;
+  double* out_w;
   __device__ void operator()(const double* out) const {
+    if (!c && !pt) return;
+    double rn2 = out[0];
+    if (pt) { rn2 = xreduce_sum(pt, rn2); if (out_w) out_w[0] = rn2; }
     if (!c) return;
-    const double rn2 = out[0];
     c->rn2 = rn2;
     c->cycles += 1;
     if (c->cycles > 0) c->total_cycles += 1;
@@ -210,7 +272,7 @@ k_smooth_rb(LevelGeom g, const double* __restrict__ xin, const double* __restric
 template <int OP, bool RECT, bool WRITE, bool NORM>
 __global__ void __launch_bounds__(256)
 k_residual(LevelGeom g, const double* __restrict__ x, const double* __restrict__ b, double* __restrict__ r,
-           double alpha, double beta, Reducer red, double* out, SolveCtl* ctl) {
+           double alpha, double beta, Reducer red, double* out, SolveCtl* ctl, const PeerTable* pt) {
   const int j = blockIdx.x * blockDim.x + threadIdx.x;
   double acc[1] = {0.0};
   for (int i = chunk_lo(g.nx), i_hi = chunk_hi(g.nx); i < i_hi; i++) {
@@ -224,7 +286,7 @@ k_residual(LevelGeom g, const double* __restrict__ x, const double* __restrict__
       }
     }
   }
-  if (NORM) grid_reduce<1, OpSum>(acc, red, out, CtlEpilogue{ctl});
+  if (NORM) grid_reduce<1, OpSum>(acc, red, out, CtlEpilogue{ctl, pt, out});
 }
 
 // y = A x, optionally with the dots (w, y) and (y, y)
@@ -409,10 +471,11 @@ __global__ void __launch_bounds__(256) k_bicg_xr(size_t n, double* __restrict__ 
   grid_reduce<2, OpSum>(acc, red, out);
 }
 // out = {(a,b)}
-__global__ void __launch_bounds__(256) k_dot(size_t n, const double* __restrict__ a, const double* __restrict__ b, Reducer red, double* out) {
+__global__ void __launch_bounds__(256) k_dot(size_t n, const double* __restrict__ a, const double* __restrict__ b, Reducer red, double* out,
+                                             const PeerTable* pt) {
   double acc[1] = {0.0};
   for (size_t k = blockIdx.x * (size_t)blockDim.x + threadIdx.x; k < n; k += (size_t)gridDim.x * blockDim.x) acc[0] += a[k] * b[k];
-  grid_reduce<1, OpSum>(acc, red, out);
+  grid_reduce<1, OpSum>(acc, red, out, SumEpilogue{pt, out});
 }
 // out = {sum a}
 __global__ void __launch_bounds__(256) k_sum(size_t n, const double* __restrict__ a, Reducer red, double* out) {

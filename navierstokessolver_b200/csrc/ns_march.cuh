@@ -104,22 +104,12 @@ struct MarchXfer {
   long long dL, dR;                          // xout  (0: no neighbour on that side / no push)
   long long dbL, dbR;                        // coarse right-hand side (RES == 1)
   int pushw, nxc;                            // columns pushed per side; coarse columns of this slab
-  unsigned long long *sigL, *sigR;           // neighbours' arrival counters (peer-mapped)
-  const unsigned long long *waitL, *waitR;   // this rank's arrival counters
-  unsigned long long needL, needR;           // pushes that must have arrived (from the left / right) before halo columns are read
   int zone;                                  // chunks starting within `zone` columns of a slab end push, signal and wait
-  int* errflag;                              // set when a wait times out (instead of hanging the GPU)
+  const PeerTable* pt;                       // peer map + this rank's control header (arrival / sent counters)
+  unsigned incL, incR;                       // CTAs of this launch that signal leftwards / rightwards (the same on every rank)
+  int rb;                                    // > 0: the first two chunks are the short boundary chunks [0, rb) and [nx - rb, nx)
+  int gather;                                // RES == 1 onto a replicated coarse level: store the slab on every rank
 };
-
-__device__ __forceinline__ void wait_arrivals(const unsigned long long* p, unsigned long long need, int* err) {
-  const long long t0 = clock64();
-  for (;;) {
-    unsigned long long v;
-    asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
-    if (v >= need) break;
-    if (clock64() - t0 > 6000000000LL) { *err = 1; break; }   // ~3 s: report, do not hang
-  }
-}
 
 // Per-thread state of the march: one ring of columns (PF prefetched ones ahead of the K being worked on) and
 // running pointers (one add per column instead of a 64-bit multiply per access).
@@ -208,6 +198,7 @@ struct Marcher {
                 *pbc = v;
                 if (pl) pbc[xf.dbL] = v;
                 if (pr) pbc[xf.dbR] = v;
+                if (PUSH && xf.gather) for (int r = 0; r < xf.pt->world; r++) if (r != xf.pt->rank) pbc[xf.pt->off[r]] = v;
               }
             } else {
               const double2 v = make_double2(t.x * xf.rscale, t.y * xf.rscale);
@@ -215,10 +206,12 @@ struct Marcher {
                 *reinterpret_cast<double2*>(pbc) = v;
                 if (pl) *reinterpret_cast<double2*>(pbc + xf.dbL) = v;
                 if (pr) *reinterpret_cast<double2*>(pbc + xf.dbR) = v;
+                if (PUSH && xf.gather) for (int r = 0; r < xf.pt->world; r++) if (r != xf.pt->rank) *reinterpret_cast<double2*>(pbc + xf.pt->off[r]) = v;
               } else if (jstore1) {
                 *pbc = v.x;
                 if (pl) pbc[xf.dbL] = v.x;
                 if (pr) pbc[xf.dbR] = v.x;
+                if (PUSH && xf.gather) for (int r = 0; r < xf.pt->world; r++) if (r != xf.pt->rank) pbc[xf.pt->off[r]] = v.x;
               }
             }
             pbc += xf.ldbc;
@@ -243,7 +236,15 @@ k_march(LevelGeom g, const double* __restrict__ mcx, const double* __restrict__ 
   extern __shared__ double s_c[];            // (cw, ce, dx) of columns [r0, r0 + nrows)
   const int lane = threadIdx.x & 31;
   const int wj = blockIdx.x * MARCH_WARPS + (threadIdx.x >> 5);
-  const int ib = blockIdx.y * RI, ie = min(ib + RI, g.nx);
+  // Several ranks: the columns a neighbour needs come out of two SHORT chunks that are scheduled first, so that they
+  // are pushed and signalled long before the neighbour's next pass asks for them (and a late start costs little).
+  int ib = blockIdx.y * RI, ie = min(ib + RI, g.nx);
+  if (PUSH && xf.rb) {
+    const int y = blockIdx.y;
+    if (y == 0) { ib = 0; ie = xf.rb; }
+    else if (y == 1) { ib = g.nx - xf.rb; ie = g.nx; }
+    else { ib = xf.rb + (y - 2) * RI; ie = min(ib + RI, g.nx - xf.rb); }
+  }
   const int nbeg = ib - LL, nend = ie + LL;  // columns needed: [nbeg, nend) inside [-HX + 1, nx + HX)
   // start on a column whose half-sweeps update the .x cells: (gi0 + n0 - 1) even; n0 >= -HX
   const int n0 = nbeg - ((g.gi0 + nbeg - 1) & 1);
@@ -255,8 +256,17 @@ k_march(LevelGeom g, const double* __restrict__ mcx, const double* __restrict__ 
     s_c[3 * q + 2] = mcx[3 * a + 2];
   }
   if (PUSH && xf.zone && threadIdx.x == 0) {   // halo columns of this chunk come from a neighbour's push
-    if (ib < xf.zone && xf.waitL && xf.needL) wait_arrivals(xf.waitL, xf.needL, xf.errflag);
-    if (ie > g.nx - xf.zone && xf.waitR && xf.needR) wait_arrivals(xf.waitR, xf.needR, xf.errflag);
+    // what has arrived from the left is what every rank has sent rightwards so far, and vice versa; the counts are
+    // kept on the device (updated by the last CTA of every launch) so that a replayed graph stays consistent
+    const PeerTable* pt = xf.pt;
+    if (ib < xf.zone && pt->rank > 0) {
+      const unsigned long long need = pt->hdr[HDR_SENT_R];
+      if (need) wait_word(pt->hdr + HDR_ARR_L, need, false, pt->err);
+    }
+    if (ie > g.nx - xf.zone && pt->rank < pt->world - 1) {
+      const unsigned long long need = pt->hdr[HDR_SENT_L];
+      if (need) wait_word(pt->hdr + HDR_ARR_R, need, false, pt->err);
+    }
   }
   __syncthreads();
 
@@ -297,18 +307,32 @@ k_march(LevelGeom g, const double* __restrict__ mcx, const double* __restrict__ 
     m.template step<true>(n);
     m.template step<false>(n + 1);
   }
-  if (PUSH && (xf.sigL || xf.sigR)) {   // pushed columns are visible system-wide before the neighbour is told
-    __threadfence_system();
-    __syncthreads();
+  if (PUSH) {
+    __syncthreads();          // every store of this CTA happens before thread 0's fence (cumulativity)
     if (threadIdx.x == 0) {
-      __threadfence_system();
-      if (ib < xf.zone && xf.sigL) atomicAdd_system(xf.sigL, 1ull);
-      if (ie > g.nx - xf.zone && xf.sigR) atomicAdd_system(xf.sigR, 1ull);
+      const PeerTable* pt = xf.pt;
+      unsigned long long* hdr = pt->hdr;
+      const bool sl = xf.zone && ib < xf.zone && pt->rank > 0, sr = xf.zone && ie > g.nx - xf.zone && pt->rank < pt->world - 1;
+      const bool ga = RES == 1 && xf.gather;
+      // pushed columns are visible system-wide before the neighbour is told; CTAs that pushed nothing skip the
+      // system-scope fence (it is expensive, and thousands of them at the end of a pass serialise)
+      if (sl || sr || ga) __threadfence_system();
+      if (sl) atomicAdd_system(hdr + pt->off[pt->rank - 1] + HDR_ARR_R, 1ull);
+      if (sr) atomicAdd_system(hdr + pt->off[pt->rank + 1] + HDR_ARR_L, 1ull);
+      if (ga)
+        for (int r = 0; r < pt->world; r++) atomicAdd_system(hdr + pt->off[r] + HDR_TAIL_ARR, 1ull);
+      const unsigned long long total = (unsigned long long)gridDim.x * gridDim.y;
+      if (atomicAdd(hdr + HDR_TICKET, 1ull) == total - 1) {   // every CTA has read the sent counters: advance them
+        hdr[HDR_SENT_L] += xf.incL;
+        hdr[HDR_SENT_R] += xf.incR;
+        hdr[HDR_TICKET] = 0;
+        __threadfence();
+      }
     }
   }
   if (RES == 2) {
     double acc[1] = {m.acc};
-    grid_reduce<1, OpSum>(acc, xf.red, xf.out, CtlEpilogue{xf.ctl});
+    grid_reduce<1, OpSum>(acc, xf.red, xf.out, CtlEpilogue{xf.ctl, xf.pt, xf.out});
   }
 }
 

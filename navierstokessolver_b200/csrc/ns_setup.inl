@@ -101,8 +101,7 @@ static void destroy_ctx(nsgpu_ctx* ctx) {
   if (!ctx) return;
   cudaSetDevice(ctx->device);
   if (ctx->stream) cudaStreamSynchronize(ctx->stream);
-  if (ctx->peerL) cudaIpcCloseMemHandle(ctx->peerL);
-  if (ctx->peerR) cudaIpcCloseMemHandle(ctx->peerR);
+  for (int r = 0; r < MAX_RANKS; r++) if (ctx->peers[r]) cudaIpcCloseMemHandle(ctx->peers[r]);
   if (ctx->comm) ncclCommDestroy(ctx->comm);
   if (ctx->arena) cudaFree(ctx->arena);
   for (auto& L : ctx->levels)
@@ -165,7 +164,9 @@ static int create_impl(nsgpu_ctx* ctx, const nsgpu_grid* G, const nsgpu_params* 
 
   // ---- several ranks: one arena for everything the marching passes write, opened by both neighbours (CUDA IPC)
   if (const char* e = getenv("NSGPU_P2P")) ctx->use_p2p = atoi(e);
-  if (ctx->world > 1 && ctx->use_p2p && plan.rect) {
+  if (const char* e = getenv("NSGPU_TRACE")) ctx->trace = atoi(e);
+  if (const char* e = getenv("NSGPU_RB")) ctx->march_rb = atoi(e);
+  if (ctx->world > 1 && ctx->world <= MAX_RANKS && ctx->use_p2p && plan.rect && plan.levels[0].gnx % ctx->world == 0) {   // equal slabs: equal arena layouts
     size_t doubles = 0;
     for (size_t l = 0; l < plan.levels.size(); l++) {
       const size_t ld = ((plan.levels[l].ny + 3) / 4) * 4 + 2 * PJ;
@@ -175,8 +176,7 @@ static int create_impl(nsgpu_ctx* ctx, const nsgpu_grid* G, const nsgpu_params* 
     ctx->arena_bytes = doubles * sizeof(double) + (1 << 20);
     NS_CUDA(cudaMalloc((void**)&ctx->arena, ctx->arena_bytes));
     NS_CUDA(cudaMemset(ctx->arena, 0, ctx->arena_bytes));
-    ctx->arrivals = (unsigned long long*)ctx->arena;    // first 256 bytes: arrival counters
-    ctx->arena_used = 256;
+    ctx->arena_used = HDR_WORDS * sizeof(unsigned long long);   // control header: arrival / sent counters, reduction slots
     // exchange the IPC handles through the communicator that exists anyway
     cudaIpcMemHandle_t mine;
     NS_CUDA(cudaIpcGetMemHandle(&mine, ctx->arena));
@@ -190,8 +190,9 @@ static int create_impl(nsgpu_ctx* ctx, const nsgpu_grid* G, const nsgpu_params* 
     NS_CUDA(cudaMemcpy(all.data(), d_h, 64 * (size_t)ctx->world, cudaMemcpyDeviceToHost));
     cudaFree(d_h);
     bool ok = true;
-    if (ctx->rank > 0 && cudaIpcOpenMemHandle((void**)&ctx->peerL, all[ctx->rank - 1], cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) ok = false;
-    if (ctx->rank < ctx->world - 1 && cudaIpcOpenMemHandle((void**)&ctx->peerR, all[ctx->rank + 1], cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) ok = false;
+    for (int r = 0; r < ctx->world; r++)
+      if (r != ctx->rank && cudaIpcOpenMemHandle((void**)&ctx->peers[r], all[r], cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) { ctx->peers[r] = nullptr; ok = false; }
+    if (ok) { ctx->peerL = ctx->rank > 0 ? ctx->peers[ctx->rank - 1] : nullptr; ctx->peerR = ctx->rank < ctx->world - 1 ? ctx->peers[ctx->rank + 1] : nullptr; }
     // every rank must agree, or the halo protocols would differ: all-reduce the outcome
     int* d_ok = nullptr;
     NS_CUDA(cudaMalloc((void**)&d_ok, sizeof(int)));
@@ -205,8 +206,7 @@ static int create_impl(nsgpu_ctx* ctx, const nsgpu_grid* G, const nsgpu_params* 
     cudaGetLastError();
     if (!all_ok) {
       fprintf(stderr, "nsgpu: CUDA IPC mapping of the neighbour slabs failed; halo columns go through NCCL\n");
-      if (ctx->peerL) cudaIpcCloseMemHandle(ctx->peerL);
-      if (ctx->peerR) cudaIpcCloseMemHandle(ctx->peerR);
+      for (int r = 0; r < MAX_RANKS; r++) if (ctx->peers[r]) { cudaIpcCloseMemHandle(ctx->peers[r]); ctx->peers[r] = nullptr; }
       ctx->peerL = ctx->peerR = nullptr;
       ctx->use_p2p = 0;
     }
@@ -257,6 +257,14 @@ static int create_impl(nsgpu_ctx* ctx, const nsgpu_grid* G, const nsgpu_params* 
         TailDesc& T = ctx->tail[op];
         T.nlev = nl - ts; T.nu_pre = ctx->nu_pre; T.nu_post = ctx->nu_post;
         T.coarse_sweeps = ctx->levels.back().coarse_sweeps; T.gi0 = 0;
+        // The coarsest grid of a long domain is long too (y cannot be coarsened any further): plain Gauss-Seidel would need
+        // O(n^2) sweeps there.  Optimal SOR for the Neumann problem on n cells, Jacobi radius cos(pi / n).
+        T.coarse_omega = 1.0;
+        if (op == 1) {
+          const int n = std::max(ctx->levels.back().g.gnx, ctx->levels.back().g.ny);
+          if (n >= 4) T.coarse_omega = 2.0 / (1.0 + std::sin(3.14159265358979323846 / n));
+          if (const char* e = getenv("NSGPU_COARSE_OMEGA")) T.coarse_omega = atof(e);
+        }
         int off = 0;
         for (int k = 0; k < T.nlev; k++) {
           const Level& L = ctx->levels[ts + k];
@@ -296,7 +304,23 @@ static int create_impl(nsgpu_ctx* ctx, const nsgpu_grid* G, const nsgpu_params* 
   { void* p = nullptr; NS_CUDA(cudaMalloc(&p, 3 * sizeof(SolveCtl))); ctx->owned.push_back(p); NS_CUDA(cudaMemset(p, 0, 3 * sizeof(SolveCtl))); ctx->d_ctl = (SolveCtl*)p; }
   NS_CUDA(cudaMallocHost((void**)&ctx->h_ctl, 3 * sizeof(SolveCtl)));
   memset(ctx->h_ctl, 0, 3 * sizeof(SolveCtl));
+  if (ctx->world > 1 && ctx->use_p2p) {   // the peer map the kernels use
+    PeerTable t{};
+    t.world = ctx->world; t.rank = ctx->rank;
+    for (int r = 0; r < ctx->world; r++) t.off[r] = r == ctx->rank ? 0 : (long long)((ctx->peers[r] - ctx->arena) / (ptrdiff_t)sizeof(double));
+    t.hdr = (unsigned long long*)ctx->arena;
+    t.err = ctx->d_errflag;
+    void* p = nullptr;
+    NS_CUDA(cudaMalloc(&p, sizeof(PeerTable)));
+    ctx->owned.push_back(p);
+    NS_CUDA(cudaMemcpy(p, &t, sizeof t, cudaMemcpyHostToDevice));
+    ctx->d_pt = (PeerTable*)p;
+  }
   NS_CUDA(cudaDeviceSynchronize());
+  if (ctx->world > 1) {   // nobody pushes into an arena that is still being zeroed
+    NS_NCCL(ncclAllReduce(ctx->d_scal + 40, ctx->d_scal + 40, 1, ncclDouble, ncclSum, ctx->comm, ctx->stream));
+    NS_CUDA(cudaStreamSynchronize(ctx->stream));
+  }
   return 0;
 }
 

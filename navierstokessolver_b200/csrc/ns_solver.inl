@@ -44,6 +44,7 @@ static int halo_exchange(nsgpu_ctx* ctx, const Level& L, double* f, int width, b
     auto it = ctx->halo_w.find(f);
     if (it != ctx->halo_w.end() && it->second >= width) return 0;
   }
+  if (ctx->capturing) ctx->capture_nccl = true;   // solve graphs hold this library's kernels only
   const size_t n = (size_t)width * L.g.ld;
   const int nx = L.g.nx;
   NS_NCCL(ncclGroupStart());
@@ -59,8 +60,31 @@ static int halo_exchange(nsgpu_ctx* ctx, const Level& L, double* f, int width, b
   return 0;
 }
 
+// tracing (NSGPU_TRACE=1): key = level * 1000 + nsw * 100 + res * 10 + prolong * 2 + push; 99999 = coarse tail
+static inline void trace_begin(nsgpu_ctx* ctx, int key) {
+  if (!ctx->trace || ctx->capturing) return;
+  nsgpu_ctx::TraceEv t; t.key = key;
+  cudaEventCreate(&t.a); cudaEventCreate(&t.b);
+  cudaEventRecord(t.a, ctx->stream);
+  ctx->trace_ev.push_back(t);
+}
+static inline void trace_end(nsgpu_ctx* ctx) {
+  if (!ctx->trace || ctx->capturing || ctx->trace_ev.empty()) return;
+  cudaEventRecord(ctx->trace_ev.back().b, ctx->stream);
+}
+static void trace_collect(nsgpu_ctx* ctx) {   // after a stream synchronize
+  for (auto& t : ctx->trace_ev) {
+    float ms = 0;
+    if (cudaEventElapsedTime(&ms, t.a, t.b) == cudaSuccess) { auto& e = ctx->trace_acc[t.key]; e.first += ms; e.second += 1; }
+    cudaEventDestroy(t.a); cudaEventDestroy(t.b);
+  }
+  ctx->trace_ev.clear();
+  cudaGetLastError();
+}
+
 static int allreduce(nsgpu_ctx* ctx, double* d, int n, ncclRedOp_t op) {
   if (ctx->world == 1) return 0;
+  if (ctx->capturing) ctx->capture_nccl = true;
   NS_NCCL(ncclAllReduce(d, d, n, ncclDouble, op, ctx->comm, ctx->stream));
   return 0;
 }
@@ -149,8 +173,17 @@ static int march_pass(nsgpu_ctx* ctx, const Level& L, OpCoef c, int nsw, double*
 #undef NS_MARCH_RES
 #undef NS_MARCH
   const int ri = march_chunk(ctx, L, uj, 2 * lead + 2 * nsw + 2, march_wave(kern));
-  const dim3 grid(((L.g.ny + uj - 1) / uj + MARCH_WARPS - 1) / MARCH_WARPS, (L.g.nx + ri - 1) / ri);
-  const size_t sh = (size_t)3 * (ri + 2 * lead + 2 * nsw + 8) * sizeof(double);   // >= nrows of k_march
+  dim3 grid(((L.g.ny + uj - 1) / uj + MARCH_WARPS - 1) / MARCH_WARPS, (L.g.nx + ri - 1) / ri);
+  // several ranks: short boundary chunks (even width >= the push zone), see k_march
+  int rb = 0;
+  if (push && ctx->march_rb > 0) {
+    rb = std::max(ctx->march_rb, 2 * (HX - 1));
+    rb += rb & 1;
+    const unsigned gy = 2 + (unsigned)((L.g.nx - 2 * rb + ri - 1) / ri);
+    if (L.g.nx >= 2 * rb + 4 && (L.g.nx & 1) == 0 && (long long)grid.x * gy <= RED_MAX_BLOCKS) grid.y = gy; else rb = 0;
+  }
+  const size_t sh = (size_t)3 * (std::max(ri, rb) + 2 * lead + 2 * nsw + 8) * sizeof(double);   // >= nrows of k_march
+  const bool gather = push && Cr && Cr->replicated;   // the slab of the replicated coarse right-hand side goes to every rank
   if (push) {
     const long long offL = ctx->peerL ? (long long)((ctx->peerL - ctx->arena) / (ptrdiff_t)sizeof(double)) : 0;
     const long long offR = ctx->peerR ? (long long)((ctx->peerR - ctx->arena) / (ptrdiff_t)sizeof(double)) : 0;
@@ -162,22 +195,23 @@ static int march_pass(nsgpu_ctx* ctx, const Level& L, OpCoef c, int nsw, double*
       xf.dbL = ctx->peerL ? offL + (long long)Cr->g.nx * Cr->g.ld : 0;
       xf.dbR = ctx->peerR ? offR - (long long)Cr->g.nx * Cr->g.ld : 0;
     }
-    xf.sigL = ctx->peerL ? (unsigned long long*)ctx->peerL + 1 : nullptr;   // the left neighbour's "arrived from the right"
-    xf.sigR = ctx->peerR ? (unsigned long long*)ctx->peerR + 0 : nullptr;   // the right neighbour's "arrived from the left"
-    xf.waitL = ctx->peerL ? ctx->arrivals + 0 : nullptr;
-    xf.waitR = ctx->peerR ? ctx->arrivals + 1 : nullptr;
-    // what arrives from the left neighbour is what every rank sends rightwards, and vice versa
-    xf.needL = ctx->sent_right;
-    xf.needR = ctx->sent_left;
     xf.zone = xf.pushw * (push_b ? L.cx : 1);
-    xf.errflag = ctx->d_errflag;
-  }
-  kern<<<grid, MARCH_THREADS, sh, ctx->stream>>>(L.g, L.mcx[c.op], L.mcy[c.op], xin, b, xout, ri, xf);
-  if (push) {
+    xf.pt = ctx->d_pt;
+    xf.gather = gather ? 1 : 0;
     // chunks that start inside the left zone / end inside the right zone signal once per CTA
     const int gy = (int)grid.y, zone = std::min(xf.zone, L.g.nx);
-    ctx->sent_left += (unsigned long long)grid.x * ((zone + ri - 1) / ri);
-    ctx->sent_right += (unsigned long long)grid.x * (gy - (L.g.nx - zone) / ri);
+    xf.rb = rb;
+    if (rb) xf.incL = xf.incR = grid.x;   // rb >= zone: one boundary chunk per side
+    else {
+      xf.incL = grid.x * (unsigned)((zone + ri - 1) / ri);
+      xf.incR = grid.x * (unsigned)(gy - (L.g.nx - zone) / ri);
+    }
+    if (gather) ctx->last_gather_ctas = grid.x * grid.y;
+  } else if (res == 2 && ctx->d_pt) xf.pt = ctx->d_pt;   // the residual norm is summed over the ranks in the epilogue
+  trace_begin(ctx, (int)(&L - ctx->levels.data()) * 1000 + nsw * 100 + res * 10 + (Cp ? 2 : 0) + (push ? 1 : 0) + (omega > 0 ? 50000 : 0));
+  kern<<<grid, MARCH_THREADS, sh, ctx->stream>>>(L.g, L.mcx[c.op], L.mcy[c.op], xin, b, xout, ri, xf);
+  trace_end(ctx);
+  if (push) {
     ctx->halo_w[xout] = xf.pushw;
     if (push_b) ctx->halo_w[Cr->b] = xf.pushw;
   } else {
@@ -185,6 +219,7 @@ static int march_pass(nsgpu_ctx* ctx, const Level& L, OpCoef c, int nsw, double*
     if (Cr) ctx->halo_w.erase(Cr->b);
   }
   NS_LAUNCH_CHECK();
+  if (gather) return 0;
   if (Cr && Cr->replicated && !L.replicated && ctx->world > 1) {
     // every rank contributes its slab of the coarse right-hand side; in place: the slabs are contiguous column ranges
     const size_t count = (size_t)(L.g.nx / L.cx) * Cr->g.ld;
@@ -214,7 +249,10 @@ static int vcycle_fused(nsgpu_ctx* ctx, int l, OpCoef c, double** x, double** xt
   Level& L = ctx->levels[l];
   if (ctx->tail_start > 0 && l == ctx->tail_start && L.march_ok[c.op]) {   // the rest of the cycle in one single-CTA kernel
     const TailDesc& T = ctx->tail[c.op];
-    k_coarse_tail<<<1, TAIL_THREADS, (size_t)T.smem_doubles * sizeof(double), ctx->stream>>>(T, b, *x);
+    const bool gathered = ctx->d_pt && L.replicated && ctx->last_gather_ctas > 0;
+    trace_begin(ctx, 99999);
+    k_coarse_tail<<<1, TAIL_THREADS, (size_t)T.smem_doubles * sizeof(double), ctx->stream>>>(T, b, *x, gathered ? ctx->d_pt : nullptr, ctx->last_gather_ctas);
+    trace_end(ctx);
     NS_LAUNCH_CHECK();
     return 0;
   }
@@ -261,21 +299,21 @@ static int smooth(nsgpu_ctx* ctx, const Level& L, OpCoef c, double** x, double**
 
 // d_out[0] = ||b - A x||^2 over the local slab (all-reduced over ranks)
 static int residual_norm2(nsgpu_ctx* ctx, const Level& L, OpCoef c, double* x, const double* b, double* d_out, SolveCtl* ctl = nullptr) {
-  int rc = halo_exchange(ctx, L, x, 2);
+  int rc = halo_exchange(ctx, L, x, 2, ctl != nullptr);   // device-controlled solves exchange x before their head
   if (rc) return rc;
   const dim3 grid = grid_cols(L.g, 256);
-#define CALL(OP, RECT) k_residual<OP, RECT, false, true><<<grid, 256, 0, ctx->stream>>>(L.g, x, b, nullptr, c.alpha, c.beta, ctx->red, d_out, ctl)
+#define CALL(OP, RECT) k_residual<OP, RECT, false, true><<<grid, 256, 0, ctx->stream>>>(L.g, x, b, nullptr, c.alpha, c.beta, ctx->red, d_out, ctl, ctx->d_pt)
   NS_DISPATCH_OP_RECT(c.op, ctx->rect, CALL);
 #undef CALL
   NS_LAUNCH_CHECK();
-  return allreduce(ctx, d_out, 1, ncclSum);
+  return ctx->d_pt ? 0 : allreduce(ctx, d_out, 1, ncclSum);   // peer map: summed over the ranks in the kernel's epilogue
 }
 
 static int residual_vec(nsgpu_ctx* ctx, const Level& L, OpCoef c, double* x, const double* b, double* r, double* d_norm2) {
   int rc = halo_exchange(ctx, L, x, 2);
   if (rc) return rc;
   const dim3 grid = grid_cols(L.g, 256);
-#define CALL(OP, RECT) k_residual<OP, RECT, true, true><<<grid, 256, 0, ctx->stream>>>(L.g, x, b, r, c.alpha, c.beta, ctx->red, d_norm2, nullptr)
+#define CALL(OP, RECT) k_residual<OP, RECT, true, true><<<grid, 256, 0, ctx->stream>>>(L.g, x, b, r, c.alpha, c.beta, ctx->red, d_norm2, nullptr, nullptr)
   NS_DISPATCH_OP_RECT(c.op, ctx->rect, CALL);
 #undef CALL
   NS_LAUNCH_CHECK();
@@ -349,9 +387,9 @@ static int read_scalars(nsgpu_ctx* ctx, const double* d, int n, double* h) {
 static int norm2_vec(nsgpu_ctx* ctx, const Level& L, const double* a, double* d_out) {
   const size_t n = (size_t)L.g.nx * L.g.ld;
   const int blocks = (int)std::min<size_t>((n + 255) / 256, 148 * 8);
-  k_dot<<<blocks, 256, 0, ctx->stream>>>(n, a + (size_t)HX * L.g.ld, a + (size_t)HX * L.g.ld, ctx->red, d_out);
+  k_dot<<<blocks, 256, 0, ctx->stream>>>(n, a + (size_t)HX * L.g.ld, a + (size_t)HX * L.g.ld, ctx->red, d_out, ctx->d_pt);
   NS_LAUNCH_CHECK();
-  return allreduce(ctx, d_out, 1, ncclSum);
+  return ctx->d_pt ? 0 : allreduce(ctx, d_out, 1, ncclSum);
 }
 
 // V-cycle for the host-driven solvers: fused marching passes where every level supports them, generic kernels otherwise.
@@ -396,7 +434,7 @@ static int solve_mg(nsgpu_ctx* ctx, OpCoef c, double** x, double** xt, const dou
       if ((rc = vcycle_any(ctx, c, x, xt, b, false))) return rc;
     }
     out->cycles++;
-    if (fused) { if ((rc = allreduce(ctx, ctx->d_scal + 1, 1, ncclSum))) return rc; }
+    if (fused) { if (!ctx->d_pt && (rc = allreduce(ctx, ctx->d_scal + 1, 1, ncclSum))) return rc; }
     else if ((rc = residual_norm2(ctx, L, c, *x, b, ctx->d_scal + 1))) return rc;
     if ((rc = read_scalars(ctx, ctx->d_scal + 1, 1, h))) return rc;
     rn = std::sqrt(h[0]);
@@ -527,7 +565,18 @@ static int solve_tail(nsgpu_ctx* ctx, int slot, double* x) {
   } while (0)
 
 // Builds head -> WHILE(go){ V-cycle + residual norm } -> tail for (x, xt, b).  Returns 0 ok, 1 unsupported, < 0 error.
+static int build_solve_graph_(nsgpu_ctx* ctx, int slot, OpCoef c, double* x, double* xt, const double* b, double rtol);
 static int build_solve_graph(nsgpu_ctx* ctx, int slot, OpCoef c, double* x, double* xt, const double* b, double rtol) {
+  ctx->capturing = true; ctx->capture_nccl = false;
+  int rc = build_solve_graph_(ctx, slot, c, x, xt, b, rtol);
+  ctx->capturing = false;
+  if (rc == 0 && ctx->capture_nccl) {
+    fprintf(stderr, "nsgpu: a solve would need NCCL inside its loop; direct launches instead of graphs\n");
+    rc = 1;
+  }
+  return rc;
+}
+static int build_solve_graph_(nsgpu_ctx* ctx, int slot, OpCoef c, double* x, double* xt, const double* b, double rtol) {
   SolveGraph& G = ctx->sgraph[slot];
   if (G.exec) { cudaGraphExecDestroy(G.exec); G.exec = nullptr; }
   if (G.graph) { cudaGraphDestroy(G.graph); G.graph = nullptr; }
@@ -587,6 +636,10 @@ static int build_solve_graph(nsgpu_ctx* ctx, int slot, OpCoef c, double* x, doub
 // Issues the whole solve on the stream; results land in h_ctl[slot] (decode_solve after a synchronize).
 static int solve_mg_dev(nsgpu_ctx* ctx, int slot, OpCoef c, double** x, double** xt, const double* b, double rtol) {
   int rc;
+  if (ctx->world > 1) {   // the only NCCL step of the solve: the initial guess' halo columns, as wide as the passes push
+    if ((rc = halo_exchange(ctx, ctx->levels[0], *x, HX - 1))) return rc;
+    ctx->halo_w[*x] = std::min(HX - 1, ctx->levels[0].g.nx);
+  }
   if (ctx->use_graph) {
     SolveGraph& G = ctx->sgraph[slot];
     if (!G.exec || G.x != *x || G.xt != *xt || G.b != b || G.rtol != rtol) {
@@ -635,7 +688,7 @@ static void decode_solve(nsgpu_ctx* ctx, int slot, SolveResult* out) {
 }
 
 static inline bool dev_solve_ok(const nsgpu_ctx* ctx, OpCoef c) {
-  if (ctx->solver != 0 || ctx->world != 1) return false;
+  if (ctx->solver != 0 || (ctx->world != 1 && !ctx->d_pt)) return false;
   if (c.op == 0 && ctx->vel_omega > 0.0) return march_level_ok(ctx, ctx->levels[0], c);
   return all_levels_march(ctx, c);
 }

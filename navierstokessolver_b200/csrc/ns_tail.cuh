@@ -27,13 +27,14 @@ struct TailLevel {
 
 struct TailDesc {
   int nlev, nu_pre, nu_post, coarse_sweeps, smem_doubles, gi0;
+  double coarse_omega;   // over-relaxation of the sweeps on the coarsest level (1: plain Gauss-Seidel)
   TailLevel lv[TAIL_MAX_LEVELS];
 };
 
 // shared layout of a level: (nx + 2) x (ny + 2) with a zero ring, value(i, j) at (i + 1) * (ny + 2) + j + 1
 __device__ __forceinline__ int tidx(const TailLevel& L, int i, int j) { return (i + 1) * (L.ny + 2) + j + 1; }
 
-__device__ void tail_smooth(const TailDesc& d, const TailLevel& L, double* sm, int sweeps) {
+__device__ void tail_smooth(const TailDesc& d, const TailLevel& L, double* sm, int sweeps, double omega = 1.0) {
   double* x = sm + L.xoff;
   const double* b = sm + L.boff;
   const double* sx = sm + L.sxoff;
@@ -48,7 +49,8 @@ __device__ void tail_smooth(const TailDesc& d, const TailLevel& L, double* sm, i
         v = fma(sx[3 * i + 1], x[q + p], v);
         v = fma(sy[3 * j], x[q - 1], v);
         v = fma(sy[3 * j + 1], x[q + 1], v);
-        x[q] = v * fast_rcp(sx[3 * i + 2] + sy[3 * j + 2]);
+        const double gs = v * fast_rcp(sx[3 * i + 2] + sy[3 * j + 2]);
+        x[q] = omega == 1.0 ? gs : fma(omega, gs - x[q], x[q]);
       }
     }
     __syncthreads();
@@ -94,9 +96,14 @@ __device__ void tail_prolong(const TailLevel& F, const TailLevel& C, double* sm)
 
 // b0: right-hand side of the first tail level (global, padded layout); x0: its solution array (global)
 __global__ void __launch_bounds__(TAIL_THREADS)
-k_coarse_tail(TailDesc d, const double* __restrict__ b0, double* __restrict__ x0) {
+k_coarse_tail(TailDesc d, const double* __restrict__ b0, double* __restrict__ x0, const PeerTable* pt, unsigned gather_ctas) {
   extern __shared__ double sm[];
   for (int c = threadIdx.x; c < d.smem_doubles; c += TAIL_THREADS) sm[c] = 0.0;
+  if (pt && threadIdx.x == 0) {   // several ranks: every rank's restriction pass stores its slab of b0 here (peer memory)
+    const unsigned long long need = pt->hdr[HDR_TAIL_NEED] + (unsigned long long)pt->world * gather_ctas;
+    wait_word(pt->hdr + HDR_TAIL_ARR, need, false, pt->err);
+    pt->hdr[HDR_TAIL_NEED] = need;
+  }
   __syncthreads();
   for (int l = 0; l < d.nlev; l++) {
     const TailLevel& L = d.lv[l];
@@ -116,7 +123,7 @@ k_coarse_tail(TailDesc d, const double* __restrict__ b0, double* __restrict__ x0
     tail_smooth(d, d.lv[l], sm, d.nu_pre);
     tail_restrict(d.lv[l], d.lv[l + 1], sm);
   }
-  tail_smooth(d, d.lv[d.nlev - 1], sm, d.coarse_sweeps);   // the last tail level is the coarsest level of the hierarchy
+  tail_smooth(d, d.lv[d.nlev - 1], sm, d.coarse_sweeps, d.coarse_omega);   // the last tail level is the coarsest level of the hierarchy
   for (int l = d.nlev - 2; l >= 0; l--) {         // up: prolong, post-smooth
     tail_prolong(d.lv[l], d.lv[l + 1], sm);
     tail_smooth(d, d.lv[l], sm, d.nu_post);
