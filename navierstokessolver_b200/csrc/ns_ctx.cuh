@@ -99,7 +99,8 @@ struct nsgpu_ctx {
   int trace = 0;
   std::vector<TraceEv> trace_ev;
   std::unordered_map<int, std::pair<double, long>> trace_acc;
-  int march_rb = 12;                             // width of the short boundary chunks of pushing passes (NSGPU_RB, 0 = off)
+  int march_rb_min_nx = 0;                       // levels with fewer columns keep uniform chunks (NSGPU_RB_MINNX)
+  int march_rb = 0;                              // width of the short boundary chunks of pushing passes (NSGPU_RB, 0 = off)
   unsigned last_gather_ctas = 0;                 // CTAs of the last restriction pass that gathered onto the replicated level
   int* d_errflag = nullptr;
   int use_p2p = 1;

@@ -140,7 +140,9 @@ static inline double mean_of(const std::vector<double>& a) {
 
 // Validates the descriptor and builds edges, flags, the slab of `rank` and the multigrid coarsening plan.
 // Returns 0 or a negative nsgpu_status with `err` filled.
-static inline int make_host_plan(const nsgpu_grid* G, int rank, int world, int max_levels_in, HostPlan& P, std::string& err) {
+// rep_cells: several ranks replicate every level of at most this many GLOBAL cells (never fewer than the coarse tail's 4096)
+static inline int make_host_plan(const nsgpu_grid* G, int rank, int world, int max_levels_in, HostPlan& P, std::string& err,
+                                 long long rep_cells = 4096) {
   if (!G) { err = "null grid"; return NSGPU_ERR_ARG; }
   if (G->nx < 1 || G->ny < 1 || !G->hx || !G->hy) { err = "bad grid extents"; return NSGPU_ERR_ARG; }
   if (G->n_edges < 1 || G->n_edges > 255 || !G->edge_nx || !G->edge_ny || !G->edge_bc_type || !G->edge_bc_info) {
@@ -252,8 +254,9 @@ static inline int make_host_plan(const nsgpu_grid* G, int rank, int world, int m
     const int nx_l = P.lnx.back();
     const double mx = mean_of(F.hx), my = mean_of(F.hy);
     // Several ranks on a plain rectangle: slabs keep at least HX columns (the fused marching passes take their whole
-    // halo from ONE neighbour); as soon as a level is small enough for the single-CTA coarse tail it is replicated on
-    // every rank (all-gather of its right-hand side), so the coarse part of the cycle needs no communication at all.
+    // halo from ONE neighbour); as soon as a level is small (rep_cells; at the latest when it fits the single-CTA coarse
+    // tail) it is replicated on every rank (all-gather of its right-hand side): on small levels a pass costs launch and
+    // neighbour latency, not bandwidth, so redundant work is cheaper than one more synchronisation per pass.
     const bool fast = rect && world > 1 && !(P.side_out[0] || P.side_out[1] || P.side_out[2] || P.side_out[3]);
     const bool replicated = P.rep_start > 0;
     const int min_nx = world == 1 || replicated ? 1 : (fast ? HX : 2);
@@ -292,7 +295,7 @@ static inline int make_host_plan(const nsgpu_grid* G, int rank, int world, int m
         }
     }
     P.lcx.push_back(cx); P.lcy.push_back(cy);
-    if (fast && !replicated && (long long)C.gnx * C.ny <= 4096) P.rep_start = (int)P.levels.size();   // TAIL_MAX_CELLS
+    if (fast && !replicated && (long long)C.gnx * C.ny <= std::max(rep_cells, 4096LL)) P.rep_start = (int)P.levels.size();   // 4096: TAIL_MAX_CELLS
     if (P.rep_start > 0) { P.lnx.push_back(C.gnx); P.lgi0.push_back(0); }
     else { P.lnx.push_back(nx_l / cx); P.lgi0.push_back(P.lgi0.back() / cx); }
     P.levels.push_back(std::move(C));

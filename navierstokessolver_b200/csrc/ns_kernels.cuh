@@ -145,7 +145,7 @@ __device__ inline double xreduce_sum(const PeerTable* pt, double mine) {
   __threadfence_system();
   for (int r = 0; r < pt->world; r++) {
     unsigned long long* q = my_slot + pt->off[r] + 1;
-    asm volatile("st.release.sys.global.u64 [%0], %1;" :: "l"(q), "l"(s) : "memory");
+    asm volatile("st.relaxed.sys.global.u64 [%0], %1;" :: "l"(q), "l"(s) : "memory");   // ordered after the values by the fence
   }
   double sum = 0.0;
   for (int r = 0; r < pt->world; r++) {
@@ -154,6 +154,14 @@ __device__ inline double xreduce_sum(const PeerTable* pt, double mine) {
     sum += reinterpret_cast<const volatile double*>(q)[0];
   }
   return sum;
+}
+
+// Several ranks: the slabs of a replicated right-hand side are stored by every rank's restriction pass (peer memory);
+// this one-thread kernel holds the stream until all of them have arrived.
+__global__ void k_wait_gather(const PeerTable* pt, unsigned gather_ctas) {
+  const unsigned long long need = pt->hdr[HDR_TAIL_NEED] + (unsigned long long)pt->world * gather_ctas;
+  wait_word(pt->hdr + HDR_TAIL_ARR, need, false, pt->err);
+  pt->hdr[HDR_TAIL_NEED] = need;
 }
 
 struct SumEpilogue {   // out[0] <- sum over ranks

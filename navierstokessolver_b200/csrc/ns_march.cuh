@@ -105,7 +105,9 @@ struct MarchXfer {
   long long dbL, dbR;                        // coarse right-hand side (RES == 1)
   int pushw, nxc;                            // columns pushed per side; coarse columns of this slab
   int zone;                                  // chunks starting within `zone` columns of a slab end push, signal and wait
-  const PeerTable* pt;                       // peer map + this rank's control header (arrival / sent counters)
+  const PeerTable* pt;                       // peer map (gather, reductions)
+  unsigned long long* hdr;                   // this rank's control header (arrival / sent counters)
+  long long offL, offR;                      // arena offsets (8-byte words) of the neighbours, 0 = none
   unsigned incL, incR;                       // CTAs of this launch that signal leftwards / rightwards (the same on every rank)
   int rb;                                    // > 0: the first two chunks are the short boundary chunks [0, rb) and [nx - rb, nx)
   int gather;                                // RES == 1 onto a replicated coarse level: store the slab on every rank
@@ -223,6 +225,7 @@ struct Marcher {
   }
 };
 
+// NOTE: no minBlocksPerSM here -- naming one (even 1) makes ptxas spend 15-40 more registers on every variant.
 template <int NSW, bool PROLONG, int RES, int PF, bool SOR = false, bool PUSH = false>
 __global__ void __launch_bounds__(MARCH_THREADS)
 k_march(LevelGeom g, const double* __restrict__ mcx, const double* __restrict__ mcy, const double* __restrict__ xin,
@@ -258,14 +261,13 @@ k_march(LevelGeom g, const double* __restrict__ mcx, const double* __restrict__ 
   if (PUSH && xf.zone && threadIdx.x == 0) {   // halo columns of this chunk come from a neighbour's push
     // what has arrived from the left is what every rank has sent rightwards so far, and vice versa; the counts are
     // kept on the device (updated by the last CTA of every launch) so that a replayed graph stays consistent
-    const PeerTable* pt = xf.pt;
-    if (ib < xf.zone && pt->rank > 0) {
-      const unsigned long long need = pt->hdr[HDR_SENT_R];
-      if (need) wait_word(pt->hdr + HDR_ARR_L, need, false, pt->err);
+    if (ib < xf.zone && xf.offL) {
+      const unsigned long long need = xf.hdr[HDR_SENT_R];
+      if (need) wait_word(xf.hdr + HDR_ARR_L, need, false, xf.pt->err);
     }
-    if (ie > g.nx - xf.zone && pt->rank < pt->world - 1) {
-      const unsigned long long need = pt->hdr[HDR_SENT_L];
-      if (need) wait_word(pt->hdr + HDR_ARR_R, need, false, pt->err);
+    if (ie > g.nx - xf.zone && xf.offR) {
+      const unsigned long long need = xf.hdr[HDR_SENT_L];
+      if (need) wait_word(xf.hdr + HDR_ARR_R, need, false, xf.pt->err);
     }
   }
   __syncthreads();
@@ -311,14 +313,14 @@ k_march(LevelGeom g, const double* __restrict__ mcx, const double* __restrict__ 
     __syncthreads();          // every store of this CTA happens before thread 0's fence (cumulativity)
     if (threadIdx.x == 0) {
       const PeerTable* pt = xf.pt;
-      unsigned long long* hdr = pt->hdr;
-      const bool sl = xf.zone && ib < xf.zone && pt->rank > 0, sr = xf.zone && ie > g.nx - xf.zone && pt->rank < pt->world - 1;
+      unsigned long long* hdr = xf.hdr;
+      const bool sl = xf.zone && ib < xf.zone && xf.offL, sr = xf.zone && ie > g.nx - xf.zone && xf.offR;
       const bool ga = RES == 1 && xf.gather;
       // pushed columns are visible system-wide before the neighbour is told; CTAs that pushed nothing skip the
       // system-scope fence (it is expensive, and thousands of them at the end of a pass serialise)
       if (sl || sr || ga) __threadfence_system();
-      if (sl) atomicAdd_system(hdr + pt->off[pt->rank - 1] + HDR_ARR_R, 1ull);
-      if (sr) atomicAdd_system(hdr + pt->off[pt->rank + 1] + HDR_ARR_L, 1ull);
+      if (sl) atomicAdd_system(hdr + xf.offL + HDR_ARR_R, 1ull);
+      if (sr) atomicAdd_system(hdr + xf.offR + HDR_ARR_L, 1ull);
       if (ga)
         for (int r = 0; r < pt->world; r++) atomicAdd_system(hdr + pt->off[r] + HDR_TAIL_ARR, 1ull);
       const unsigned long long total = (unsigned long long)gridDim.x * gridDim.y;

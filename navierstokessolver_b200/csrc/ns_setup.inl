@@ -137,7 +137,9 @@ static int create_impl(nsgpu_ctx* ctx, const nsgpu_grid* G, const nsgpu_params* 
   if (const char* e = getenv("NSGPU_GRAPH")) ctx->use_graph = atoi(e);
   HostPlan plan;
   {
-    int rc = make_host_plan(G, ctx->rank, ctx->world, P->max_levels, plan, ctx->err);
+    long long rep_cells = 262144;
+    if (const char* e = getenv("NSGPU_REP_CELLS")) rep_cells = atoll(e);
+    int rc = make_host_plan(G, ctx->rank, ctx->world, P->max_levels, plan, ctx->err, rep_cells);
     if (rc) return rc;
   }
   ctx->gnx = G->nx; ctx->ny = G->ny;
@@ -166,6 +168,7 @@ static int create_impl(nsgpu_ctx* ctx, const nsgpu_grid* G, const nsgpu_params* 
   if (const char* e = getenv("NSGPU_P2P")) ctx->use_p2p = atoi(e);
   if (const char* e = getenv("NSGPU_TRACE")) ctx->trace = atoi(e);
   if (const char* e = getenv("NSGPU_RB")) ctx->march_rb = atoi(e);
+  if (const char* e = getenv("NSGPU_RB_MINNX")) ctx->march_rb_min_nx = atoi(e);
   if (ctx->world > 1 && ctx->world <= MAX_RANKS && ctx->use_p2p && plan.rect && plan.levels[0].gnx % ctx->world == 0) {   // equal slabs: equal arena layouts
     size_t doubles = 0;
     for (size_t l = 0; l < plan.levels.size(); l++) {
@@ -251,7 +254,7 @@ static int create_impl(nsgpu_ctx* ctx, const nsgpu_grid* G, const nsgpu_params* 
     int ts = 0;
     for (int l = 1; l < nl; l++)
       if ((long long)ctx->levels[l].g.gnx * ctx->levels[l].g.ny <= TAIL_MAX_CELLS) { ts = l; break; }
-    if (plan.rep_start > 0 && ts != plan.rep_start) { ctx->err = "internal: replicated levels do not start at the coarse tail"; return NSGPU_ERR_ARG; }
+    if (plan.rep_start > 0 && (ts == 0 || ts < plan.rep_start)) { ctx->err = "internal: the coarse tail starts on a distributed level"; return NSGPU_ERR_ARG; }
     if (ts > 0 && nl - ts <= TAIL_MAX_LEVELS) {
       for (int op = 0; op < 2; op++) {
         TailDesc& T = ctx->tail[op];

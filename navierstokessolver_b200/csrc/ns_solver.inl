@@ -114,21 +114,23 @@ static int march_wave(MarchKernel kern) {
 // Chunk length (columns per CTA).  Every warp marches `ri + ovh` columns and the CTAs run in ceil(ctas / wave) waves
 // of equal work, so the estimated time is waves * (ri + ovh): exact multiples of a wave win on the big levels, the
 // shortest chunks (most warps) on the small, latency-bound ones.
-static inline int march_chunk(const nsgpu_ctx* ctx, const Level& L, int uj, int ovh, int wave) {
+static inline int march_chunk(const nsgpu_ctx* ctx, const Level& L, int uj, int ovh, int wave, int rb = 0) {
+  // rb > 0: two short boundary chunks of rb columns each come on top of the chunks of the interior
   const int gx = ((L.g.ny + uj - 1) / uj + MARCH_WARPS - 1) / MARCH_WARPS;
+  const int nxi = L.g.nx - 2 * rb, extra = rb ? 2 : 0;
   int ri = 0;
-  if (ctx->march_ri > 0) ri = std::min(ctx->march_ri + (ctx->march_ri & 1), L.g.nx + (L.g.nx & 1));
+  if (ctx->march_ri > 0) ri = std::min(ctx->march_ri + (ctx->march_ri & 1), nxi + (nxi & 1));
   else {
     long long best = -1;
-    const int hi = std::min(L.g.nx + (L.g.nx & 1), 1024);
+    const int hi = std::min(nxi + (nxi & 1), 1024);
     for (int r = 4; r <= hi; r += 2) {
-      const long long ctas = (long long)gx * ((L.g.nx + r - 1) / r);
+      const long long ctas = (long long)gx * (extra + (nxi + r - 1) / r);
       const long long cost = ((ctas + wave - 1) / wave) * (r + ovh);
       if (best < 0 || cost < best) { best = cost; ri = r; }
     }
     if (ri == 0) ri = 4;
   }
-  while ((long long)gx * ((L.g.nx + ri - 1) / ri) > RED_MAX_BLOCKS) ri *= 2;
+  while ((long long)gx * (extra + (nxi + ri - 1) / ri) > RED_MAX_BLOCKS) ri *= 2;
   return ri;
 }
 
@@ -151,7 +153,8 @@ static int march_pass(nsgpu_ctx* ctx, const Level& L, OpCoef c, int nsw, double*
   xf.omega = omega;
   const int uj = march_uj(nsw, res);
   // several ranks: push the boundary columns into the neighbours' halos from inside the pass (peer memory over NVLink)
-  const bool push = ctx->world > 1 && ctx->use_p2p && ctx->arena && !L.replicated && (ctx->peerL || ctx->peerR);
+  static const bool nopush = getenv("NSGPU_NOPUSH") != nullptr;   // debugging: arena mapped, halo columns through NCCL
+  const bool push = ctx->world > 1 && ctx->use_p2p && ctx->arena && !L.replicated && (ctx->peerL || ctx->peerR) && !nopush;
   const bool push_b = push && Cr && !Cr->replicated;
   MarchKernel kern = nullptr;
 #define NS_MARCH(NSW, PRO, RES, PF) do { if (push) kern = k_march<NSW, PRO, RES, PF, false, true>; else kern = k_march<NSW, PRO, RES, PF, false, false>; } while (0)
@@ -172,16 +175,16 @@ static int march_pass(nsgpu_ctx* ctx, const Level& L, OpCoef c, int nsw, double*
   else { if (Cp) NS_MARCH_RES(2, true); else NS_MARCH_RES(2, false); }
 #undef NS_MARCH_RES
 #undef NS_MARCH
-  const int ri = march_chunk(ctx, L, uj, 2 * lead + 2 * nsw + 2, march_wave(kern));
-  dim3 grid(((L.g.ny + uj - 1) / uj + MARCH_WARPS - 1) / MARCH_WARPS, (L.g.nx + ri - 1) / ri);
   // several ranks: short boundary chunks (even width >= the push zone), see k_march
   int rb = 0;
-  if (push && ctx->march_rb > 0) {
+  if (push && ctx->march_rb > 0 && L.g.nx >= ctx->march_rb_min_nx) {
     rb = std::max(ctx->march_rb, 2 * (HX - 1));
     rb += rb & 1;
-    const unsigned gy = 2 + (unsigned)((L.g.nx - 2 * rb + ri - 1) / ri);
-    if (L.g.nx >= 2 * rb + 4 && (L.g.nx & 1) == 0 && (long long)grid.x * gy <= RED_MAX_BLOCKS) grid.y = gy; else rb = 0;
+    if (L.g.nx < 2 * rb + 4 || (L.g.nx & 1)) rb = 0;
   }
+  const int ri = march_chunk(ctx, L, uj, 2 * lead + 2 * nsw + 2, march_wave(kern), rb);
+  dim3 grid(((L.g.ny + uj - 1) / uj + MARCH_WARPS - 1) / MARCH_WARPS, (L.g.nx + ri - 1) / ri);
+  if (rb) grid.y = 2 + (unsigned)((L.g.nx - 2 * rb + ri - 1) / ri);
   const size_t sh = (size_t)3 * (std::max(ri, rb) + 2 * lead + 2 * nsw + 8) * sizeof(double);   // >= nrows of k_march
   const bool gather = push && Cr && Cr->replicated;   // the slab of the replicated coarse right-hand side goes to every rank
   if (push) {
@@ -197,6 +200,7 @@ static int march_pass(nsgpu_ctx* ctx, const Level& L, OpCoef c, int nsw, double*
     }
     xf.zone = xf.pushw * (push_b ? L.cx : 1);
     xf.pt = ctx->d_pt;
+    xf.hdr = (unsigned long long*)ctx->arena; xf.offL = offL; xf.offR = offR;
     xf.gather = gather ? 1 : 0;
     // chunks that start inside the left zone / end inside the right zone signal once per CTA
     const int gy = (int)grid.y, zone = std::min(xf.zone, L.g.nx);
@@ -219,7 +223,11 @@ static int march_pass(nsgpu_ctx* ctx, const Level& L, OpCoef c, int nsw, double*
     if (Cr) ctx->halo_w.erase(Cr->b);
   }
   NS_LAUNCH_CHECK();
-  if (gather) return 0;
+  if (gather) {
+    k_wait_gather<<<1, 1, 0, ctx->stream>>>(ctx->d_pt, ctx->last_gather_ctas);
+    NS_LAUNCH_CHECK();
+    return 0;
+  }
   if (Cr && Cr->replicated && !L.replicated && ctx->world > 1) {
     // every rank contributes its slab of the coarse right-hand side; in place: the slabs are contiguous column ranges
     const size_t count = (size_t)(L.g.nx / L.cx) * Cr->g.ld;
@@ -249,9 +257,8 @@ static int vcycle_fused(nsgpu_ctx* ctx, int l, OpCoef c, double** x, double** xt
   Level& L = ctx->levels[l];
   if (ctx->tail_start > 0 && l == ctx->tail_start && L.march_ok[c.op]) {   // the rest of the cycle in one single-CTA kernel
     const TailDesc& T = ctx->tail[c.op];
-    const bool gathered = ctx->d_pt && L.replicated && ctx->last_gather_ctas > 0;
     trace_begin(ctx, 99999);
-    k_coarse_tail<<<1, TAIL_THREADS, (size_t)T.smem_doubles * sizeof(double), ctx->stream>>>(T, b, *x, gathered ? ctx->d_pt : nullptr, ctx->last_gather_ctas);
+    k_coarse_tail<<<1, TAIL_THREADS, (size_t)T.smem_doubles * sizeof(double), ctx->stream>>>(T, b, *x, nullptr, 0u);
     trace_end(ctx);
     NS_LAUNCH_CHECK();
     return 0;
