@@ -38,9 +38,10 @@ struct SolveResult { int cycles = 0; double rel = 0.0; bool converged = false; b
 struct SolveGraph {
   cudaGraph_t graph = nullptr;
   cudaGraphExec_t exec = nullptr;
-  const double *x = nullptr, *xt = nullptr, *b = nullptr;   // buffers the graph was built for
+  const double *x = nullptr, *xt = nullptr, *b = nullptr, *x0 = nullptr;   // buffers the graph was built for
   double rtol = 0;
   int launches_fixed = 0, launches_body = 0;                 // kernels outside / inside the loop body
+  int head_iterations = 0;                                   // iterations the head runs itself (counted in launches_fixed)
 };
 
 }  // namespace nsgpu

@@ -184,6 +184,7 @@ struct CtlEpilogue {
     if (c->cycles > 0) c->total_cycles += 1;
     const bool zero = !(c->bn2 > 0.0);
     c->zero_rhs = zero ? 1 : 0;
+    if (zero) c->cycles = 0;   // x = 0 is the answer, whatever ran before
     const bool go = !zero && (rn2 > c->tol2 * c->bn2) && (c->cycles < c->max_cycles) && (rn2 == rn2);
     c->go = go ? 1 : 0;
     if (!go && !zero && !(rn2 <= c->tol2 * c->bn2)) c->fails += 1;
@@ -191,9 +192,10 @@ struct CtlEpilogue {
   }
 };
 
-// ctl <- start of a solve: cycles = -1 (the first residual reduction brings it to 0)
-__global__ void k_ctl_init(SolveCtl* c, double tol2, int max_cycles, unsigned long long handle) {
-  c->tol2 = tol2; c->max_cycles = max_cycles; c->cycles = -1; c->go = 0; c->zero_rhs = 0; c->handle = handle; c->rn2 = 0.0;
+// ctl <- start of a solve: cycles0 = -1 when the first residual reduction is the initial guess' (it brings it to 0),
+// 0 when it already closes the first iteration
+__global__ void k_ctl_init(SolveCtl* c, double tol2, int max_cycles, unsigned long long handle, int cycles0) {
+  c->tol2 = tol2; c->max_cycles = max_cycles; c->cycles = cycles0; c->go = 0; c->zero_rhs = 0; c->handle = handle; c->rn2 = 0.0;
 }
 // x <- 0 when the right-hand side was identically zero (KSPSolve returns x = 0 for b = 0)
 __global__ void __launch_bounds__(256) k_zero_if(size_t n, double* __restrict__ x, const SolveCtl* __restrict__ c) {

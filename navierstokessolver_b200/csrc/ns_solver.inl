@@ -237,12 +237,13 @@ static int march_pass(nsgpu_ctx* ctx, const Level& L, OpCoef c, int nsw, double*
 }
 
 // `n` sweeps as passes of two (and one single if n is odd).  first_* apply to the first pass, last_* to the last.
+// src0: the first pass reads its iterate from there instead of *x (initial guess kept in another array).
 static int march_sweeps(nsgpu_ctx* ctx, const Level& L, OpCoef c, int n, double** x, double** xt, const double* b, bool xzero,
-                        const Level* Cp, double* xc, const Level* Cr, double* norm_out, SolveCtl* ctl) {
+                        const Level* Cp, double* xc, const Level* Cr, double* norm_out, SolveCtl* ctl, double* src0 = nullptr) {
   for (int k = 0; k < n;) {
     const int nsw = (n - k >= 2) ? 2 : 1;
     const bool first = k == 0, last = k + nsw >= n;
-    int rc = march_pass(ctx, L, c, nsw, (xzero && first) ? nullptr : *x, b, *xt, first ? Cp : nullptr, first ? xc : nullptr,
+    int rc = march_pass(ctx, L, c, nsw, (xzero && first) ? nullptr : (first && src0 ? src0 : *x), b, *xt, first ? Cp : nullptr, first ? xc : nullptr,
                         last ? Cr : nullptr, last ? norm_out : nullptr, last ? ctl : nullptr);
     if (rc) return rc;
     std::swap(*x, *xt);
@@ -253,7 +254,7 @@ static int march_sweeps(nsgpu_ctx* ctx, const Level& L, OpCoef c, int n, double*
 
 // One V(nu_pre, nu_post) cycle with every transfer fused into a smoothing pass: two passes per level.
 static int vcycle_fused(nsgpu_ctx* ctx, int l, OpCoef c, double** x, double** xt, const double* b, bool xzero, double* norm_out,
-                        SolveCtl* ctl) {
+                        SolveCtl* ctl, double* src0 = nullptr) {
   Level& L = ctx->levels[l];
   if (ctx->tail_start > 0 && l == ctx->tail_start && L.march_ok[c.op]) {   // the rest of the cycle in one single-CTA kernel
     const TailDesc& T = ctx->tail[c.op];
@@ -265,11 +266,11 @@ static int vcycle_fused(nsgpu_ctx* ctx, int l, OpCoef c, double** x, double** xt
   }
   if (l == (int)ctx->levels.size() - 1) {
     const int n = ctx->levels.size() == 1 ? ctx->nu_pre + ctx->nu_post : L.coarse_sweeps;
-    return march_sweeps(ctx, L, c, n, x, xt, b, xzero, nullptr, nullptr, nullptr, norm_out, ctl);
+    return march_sweeps(ctx, L, c, n, x, xt, b, xzero, nullptr, nullptr, nullptr, norm_out, ctl, src0);
   }
   Level& C = ctx->levels[l + 1];
   int rc;
-  if ((rc = march_sweeps(ctx, L, c, ctx->nu_pre, x, xt, b, xzero, nullptr, nullptr, &C, nullptr, nullptr))) return rc;
+  if ((rc = march_sweeps(ctx, L, c, ctx->nu_pre, x, xt, b, xzero, nullptr, nullptr, &C, nullptr, nullptr, src0))) return rc;
   double *cx = C.x, *cxt = C.xt;
   if ((rc = vcycle_fused(ctx, l + 1, c, &cx, &cxt, C.b, true, nullptr, nullptr))) return rc;
   C.x = cx; C.xt = cxt;
@@ -526,11 +527,11 @@ static int solve_bicgstab(nsgpu_ctx* ctx, OpCoef c, double** xp, double** xtp, c
 
 // One iteration of a device-controlled solve: a V-cycle, or (velocity, SOR mode) four over-relaxed sweeps; the last
 // pass reduces the residual norm and its epilogue updates the control block.
-static int solve_body(nsgpu_ctx* ctx, int slot, OpCoef c, double** x, double** xt, const double* b) {
+static int solve_body(nsgpu_ctx* ctx, int slot, OpCoef c, double** x, double** xt, const double* b, double* src0 = nullptr) {
   SolveCtl* ctl = ctx->d_ctl + slot;
   if (c.op == 0 && ctx->vel_omega > 0.0) {
     const Level& L = ctx->levels[0];
-    int rc = march_pass(ctx, L, c, 2, *x, b, *xt, nullptr, nullptr, nullptr, nullptr, nullptr, ctx->vel_omega);
+    int rc = march_pass(ctx, L, c, 2, src0 ? src0 : *x, b, *xt, nullptr, nullptr, nullptr, nullptr, nullptr, ctx->vel_omega);
     if (rc) return rc;
     std::swap(*x, *xt);
     rc = march_pass(ctx, L, c, 2, *x, b, *xt, nullptr, nullptr, nullptr, &ctl->rn2, ctl, ctx->vel_omega);
@@ -538,16 +539,32 @@ static int solve_body(nsgpu_ctx* ctx, int slot, OpCoef c, double** x, double** x
     std::swap(*x, *xt);
     return 0;
   }
-  return vcycle_fused(ctx, 0, c, x, xt, b, false, &ctl->rn2, ctl);
+  return vcycle_fused(ctx, 0, c, x, xt, b, false, &ctl->rn2, ctl, src0);
 }
 
-static int solve_head(nsgpu_ctx* ctx, int slot, OpCoef c, double* x, const double* b, double rtol, unsigned long long handle) {
+// Head of a solve: |b|^2, then the FIRST iteration, unconditionally, reading the initial guess from x0 (which may be
+// another array: no copy of the guess, no separate residual pass for it).  Its residual reduction sets the loop
+// condition.  The reference's KSP tests the initial residual first; here a guess that is already converged costs one
+// iteration more and comes out more accurate.
+static int solve_head(nsgpu_ctx* ctx, int slot, OpCoef c, double* x, double* xt, double* x0, const double* b, double rtol,
+                      unsigned long long handle) {
   const Level& L = ctx->levels[0];
   SolveCtl* ctl = ctx->d_ctl + slot;
-  k_ctl_init<<<1, 1, 0, ctx->stream>>>(ctl, rtol * rtol, ctx->max_cycles, handle);
+  const bool iterate = (c.op == 0 && ctx->vel_omega > 0.0) || ctx->nu_pre >= 1 || ctx->levels.size() == 1;
+  k_ctl_init<<<1, 1, 0, ctx->stream>>>(ctl, rtol * rtol, ctx->max_cycles, handle, iterate ? 0 : -1);
   NS_LAUNCH_CHECK();
   int rc;
   if ((rc = norm2_vec(ctx, L, b, &ctl->bn2))) return rc;
+  if (iterate) {
+    double *xa = x, *xb = xt;
+    if ((rc = solve_body(ctx, slot, c, &xa, &xb, b, x0 && x0 != x ? x0 : nullptr))) return rc;
+    if (xa != x) { ctx->err = "internal: an iteration does not return to its buffer"; return NSGPU_ERR_ARG; }
+    return 0;
+  }
+  if (x0 && x0 != x) {
+    cudaError_t e = cudaMemcpyAsync(x, x0, L.stride * sizeof(double), cudaMemcpyDeviceToDevice, ctx->stream);
+    if (e != cudaSuccess) { ctx->err = cudaGetErrorString(e); return NSGPU_ERR_CUDA; }
+  }
   return residual_norm2(ctx, L, c, x, b, &ctl->rn2, ctl);
 }
 
@@ -572,10 +589,10 @@ static int solve_tail(nsgpu_ctx* ctx, int slot, double* x) {
   } while (0)
 
 // Builds head -> WHILE(go){ V-cycle + residual norm } -> tail for (x, xt, b).  Returns 0 ok, 1 unsupported, < 0 error.
-static int build_solve_graph_(nsgpu_ctx* ctx, int slot, OpCoef c, double* x, double* xt, const double* b, double rtol);
-static int build_solve_graph(nsgpu_ctx* ctx, int slot, OpCoef c, double* x, double* xt, const double* b, double rtol) {
+static int build_solve_graph_(nsgpu_ctx* ctx, int slot, OpCoef c, double* x, double* xt, double* x0, const double* b, double rtol);
+static int build_solve_graph(nsgpu_ctx* ctx, int slot, OpCoef c, double* x, double* xt, double* x0, const double* b, double rtol) {
   ctx->capturing = true; ctx->capture_nccl = false;
-  int rc = build_solve_graph_(ctx, slot, c, x, xt, b, rtol);
+  int rc = build_solve_graph_(ctx, slot, c, x, xt, x0, b, rtol);
   ctx->capturing = false;
   if (rc == 0 && ctx->capture_nccl) {
     fprintf(stderr, "nsgpu: a solve would need NCCL inside its loop; direct launches instead of graphs\n");
@@ -583,7 +600,7 @@ static int build_solve_graph(nsgpu_ctx* ctx, int slot, OpCoef c, double* x, doub
   }
   return rc;
 }
-static int build_solve_graph_(nsgpu_ctx* ctx, int slot, OpCoef c, double* x, double* xt, const double* b, double rtol) {
+static int build_solve_graph_(nsgpu_ctx* ctx, int slot, OpCoef c, double* x, double* xt, double* x0, const double* b, double rtol) {
   SolveGraph& G = ctx->sgraph[slot];
   if (G.exec) { cudaGraphExecDestroy(G.exec); G.exec = nullptr; }
   if (G.graph) { cudaGraphDestroy(G.graph); G.graph = nullptr; }
@@ -595,7 +612,7 @@ static int build_solve_graph_(nsgpu_ctx* ctx, int slot, OpCoef c, double* x, dou
   int rc;
   // head
   NS_GRAPH_TRY(cudaStreamBeginCaptureToGraph(ctx->stream, G.graph, nullptr, nullptr, 0, mode));
-  rc = solve_head(ctx, slot, c, x, b, rtol, (unsigned long long)handle);
+  rc = solve_head(ctx, slot, c, x, xt, x0, b, rtol, (unsigned long long)handle);
   cudaStreamCaptureStatus st;
   const cudaGraphNode_t* deps = nullptr;
   size_t ndeps = 0;
@@ -636,21 +653,24 @@ static int build_solve_graph_(nsgpu_ctx* ctx, int slot, OpCoef c, double* x, dou
   ctx->launches = l0;   // capture is not execution
   G.launches_fixed = (int)((l1 - l0) + (l3 - l2));
   G.launches_body = (int)(l2 - l1);
-  G.x = x; G.xt = xt; G.b = b; G.rtol = rtol;
+  G.x = x; G.xt = xt; G.b = b; G.x0 = x0; G.rtol = rtol;
+  G.head_iterations = ((c.op == 0 && ctx->vel_omega > 0.0) || ctx->nu_pre >= 1 || ctx->levels.size() == 1) ? 1 : 0;
   return 0;
 }
 
 // Issues the whole solve on the stream; results land in h_ctl[slot] (decode_solve after a synchronize).
-static int solve_mg_dev(nsgpu_ctx* ctx, int slot, OpCoef c, double** x, double** xt, const double* b, double rtol) {
+// x0: where the initial guess is (nullptr or *x: in place)
+static int solve_mg_dev(nsgpu_ctx* ctx, int slot, OpCoef c, double** x, double** xt, double* x0, const double* b, double rtol) {
   int rc;
+  if (!x0) x0 = *x;
   if (ctx->world > 1) {   // the only NCCL step of the solve: the initial guess' halo columns, as wide as the passes push
-    if ((rc = halo_exchange(ctx, ctx->levels[0], *x, HX - 1))) return rc;
-    ctx->halo_w[*x] = std::min(HX - 1, ctx->levels[0].g.nx);
+    if ((rc = halo_exchange(ctx, ctx->levels[0], x0, HX - 1))) return rc;
+    ctx->halo_w[x0] = std::min(HX - 1, ctx->levels[0].g.nx);
   }
   if (ctx->use_graph) {
     SolveGraph& G = ctx->sgraph[slot];
-    if (!G.exec || G.x != *x || G.xt != *xt || G.b != b || G.rtol != rtol) {
-      rc = build_solve_graph(ctx, slot, c, *x, *xt, b, rtol);
+    if (!G.exec || G.x != *x || G.xt != *xt || G.b != b || G.x0 != x0 || G.rtol != rtol) {
+      rc = build_solve_graph(ctx, slot, c, *x, *xt, x0, b, rtol);
       if (rc < 0) return rc;
       if (rc > 0) {
         cudaStreamCaptureStatus st = cudaStreamCaptureStatusNone;
@@ -668,7 +688,7 @@ static int solve_mg_dev(nsgpu_ctx* ctx, int slot, OpCoef c, double** x, double**
       return 0;
     }
   }
-  if ((rc = solve_head(ctx, slot, c, *x, b, rtol, 0ull))) return rc;
+  if ((rc = solve_head(ctx, slot, c, *x, *xt, x0, b, rtol, 0ull))) return rc;
   for (;;) {
     cudaError_t e = cudaMemcpyAsync(ctx->h_ctl + slot, ctx->d_ctl + slot, sizeof(SolveCtl), cudaMemcpyDeviceToHost, ctx->stream);
     if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
@@ -687,7 +707,8 @@ static void decode_solve(nsgpu_ctx* ctx, int slot, SolveResult* out) {
   out->converged = !(h.bn2 > 0) || h.rn2 <= h.tol2 * h.bn2;
   const int new_cycles = h.total_cycles - ctx->seen_cycles[slot];
   if (ctx->graph_cycles_pending[slot]) {
-    ctx->launches += (int64_t)new_cycles * ctx->sgraph[slot].launches_body;
+    const int in_heads = ctx->graph_cycles_pending[slot] * ctx->sgraph[slot].head_iterations;   // already in launches_fixed
+    ctx->launches += (int64_t)std::max(new_cycles - in_heads, 0) * ctx->sgraph[slot].launches_body;
     ctx->graph_cycles_pending[slot] = 0;
   }
   if (slot == 2) ctx->fine_sweeps_phi += (double)new_cycles * (ctx->nu_pre + ctx->nu_post);
@@ -701,9 +722,13 @@ static inline bool dev_solve_ok(const nsgpu_ctx* ctx, OpCoef c) {
 }
 
 // slot: 0 = u, 1 = v, 2 = phi.  On the device-controlled path the result is pending until finish_results().
-static int solve(nsgpu_ctx* ctx, int slot, OpCoef c, double** x, const double* b, double rtol, SolveResult* out) {
-  if (dev_solve_ok(ctx, c)) { out->pending = true; return solve_mg_dev(ctx, slot, c, x, &ctx->tmp, b, rtol); }
+static int solve(nsgpu_ctx* ctx, int slot, OpCoef c, double** x, const double* b, double rtol, SolveResult* out, double* x0 = nullptr) {
+  if (dev_solve_ok(ctx, c)) { out->pending = true; return solve_mg_dev(ctx, slot, c, x, &ctx->tmp, x0, b, rtol); }
   out->pending = false;
+  if (x0 && x0 != *x) {   // host-driven solvers iterate in place
+    cudaError_t e = cudaMemcpyAsync(*x, x0, ctx->levels[0].stride * sizeof(double), cudaMemcpyDeviceToDevice, ctx->stream);
+    if (e != cudaSuccess) { ctx->err = cudaGetErrorString(e); return NSGPU_ERR_CUDA; }
+  }
   if (ctx->solver == 1) return solve_bicgstab(ctx, c, x, &ctx->tmp, b, rtol, out);
   return solve_mg(ctx, c, x, &ctx->tmp, b, rtol, out);
 }
@@ -737,13 +762,11 @@ static int phase_velocity(nsgpu_ctx* ctx, SolveResult* ru, SolveResult* rv) {   
   ctx->halo_w.clear();   // every field may have been rewritten by a non-marching kernel since
   const Level& L = ctx->levels[0];
   // initial guess u^n (the reference starts from zero; the converged u* is the same to tolerance)
-  cudaMemcpyAsync(ctx->ustar, ctx->u, L.stride * sizeof(double), cudaMemcpyDeviceToDevice, ctx->stream);
-  cudaMemcpyAsync(ctx->vstar, ctx->v, L.stride * sizeof(double), cudaMemcpyDeviceToDevice, ctx->stream);
   int rc;
   if ((rc = halo_exchange(ctx, L, ctx->rhs_u, HX - 1))) return rc;   // the fused passes recompute up to 4 halo columns
   if ((rc = halo_exchange(ctx, L, ctx->rhs_v, HX - 1))) return rc;
-  if ((rc = solve(ctx, 0, coef_v(ctx), &ctx->ustar, ctx->rhs_u, ctx->rtol_u, ru))) return rc;
-  if ((rc = solve(ctx, 1, coef_v(ctx), &ctx->vstar, ctx->rhs_v, ctx->rtol_u, rv))) return rc;
+  if ((rc = solve(ctx, 0, coef_v(ctx), &ctx->ustar, ctx->rhs_u, ctx->rtol_u, ru, ctx->u))) return rc;
+  if ((rc = solve(ctx, 1, coef_v(ctx), &ctx->vstar, ctx->rhs_v, ctx->rtol_u, rv, ctx->v))) return rc;
   return 0;
 }
 
