@@ -181,6 +181,44 @@ struct StepConst { double dt, re; };
 
 struct RhsOut { double rhs_u, rhs_v, nu, nv; };
 
+// ApplyBoundaryConditions (FS.cpp:458-510) for a cell that touches an edge: adds the boundary terms to (ru, rv).
+// gpx, gpy point at the cell.
+template <bool RECT>
+NS_HD void rhs_boundary_terms(const LevelGeom& g, const EdgeDev* edges, StepConst sc, unsigned f, int i, int j,
+                              const double* gpx, const double* gpy, double& ru, double& rv) {
+  const int ld = g.ld;
+  const double hxi = g.hx[i + HX], hyj = g.hy[j + PJ];
+  const double ire = 1.0 / sc.re;
+  int first = 0;
+  while (f & (1u << first)) first++;
+  double D;
+  if (first < 2) {  // first adjacent edge is vertical: d/dy of dphi/dx
+    const double r0 = g.rsy[j - 1 + PJ], r1 = g.rsy[j + PJ];
+    if (!(f & F_N)) D = 2.0 * (gpx[0] - gpx[-1]) * r0;
+    else if (!(f & F_S)) D = 2.0 * (gpx[1] - gpx[0]) * r1;
+    else D = gpx[1] * r1 - gpx[-1] * r0 - gpx[0] * (r1 - r0);
+  } else {          // horizontal: d/dx of dphi/dy
+    const double r0 = g.rsx[i - 1 + HX], r1 = g.rsx[i + HX];
+    if (!(f & F_E)) D = 2.0 * (gpy[0] - gpy[-ld]) * r0;
+    else if (!(f & F_W)) D = 2.0 * (gpy[ld] - gpy[0]) * r1;
+    else D = gpy[ld] * r1 - gpy[-ld] * r0 - gpy[0] * (r1 - r0);
+  }
+  for (int k = 0; k < 4; k++) {
+    if (f & (1u << k)) continue;
+    const EdgeDev e = edges[side_edge_id<RECT>(g, i, j, k)];
+    const double n = (k & 1) ? 1.0 : -1.0;
+    if (k < 2) {
+      const double cf = sc.dt * (0.5 * ire * g.bx[i + HX]);
+      if (e.outflow) { rv += cf * (sc.dt * n * hxi * D); }
+      else { ru += cf * e.cu; rv += cf * (e.cv + 2.0 * sc.dt * (gpy[0] + n * hxi * D * 0.5)); }
+    } else {
+      const double cf = sc.dt * (0.5 * ire * g.by[j + PJ]);
+      if (e.outflow) { ru += cf * (sc.dt * n * hyj * D); }
+      else { rv += cf * e.cv; ru += cf * (e.cu + 2.0 * sc.dt * (gpx[0] + n * hyj * D * 0.5)); }
+    }
+  }
+}
+
 // ConstructRHS_V for cell (i, j).  u, v, gpx, gpy point at the cell; nu0/nv0 = convectiveDer_{u,v}0[id].
 template <bool RECT>
 NS_HD RhsOut rhs_cell(const LevelGeom& g, const EdgeDev* edges, StepConst sc, int i, int j, const double* u,
@@ -257,36 +295,7 @@ NS_HD RhsOut rhs_cell(const LevelGeom& g, const EdgeDev* edges, StepConst sc, in
   double rv = vc + 0.5 * sc.dt * nv0 + diff_v - 1.5 * sc.dt * out.nv;
 
   // --- ApplyBoundaryConditions (FS.cpp:458-510): only cells that touch an edge
-  if ((f & 15u) != 15u) {
-    int first = 0;
-    while (f & (1u << first)) first++;
-    double D;
-    if (first < 2) {  // first adjacent edge is vertical: d/dy of dphi/dx
-      const double r0 = g.rsy[j - 1 + PJ], r1 = g.rsy[j + PJ];
-      if (!(f & F_N)) D = 2.0 * (gpx[0] - gpx[-1]) * r0;
-      else if (!(f & F_S)) D = 2.0 * (gpx[1] - gpx[0]) * r1;
-      else D = gpx[1] * r1 - gpx[-1] * r0 - gpx[0] * (r1 - r0);
-    } else {          // horizontal: d/dx of dphi/dy
-      const double r0 = g.rsx[i - 1 + HX], r1 = g.rsx[i + HX];
-      if (!(f & F_E)) D = 2.0 * (gpy[0] - gpy[-ld]) * r0;
-      else if (!(f & F_W)) D = 2.0 * (gpy[ld] - gpy[0]) * r1;
-      else D = gpy[ld] * r1 - gpy[-ld] * r0 - gpy[0] * (r1 - r0);
-    }
-    for (int k = 0; k < 4; k++) {
-      if (f & (1u << k)) continue;
-      const EdgeDev e = edges[side_edge_id<RECT>(g, i, j, k)];
-      const double n = (k & 1) ? 1.0 : -1.0;
-      if (k < 2) {
-        const double cf = sc.dt * (0.5 * ire * g.bx[i + HX]);
-        if (e.outflow) { rv += cf * (sc.dt * n * hxi * D); }
-        else { ru += cf * e.cu; rv += cf * (e.cv + 2.0 * sc.dt * (gpy[0] + n * hxi * D * 0.5)); }
-      } else {
-        const double cf = sc.dt * (0.5 * ire * g.by[j + PJ]);
-        if (e.outflow) { ru += cf * (sc.dt * n * hyj * D); }
-        else { rv += cf * e.cv; ru += cf * (e.cu + 2.0 * sc.dt * (gpx[0] + n * hyj * D * 0.5)); }
-      }
-    }
-  }
+  if ((f & 15u) != 15u) rhs_boundary_terms<RECT>(g, edges, sc, f, i, j, gpx, gpy, ru, rv);
   out.rhs_u = ru;
   out.rhs_v = rv;
   return out;

@@ -10,6 +10,7 @@
 #include <cmath>
 #include "../../include/nsgpu.h"
 #include "ns_kernels.cuh"
+#include "ns_rhs.cuh"
 #include "ns_march.cuh"
 #include "ns_tail.cuh"
 #include "ns_hostgeom.h"
@@ -100,6 +101,7 @@ struct nsgpu_ctx {
   int trace = 0;
   std::vector<TraceEv> trace_ev;
   std::unordered_map<int, std::pair<double, long>> trace_acc;
+  int rhs_march = 1;                             // ConstructRHS_V on rectangles through k_rhs_march (NSGPU_RHS_MARCH=0: cell kernel)
   int march_rb_min_nx = 0;                       // levels with fewer columns keep uniform chunks (NSGPU_RB_MINNX)
   int march_rb = 0;                              // width of the short boundary chunks of pushing passes (NSGPU_RB, 0 = off)
   unsigned last_gather_ctas = 0;                 // CTAs of the last restriction pass that gathered onto the replicated level

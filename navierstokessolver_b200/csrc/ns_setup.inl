@@ -168,6 +168,7 @@ static int create_impl(nsgpu_ctx* ctx, const nsgpu_grid* G, const nsgpu_params* 
   if (const char* e = getenv("NSGPU_P2P")) ctx->use_p2p = atoi(e);
   if (const char* e = getenv("NSGPU_TRACE")) ctx->trace = atoi(e);
   if (const char* e = getenv("NSGPU_RB")) ctx->march_rb = atoi(e);
+  if (const char* e = getenv("NSGPU_RHS_MARCH")) ctx->rhs_march = atoi(e);
   if (const char* e = getenv("NSGPU_RB_MINNX")) ctx->march_rb_min_nx = atoi(e);
   if (ctx->world > 1 && ctx->world <= MAX_RANKS && ctx->use_p2p && plan.rect && plan.levels[0].gnx % ctx->world == 0) {   // equal slabs: equal arena layouts
     size_t doubles = 0;

@@ -750,6 +750,16 @@ static int phase_rhs(nsgpu_ctx* ctx) {   // ConstructRHS_V, FS.cpp:546
   if ((rc = halo_exchange(ctx, L, ctx->v, 2))) return rc;
   if ((rc = halo_exchange(ctx, L, ctx->gpy, 1))) return rc;
   const StepConst sc{ctx->dt, ctx->re};
+  if (ctx->rect && ctx->rhs_march && L.g.nx >= 2) {   // rectangles: marching kernel, every slope and face flux once
+    const int gx = ((L.g.ny + RHS_UJ - 1) / RHS_UJ + RHS_WARPS - 1) / RHS_WARPS;
+    const int chunks = std::max(1, std::min(L.g.nx / 8, (148 * 10 + gx - 1) / gx));
+    const int ri = (L.g.nx + chunks - 1) / chunks;
+    const dim3 grid(gx, (L.g.nx + ri - 1) / ri);
+    k_rhs_march<<<grid, RHS_THREADS, 0, ctx->stream>>>(L.g, ctx->d_edges, sc, ctx->u, ctx->v, ctx->conv_u, ctx->conv_v, ctx->gpx, ctx->gpy,
+                                                       ctx->rhs_u, ctx->rhs_v, ri);
+    NS_LAUNCH_CHECK();
+    return 0;
+  }
   const dim3 grid((L.g.ny + 127) / 128, L.g.nx);
 #define CALL(RECT) k_rhs_build<RECT><<<grid, 128, 0, ctx->stream>>>(L.g, ctx->d_edges, sc, ctx->u, ctx->v, ctx->conv_u, ctx->conv_v, ctx->gpx, ctx->gpy, ctx->rhs_u, ctx->rhs_v)
   NS_DISPATCH_RECT(ctx->rect, CALL);
