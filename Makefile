@@ -1,6 +1,6 @@
 # Build of the B200-native library, the host driver and the test-side helpers.
 #   make            libnsgpu.so (sm_100a kernels + C ABI + host Grid/FluidSolver) and bin/main
-#   make oracle     CPU oracle (test infrastructure): oracle/libnsport.so, oracle/_ref/* when /root/reference exists
+#   make oracle     CPU oracle (test infrastructure): oracle/_ref/* from the reference's sources, when /root/reference exists
 #   make emul       tests/emul/libnsemul.so: host compile of the per-cell device functions, for the CPU-only tests
 NVCC ?= nvcc
 CXX = /usr/bin/g++
@@ -23,7 +23,6 @@ bin/main: $(PKG)/libnsgpu.so $(HOST)/main/ns_main.cpp
 	$(CXX) -std=c++17 -O2 -Iinclude -I$(HOST) $(HOST)/main/ns_main.cpp -L$(PKG) -lnsgpu -Wl,-rpath,'$$ORIGIN/../$(PKG)' -o $@
 
 oracle:
-	$(MAKE) -C oracle port
 	if [ -d /root/reference/SRC ]; then $(MAKE) -C oracle ref; fi
 
 emul: tests/emul/libnsemul.so

@@ -226,7 +226,7 @@ def ours(args, rank, world, local_rank):
                 "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
                 "data": "synthetic",
                 "config": {"workload": "lid-driven cavity Re=%g from rest, %dx%d cells (%d columns per GPU), dt=0.25/%d" % (args.re, gnx, ny, nxl, n),
-                           "parallelism": "x-slabs, %d rank(s), NCCL halo exchange + scalar allreduce" % world,
+                           "parallelism": ("x-slabs, %d rank(s); solves: halo columns, norms and the replicated coarse rhs through NVLink peer memory from inside the kernels (NCCL only outside the solves)" % world) if world > 1 else "1 rank (no exchange)",
                            "solver": ("BiCGStab + V(2,2)" if args.solver else "phi: multigrid V(2,2), fused red-black GS passes; u*, v*: red-black SOR or multigrid (auto)")
                                      + ", true-residual rtol %g all solves, %s" % (args.rtol, "one CUDA graph per solve (device-side WHILE)" if args.graph else "direct launches"),
                            "levels": s.num_levels, "cache": "inputs larger than L2 (13 resident fields x %.0f MB per GPU)" % (cells_local * 8 / 1e6)},
