@@ -28,6 +28,10 @@ namespace nsgpu {
 constexpr int MARCH_WARPS = 4;                 // warps per CTA (adjacent strips)
 constexpr int MARCH_THREADS = 32 * MARCH_WARPS;
 constexpr int MARCH_PF = 3;                    // default number of columns prefetched ahead in registers
+#ifndef NS_MARCH_PFD
+#define NS_MARCH_PFD 4
+#endif
+constexpr int MARCH_PFD = NS_MARCH_PFD;   // L2 prefetch distance beyond the register ring (fused variants): lead + PF + MARCH_PFD + 2 <= HX + SLACK_COLS
 
 __host__ __device__ constexpr int march_halo(int nsw, int res) { return 2 * nsw + (res ? 2 : 0); }      // cells, y
 __host__ __device__ constexpr int march_lead(int nsw, int res) { return 2 * nsw + (res ? 1 : 0); }      // columns, x
@@ -129,6 +133,7 @@ struct Marcher {
   double* __restrict__ pbc;                         // RES == 1: next coarse column to emit
   const double* __restrict__ pxc;                   // PROLONG: coarse column base + row offset
   int ld, ny, j0, ib, ie, nxl;
+  size_t pfo;                                       // MARCH_PFD columns, in doubles
   bool useful, jstore2, jstore1, pushL, pushR;
   MarchXfer xf;
   double2 racc;
@@ -139,6 +144,13 @@ struct Marcher {
   // behind every field) and only feed pipeline stages whose results are never stored.
   __device__ __forceinline__ void load_col(int n, double2& vx, double2& vb) {
     vx = make_double2(0.0, 0.0);
+    // The register ring prefetches PF columns ahead, which is shorter than the DRAM latency on the fused variants; a
+    // register-free L2 prefetch MARCH_PFD columns further ahead turns those loads into L2 hits.  Unconditional: the
+    // SLACK_COLS columns behind every field cover it.  Not compiled into the plain sweep (PF = 6 is enough there).
+    if (MARCH_PFD > 0 && (NSW > 1 || PROLONG || RES)) {
+      if (px) asm volatile("prefetch.global.L2 [%0];" :: "l"(px + pfo));
+      asm volatile("prefetch.global.L2 [%0];" :: "l"(pb + pfo));
+    }
     if (px) { vx = *reinterpret_cast<const double2*>(px); px += ld; }
     vb = *reinterpret_cast<const double2*>(pb);
     pb += ld;
@@ -276,6 +288,7 @@ k_march(LevelGeom g, const double* __restrict__ mcx, const double* __restrict__ 
   M m;
   m.xf = xf;
   m.ld = g.ld; m.ny = g.ny; m.ib = ib; m.ie = ie; m.nxl = g.nx;
+  m.pfo = (size_t)MARCH_PFD * g.ld;
   m.pushL = PUSH && xf.dL != 0 && ib < xf.zone;
   m.pushR = PUSH && xf.dR != 0 && ie > g.nx - xf.zone;
   m.j0 = wj * UJ - HJ + 2 * lane;                            // even, >= -HJ >= -PJ
