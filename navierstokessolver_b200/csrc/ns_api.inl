@@ -113,6 +113,11 @@ int nsgpu_create(const nsgpu_grid* grid, const nsgpu_params* params, nsgpu_ctx**
 }
 
 void nsgpu_destroy(nsgpu_ctx* ctx) {
+  if (ctx && ctx->tail_dbg) {
+    long long h[64];
+    if (cudaMemcpy(h, ctx->tail_dbg, sizeof h, cudaMemcpyDeviceToHost) == cudaSuccess)
+      for (int k = 1; k < 64 && h[k]; k++) fprintf(stderr, "nsgpu tail stamp %2d  +%8lld cycles (total %8lld)\n", k, h[k] - h[k - 1], h[k] - h[0]);
+  }
   if (ctx && ctx->trace && !ctx->trace_acc.empty()) {
     std::vector<std::pair<int, std::pair<double, long>>> rows(ctx->trace_acc.begin(), ctx->trace_acc.end());
     std::sort(rows.begin(), rows.end(), [](const auto& a, const auto& b) { return a.first < b.first; });

@@ -101,6 +101,8 @@ struct nsgpu_ctx {
   int trace = 0;
   std::vector<TraceEv> trace_ev;
   std::unordered_map<int, std::pair<double, long>> trace_acc;
+  double* tail_img[2] = {nullptr, nullptr};      // per operator: the launch-invariant part of the coarse tail's shared memory (k_tail_image)
+  long long* tail_dbg = nullptr;                 // NSGPU_TAIL_DBG=1: clock64 stamps of the coarse tail's phases (printed at destroy)
   int rhs_march = 1;                             // ConstructRHS_V on rectangles through k_rhs_march (NSGPU_RHS_MARCH=0: cell kernel)
   int march_rb_min_nx = 0;                       // levels with fewer columns keep uniform chunks (NSGPU_RB_MINNX)
   int march_rb = 0;                              // width of the short boundary chunks of pushing passes (NSGPU_RB, 0 = off)

@@ -169,6 +169,7 @@ static int create_impl(nsgpu_ctx* ctx, const nsgpu_grid* G, const nsgpu_params* 
   if (const char* e = getenv("NSGPU_TRACE")) ctx->trace = atoi(e);
   if (const char* e = getenv("NSGPU_RB")) ctx->march_rb = atoi(e);
   if (const char* e = getenv("NSGPU_RHS_MARCH")) ctx->rhs_march = atoi(e);
+  if (getenv("NSGPU_TAIL_DBG")) { void* q = nullptr; if (cudaMalloc(&q, 64 * sizeof(long long)) == cudaSuccess) { cudaMemset(q, 0, 64 * sizeof(long long)); ctx->owned.push_back(q); ctx->tail_dbg = (long long*)q; } }
   if (const char* e = getenv("NSGPU_RB_MINNX")) ctx->march_rb_min_nx = atoi(e);
   if (ctx->world > 1 && ctx->world <= MAX_RANKS && ctx->use_p2p && plan.rect && plan.levels[0].gnx % ctx->world == 0) {   // equal slabs: equal arena layouts
     size_t doubles = 0;
@@ -278,15 +279,24 @@ static int create_impl(nsgpu_ctx* ctx, const nsgpu_grid* G, const nsgpu_params* 
           const int cells = (t.nx + 2) * (t.ny + 2);
           t.xoff = off; off += cells;
           t.boff = off; off += cells;
+          t.rdoff = off; off += cells;
           t.sxoff = off; off += 3 * t.nx;
           t.syoff = off; off += 3 * t.ny;
         }
-        T.smem_doubles = off;
+        T.smem_doubles = off + (off & 1);   // even: the image is copied as double2
       }
       const size_t bytes = (size_t)ctx->tail[0].smem_doubles * sizeof(double);
       if (plan.rep_start > 0 && (bytes > 200 * 1024 || nl - ts > TAIL_MAX_LEVELS)) { ctx->err = "internal: coarse tail does not fit"; return NSGPU_ERR_ARG; }
       if (bytes <= 200 * 1024) {
         NS_CUDA(cudaFuncSetAttribute(k_coarse_tail, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
+        for (int op = 0; op < 2; op++) {
+          void* q = nullptr;
+          NS_CUDA(cudaMalloc(&q, bytes));
+          ctx->owned.push_back(q);
+          ctx->tail_img[op] = (double*)q;
+          k_tail_image<<<1, TAIL_THREADS, 0, ctx->stream>>>(ctx->tail[op], ctx->tail_img[op]);
+          NS_CUDA(cudaGetLastError());
+        }
         ctx->tail_start = ts;
       }
     }

@@ -259,7 +259,7 @@ static int vcycle_fused(nsgpu_ctx* ctx, int l, OpCoef c, double** x, double** xt
   if (ctx->tail_start > 0 && l == ctx->tail_start && L.march_ok[c.op]) {   // the rest of the cycle in one single-CTA kernel
     const TailDesc& T = ctx->tail[c.op];
     trace_begin(ctx, 99999);
-    k_coarse_tail<<<1, TAIL_THREADS, (size_t)T.smem_doubles * sizeof(double), ctx->stream>>>(T, b, *x, nullptr, 0u);
+    k_coarse_tail<<<1, TAIL_THREADS, (size_t)T.smem_doubles * sizeof(double), ctx->stream>>>(T, ctx->tail_img[c.op], b, *x, nullptr, 0u, ctx->tail_dbg);
     trace_end(ctx);
     NS_LAUNCH_CHECK();
     return 0;
