@@ -31,6 +31,7 @@ static int ensure_stage(nsgpu_ctx* ctx) {
 // host compact-id order -> padded device layout
 static int upload_field(nsgpu_ctx* ctx, double* dev, const double* host) {
   ctx->halo_w.clear();
+  ctx->bn2_ready[0] = ctx->bn2_ready[1] = ctx->bn2_ready[2] = false;   // a right-hand side may be what is being replaced
   const Level& L = ctx->levels[0];
   const LevelGeom& g = L.g;
   NS_CUDA(cudaSetDevice(ctx->device));

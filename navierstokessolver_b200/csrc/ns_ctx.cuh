@@ -40,6 +40,7 @@ struct SolveGraph {
   cudaGraph_t graph = nullptr;
   cudaGraphExec_t exec = nullptr;
   const double *x = nullptr, *xt = nullptr, *b = nullptr, *x0 = nullptr;   // buffers the graph was built for
+  bool bn2_pre = false;                                      // the head takes |b|^2 from d_scal instead of reducing b
   double rtol = 0;
   int launches_fixed = 0, launches_body = 0;                 // kernels outside / inside the loop body
   int head_iterations = 0;                                   // iterations the head runs itself (counted in launches_fixed)
@@ -101,6 +102,8 @@ struct nsgpu_ctx {
   int trace = 0;
   std::vector<TraceEv> trace_ev;
   std::unordered_map<int, std::pair<double, long>> trace_acc;
+  int fuse_bn2 = 1;                              // NSGPU_FUSE_BN2=0: |b|^2 by a separate reduction pass over b
+  bool bn2_ready[3] = {false, false, false};     // |b|^2 of the next solve of slot k is already in d_scal[30 + k] (written with b)
   double* tail_img[2] = {nullptr, nullptr};      // per operator: the launch-invariant part of the coarse tail's shared memory (k_tail_image)
   long long* tail_dbg = nullptr;                 // NSGPU_TAIL_DBG=1: clock64 stamps of the coarse tail's phases (printed at destroy)
   int rhs_march = 1;                             // ConstructRHS_V on rectangles through k_rhs_march (NSGPU_RHS_MARCH=0: cell kernel)

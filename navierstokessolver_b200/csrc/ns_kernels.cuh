@@ -194,7 +194,8 @@ struct CtlEpilogue {
 
 // ctl <- start of a solve: cycles0 = -1 when the first residual reduction is the initial guess' (it brings it to 0),
 // 0 when it already closes the first iteration
-__global__ void k_ctl_init(SolveCtl* c, double tol2, int max_cycles, unsigned long long handle, int cycles0) {
+__global__ void k_ctl_init(SolveCtl* c, double tol2, int max_cycles, unsigned long long handle, int cycles0, const double* bn2_src) {
+  if (bn2_src) c->bn2 = *bn2_src;   // |b|^2 came out of the kernel that wrote b
   c->tol2 = tol2; c->max_cycles = max_cycles; c->cycles = cycles0; c->go = 0; c->zero_rhs = 0; c->handle = handle; c->rn2 = 0.0;
 }
 // x <- 0 when the right-hand side was identically zero (KSPSolve returns x = 0 for b = 0)
@@ -379,16 +380,17 @@ __global__ void __launch_bounds__(256)
 k_div_rhs(LevelGeom g, const EdgeDev* __restrict__ edges, StepConst sc, const double* __restrict__ u,
           const double* __restrict__ v, double* __restrict__ b, Reducer red, double* out) {
   const int j = blockIdx.x * blockDim.x + threadIdx.x;
-  double acc[1] = {0.0};
+  double acc[2] = {0.0, 0.0};   // sum and sum of squares: the mean to remove and |b - mean|^2 = S2 - S1^2 / n
   for (int i = chunk_lo(g.nx), i_hi = chunk_hi(g.nx); i < i_hi; i++) {
     if (j < g.ny && cell_flags<RECT>(g, i, j) != F_OUTSIDE) {
       const size_t id = cidx(g, i, j);
       const double d = div_cell<RECT>(g, edges, sc, i, j, u + id, v + id);
       b[id] = d;
       acc[0] += d;
+      acc[1] = fma(d, d, acc[1]);
     }
   }
-  grid_reduce<1, OpSum>(acc, red, out);
+  grid_reduce<2, OpSum>(acc, red, out);
 }
 
 // b -= *sum / n over fluid cells (MatNullSpaceRemove: plain arithmetic mean over ids, FS.cpp:550)
@@ -496,5 +498,7 @@ __global__ void __launch_bounds__(256) k_sum(size_t n, const double* __restrict_
 // tiny scalar kernels of the Krylov recurrences: dst = num/den
 __global__ void k_scalar_div(double* dst, const double* num, const double* den) { *dst = *num / *den; }
 __global__ void k_scalar_copy(double* dst, const double* src) { *dst = *src; }
+// |b - mean|^2 from s = {sum b, sum b^2} over n cells (inv_n = 1 / n; 0: the mean stays in)
+__global__ void k_bn2_from_sums(double* dst, const double* s, double inv_n) { *dst = fmax(s[1] - s[0] * s[0] * inv_n, 0.0); }
 
 }  // namespace nsgpu

@@ -13,6 +13,7 @@
 #pragma once
 #include <cuda_runtime.h>
 #include "ns_cell.cuh"
+#include "ns_kernels.cuh"
 
 namespace nsgpu {
 
@@ -48,7 +49,7 @@ __global__ void __launch_bounds__(RHS_THREADS)
 k_rhs_march(LevelGeom g, const EdgeDev* __restrict__ edges, StepConst sc, const double* __restrict__ u,
             const double* __restrict__ v, double* __restrict__ nu0, double* __restrict__ nv0,
             const double* __restrict__ gpx, const double* __restrict__ gpy, double* __restrict__ rhs_u,
-            double* __restrict__ rhs_v, int RI) {
+            double* __restrict__ rhs_v, int RI, Reducer red, double* __restrict__ norms) {
   const int lane = threadIdx.x & 31;
   const int wj = blockIdx.x * RHS_WARPS + (threadIdx.x >> 5);
   const int j = wj * RHS_UJ + lane - 2;                  // rows -2, -1, ny, ny+1 are zero padding (PJ = 8)
@@ -75,6 +76,7 @@ k_rhs_march(LevelGeom g, const EdgeDev* __restrict__ edges, StepConst sc, const 
   double uM = 0, uC = 0, uP = 0, uQ = 0, vM = 0, vC = 0, vP = 0, vQ = 0;
   double sxCu = 0, sxCv = 0, sxPu = 0, sxPv = 0;   // x slopes of columns i and i+1
   double cWsq = 0, cWuv = 0;                       // east-face fluxes of cell i-1 = west-face fluxes of cell i
+  double nrm[2] = {0.0, 0.0};                      // |rhs_u|^2, |rhs_v|^2 of the cells this thread stores
 
   // n: column entering the ring; cell i = n - 2 is finished; the first finished cell is ib - 1 (its east face only)
   for (int n = ib - 2; n < ie + 2; n++) {
@@ -166,11 +168,14 @@ k_rhs_march(LevelGeom g, const EdgeDev* __restrict__ edges, StepConst sc, const 
       }
       rhs_u[id] = ru;
       rhs_v[id] = rv;
+      nrm[0] = fma(ru, ru, nrm[0]);
+      nrm[1] = fma(rv, rv, nrm[1]);
       nu0[id] = nu;
       nv0[id] = nv;
     }
     cWsq = cEsq; cWuv = cEuv;
   }
+  if (norms) grid_reduce<2, OpSum>(nrm, red, norms);   // the velocity solves' |b|^2 (uniform branch)
 }
 
 }  // namespace nsgpu

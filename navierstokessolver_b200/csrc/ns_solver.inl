@@ -547,14 +547,14 @@ static int solve_body(nsgpu_ctx* ctx, int slot, OpCoef c, double** x, double** x
 // condition.  The reference's KSP tests the initial residual first; here a guess that is already converged costs one
 // iteration more and comes out more accurate.
 static int solve_head(nsgpu_ctx* ctx, int slot, OpCoef c, double* x, double* xt, double* x0, const double* b, double rtol,
-                      unsigned long long handle) {
+                      unsigned long long handle, bool bn2_pre) {
   const Level& L = ctx->levels[0];
   SolveCtl* ctl = ctx->d_ctl + slot;
   const bool iterate = (c.op == 0 && ctx->vel_omega > 0.0) || ctx->nu_pre >= 1 || ctx->levels.size() == 1;
-  k_ctl_init<<<1, 1, 0, ctx->stream>>>(ctl, rtol * rtol, ctx->max_cycles, handle, iterate ? 0 : -1);
+  k_ctl_init<<<1, 1, 0, ctx->stream>>>(ctl, rtol * rtol, ctx->max_cycles, handle, iterate ? 0 : -1, bn2_pre ? ctx->d_scal + 30 + slot : nullptr);
   NS_LAUNCH_CHECK();
   int rc;
-  if ((rc = norm2_vec(ctx, L, b, &ctl->bn2))) return rc;
+  if (!bn2_pre && (rc = norm2_vec(ctx, L, b, &ctl->bn2))) return rc;
   if (iterate) {
     double *xa = x, *xb = xt;
     if ((rc = solve_body(ctx, slot, c, &xa, &xb, b, x0 && x0 != x ? x0 : nullptr))) return rc;
@@ -589,10 +589,10 @@ static int solve_tail(nsgpu_ctx* ctx, int slot, double* x) {
   } while (0)
 
 // Builds head -> WHILE(go){ V-cycle + residual norm } -> tail for (x, xt, b).  Returns 0 ok, 1 unsupported, < 0 error.
-static int build_solve_graph_(nsgpu_ctx* ctx, int slot, OpCoef c, double* x, double* xt, double* x0, const double* b, double rtol);
-static int build_solve_graph(nsgpu_ctx* ctx, int slot, OpCoef c, double* x, double* xt, double* x0, const double* b, double rtol) {
+static int build_solve_graph_(nsgpu_ctx* ctx, int slot, OpCoef c, double* x, double* xt, double* x0, const double* b, double rtol, bool bn2_pre);
+static int build_solve_graph(nsgpu_ctx* ctx, int slot, OpCoef c, double* x, double* xt, double* x0, const double* b, double rtol, bool bn2_pre) {
   ctx->capturing = true; ctx->capture_nccl = false;
-  int rc = build_solve_graph_(ctx, slot, c, x, xt, x0, b, rtol);
+  int rc = build_solve_graph_(ctx, slot, c, x, xt, x0, b, rtol, bn2_pre);
   ctx->capturing = false;
   if (rc == 0 && ctx->capture_nccl) {
     fprintf(stderr, "nsgpu: a solve would need NCCL inside its loop; direct launches instead of graphs\n");
@@ -600,7 +600,7 @@ static int build_solve_graph(nsgpu_ctx* ctx, int slot, OpCoef c, double* x, doub
   }
   return rc;
 }
-static int build_solve_graph_(nsgpu_ctx* ctx, int slot, OpCoef c, double* x, double* xt, double* x0, const double* b, double rtol) {
+static int build_solve_graph_(nsgpu_ctx* ctx, int slot, OpCoef c, double* x, double* xt, double* x0, const double* b, double rtol, bool bn2_pre) {
   SolveGraph& G = ctx->sgraph[slot];
   if (G.exec) { cudaGraphExecDestroy(G.exec); G.exec = nullptr; }
   if (G.graph) { cudaGraphDestroy(G.graph); G.graph = nullptr; }
@@ -612,7 +612,7 @@ static int build_solve_graph_(nsgpu_ctx* ctx, int slot, OpCoef c, double* x, dou
   int rc;
   // head
   NS_GRAPH_TRY(cudaStreamBeginCaptureToGraph(ctx->stream, G.graph, nullptr, nullptr, 0, mode));
-  rc = solve_head(ctx, slot, c, x, xt, x0, b, rtol, (unsigned long long)handle);
+  rc = solve_head(ctx, slot, c, x, xt, x0, b, rtol, (unsigned long long)handle, bn2_pre);
   cudaStreamCaptureStatus st;
   const cudaGraphNode_t* deps = nullptr;
   size_t ndeps = 0;
@@ -653,7 +653,7 @@ static int build_solve_graph_(nsgpu_ctx* ctx, int slot, OpCoef c, double* x, dou
   ctx->launches = l0;   // capture is not execution
   G.launches_fixed = (int)((l1 - l0) + (l3 - l2));
   G.launches_body = (int)(l2 - l1);
-  G.x = x; G.xt = xt; G.b = b; G.x0 = x0; G.rtol = rtol;
+  G.x = x; G.xt = xt; G.b = b; G.x0 = x0; G.rtol = rtol; G.bn2_pre = bn2_pre;
   G.head_iterations = ((c.op == 0 && ctx->vel_omega > 0.0) || ctx->nu_pre >= 1 || ctx->levels.size() == 1) ? 1 : 0;
   return 0;
 }
@@ -663,14 +663,16 @@ static int build_solve_graph_(nsgpu_ctx* ctx, int slot, OpCoef c, double* x, dou
 static int solve_mg_dev(nsgpu_ctx* ctx, int slot, OpCoef c, double** x, double** xt, double* x0, const double* b, double rtol) {
   int rc;
   if (!x0) x0 = *x;
+  const bool bn2_pre = ctx->bn2_ready[slot];
+  ctx->bn2_ready[slot] = false;
   if (ctx->world > 1) {   // the only NCCL step of the solve: the initial guess' halo columns, as wide as the passes push
     if ((rc = halo_exchange(ctx, ctx->levels[0], x0, HX - 1))) return rc;
     ctx->halo_w[x0] = std::min(HX - 1, ctx->levels[0].g.nx);
   }
   if (ctx->use_graph) {
     SolveGraph& G = ctx->sgraph[slot];
-    if (!G.exec || G.x != *x || G.xt != *xt || G.b != b || G.x0 != x0 || G.rtol != rtol) {
-      rc = build_solve_graph(ctx, slot, c, *x, *xt, x0, b, rtol);
+    if (!G.exec || G.x != *x || G.xt != *xt || G.b != b || G.x0 != x0 || G.rtol != rtol || G.bn2_pre != bn2_pre) {
+      rc = build_solve_graph(ctx, slot, c, *x, *xt, x0, b, rtol, bn2_pre);
       if (rc < 0) return rc;
       if (rc > 0) {
         cudaStreamCaptureStatus st = cudaStreamCaptureStatusNone;
@@ -688,7 +690,7 @@ static int solve_mg_dev(nsgpu_ctx* ctx, int slot, OpCoef c, double** x, double**
       return 0;
     }
   }
-  if ((rc = solve_head(ctx, slot, c, *x, *xt, x0, b, rtol, 0ull))) return rc;
+  if ((rc = solve_head(ctx, slot, c, *x, *xt, x0, b, rtol, 0ull, bn2_pre))) return rc;
   for (;;) {
     cudaError_t e = cudaMemcpyAsync(ctx->h_ctl + slot, ctx->d_ctl + slot, sizeof(SolveCtl), cudaMemcpyDeviceToHost, ctx->stream);
     if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
@@ -725,6 +727,7 @@ static inline bool dev_solve_ok(const nsgpu_ctx* ctx, OpCoef c) {
 static int solve(nsgpu_ctx* ctx, int slot, OpCoef c, double** x, const double* b, double rtol, SolveResult* out, double* x0 = nullptr) {
   if (dev_solve_ok(ctx, c)) { out->pending = true; return solve_mg_dev(ctx, slot, c, x, &ctx->tmp, x0, b, rtol); }
   out->pending = false;
+  ctx->bn2_ready[slot] = false;
   if (x0 && x0 != *x) {   // host-driven solvers iterate in place
     cudaError_t e = cudaMemcpyAsync(*x, x0, ctx->levels[0].stride * sizeof(double), cudaMemcpyDeviceToDevice, ctx->stream);
     if (e != cudaSuccess) { ctx->err = cudaGetErrorString(e); return NSGPU_ERR_CUDA; }
@@ -756,10 +759,15 @@ static int phase_rhs(nsgpu_ctx* ctx) {   // ConstructRHS_V, FS.cpp:546
     const int ri = (L.g.nx + chunks - 1) / chunks;
     const dim3 grid(gx, (L.g.nx + ri - 1) / ri);
     k_rhs_march<<<grid, RHS_THREADS, 0, ctx->stream>>>(L.g, ctx->d_edges, sc, ctx->u, ctx->v, ctx->conv_u, ctx->conv_v, ctx->gpx, ctx->gpy,
-                                                       ctx->rhs_u, ctx->rhs_v, ri);
+                                                       ctx->rhs_u, ctx->rhs_v, ri, ctx->red, ctx->fuse_bn2 ? ctx->d_scal + 30 : nullptr);
     NS_LAUNCH_CHECK();
+    if (ctx->fuse_bn2) {
+      if ((rc = allreduce(ctx, ctx->d_scal + 30, 2, ncclSum))) return rc;
+      ctx->bn2_ready[0] = ctx->bn2_ready[1] = true;
+    }
     return 0;
   }
+  ctx->bn2_ready[0] = ctx->bn2_ready[1] = false;
   const dim3 grid((L.g.ny + 127) / 128, L.g.nx);
 #define CALL(RECT) k_rhs_build<RECT><<<grid, 128, 0, ctx->stream>>>(L.g, ctx->d_edges, sc, ctx->u, ctx->v, ctx->conv_u, ctx->conv_v, ctx->gpx, ctx->gpy, ctx->rhs_u, ctx->rhs_v)
   NS_DISPATCH_RECT(ctx->rect, CALL);
@@ -788,14 +796,17 @@ static int phase_div(nsgpu_ctx* ctx, bool remove_mean) {   // FS.cpp:549-550
   if ((rc = halo_exchange(ctx, L, ctx->vstar, 1))) return rc;
   const StepConst sc{ctx->dt, ctx->re};
   const dim3 grid = grid_cols(L.g, 256);
-#define CALL(RECT) k_div_rhs<RECT><<<grid, 256, 0, ctx->stream>>>(L.g, ctx->d_edges, sc, ctx->ustar, ctx->vstar, ctx->rhs_phi, ctx->red, ctx->d_scal + 16)
+#define CALL(RECT) k_div_rhs<RECT><<<grid, 256, 0, ctx->stream>>>(L.g, ctx->d_edges, sc, ctx->ustar, ctx->vstar, ctx->rhs_phi, ctx->red, ctx->d_scal + 28)
   NS_DISPATCH_RECT(ctx->rect, CALL);
 #undef CALL
   NS_LAUNCH_CHECK();
+  if ((rc = allreduce(ctx, ctx->d_scal + 28, 2, ncclSum))) return rc;
+  k_bn2_from_sums<<<1, 1, 0, ctx->stream>>>(ctx->d_scal + 32, ctx->d_scal + 28, remove_mean ? 1.0 / (double)ctx->n_cells_global : 0.0);
+  NS_LAUNCH_CHECK();
+  ctx->bn2_ready[2] = ctx->fuse_bn2 != 0;
   if (remove_mean) {
-    if ((rc = allreduce(ctx, ctx->d_scal + 16, 1, ncclSum))) return rc;
     const double inv_n = 1.0 / (double)ctx->n_cells_global;
-#define CALL(RECT) k_sub_mean<RECT><<<grid, 256, 0, ctx->stream>>>(L.g, ctx->rhs_phi, ctx->d_scal + 16, inv_n)
+#define CALL(RECT) k_sub_mean<RECT><<<grid, 256, 0, ctx->stream>>>(L.g, ctx->rhs_phi, ctx->d_scal + 28, inv_n)
     NS_DISPATCH_RECT(ctx->rect, CALL);
 #undef CALL
     NS_LAUNCH_CHECK();
