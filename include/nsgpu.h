@@ -103,6 +103,16 @@ int nsgpu_local_range(const nsgpu_ctx* ctx, int32_t* i0, int32_t* i1, int64_t* i
 /* n passes of the Solve() loop body, FS.cpp:546-557 (state stays resident on the device) */
 int nsgpu_step(nsgpu_ctx* ctx, int32_t n_steps, nsgpu_step_info* last);
 
+/* One time step with the whole state in HOST memory (what a caller that keeps the reference's Vecs on the host has:
+ * u, v, phi, convectiveDer_u0/v0, gradphi_x/y, FS.h:22-33; compact-id order, this rank's range; page-locked buffers
+ * make the copies asynchronous).  The seven arrays are uploaded, the step runs, the seven arrays are overwritten with
+ * the new state.  Copies overlap the phases: phi travels up while ConstructRHS_V and the velocity solves run, the
+ * convective terms travel down during the solves, phi during CorrectVelocities.  Rectangular domains. */
+typedef struct nsgpu_host_state {
+  double *u, *v, *phi, *conv_u0, *conv_v0, *gradphi_x, *gradphi_y;
+} nsgpu_host_state;
+int nsgpu_step_host(nsgpu_ctx* ctx, const nsgpu_host_state* io, nsgpu_step_info* info);
+
 /* the phases one at a time (used by the parity tests) */
 int nsgpu_rhs_build(nsgpu_ctx* ctx);                           /* ConstructRHS_V            FS.cpp:327-363 (+183-325, 458-510) */
 int nsgpu_solve_velocity(nsgpu_ctx* ctx, nsgpu_step_info* info); /* KSPSolve(uSolver) x2      FS.cpp:547-548 */

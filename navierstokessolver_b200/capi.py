@@ -33,6 +33,11 @@ class _Params(C.Structure):
                 ("use_graph", C.c_int32), ("max_levels", C.c_int32), ("vel_solver", C.c_int32), ("reserved", C.c_int32 * 6)]
 
 
+class HostState(C.Structure):
+    """nsgpu_host_state (include/nsgpu.h)."""
+    _fields_ = [(n, C.POINTER(C.c_double)) for n in ("u", "v", "phi", "conv_u0", "conv_v0", "gradphi_x", "gradphi_y")]
+
+
 class StepInfo(C.Structure):
     _fields_ = [("umin", C.c_double), ("umax", C.c_double), ("vmin", C.c_double), ("vmax", C.c_double),
                 ("it_u", C.c_int32), ("it_v", C.c_int32), ("it_phi", C.c_int32),
@@ -70,6 +75,7 @@ def _load():
     L.nsgpu_last_error.restype = C.c_char_p
     L.nsgpu_local_range.argtypes = [P, C.POINTER(C.c_int32), C.POINTER(C.c_int32), C.POINTER(C.c_int64), C.POINTER(C.c_int64)]
     L.nsgpu_step.argtypes = [P, C.c_int32, C.POINTER(StepInfo)]
+    L.nsgpu_step_host.argtypes = [P, C.POINTER(HostState), C.POINTER(StepInfo)]
     L.nsgpu_phase_ms.argtypes = [P, C.POINTER(C.c_float)]
     L.nsgpu_rhs_build.argtypes = [P]
     L.nsgpu_solve_velocity.argtypes = [P, C.POINTER(StepInfo)]
@@ -96,7 +102,7 @@ EXPORTED = ["nsgpu_nccl_unique_id", "nsgpu_create", "nsgpu_destroy", "nsgpu_last
             "nsgpu_step", "nsgpu_rhs_build", "nsgpu_solve_velocity", "nsgpu_div_rhs", "nsgpu_solve_phi",
             "nsgpu_correct", "nsgpu_poisson_sweeps", "nsgpu_apply_operator", "nsgpu_pressure", "nsgpu_get_array",
             "nsgpu_set_array", "nsgpu_get_fields", "nsgpu_set_fields", "nsgpu_num_levels", "nsgpu_kernel_launches",
-            "nsgpu_synchronize", "nsgpu_phase_ms"]
+            "nsgpu_synchronize", "nsgpu_phase_ms", "nsgpu_step_host"]
 
 
 def _dp(a):
@@ -197,6 +203,15 @@ class GpuFluidSolver:
     def step(self, n=1):
         info = StepInfo()
         self._chk(lib.nsgpu_step(self._h, n, C.byref(info)), soft=(-5,))
+        return info
+
+    def step_host(self, state):
+        """One time step with the whole state in host arrays (nsgpu_step_host): `state` maps U, V, PHI, CONV_U0, CONV_V0,
+        GRADPHI_X, GRADPHI_Y to contiguous float64 arrays of this rank's id range; they are overwritten with the new state.
+        Page-locked arrays make the copies overlap the phases."""
+        io = HostState(*[_dp(state[k]) for k in (U, V, PHI, CONV_U0, CONV_V0, GRADPHI_X, GRADPHI_Y)])
+        info = StepInfo()
+        self._chk(lib.nsgpu_step_host(self._h, C.byref(io), C.byref(info)), soft=(-5,))
         return info
 
     def rhs_build(self):

@@ -224,9 +224,49 @@ int nsgpu_correct(nsgpu_ctx* ctx, nsgpu_step_info* info) {
   return 0;
 }
 
-int nsgpu_step(nsgpu_ctx* ctx, int32_t n_steps, nsgpu_step_info* last) {
+}  // extern "C"
+
+namespace nsgpu {
+
+// async copies of one field between the compact host order and the padded device layout (rectangles only)
+static cudaError_t copy_in(nsgpu_ctx* ctx, double* dev, const double* host, cudaStream_t st) {
+  const LevelGeom& g = ctx->levels[0].g;
+  return cudaMemcpy2DAsync(dev + cidx(g, 0, 0), (size_t)g.ld * sizeof(double), host, (size_t)g.ny * sizeof(double),
+                           (size_t)g.ny * sizeof(double), (size_t)g.nx, cudaMemcpyHostToDevice, st);
+}
+static cudaError_t copy_out(nsgpu_ctx* ctx, const double* dev, double* host, cudaStream_t st) {
+  const LevelGeom& g = ctx->levels[0].g;
+  return cudaMemcpy2DAsync(host, (size_t)g.ny * sizeof(double), dev + cidx(g, 0, 0), (size_t)g.ld * sizeof(double),
+                           (size_t)g.ny * sizeof(double), (size_t)g.nx, cudaMemcpyDeviceToHost, st);
+}
+
+// n_steps time steps; io != nullptr (one step): the state comes from / goes back to host buffers, see nsgpu_step_host
+static int step_impl(nsgpu_ctx* ctx, int32_t n_steps, nsgpu_step_info* last, const nsgpu_host_state* io) {
   if (!ctx || n_steps < 0) return NSGPU_ERR_ARG;
   cudaSetDevice(ctx->device);
+  if (io) {
+    if (n_steps != 1 || !ctx->rect) { ctx->err = "nsgpu_step_host: one step, rectangular domains"; return NSGPU_ERR_ARG; }
+    if (!ctx->s_in) {
+      NS_CUDA(cudaStreamCreateWithFlags(&ctx->s_in, cudaStreamNonBlocking));
+      NS_CUDA(cudaStreamCreateWithFlags(&ctx->s_out, cudaStreamNonBlocking));
+      for (auto& e : ctx->ev_io) NS_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+    }
+    ctx->halo_w.clear();
+    ctx->bn2_ready[0] = ctx->bn2_ready[1] = ctx->bn2_ready[2] = false;
+    // upload stream: everything ConstructRHS_V reads first, phi (needed by the third solve only) behind it
+    NS_CUDA(cudaEventRecord(ctx->ev_io[0], ctx->stream));          // earlier work on the solver's stream reads these arrays
+    NS_CUDA(cudaStreamWaitEvent(ctx->s_in, ctx->ev_io[0], 0));
+    NS_CUDA(copy_in(ctx, ctx->u, io->u, ctx->s_in));
+    NS_CUDA(copy_in(ctx, ctx->v, io->v, ctx->s_in));
+    NS_CUDA(copy_in(ctx, ctx->conv_u, io->conv_u0, ctx->s_in));
+    NS_CUDA(copy_in(ctx, ctx->conv_v, io->conv_v0, ctx->s_in));
+    NS_CUDA(copy_in(ctx, ctx->gpx, io->gradphi_x, ctx->s_in));
+    NS_CUDA(copy_in(ctx, ctx->gpy, io->gradphi_y, ctx->s_in));
+    NS_CUDA(cudaEventRecord(ctx->ev_io[1], ctx->s_in));
+    NS_CUDA(copy_in(ctx, ctx->phi, io->phi, ctx->s_in));
+    NS_CUDA(cudaEventRecord(ctx->ev_io[2], ctx->s_in));
+    NS_CUDA(cudaStreamWaitEvent(ctx->stream, ctx->ev_io[1], 0));
+  }
   SolveResult ru, rv, rp;
   double mm[4] = {0, 0, 0, 0};
   const int64_t l0 = ctx->launches;
@@ -238,18 +278,39 @@ int nsgpu_step(nsgpu_ctx* ctx, int32_t n_steps, nsgpu_step_info* last) {
     if (last) cudaEventRecord(ctx->evp[0], ctx->stream);
     if ((rc = phase_rhs(ctx))) return rc;
     if (last) cudaEventRecord(ctx->evp[1], ctx->stream);
+    if (io) {   // the convective terms are final: they go home while the solves run
+      NS_CUDA(cudaEventRecord(ctx->ev_io[3], ctx->stream));
+      NS_CUDA(cudaStreamWaitEvent(ctx->s_out, ctx->ev_io[3], 0));
+      NS_CUDA(copy_out(ctx, ctx->conv_u, io->conv_u0, ctx->s_out));
+      NS_CUDA(copy_out(ctx, ctx->conv_v, io->conv_v0, ctx->s_out));
+    }
     if ((rc = phase_velocity(ctx, &ru, &rv))) return rc;
     if (last) cudaEventRecord(ctx->evp[2], ctx->stream);
     if ((rc = phase_div(ctx, true))) return rc;
     if (last) cudaEventRecord(ctx->evp[3], ctx->stream);
+    if (io) NS_CUDA(cudaStreamWaitEvent(ctx->stream, ctx->ev_io[2], 0));   // phi has arrived
     if ((rc = phase_phi(ctx, &rp))) return rc;
     if (last) cudaEventRecord(ctx->evp[4], ctx->stream);
+    if (io) {   // phi is final (mean pinned): out, under the correction step
+      NS_CUDA(cudaEventRecord(ctx->ev_io[4], ctx->stream));
+      NS_CUDA(cudaStreamWaitEvent(ctx->s_out, ctx->ev_io[4], 0));
+      NS_CUDA(copy_out(ctx, ctx->phi, io->phi, ctx->s_out));
+    }
     if ((rc = phase_correct(ctx, last ? mm : nullptr))) return rc;
     if (last) cudaEventRecord(ctx->evp[5], ctx->stream);
+    if (io) {
+      NS_CUDA(cudaEventRecord(ctx->ev_io[5], ctx->stream));
+      NS_CUDA(cudaStreamWaitEvent(ctx->s_out, ctx->ev_io[5], 0));
+      NS_CUDA(copy_out(ctx, ctx->u, io->u, ctx->s_out));
+      NS_CUDA(copy_out(ctx, ctx->v, io->v, ctx->s_out));
+      NS_CUDA(copy_out(ctx, ctx->gpx, io->gradphi_x, ctx->s_out));
+      NS_CUDA(copy_out(ctx, ctx->gpy, io->gradphi_y, ctx->s_out));
+    }
     if (!((ru.pending || ru.converged) && (rv.pending || rv.converged) && (rp.pending || rp.converged))) status = NSGPU_ERR_NOT_CONVERGED;   // silent in the reference
   }
   NS_CUDA(cudaEventRecord(ctx->ev1, ctx->stream));
   if ((rc = sync_check(ctx))) return rc;
+  if (io) { NS_CUDA(cudaStreamSynchronize(ctx->s_out)); NS_CUDA(cudaStreamSynchronize(ctx->s_in)); }
   trace_collect(ctx);
   if (n_steps > 0) {
     const bool pend[3] = {ru.pending, rv.pending, rp.pending};
@@ -276,6 +337,17 @@ int nsgpu_step(nsgpu_ctx* ctx, int32_t n_steps, nsgpu_step_info* last) {
     last->status = status;
   }
   return status;
+}
+
+}  // namespace nsgpu
+
+extern "C" {
+
+int nsgpu_step(nsgpu_ctx* ctx, int32_t n_steps, nsgpu_step_info* last) { return nsgpu::step_impl(ctx, n_steps, last, nullptr); }
+
+int nsgpu_step_host(nsgpu_ctx* ctx, const nsgpu_host_state* io, nsgpu_step_info* info) {
+  if (!io || !io->u || !io->v || !io->phi || !io->conv_u0 || !io->conv_v0 || !io->gradphi_x || !io->gradphi_y) return NSGPU_ERR_ARG;
+  return nsgpu::step_impl(ctx, 1, info, io);
 }
 
 int nsgpu_poisson_sweeps(nsgpu_ctx* ctx, int32_t n_sweeps, double* residual_l2, float* ms) {

@@ -108,6 +108,7 @@ static void destroy_ctx(nsgpu_ctx* ctx) {
     for (void* p : L.owned) cudaFree(p);
   for (void* p : ctx->owned) cudaFree(p);
   for (auto& sg : ctx->sgraph) { if (sg.exec) cudaGraphExecDestroy(sg.exec); if (sg.graph) cudaGraphDestroy(sg.graph); }
+  if (ctx->s_in) { cudaStreamDestroy(ctx->s_in); cudaStreamDestroy(ctx->s_out); for (auto& e : ctx->ev_io) if (e) cudaEventDestroy(e); }
   if (ctx->h_scal) cudaFreeHost(ctx->h_scal);
   if (ctx->h_ctl) cudaFreeHost(ctx->h_ctl);
   if (ctx->h_stage) cudaFreeHost(ctx->h_stage);

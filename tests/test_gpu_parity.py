@@ -173,6 +173,26 @@ def test_graph_solves_equal_direct_launches(n, sim, workdir):
     assert ia.kernel_launches == ib.kernel_launches
 
 
+def test_step_with_host_state_equals_resident_steps(workdir):
+    """nsgpu_step_host (state streamed from / to host arrays, copies overlapped with the phases) against the same steps
+    with the state resident on the device: identical fields, three steps in a row."""
+    import navierstokessolver_b200 as ns
+    g = ns.GridDesc.cavity(96, nx=160, lx=160 / 96.0)
+    a = ns.GpuFluidSolver(g, 0.002, 400.0)
+    b = ns.GpuFluidSolver(g, 0.002, 400.0)
+    keys = (U, V, PHI, CONV_U0, CONV_V0, GRADPHI_X, GRADPHI_Y)
+    a.step(2)
+    b.step(2)
+    state = {k: b.get(k).copy() for k in keys}
+    for _ in range(3):
+        ia = a.step(1)
+        ib = b.step_host(state)
+        assert (ia.it_u, ia.it_v, ia.it_phi, ia.status) == (ib.it_u, ib.it_v, ib.it_phi, ib.status)
+        for k in keys:
+            assert np.array_equal(state[k], a.get(k)), k
+            assert np.array_equal(b.get(k), a.get(k)), k
+
+
 def test_velocity_sor_and_multigrid_agree(workdir):
     """u*, v* from red-black SOR (optimal factor) and from multigrid: two converged solvers of the same LHS_V systems."""
     ref = refapi.RefSolver(f"{CASES}/cavity_128.grid", f"{CASES}/cavity_re1000_128.sim")
