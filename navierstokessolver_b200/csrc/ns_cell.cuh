@@ -90,7 +90,9 @@ NS_HD int side_edge_id(const LevelGeom& g, int i, int j, int k) {
 }
 
 // ---------------------------------------------------------------------------------------------------------
-// Operators.  OP 0: L_V rows (velocity ghosts, ghost[0]); OP 1: L_phi rows (ghost[1]).
+// Operators.  OP 0: L_V rows (velocity ghosts, ghost[0]); OP 1: L_phi rows (ghost[1]); OP 2: L_phi with every
+// boundary side treated as a wall (ghost = phi_c) -- never the system that is solved, only the symmetric operator whose
+// V-cycle preconditions the Krylov iteration on outflow domains (ns_solver.inl, solve_bicgstab).
 //   (L x)_c = diagL * x_c + offL
 // x points at the cell itself (so x[+-1] are the y neighbours, x[+-ld] the x neighbours).
 // The outflow rows of L_phi reach two cells inward (FS.cpp:100).
@@ -102,16 +104,16 @@ NS_HD void row_eval(const LevelGeom& g, unsigned f, int i, int j, double xW, dou
   double d = 0.0, o = 0.0;
   if (f & F_W) { d -= ax.m; o += ax.m * xW; }
   else if (OP == 0) { if (!(f & F_OW)) d -= 2.0 * g.bx[i + HX]; }
-  else if (f & F_OW) { double w = g.bx[i + HX]; d += 1.5 * w; o += w * (-2.0 * xE + 0.5 * xfar[2 * g.ld]); }
+  else if (OP == 1 && (f & F_OW)) { double w = g.bx[i + HX]; d += 1.5 * w; o += w * (-2.0 * xE + 0.5 * xfar[2 * g.ld]); }
   if (f & F_E) { d -= ax.p; o += ax.p * xE; }
   else if (OP == 0) { if (!(f & F_OE)) d -= 2.0 * g.bx[i + HX]; }
-  else if (f & F_OE) { double w = g.bx[i + HX]; d += 1.5 * w; o += w * (-2.0 * xW + 0.5 * xfar[-2 * g.ld]); }
+  else if (OP == 1 && (f & F_OE)) { double w = g.bx[i + HX]; d += 1.5 * w; o += w * (-2.0 * xW + 0.5 * xfar[-2 * g.ld]); }
   if (f & F_S) { d -= ay.m; o += ay.m * xS; }
   else if (OP == 0) { if (!(f & F_OS)) d -= 2.0 * g.by[j + PJ]; }
-  else if (f & F_OS) { double w = g.by[j + PJ]; d += 1.5 * w; o += w * (-2.0 * xN + 0.5 * xfar[2]); }
+  else if (OP == 1 && (f & F_OS)) { double w = g.by[j + PJ]; d += 1.5 * w; o += w * (-2.0 * xN + 0.5 * xfar[2]); }
   if (f & F_N) { d -= ay.p; o += ay.p * xN; }
   else if (OP == 0) { if (!(f & F_ON)) d -= 2.0 * g.by[j + PJ]; }
-  else if (f & F_ON) { double w = g.by[j + PJ]; d += 1.5 * w; o += w * (-2.0 * xS + 0.5 * xfar[-2]); }
+  else if (OP == 1 && (f & F_ON)) { double w = g.by[j + PJ]; d += 1.5 * w; o += w * (-2.0 * xS + 0.5 * xfar[-2]); }
   diagL = d;
   offL = o;
 }

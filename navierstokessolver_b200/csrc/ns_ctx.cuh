@@ -77,7 +77,13 @@ struct nsgpu_ctx {
   double *conv_u = nullptr, *conv_v = nullptr, *gpx = nullptr, *gpy = nullptr;
   double *rhs_u = nullptr, *rhs_v = nullptr, *rhs_phi = nullptr, *ustar = nullptr, *vstar = nullptr;
   double* tmp = nullptr;        // ping-pong partner of the fine-level smoother
-  double* kry[8] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};  // BiCGStab vectors (solver == 1)
+  double* kry[8] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};  // BiCGStab vectors (solver == 1, or aug)
+  // outflow (bcType 4) domains: the phi solve reproduces the fixed point of the reference's ILU(0)-preconditioned, null-space-
+  // projected KSP:  A phi + c w = b, mean(phi) = 0, w = ILU(0)(LHS_phi) 1 (ns_hostgeom.h, phi_ilu0_image_of_ones)
+  bool aug = false;
+  double* aug_w = nullptr;      // w in the field layout (zeros in padding and masked cells)
+  double* aug_t = nullptr;      // scratch vector of the preconditioner
+  double aug_ww = 0.0;          // (w, w) over the global domain
 
   nsgpu::Reducer red{};
   double* d_scal = nullptr;     // device scalars (64 doubles)

@@ -3,6 +3,7 @@
 // ConstructGhostStencils / ConstructLHS set up in the reference (FS.cpp:84-164).
 #pragma once
 #include <algorithm>
+#include <cmath>
 #include <cstdint>
 #include <cstdio>
 #include <string>
@@ -301,6 +302,105 @@ static inline int make_host_plan(const nsgpu_grid* G, int rank, int world, int m
     P.levels.push_back(std::move(C));
   }
   P.lcx.push_back(1); P.lcy.push_back(1);
+  return 0;
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// Outflow (bcType 4) domains: what the reference's Poisson solve converges to.
+//
+// With a type-4 edge LHS_phi keeps the constants as right null space (zero row sums) but its left null vector is no
+// longer constant (the 2.5/-2/0.5 ghost rows, FS.cpp:100), and the right-hand side the reference builds is not orthogonal to it:
+// LHS_phi x = b has NO solution.  KSPSolve still "converges" (FS.cpp:551): with MatSetNullSpace the left-preconditioned
+// iteration works on P M^-1 (b - A x), P = removal of the mean, M = the ILU(0) factors of A in natural ordering
+// (PCBJACOBI with one block, FS.cpp:78), and its fixed point is
+//        A x + c (M 1) = b,   mean(x) = 0        (x, c unknown; measured against the oracle: 8e-11)
+// So the reference's answer is defined by w = M 1 = L (U 1).  This function restates ILU(0) of LHS_phi on the host, once per
+// context, O(N): rows in compact-id order (Grid.cpp:149-161), columns sorted, the pattern of ConstructLHS + AddGhostStencils
+// (FS.cpp:105-164: cell, present neighbours, and the second inward cell of an outflow side).  Returns w in global id order.
+static inline bool plan_has_outflow(const HostPlan& P) {
+  for (const EdgeDev& e : P.edges) if (e.outflow) return true;
+  return false;
+}
+
+static inline int phi_ilu0_image_of_ones(const nsgpu_grid* G, const HostPlan& P, std::vector<double>& w, std::string& err) {
+  const HostLevel& H = P.levels[0];
+  const int gnx = H.gnx, ny = H.ny;
+  const int64_t N = P.n_cells_global;
+  auto id_of = [&](int i, int j) -> int64_t {
+    if (i < 0 || i >= gnx || j < 0 || j >= ny) return -1;
+    return P.rect ? (int64_t)i * ny + j : (int64_t)G->cell_id[(size_t)i * ny + j];
+  };
+  auto flags_of = [&](int i, int j) -> unsigned {
+    if (!P.rect) return H.flags[(size_t)i * ny + j];
+    unsigned f = 0;
+    if (i > 0) f |= F_W; else if (P.side_out[0]) f |= F_OW;
+    if (i < gnx - 1) f |= F_E; else if (P.side_out[1]) f |= F_OE;
+    if (j > 0) f |= F_S; else if (P.side_out[2]) f |= F_OS;
+    if (j < ny - 1) f |= F_N; else if (P.side_out[3]) f |= F_ON;
+    return f;
+  };
+  std::vector<int64_t> rp((size_t)N + 1, 0), diag((size_t)N, 0);
+  std::vector<int64_t> col; std::vector<double> val;
+  col.reserve((size_t)N * 6); val.reserve((size_t)N * 6);
+  const int di[4] = {-1, 1, 0, 0}, dj[4] = {0, 0, -1, 1};
+  int64_t row = 0;
+  for (int i = 0; i < gnx; i++)
+    for (int j = 0; j < ny; j++) {
+      const int64_t c = id_of(i, j);
+      if (c < 0) continue;
+      if (c != row) { err = "internal: compact ids out of order"; return NSGPU_ERR_ARG; }
+      const unsigned f = flags_of(i, j);
+      const double hx = H.hx[i], hy = H.hy[j];
+      int64_t ec[8]; double ev[8]; int ne = 0;
+      auto add = [&](int64_t cc, double v) {
+        if (cc < 0) return;
+        for (int k = 0; k < ne; k++) if (ec[k] == cc) { ev[k] += v; return; }
+        ec[ne] = cc; ev[ne] = v; ne++;
+      };
+      double d = 0.0;
+      for (int k = 0; k < 4; k++) {
+        const bool xdir = k < 2;
+        const double h = xdir ? hx : hy;
+        if (f & (1u << k)) {
+          const double hn = xdir ? H.hx[i + di[k]] : H.hy[j + dj[k]];
+          const double a = 2.0 / (h * (h + hn));                      // FS.cpp:119-120
+          add(id_of(i + di[k], j + dj[k]), a); d -= a;
+        } else if (f & (16u << k)) {                                  // ghost = 2.5 c - 2 (c - n) + 0.5 (c - 2n), FS.cpp:100
+          const double b = 1.0 / (h * h);                             // FS.cpp:125-126
+          d += 1.5 * b;
+          add(id_of(i - di[k], j - dj[k]), -2.0 * b);
+          add(id_of(i - 2 * di[k], j - 2 * dj[k]), 0.5 * b);
+        }
+      }
+      add(c, d);
+      // sort the (at most 7) entries by column
+      for (int a = 1; a < ne; a++) { int64_t kc = ec[a]; double kv = ev[a]; int b2 = a - 1; while (b2 >= 0 && ec[b2] > kc) { ec[b2 + 1] = ec[b2]; ev[b2 + 1] = ev[b2]; b2--; } ec[b2 + 1] = kc; ev[b2 + 1] = kv; }
+      for (int a = 0; a < ne; a++) { if (ec[a] == c) diag[(size_t)row] = (int64_t)col.size(); col.push_back(ec[a]); val.push_back(ev[a]); }
+      row++;
+      rp[(size_t)row] = (int64_t)col.size();
+    }
+  if (row != N) { err = "internal: cell count mismatch in the ILU(0) setup"; return NSGPU_ERR_ARG; }
+  // ILU(0), IKJ order
+  for (int64_t i = 0; i < N; i++) {
+    for (int64_t kk = rp[(size_t)i]; kk < diag[(size_t)i]; kk++) {
+      const int64_t k = col[(size_t)kk];
+      const double piv = val[(size_t)diag[(size_t)k]];
+      const double lik = val[(size_t)kk] / piv;
+      val[(size_t)kk] = lik;
+      for (int64_t jj = diag[(size_t)k] + 1; jj < rp[(size_t)k + 1]; jj++) {
+        const int64_t jc = col[(size_t)jj];
+        for (int64_t q = kk + 1; q < rp[(size_t)i + 1]; q++)
+          if (col[(size_t)q] == jc) { val[(size_t)q] -= lik * val[(size_t)jj]; break; }
+      }
+    }
+    const double piv = val[(size_t)diag[(size_t)i]];
+    if (!(piv == piv) || piv == 0.0 || std::isinf(piv)) { err = "ILU(0) of LHS_phi broke down (zero or non-finite pivot)"; return NSGPU_ERR_ARG; }
+  }
+  // w = L (U 1)
+  std::vector<double> t((size_t)N);
+  for (int64_t i = 0; i < N; i++) { double s = 0; for (int64_t q = diag[(size_t)i]; q < rp[(size_t)i + 1]; q++) s += val[(size_t)q]; t[(size_t)i] = s; }
+  w.assign((size_t)N, 0.0);
+  for (int64_t i = 0; i < N; i++) { double s = t[(size_t)i]; for (int64_t q = rp[(size_t)i]; q < diag[(size_t)i]; q++) s += val[(size_t)q] * t[(size_t)col[(size_t)q]]; w[(size_t)i] = s; }
   return 0;
 }
 

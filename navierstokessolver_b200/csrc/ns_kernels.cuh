@@ -536,6 +536,20 @@ __global__ void __launch_bounds__(256) k_sum(size_t n, const double* __restrict_
   for (size_t k = blockIdx.x * (size_t)blockDim.x + threadIdx.x; k < n; k += (size_t)gridDim.x * blockDim.x) acc[0] += a[k];
   grid_reduce<1, OpSum>(acc, red, out);
 }
+// y += scale * (*s) * w ; out = {(d, y), (y, y)}  (d may be null: out[0] = 0) -- the rank-one term of the augmented
+// operator of outflow domains, A^ x = A x + mean(x) w, added to y = A x with the two dot products BiCGStab needs next
+__global__ void __launch_bounds__(256) k_aug_axpy(size_t n, double* __restrict__ y, const double* __restrict__ w, const double* __restrict__ s,
+                                                  double scale, const double* __restrict__ d, Reducer red, double* out) {
+  const double a = scale * *s;
+  double acc[2] = {0.0, 0.0};
+  for (size_t k = blockIdx.x * (size_t)blockDim.x + threadIdx.x; k < n; k += (size_t)gridDim.x * blockDim.x) {
+    const double yv = fma(a, w[k], y[k]);
+    y[k] = yv;
+    if (d) acc[0] = fma(d[k], yv, acc[0]);
+    acc[1] = fma(yv, yv, acc[1]);
+  }
+  grid_reduce<2, OpSum>(acc, red, out);
+}
 // tiny scalar kernels of the Krylov recurrences: dst = num/den
 __global__ void k_scalar_div(double* dst, const double* num, const double* den) { *dst = *num / *den; }
 __global__ void k_scalar_copy(double* dst, const double* src) { *dst = *src; }

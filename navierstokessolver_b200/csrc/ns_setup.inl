@@ -309,7 +309,24 @@ static int create_impl(nsgpu_ctx* ctx, const nsgpu_grid* G, const nsgpu_params* 
   double** fields[] = {&ctx->u, &ctx->v, &ctx->phi, &ctx->conv_u, &ctx->conv_v, &ctx->gpx, &ctx->gpy,
                        &ctx->rhs_u, &ctx->rhs_v, &ctx->rhs_phi, &ctx->ustar, &ctx->vstar, &ctx->tmp};
   for (double** f : fields) { int rc = dev_zeros(ctx, ctx->owned, S, f); if (rc) return rc; }
-  if (ctx->solver == 1)
+  if (plan_has_outflow(plan)) {   // FS.cpp:98-101: LHS_phi x = b is inconsistent there; see ns_hostgeom.h for what the reference returns
+    std::vector<double> w;
+    int rc = phi_ilu0_image_of_ones(G, plan, w, ctx->err);
+    if (rc) return rc;
+    const LevelGeom& g0 = ctx->levels[0].g;
+    std::vector<double> wp(S, 0.0);
+    for (int i = 0; i < g0.nx; i++)
+      for (int j = 0; j < g0.ny; j++) {
+        const int64_t id = plan.rect ? (int64_t)i * g0.ny + j : (int64_t)plan.local_id[(size_t)i * g0.ny + j];
+        if (id >= 0) wp[cidx(g0, i, j)] = w[(size_t)(plan.id0 + id)];
+      }
+    for (double x : w) ctx->aug_ww += x * x;
+    if ((rc = dev_zeros(ctx, ctx->owned, S, &ctx->aug_w))) return rc;
+    if ((rc = dev_zeros(ctx, ctx->owned, S, &ctx->aug_t))) return rc;
+    NS_CUDA(cudaMemcpy(ctx->aug_w, wp.data(), S * sizeof(double), cudaMemcpyHostToDevice));
+    ctx->aug = ctx->aug_ww > 0.0;
+  }
+  if (ctx->solver == 1 || ctx->aug)
     for (int k = 0; k < 8; k++) { int rc = dev_zeros(ctx, ctx->owned, S, &ctx->kry[k]); if (rc) return rc; }
   { const EdgeDev* p; int rc = dev_upload(ctx, ctx->owned, plan.edges, &p); if (rc) return rc; ctx->d_edges = const_cast<EdgeDev*>(p); }
   { int rc = dev_zeros(ctx, ctx->owned, (size_t)4 * RED_MAX_BLOCKS, &ctx->red.partials); if (rc) return rc; }

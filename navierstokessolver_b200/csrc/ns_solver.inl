@@ -6,6 +6,7 @@ namespace nsgpu {
 struct OpCoef { int op; double alpha, beta; };
 static inline OpCoef coef_v(const nsgpu_ctx* c) { return OpCoef{0, 1.0, c->dt / (2.0 * c->re)}; }   // LHS_V   FS.cpp:140-141
 static inline OpCoef coef_phi() { return OpCoef{1, 0.0, -1.0}; }                                    // LHS_phi
+static inline OpCoef coef_phi_walls() { return OpCoef{2, 0.0, -1.0}; }   // L_phi with wall ghosts on every side (preconditioner only)
 
 #define NS_LAUNCH_CHECK()                                                             \
   do {                                                                                \
@@ -23,7 +24,8 @@ static inline OpCoef coef_phi() { return OpCoef{1, 0.0, -1.0}; }                
 #define NS_DISPATCH_OP_RECT(op, rect, CALL) \
   do {                                      \
     if ((op) == 0) { if (rect) { CALL(0, true); } else { CALL(0, false); } } \
-    else { if (rect) { CALL(1, true); } else { CALL(1, false); } }           \
+    else if ((op) == 1) { if (rect) { CALL(1, true); } else { CALL(1, false); } } \
+    else { if (rect) { CALL(2, true); } else { CALL(2, false); } }           \
   } while (0)
 #define NS_DISPATCH_RECT(rect, CALL) \
   do { if (rect) { CALL(true); } else { CALL(false); } } while (0)
@@ -94,6 +96,7 @@ static int allreduce(nsgpu_ctx* ctx, double* d, int n, ncclRedOp_t op) {
 
 static inline bool march_level_ok(const nsgpu_ctx* ctx, const Level& L, OpCoef c) {
   // with several ranks the 5-column halo of a fused pass has to come from ONE neighbour
+  if (c.op > 1) return false;   // the wall-only L_phi of the outflow preconditioner runs on the generic kernels
   return ctx->march && ctx->rect && L.march_ok[c.op] && (ctx->world == 1 || L.replicated || L.g.nx >= HX);
 }
 
@@ -453,6 +456,64 @@ static int solve_mg(nsgpu_ctx* ctx, OpCoef c, double** x, double** xt, const dou
   return 0;
 }
 
+// ---------------------------------------------------------------------------------------------------------
+// Outflow domains (ctx->aug): the phi solve is  A^ x = A x + mean(x) w = b  (nonsingular); x - mean(x) is the phi the reference's
+// KSP converges to and mean(x) its c (ns_hostgeom.h).  d_scal[41..46]: sum x, (v, w), sum z, {scratch, |r|^2}, saved sum of x.
+
+static int vec_sum(nsgpu_ctx* ctx, const Level& L, const double* a, double* d_out) {
+  const size_t n = (size_t)L.g.nx * L.g.ld;
+  const int blocks = (int)std::min<size_t>((n + 255) / 256, 148 * 8);
+  k_sum<<<blocks, 256, 0, ctx->stream>>>(n, a + (size_t)HX * L.g.ld, ctx->red, d_out);
+  NS_LAUNCH_CHECK();
+  return allreduce(ctx, d_out, 1, ncclSum);
+}
+
+// field += gamma * (*d_s) on the fluid cells
+static int add_scaled_const(nsgpu_ctx* ctx, const Level& L, double* field, const double* d_s, double gamma) {
+  const dim3 grid = grid_cols(L.g, 256);
+#define CALL(RECT) k_sub_mean<RECT><<<grid, 256, 0, ctx->stream>>>(L.g, field, d_s, -gamma)
+  NS_DISPATCH_RECT(ctx->rect, CALL);
+#undef CALL
+  NS_LAUNCH_CHECK();
+  ctx->halo_w.clear();
+  return 0;
+}
+
+// y += sign * mean(x) * w;  d_out = {(dotwith, y), (y, y)}
+static int aug_rank_one(nsgpu_ctx* ctx, const Level& L, const double* x, double* y, double sign, const double* dotwith, double* d_out) {
+  int rc;
+  if ((rc = vec_sum(ctx, L, x, ctx->d_scal + 41))) return rc;
+  const size_t n = (size_t)L.g.nx * L.g.ld, off = (size_t)HX * L.g.ld;
+  const int blocks = (int)std::min<size_t>((n + 255) / 256, 148 * 8);
+  k_aug_axpy<<<blocks, 256, 0, ctx->stream>>>(n, y + off, ctx->aug_w + off, ctx->d_scal + 41, sign / (double)ctx->n_cells_global,
+                                              dotwith ? dotwith + off : nullptr, ctx->red, d_out);
+  NS_LAUNCH_CHECK();
+  ctx->halo_w.clear();
+  return allreduce(ctx, d_out, 2, ncclSum);
+}
+
+static int vcycle_any(nsgpu_ctx* ctx, OpCoef c, double** x, double** xt, const double* b, bool xzero);
+
+// z = V_walls(v - mean v), its mean removed, + (v, w) / (w, w): the wall-only L_phi is symmetric and its V-cycle converges; the
+// constant carries the component of v along w, which only the constant mode of x can produce (A^ 1 = w).
+static int aug_precond(nsgpu_ctx* ctx, const Level& L, const double* v, double** z, double** zt) {
+  int rc;
+  const size_t n = (size_t)L.g.nx * L.g.ld, off = (size_t)HX * L.g.ld;
+  const int blocks = (int)std::min<size_t>((n + 255) / 256, 148 * 8);
+  const double inv_n = 1.0 / (double)ctx->n_cells_global;
+  if ((rc = vec_sum(ctx, L, v, ctx->d_scal + 41))) return rc;
+  k_dot<<<blocks, 256, 0, ctx->stream>>>(n, v + off, ctx->aug_w + off, ctx->red, ctx->d_scal + 42, nullptr);
+  NS_LAUNCH_CHECK();
+  if ((rc = allreduce(ctx, ctx->d_scal + 42, 1, ncclSum))) return rc;
+  cudaError_t e = cudaMemcpyAsync(ctx->aug_t, v, L.stride * sizeof(double), cudaMemcpyDeviceToDevice, ctx->stream);
+  if (e != cudaSuccess) { ctx->err = cudaGetErrorString(e); return NSGPU_ERR_CUDA; }
+  if ((rc = add_scaled_const(ctx, L, ctx->aug_t, ctx->d_scal + 41, -inv_n))) return rc;
+  if ((rc = vcycle_any(ctx, coef_phi_walls(), z, zt, ctx->aug_t, true))) return rc;
+  if ((rc = vec_sum(ctx, L, *z, ctx->d_scal + 43))) return rc;
+  if ((rc = add_scaled_const(ctx, L, *z, ctx->d_scal + 43, -inv_n))) return rc;
+  return add_scaled_const(ctx, L, *z, ctx->d_scal + 42, 1.0 / ctx->aug_ww);
+}
+
 // Right-preconditioned BiCGStab, preconditioner = one V-cycle from a zero guess; all recurrence scalars stay
 // on the device, one 8-byte readback per iteration for the stopping test.
 //   d_scal layout: [0] rho_new [1] rho_old [2] alpha [3] omega [4..5] (r0,v),(v,v) [6..7] (t,s),(t,t)
@@ -467,8 +528,15 @@ static int solve_bicgstab(nsgpu_ctx* ctx, OpCoef c, double** xp, double** xtp, c
   double* S = ctx->d_scal;
   double h[4];
   int rc;
+  const bool aug = ctx->aug && c.op == 1;
   if ((rc = norm2_vec(ctx, L, b, S + 11))) return rc;
+  if (aug && (rc = add_scaled_const(ctx, L, x, S + 46, 1.0 / (double)ctx->n_cells_global))) return rc;   // warm start: phi^n + the last mean(x)
   if ((rc = residual_vec(ctx, L, c, x, b, r, S + 9))) return rc;
+  if (aug) {
+    if ((rc = aug_rank_one(ctx, L, x, r, -1.0, nullptr, S + 44))) return rc;
+    k_scalar_copy<<<1, 1, 0, ctx->stream>>>(S + 9, S + 45);
+    NS_LAUNCH_CHECK();
+  }
   if ((rc = read_scalars(ctx, S + 9, 3, h))) return rc;
   const double bn = std::sqrt(h[2]);
   double rn = std::sqrt(h[0]);
@@ -486,16 +554,22 @@ static int solve_bicgstab(nsgpu_ctx* ctx, OpCoef c, double** xp, double** xtp, c
     k_bicg_p<<<blocks, 256, 0, ctx->stream>>>(n, r + off, p + off, v + off, S);
     NS_LAUNCH_CHECK();
     // ph = M^-1 p
-    { double *a = ph, *bq = tmpA; if ((rc = vcycle_any(ctx, c, &a, &bq, p, true))) return rc; ph = a; tmpA = bq; }
-    if ((rc = apply_op(ctx, L, c, ph, v, r0, S + 4))) return rc;
+    { double *a = ph, *bq = tmpA; if ((rc = aug ? aug_precond(ctx, L, p, &a, &bq) : vcycle_any(ctx, c, &a, &bq, p, true))) return rc; ph = a; tmpA = bq; }
+    if (aug) {
+      if ((rc = apply_op(ctx, L, c, ph, v, nullptr, nullptr))) return rc;
+      if ((rc = aug_rank_one(ctx, L, ph, v, 1.0, r0, S + 4))) return rc;
+    } else if ((rc = apply_op(ctx, L, c, ph, v, r0, S + 4))) return rc;
     k_scalar_div<<<1, 1, 0, ctx->stream>>>(S + 2, S + 0, S + 4);   // alpha = rho / (r0, v)
     NS_LAUNCH_CHECK();
     k_bicg_s<<<blocks, 256, 0, ctx->stream>>>(n, r + off, v + off, s + off, S + 2, ctx->red, S + 8);
     NS_LAUNCH_CHECK();
     if ((rc = allreduce(ctx, S + 8, 1, ncclSum))) return rc;
     // sh = M^-1 s
-    { double *a = sh, *bq = tmpA; if ((rc = vcycle_any(ctx, c, &a, &bq, s, true))) return rc; sh = a; tmpA = bq; }
-    if ((rc = apply_op(ctx, L, c, sh, t, s, S + 6))) return rc;
+    { double *a = sh, *bq = tmpA; if ((rc = aug ? aug_precond(ctx, L, s, &a, &bq) : vcycle_any(ctx, c, &a, &bq, s, true))) return rc; sh = a; tmpA = bq; }
+    if (aug) {
+      if ((rc = apply_op(ctx, L, c, sh, t, nullptr, nullptr))) return rc;
+      if ((rc = aug_rank_one(ctx, L, sh, t, 1.0, s, S + 6))) return rc;
+    } else if ((rc = apply_op(ctx, L, c, sh, t, s, S + 6))) return rc;
     k_scalar_div<<<1, 1, 0, ctx->stream>>>(S + 3, S + 6, S + 7);   // omega = (t,s)/(t,t)
     NS_LAUNCH_CHECK();
     k_scalar_copy<<<1, 1, 0, ctx->stream>>>(S + 1, S + 0);         // rho_old = rho_new
@@ -513,7 +587,13 @@ static int solve_bicgstab(nsgpu_ctx* ctx, OpCoef c, double** xp, double** xtp, c
   }
   ctx->kry[6] = ph; ctx->kry[7] = sh; ctx->tmp = tmpA;
   // the recurrence residual can drift from the true one: report the true residual
-  if ((rc = residual_norm2(ctx, L, c, x, b, S + 9))) return rc;
+  if (aug) {
+    if ((rc = residual_vec(ctx, L, c, x, b, r, S + 9))) return rc;
+    if ((rc = aug_rank_one(ctx, L, x, r, -1.0, nullptr, S + 44))) return rc;
+    k_scalar_copy<<<1, 1, 0, ctx->stream>>>(S + 9, S + 45);
+    NS_LAUNCH_CHECK();
+    if ((rc = vec_sum(ctx, L, x, S + 46))) return rc;   // mean(x) * n: next step's warm start (phase_phi removes it from phi)
+  } else if ((rc = residual_norm2(ctx, L, c, x, b, S + 9))) return rc;
   if ((rc = read_scalars(ctx, S + 9, 1, h))) return rc;
   rn = std::sqrt(h[0]);
   out->rel = rn / bn;
@@ -732,7 +812,7 @@ static int solve(nsgpu_ctx* ctx, int slot, OpCoef c, double** x, const double* b
     cudaError_t e = cudaMemcpyAsync(*x, x0, ctx->levels[0].stride * sizeof(double), cudaMemcpyDeviceToDevice, ctx->stream);
     if (e != cudaSuccess) { ctx->err = cudaGetErrorString(e); return NSGPU_ERR_CUDA; }
   }
-  if (ctx->solver == 1) return solve_bicgstab(ctx, c, x, &ctx->tmp, b, rtol, out);
+  if (ctx->solver == 1 || (ctx->aug && c.op == 1)) return solve_bicgstab(ctx, c, x, &ctx->tmp, b, rtol, out);
   return solve_mg(ctx, c, x, &ctx->tmp, b, rtol, out);
 }
 

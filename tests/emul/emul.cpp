@@ -27,6 +27,10 @@ struct Emul {
   int nu_pre = 2, nu_post = 2;
   std::vector<double> f[13];   // NSGPU_* ids 0..11, 12 = tmp
   std::string err;
+  // outflow domains: w = ILU(0)(LHS_phi) * 1 in the padded layout, (w, w), sum of phi before the last mean removal
+  bool aug = false;
+  std::vector<double> aug_w;
+  double aug_ww = 0.0, aug_shift = 0.0;
 };
 
 void bind(ELevel& L, const HostPlan& P) {
@@ -60,6 +64,7 @@ void smoothphase_t(const LevelGeom& g, std::vector<double>& x, std::vector<doubl
 }
 void smooth(const Emul& E, const ELevel& L, Coef c, std::vector<double>& x, std::vector<double>& xt, const std::vector<double>& b, int n) {
   if (c.op == 0) { if (E.plan.rect) smoothphase_t<0, true>(L.g, x, xt, b, c.alpha, c.beta, n); else smoothphase_t<0, false>(L.g, x, xt, b, c.alpha, c.beta, n); }
+  else if (c.op == 2) { if (E.plan.rect) smoothphase_t<2, true>(L.g, x, xt, b, c.alpha, c.beta, n); else smoothphase_t<2, false>(L.g, x, xt, b, c.alpha, c.beta, n); }
   else { if (E.plan.rect) smoothphase_t<1, true>(L.g, x, xt, b, c.alpha, c.beta, n); else smoothphase_t<1, false>(L.g, x, xt, b, c.alpha, c.beta, n); }
 }
 
@@ -69,6 +74,7 @@ double apply_at(const LevelGeom& g, int i, int j, const std::vector<double>& x, 
 }
 double apply_any(const Emul& E, const LevelGeom& g, Coef c, int i, int j, const std::vector<double>& x) {
   if (c.op == 0) return E.plan.rect ? apply_at<0, true>(g, i, j, x, c.alpha, c.beta) : apply_at<0, false>(g, i, j, x, c.alpha, c.beta);
+  if (c.op == 2) return E.plan.rect ? apply_at<2, true>(g, i, j, x, c.alpha, c.beta) : apply_at<2, false>(g, i, j, x, c.alpha, c.beta);
   return E.plan.rect ? apply_at<1, true>(g, i, j, x, c.alpha, c.beta) : apply_at<1, false>(g, i, j, x, c.alpha, c.beta);
 }
 unsigned flags_any(const Emul& E, const LevelGeom& g, int i, int j) { return E.plan.rect ? fl<true>(g, i, j) : fl<false>(g, i, j); }
@@ -126,6 +132,70 @@ int solve_mg(Emul& E, Coef c, std::vector<double>& x, const std::vector<double>&
   }
   *rel = rn / bn;
   return cycles;
+}
+
+// ---- outflow domains (mirrors solve_bicgstab's augmented branch in csrc/ns_solver.inl) ------------------------------
+// Right-preconditioned BiCGStab on  A^ x = A x + mean(x) w  (nonsingular; x - mean(x) is the reference's phi, mean(x) its c),
+// preconditioner  P v = V_walls(v - mean v), mean removed, + (v.w)/(w.w) * 1  (V_walls: one V-cycle of the wall-only L_phi, op 2).
+double fluid_sum(const Emul& E, const std::vector<double>& a) { double s = 0; for (double v : a) s += v; (void)E; return s; }
+void add_const(const Emul& E, std::vector<double>& a, double c) {
+  const LevelGeom& g = E.lv[0].g;
+  for (int i = 0; i < g.nx; i++)
+    for (int j = 0; j < g.ny; j++)
+      if (flags_any(E, g, i, j) != F_OUTSIDE) a[cidx(g, i, j)] += c;
+}
+void aug_apply(const Emul& E, const std::vector<double>& x, std::vector<double>& y) {
+  const LevelGeom& g = E.lv[0].g;
+  const Coef c{1, 0.0, -1.0};
+  const double m = fluid_sum(E, x) / (double)E.plan.n_cells_global;
+  std::fill(y.begin(), y.end(), 0.0);
+  for (int i = 0; i < g.nx; i++)
+    for (int j = 0; j < g.ny; j++)
+      if (flags_any(E, g, i, j) != F_OUTSIDE) { const size_t id = cidx(g, i, j); y[id] = apply_any(E, g, c, i, j, x) + m * E.aug_w[id]; }
+}
+void aug_precond(Emul& E, const std::vector<double>& v, std::vector<double>& z) {
+  const double n = (double)E.plan.n_cells_global;
+  double vw = 0; for (size_t k = 0; k < v.size(); k++) vw += v[k] * E.aug_w[k];
+  std::vector<double> t(v);
+  add_const(E, t, -fluid_sum(E, v) / n);
+  std::fill(z.begin(), z.end(), 0.0);
+  vcycle(E, 0, Coef{2, 0.0, -1.0}, z, E.f[12], t);
+  add_const(E, z, -fluid_sum(E, z) / n + vw / E.aug_ww);
+}
+double dotv(const std::vector<double>& a, const std::vector<double>& b) { double s = 0; for (size_t k = 0; k < a.size(); k++) s += a[k] * b[k]; return s; }
+
+int solve_phi_aug(Emul& E, std::vector<double>& x, const std::vector<double>& b, double rtol, int max_it, double* rel) {
+  const size_t S = x.size();
+  std::vector<double> r(S), r0, p(S, 0.0), v(S, 0.0), s(S), t(S), ph(S), sh(S), y(S);
+  add_const(E, x, E.aug_shift / (double)E.plan.n_cells_global);   // warm start: last step's phi plus last step's mean(x)
+  const double bn = std::sqrt(dotv(b, b));
+  if (bn == 0) { std::fill(x.begin(), x.end(), 0.0); *rel = 0; return 0; }
+  aug_apply(E, x, y);
+  for (size_t k = 0; k < S; k++) r[k] = b[k] - y[k];
+  r0 = r;
+  double rho = dotv(r0, r), rho_old = 1, alpha = 1, omega = 1, rn = std::sqrt(dotv(r, r));
+  int it = 0;
+  while (rn > rtol * bn && it < max_it) {
+    const double beta = (rho / rho_old) * (alpha / omega);
+    for (size_t k = 0; k < S; k++) p[k] = r[k] + beta * (p[k] - omega * v[k]);
+    aug_precond(E, p, ph);
+    aug_apply(E, ph, v);
+    alpha = rho / dotv(r0, v);
+    for (size_t k = 0; k < S; k++) s[k] = r[k] - alpha * v[k];
+    aug_precond(E, s, sh);
+    aug_apply(E, sh, t);
+    omega = dotv(t, s) / dotv(t, t);
+    for (size_t k = 0; k < S; k++) { x[k] += alpha * ph[k] + omega * sh[k]; r[k] = s[k] - omega * t[k]; }
+    rho_old = rho; rho = dotv(r0, r);
+    rn = std::sqrt(dotv(r, r));
+    it++;
+    if (!(rn == rn)) break;
+  }
+  aug_apply(E, x, y);
+  double tr = 0; for (size_t k = 0; k < S; k++) { const double d = b[k] - y[k]; tr += d * d; }
+  *rel = std::sqrt(tr) / bn;
+  E.aug_shift = fluid_sum(E, x);
+  return it;
 }
 
 template <bool RECT>
@@ -220,9 +290,34 @@ void* emul_create_rank(const nsgpu_grid* G, double dt, double re, int nu_pre, in
     if (l > 0) { L.x.assign(L.A.stride, 0.0); L.xt.assign(L.A.stride, 0.0); L.b.assign(L.A.stride, 0.0); }
   }
   for (auto& v : E->f) v.assign(E->lv[0].A.stride, 0.0);
+  if (plan_has_outflow(E->plan)) {
+    std::vector<double> w;
+    rc = phi_ilu0_image_of_ones(G, E->plan, w, E->err);
+    if (rc) { if (errbuf && errlen > 0) { strncpy(errbuf, E->err.c_str(), errlen - 1); errbuf[errlen - 1] = 0; } delete E; return nullptr; }
+    const LevelGeom& g = E->lv[0].g;
+    E->aug_w.assign(E->lv[0].A.stride, 0.0);
+    for (int i = 0; i < g.nx; i++)
+      for (int j = 0; j < g.ny; j++) {
+        const long id = E->plan.rect ? (long)i * g.ny + j : (long)E->plan.local_id[(size_t)i * g.ny + j];
+        if (id >= 0) { const double wv = w[(size_t)(E->plan.id0 + id)]; E->aug_w[cidx(g, i, j)] = wv; }
+      }
+    for (double wv : w) E->aug_ww += wv * wv;
+    E->aug = true;
+  }
   return E;
 }
 void emul_destroy(void* h) { delete (Emul*)h; }
+// w = ILU(0)(LHS_phi) * 1 in compact local id order (zeros when the domain has no outflow edge); returns (w, w) over the global domain
+double emul_phi_ilu_w(void* h, double* out) {
+  Emul* E = (Emul*)h;
+  const LevelGeom& g = E->lv[0].g;
+  for (int i = 0; i < g.nx; i++)
+    for (int j = 0; j < g.ny; j++) {
+      const long id = E->plan.rect ? (long)i * g.ny + j : (long)E->plan.local_id[(size_t)i * g.ny + j];
+      if (id >= 0) out[id] = E->aug ? E->aug_w[cidx(g, i, j)] : 0.0;
+    }
+  return E->aug_ww;
+}
 int emul_rect(void* h) { return ((Emul*)h)->plan.rect ? 1 : 0; }
 int emul_num_levels(void* h) { return (int)((Emul*)h)->lv.size(); }
 long emul_n_local(void* h) { return (long)((Emul*)h)->plan.n_local; }
@@ -258,7 +353,7 @@ void emul_apply(void* h, int op, const double* x, double* y) {
   Emul* E = (Emul*)h;
   emul_set(h, 12, x);
   const LevelGeom& g = E->lv[0].g;
-  Coef c = op == 0 ? Coef{0, 1.0, E->dt / (2.0 * E->re)} : Coef{1, 0.0, -1.0};
+  Coef c = op == 0 ? Coef{0, 1.0, E->dt / (2.0 * E->re)} : Coef{op, 0.0, -1.0};   // 1 = LHS_phi, 2 = its wall-only variant
   for (int i = 0; i < g.nx; i++)
     for (int j = 0; j < g.ny; j++) {
       const long id = E->plan.rect ? (long)i * g.ny + j : (long)E->plan.local_id[(size_t)i * g.ny + j];
@@ -270,7 +365,8 @@ void emul_apply(void* h, int op, const double* x, double* y) {
 int emul_solve(void* h, int which, double rtol, int max_cycles, double* rel) {
   Emul* E = (Emul*)h;
   if (which == 2) {
-    int n = solve_mg(*E, Coef{1, 0.0, -1.0}, E->f[NSGPU_PHI], E->f[NSGPU_RHS_PHI], rtol, max_cycles, rel);
+    int n = E->aug ? solve_phi_aug(*E, E->f[NSGPU_PHI], E->f[NSGPU_RHS_PHI], rtol, max_cycles, rel)
+                   : solve_mg(*E, Coef{1, 0.0, -1.0}, E->f[NSGPU_PHI], E->f[NSGPU_RHS_PHI], rtol, max_cycles, rel);
     phi_mean_zero(*E);
     return n;
   }

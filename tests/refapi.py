@@ -172,6 +172,8 @@ def emul_lib():
         L.emul_poisson_sweeps.argtypes = [C.c_void_p, C.c_int, _dp]
         L.emul_step.argtypes = [C.c_void_p, C.c_int, C.c_double, C.c_int, _dp, _ip]
         L.emul_step.restype = C.c_double
+        L.emul_phi_ilu_w.argtypes = [C.c_void_p, _dp]
+        L.emul_phi_ilu_w.restype = C.c_double
         _emul = L
     return _emul
 
@@ -261,6 +263,12 @@ class Emul:
         y = np.zeros(self.n)
         self.L.emul_apply(self.h, op, x.ctypes.data_as(_dp), y.ctypes.data_as(_dp))
         return y
+
+    def phi_ilu_w(self):
+        """(w, (w, w)): w = ILU(0)(LHS_phi) * 1, what csrc/ns_hostgeom.h builds for outflow domains (zeros without an outflow edge)."""
+        w = np.zeros(self.n)
+        ww = self.L.emul_phi_ilu_w(self.h, w.ctypes.data_as(_dp))
+        return w, ww
 
     def solve(self, which, rtol=1e-8, max_cycles=100):
         rel = C.c_double()

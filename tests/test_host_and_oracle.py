@@ -187,6 +187,77 @@ def test_zero_lid_oracle_stays_at_rest(workdir):
     assert not r.step(3).any() and not r.get(PHI).any()
 
 
+# ---------------------------------------------------------------------------------------------- outflow (bcType 4) domains
+def _ilu0_times_ones(A):
+    """w = L (U 1) of the ILU(0) factors of a CSR matrix in natural ordering (plain Python: the domains here have ~3000 cells)."""
+    A = A.tocsr().copy()
+    A.sort_indices()
+    n = A.shape[0]
+    ip, ix, a = A.indptr, A.indices, A.data.copy()
+    diag = np.empty(n, dtype=np.int64)
+    for i in range(n):
+        row = {ix[k]: k for k in range(ip[i], ip[i + 1])}
+        for k in range(ip[i], ip[i + 1]):
+            j = ix[k]
+            if j >= i:
+                break
+            a[k] /= a[diag[j]]
+            for kk in range(diag[j] + 1, ip[j + 1]):
+                q = row.get(ix[kk])
+                if q is not None:
+                    a[q] -= a[k] * a[kk]
+        diag[i] = row[i]
+    t = np.array([a[diag[i]:ip[i + 1]].sum() for i in range(n)])
+    return np.array([t[i] + (a[ip[i]:diag[i]] * t[ix[ip[i]:diag[i]]]).sum() for i in range(n)])
+
+
+@needs_ref
+@pytest.mark.parametrize("case", ["channel", "step"])
+def test_outflow_fixed_point_of_the_reference_solve(case, workdir):
+    """With a type-4 edge LHS_phi x = b has no solution; what the reference's KSPSolve (FS.cpp:551) returns is the solution of
+    A x + c w = b, mean(x) = 0, w = ILU(0)(A) 1 -- pinned here on the oracle, together with the host code that builds w for the GPU."""
+    r = refapi.RefSolver(f"{CASES}/{case}.grid", f"{CASES}/{case}.sim")
+    r.set_rtol(1e-13)
+    A = r.csr(1)
+    w = _ilu0_times_ones(A)
+    em = refapi.Emul(dt=r.dt, re=r.re, **r.desc_kwargs())
+    w_host, ww = em.phi_ilu_w()
+    assert _rel(w_host, w) <= 1e-13 and abs(ww - w @ w) <= 1e-12 * ww
+    r.construct_rhs_v(); r.solve_velocity(); r.construct_rhs_phi(); r.nullspace_remove()
+    b = r.get(RHS_PHI)
+    r.solve_phi()
+    phi = r.get(PHI)
+    res = b - A @ phi
+    assert np.linalg.norm(res) > 1e-3 * np.linalg.norm(b)          # nowhere near a solution of A x = b ...
+    c = (res @ w) / (w @ w)
+    assert np.linalg.norm(res - c * w) <= 1e-8 * np.linalg.norm(res)  # ... the residual is c * w
+    assert abs(phi.mean()) <= 1e-9 * np.abs(phi).max()
+    # the wall-only operator of the preconditioner (op 2) is the same grid with type 2 in place of type 4
+    kw = r.desc_kwargs()
+    kw["edge_bc_type"] = np.where(kw["edge_bc_type"] == 4, 2, kw["edge_bc_type"]).astype(np.int32)
+    walls = refapi.Emul(dt=r.dt, re=r.re, **kw)
+    x = np.random.default_rng(5).standard_normal(r.n)
+    assert _rel(em.apply(2, x), walls.apply(1, x)) <= 1e-14
+    assert _rel(em.apply(1, x), A @ x) <= 1e-12
+
+
+@needs_ref
+@pytest.mark.parametrize("case", ["channel", "step"])
+def test_outflow_whole_steps_emulation_vs_reference(case, workdir):
+    """Whole time steps on inlet / wall / outflow domains: the augmented BiCGStab (same structure as csrc/ns_solver.inl) reproduces
+    the reference's fields.  Tolerance 1e-6: the reference at its own rtol 1e-8 differs from itself at 1e-12 by 3e-6 there."""
+    ref = refapi.RefSolver(f"{CASES}/{case}.grid", f"{CASES}/{case}.sim")
+    ref.set_rtol(1e-12)
+    em = refapi.Emul(dt=ref.dt, re=ref.re, **ref.desc_kwargs())
+    for s in range(4):
+        mm = ref.step(1)
+        me, worst, cyc = em.step(1, rtol=1e-10)
+        assert worst <= 1e-9 and cyc[2] <= 40, (worst, cyc)
+        for k in (U, V, PHI):
+            assert _rel(em.get(k), ref.get(k)) <= 1e-6, (s, k)
+        assert np.allclose(me, mm, rtol=0, atol=1e-6 * np.abs(mm).max())
+
+
 def test_golden_fixture_matches_oracle_or_emulation(workdir):
     """tests/golden/cavity32_re100_5steps.npz was written by tests/golden/make_golden.py from the oracle in exact mode."""
     z = np.load(os.path.join(ROOT, "tests", "golden", "cavity32_re100_5steps.npz"))
