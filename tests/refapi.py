@@ -285,3 +285,25 @@ class Emul:
         cyc = (C.c_int * 3)()
         worst = self.L.emul_step(self.h, n, rtol, max_cycles, mm.ctypes.data_as(_dp), cyc)
         return mm, worst, list(cyc)
+
+
+# ------------------------------------------------------------------------------------------------------------------
+def golden_1024_gaps(u, v, phi):
+    """Relative gaps of full 1024 x 1024 fields (compact-id order) to tests/golden/cavity1024_re1000_3steps.npz (written by
+    tests/golden/make_golden_1024.py from the oracle at rtol 1e-12): sampled cells, six full lines, four functionals per field."""
+    z = np.load(os.path.join(ROOT, "tests", "golden", "cavity1024_re1000_3steps.npz"))
+    n, stride, lines = 1024, int(z["stride"]), [int(k) for k in z["lines"]]
+    wgt = np.cos(0.37 * np.arange(n * n) ** 0.5)
+    out = {}
+    for name, a in (("u", u), ("v", v), ("phi", phi - phi.mean())):
+        f = a.reshape(n, n)
+        scale = np.abs(z[f"{name}_cols"]).max()
+        fun = np.array([a.sum(), (a * a).sum(), np.abs(a).max(), (a * wgt).sum()])
+        ref = z[f"{name}_fun"]
+        out[name] = dict(
+            sub=float(np.abs(f[::stride, ::stride] - z[f"{name}_sub"]).max() / scale),
+            cols=float(np.abs(f[lines, :] - z[f"{name}_cols"]).max() / scale),
+            rows=float(np.abs(f[:, lines] - z[f"{name}_rows"]).max() / scale),
+            sum=float(abs(fun[0] - ref[0]) / (n * n * scale)), sumsq=float(abs(fun[1] - ref[1]) / ref[1]),
+            absmax=float(abs(fun[2] - ref[2]) / ref[2]), weighted=float(abs(fun[3] - ref[3]) / (n * n * scale)))
+    return out, z["minmax"], float(z["dt"]), float(z["re"]), int(z["steps"])

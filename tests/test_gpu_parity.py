@@ -159,6 +159,25 @@ def test_fused_sweep_equals_emulated_red_black(n, nx, workdir):
     assert abs(r_gpu - r_em) <= 1e-10 * r_em
 
 
+def test_cavity_1024_re1000_against_golden(workdir):
+    """BASELINE configs[1]: lid-driven cavity Re=1000 at 1024 x 1024 on one B200, fields vs the CPU reference.  The oracle needs
+    minutes at this size, so the comparison is with the committed sample of its fields after 3 steps from rest (rtol 1e-12;
+    tests/golden/make_golden_1024.py): min/max of every step, every 16th cell, six full lines, four functionals per field.
+    Tolerance 2e-8 per field (Tier B), GPU at true-residual rtol 1e-10."""
+    import navierstokessolver_b200 as ns
+    n = 1024
+    _, minmax, dt, re, steps = refapi.golden_1024_gaps(np.zeros(n * n), np.zeros(n * n), np.zeros(n * n))
+    gpu = ns.GpuFluidSolver(ns.GridDesc.cavity(n), dt, re, rtol_u=1e-10, rtol_phi=1e-10)
+    for s in range(steps):
+        info = gpu.step(1)
+        assert info.status == 0
+        assert np.abs(np.array([info.umin, info.umax, info.vmin, info.vmax]) - minmax[s]).max() <= 2e-8
+    gaps, *_ = refapi.golden_1024_gaps(gpu.get(U), gpu.get(V), gpu.get(PHI))
+    print("gaps to the 1024^2 golden sample:", gaps)
+    for name, g in gaps.items():
+        assert max(g.values()) <= 2e-8, (name, g)
+
+
 def test_zero_lid_stays_at_rest(workdir):
     import navierstokessolver_b200 as ns
     gpu = ns.GpuFluidSolver(ns.GridDesc.cavity(64, lid=0.0), 0.005, 100.0)

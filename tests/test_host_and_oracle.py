@@ -274,6 +274,22 @@ def test_golden_fixture_matches_oracle_or_emulation(workdir):
             assert _rel(r.get(k), z[name]) <= 1e-9
 
 
+def test_golden_1024_matches_emulation(workdir):
+    """BASELINE configs[1] (cavity Re=1000, 1024 x 1024): the committed sample of the reference's fields after 3 steps (oracle at
+    rtol 1e-12, tests/golden/make_golden_1024.py) against the host emulation of the GPU's loops -- every printed min/max, the
+    sampled cells, the wall / lid / centre lines and the field functionals."""
+    n = 1024
+    _, minmax, dt, re, steps = refapi.golden_1024_gaps(np.zeros(n * n), np.zeros(n * n), np.zeros(n * n))
+    em = refapi.Emul(np.full(n, 1.0 / n), np.full(n, 1.0 / n), [-1, 0, 1, 0], [0, 1, 0, -1], [2, 2, 2, 2], [0, 1.0, 0, 0], dt, re)
+    for s in range(steps):
+        mm, worst, cyc = em.step(1, rtol=1e-10)
+        assert worst <= 1e-10
+        assert np.abs(mm - minmax[s]).max() <= 1e-9
+    gaps, *_ = refapi.golden_1024_gaps(em.get(U), em.get(V), em.get(PHI))
+    for name, g in gaps.items():
+        assert max(g.values()) <= 1e-8, (name, g)
+
+
 @needs_ref
 def test_reference_main_compiles_unmodified_against_host_headers(workdir):
     """Drop-in check of the driver: the reference's own MAIN_Solver.cpp builds against host/FluidSolver.h + libnsgpu.so."""
