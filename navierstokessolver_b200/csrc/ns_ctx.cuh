@@ -115,6 +115,7 @@ struct nsgpu_ctx {
   double* tail_img[2] = {nullptr, nullptr};      // per operator: the launch-invariant part of the coarse tail's shared memory (k_tail_image)
   long long* tail_dbg = nullptr;                 // NSGPU_TAIL_DBG=1: clock64 stamps of the coarse tail's phases (printed at destroy)
   int rhs_march = 1;                             // ConstructRHS_V on rectangles through k_rhs_march (NSGPU_RHS_MARCH=0: cell kernel)
+  int vel_guess_rhs = 0;                         // initial guess of the u*, v* solves: 0 = u^n, v^n; 1 = the right-hand side (LHS_V = I - dt/(2Re) L is close to I)
   int march_rb_min_nx = 0;                       // levels with fewer columns keep uniform chunks (NSGPU_RB_MINNX)
   int march_rb = 0;                              // width of the short boundary chunks of pushing passes (NSGPU_RB, 0 = off)
   unsigned last_gather_ctas = 0;                 // CTAs of the last restriction pass that gathered onto the replicated level

@@ -171,6 +171,7 @@ static int create_impl(nsgpu_ctx* ctx, const nsgpu_grid* G, const nsgpu_params* 
   if (const char* e = getenv("NSGPU_RB")) ctx->march_rb = atoi(e);
   if (const char* e = getenv("NSGPU_RHS_MARCH")) ctx->rhs_march = atoi(e);
   if (const char* e = getenv("NSGPU_FUSE_BN2")) ctx->fuse_bn2 = atoi(e);
+  if (const char* e = getenv("NSGPU_VEL_GUESS")) ctx->vel_guess_rhs = atoi(e);
   if (getenv("NSGPU_TAIL_DBG")) { void* q = nullptr; if (cudaMalloc(&q, 64 * sizeof(long long)) == cudaSuccess) { cudaMemset(q, 0, 64 * sizeof(long long)); ctx->owned.push_back(q); ctx->tail_dbg = (long long*)q; } }
   if (const char* e = getenv("NSGPU_RB_MINNX")) ctx->march_rb_min_nx = atoi(e);
   if (ctx->world > 1 && ctx->world <= MAX_RANKS && ctx->use_p2p && plan.rect && plan.levels[0].gnx % ctx->world == 0) {   // equal slabs: equal arena layouts

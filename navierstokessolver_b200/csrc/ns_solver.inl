@@ -863,8 +863,9 @@ static int phase_velocity(nsgpu_ctx* ctx, SolveResult* ru, SolveResult* rv) {   
   int rc;
   if ((rc = halo_exchange(ctx, L, ctx->rhs_u, HX - 1))) return rc;   // the fused passes recompute up to 4 halo columns
   if ((rc = halo_exchange(ctx, L, ctx->rhs_v, HX - 1))) return rc;
-  if ((rc = solve(ctx, 0, coef_v(ctx), &ctx->ustar, ctx->rhs_u, ctx->rtol_u, ru, ctx->u))) return rc;
-  if ((rc = solve(ctx, 1, coef_v(ctx), &ctx->vstar, ctx->rhs_v, ctx->rtol_u, rv, ctx->v))) return rc;
+  double *gu = ctx->vel_guess_rhs ? ctx->rhs_u : ctx->u, *gv = ctx->vel_guess_rhs ? ctx->rhs_v : ctx->v;
+  if ((rc = solve(ctx, 0, coef_v(ctx), &ctx->ustar, ctx->rhs_u, ctx->rtol_u, ru, gu))) return rc;
+  if ((rc = solve(ctx, 1, coef_v(ctx), &ctx->vstar, ctx->rhs_v, ctx->rtol_u, rv, gv))) return rc;
   return 0;
 }
 
