@@ -94,10 +94,14 @@ static int allreduce(nsgpu_ctx* ctx, double* d, int n, ncclRedOp_t op) {
 // ---------------------------------------------------------------------------------------------------------
 // Fused marching passes (rectangle fast path, ns_march.cuh)
 
+// Folded tables of the marching kernels: the tables of op 1 never contain the outflow rows (they are not separable, march_ok[1] is
+// false on outflow domains), i.e. they ARE the wall-only L_phi -- op 2, the preconditioner of the outflow solve, marches on them.
+static inline int op_tab(OpCoef c) { return c.op == 2 ? 1 : c.op; }
+static inline bool march_tab_ok(const Level& L, OpCoef c) { return c.op == 2 ? L.mcx[1] != nullptr : L.march_ok[c.op]; }
+
 static inline bool march_level_ok(const nsgpu_ctx* ctx, const Level& L, OpCoef c) {
   // with several ranks the 5-column halo of a fused pass has to come from ONE neighbour
-  if (c.op > 1) return false;   // the wall-only L_phi of the outflow preconditioner runs on the generic kernels
-  return ctx->march && ctx->rect && L.march_ok[c.op] && (ctx->world == 1 || L.replicated || L.g.nx >= HX);
+  return ctx->march && ctx->rect && march_tab_ok(L, c) && (ctx->world == 1 || L.replicated || L.g.nx >= HX);
 }
 
 typedef void (*MarchKernel)(LevelGeom, const double*, const double*, const double*, const double*, double*, int, MarchXfer);
@@ -216,7 +220,7 @@ static int march_pass(nsgpu_ctx* ctx, const Level& L, OpCoef c, int nsw, double*
     if (gather) ctx->last_gather_ctas = grid.x * grid.y;
   } else if (res == 2 && ctx->d_pt) xf.pt = ctx->d_pt;   // the residual norm is summed over the ranks in the epilogue
   trace_begin(ctx, (int)(&L - ctx->levels.data()) * 1000 + nsw * 100 + res * 10 + (Cp ? 2 : 0) + (push ? 1 : 0) + (omega > 0 ? 50000 : 0));
-  kern<<<grid, MARCH_THREADS, sh, ctx->stream>>>(L.g, L.mcx[c.op], L.mcy[c.op], xin, b, xout, ri, xf);
+  kern<<<grid, MARCH_THREADS, sh, ctx->stream>>>(L.g, L.mcx[op_tab(c)], L.mcy[op_tab(c)], xin, b, xout, ri, xf);
   trace_end(ctx);
   if (push) {
     ctx->halo_w[xout] = xf.pushw;
@@ -259,10 +263,10 @@ static int march_sweeps(nsgpu_ctx* ctx, const Level& L, OpCoef c, int n, double*
 static int vcycle_fused(nsgpu_ctx* ctx, int l, OpCoef c, double** x, double** xt, const double* b, bool xzero, double* norm_out,
                         SolveCtl* ctl, double* src0 = nullptr) {
   Level& L = ctx->levels[l];
-  if (ctx->tail_start > 0 && l == ctx->tail_start && L.march_ok[c.op]) {   // the rest of the cycle in one single-CTA kernel
-    const TailDesc& T = ctx->tail[c.op];
+  if (ctx->tail_start > 0 && l == ctx->tail_start && march_tab_ok(L, c)) {   // the rest of the cycle in one single-CTA kernel
+    const TailDesc& T = ctx->tail[op_tab(c)];
     trace_begin(ctx, 99999);
-    k_coarse_tail<<<1, TAIL_THREADS, (size_t)T.smem_doubles * sizeof(double), ctx->stream>>>(T, ctx->tail_img[c.op], b, *x, nullptr, 0u, ctx->tail_dbg);
+    k_coarse_tail<<<1, TAIL_THREADS, (size_t)T.smem_doubles * sizeof(double), ctx->stream>>>(T, ctx->tail_img[op_tab(c)], b, *x, nullptr, 0u, ctx->tail_dbg);
     trace_end(ctx);
     NS_LAUNCH_CHECK();
     return 0;
