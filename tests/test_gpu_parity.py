@@ -178,6 +178,73 @@ def test_cavity_1024_re1000_against_golden(workdir):
         assert max(g.values()) <= 2e-8, (name, g)
 
 
+def _run_main(exe, grid, sim, cwd):
+    import subprocess
+    cwd.mkdir()
+    out = subprocess.run([exe, grid, sim], cwd=cwd, capture_output=True, text=True, timeout=600)
+    assert out.returncode == 0, out.stderr[-2000:]
+    return out.stdout
+
+
+def _split_stdout(text):
+    """(messages, table): the per-step lines '%d\\t%lf\\t%lf\\t%lf\\t%lf' (FS.cpp:559-560) apart from everything else."""
+    msgs, rows = [], []
+    for line in text.splitlines():
+        f = line.split("\t")
+        if len(f) == 5 and f[0].isdigit():
+            rows.append([float(x) for x in f])
+        else:
+            msgs.append(line)
+    return msgs, np.array(rows)
+
+
+@pytest.mark.parametrize("case", ["cavity", "step"])
+def test_drop_in_main_against_reference_main(case, workdir, tmp_path):
+    """The drop-in boundary end to end: bin/main (host Grid + FluidSolver + libnsgpu.so) against oracle/_ref/main_ref (the reference's
+    own MAIN_Solver.cpp, Grid.cpp, FluidSolver.cpp) on the same two input files -- same stdout (messages verbatim, the per-step
+    min/max table to its 6 printed decimals), same CellCenters.csv, same FlowData_<iter>.csv files to their 6 significant digits."""
+    import os
+    ref_exe, gpu_exe = f"{refapi.ROOT}/oracle/_ref/main_ref", f"{refapi.ROOT}/bin/main"
+    if not (os.path.exists(ref_exe) and os.path.exists(gpu_exe)):
+        pytest.skip("main_ref / bin/main not built")
+    sim = tmp_path / "case.sim"
+    if case == "cavity":
+        grid = f"{CASES}/cavity_32.grid"
+        sim.write_text("BC {\n2 0\n2 1\n2 0\n2 0\n}\ndt 0.005\nfinal_time 0.3\nre 100\nsaveIter 25\n")
+        exports = ["FlowData_25.csv", "FlowData_50.csv"]
+    else:
+        grid = f"{CASES}/step.grid"
+        sim.write_text(open(f"{CASES}/step.sim").read().replace("final_time 0.1", "final_time 0.03").replace("saveIter 1000000", "saveIter 3"))
+        assert "final_time 0.03" in sim.read_text() and "saveIter 3" in sim.read_text()
+        exports = None
+    a = _run_main(ref_exe, grid, str(sim), tmp_path / "ref")
+    b = _run_main(gpu_exe, grid, str(sim), tmp_path / "gpu")
+    ma, ta = _split_stdout(a)
+    mb, tb = _split_stdout(b)
+    assert ma == mb
+    assert ta.shape == tb.shape and len(ta) >= 5
+    assert np.array_equal(ta[:, 0], tb[:, 0])
+    # 6 printed decimals; on the outflow domain the reference's own rtol-1e-8 noise (3e-6 relative, DESIGN.md section 5) comes on top
+    assert np.abs(ta[:, 1:] - tb[:, 1:]).max() <= (2e-6 if case == "cavity" else 1e-5) * max(1.0, np.abs(ta[:, 1:]).max())
+    files = sorted(f for f in os.listdir(tmp_path / "ref") if f.endswith(".csv"))
+    assert files == sorted(f for f in os.listdir(tmp_path / "gpu") if f.endswith(".csv"))
+    if exports:
+        assert set(exports) <= set(files)
+    assert len(files) >= 3
+    assert open(tmp_path / "ref" / "CellCenters.csv").read() == open(tmp_path / "gpu" / "CellCenters.csv").read()
+    for f in files:
+        if f == "CellCenters.csv":
+            continue
+        ra, rb = open(tmp_path / "ref" / f).read().splitlines(), open(tmp_path / "gpu" / f).read().splitlines()
+        assert ra[0] == rb[0] and len(ra) == len(rb)
+        xa = np.array([[float(v) for v in l.split(",")] for l in ra[1:]])
+        xb = np.array([[float(v) for v in l.split(",")] for l in rb[1:]])
+        assert np.array_equal(xa[:, :3], xb[:, :3]), f          # point coordinates
+        for col in (3, 4, 5):                                   # U, V, Pr: 6 significant digits in the file
+            scale = np.abs(xa[:, col]).max()
+            assert np.abs(xa[:, col] - xb[:, col]).max() <= 2e-5 * scale, (f, col)
+
+
 def test_zero_lid_stays_at_rest(workdir):
     import navierstokessolver_b200 as ns
     gpu = ns.GpuFluidSolver(ns.GridDesc.cavity(64, lid=0.0), 0.005, 100.0)
