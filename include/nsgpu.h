@@ -137,6 +137,15 @@ int nsgpu_set_array(nsgpu_ctx* ctx, int32_t which, const double* in);
 int nsgpu_get_fields(nsgpu_ctx* ctx, double* u, double* v, double* phi);  /* any pointer may be NULL */
 int nsgpu_set_fields(nsgpu_ctx* ctx, const double* u, const double* v, const double* phi);
 
+/* Checkpoint / restart.  The reference has none (its state lives and dies with the process, FS.h:22-33); SURVEY.md section 8(f) lists
+ * it for the long runs to steady state.  The file holds the complete state of the time loop for this rank's id range -- the seven
+ * arrays of nsgpu_host_state -- plus the caller's step counter, so a restarted run continues bit for bit (outflow domains: to
+ * the solver tolerance, the Krylov warm-start shift is not part of the state).  Little-endian binary: 64-byte header
+ * ("NSGPUCK1", nx, ny, n_cells, id0, n_local, step, dt) then 7 x n_local doubles.  Several ranks: each rank writes "<path>.<rank>".
+ * load refuses a file whose grid extents or id range differ from the context's (NSGPU_ERR_ARG). */
+int nsgpu_checkpoint_save(nsgpu_ctx* ctx, const char* path, int64_t step);
+int nsgpu_checkpoint_load(nsgpu_ctx* ctx, const char* path, int64_t* step);
+
 /* introspection for benchmarks and tests */
 int nsgpu_num_levels(const nsgpu_ctx* ctx);
 /* device milliseconds of the five phases of the last time step run by nsgpu_step: ConstructRHS_V, the two velocity

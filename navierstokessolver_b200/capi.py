@@ -93,6 +93,8 @@ def _load():
     L.nsgpu_kernel_launches.argtypes = [P]
     L.nsgpu_kernel_launches.restype = C.c_int64
     L.nsgpu_synchronize.argtypes = [P]
+    L.nsgpu_checkpoint_save.argtypes = [P, C.c_char_p, C.c_int64]
+    L.nsgpu_checkpoint_load.argtypes = [P, C.c_char_p, C.POINTER(C.c_int64)]
     return L
 
 
@@ -102,7 +104,7 @@ EXPORTED = ["nsgpu_nccl_unique_id", "nsgpu_create", "nsgpu_destroy", "nsgpu_last
             "nsgpu_step", "nsgpu_rhs_build", "nsgpu_solve_velocity", "nsgpu_div_rhs", "nsgpu_solve_phi",
             "nsgpu_correct", "nsgpu_poisson_sweeps", "nsgpu_apply_operator", "nsgpu_pressure", "nsgpu_get_array",
             "nsgpu_set_array", "nsgpu_get_fields", "nsgpu_set_fields", "nsgpu_num_levels", "nsgpu_kernel_launches",
-            "nsgpu_synchronize", "nsgpu_phase_ms", "nsgpu_step_host"]
+            "nsgpu_synchronize", "nsgpu_phase_ms", "nsgpu_step_host", "nsgpu_checkpoint_save", "nsgpu_checkpoint_load"]
 
 
 def _dp(a):
@@ -213,6 +215,16 @@ class GpuFluidSolver:
         info = StepInfo()
         self._chk(lib.nsgpu_step_host(self._h, C.byref(io), C.byref(info)), soft=(-5,))
         return info
+
+    def checkpoint_save(self, path, step=0):
+        """Complete state of the time loop (7 arrays of this rank's id range) + the caller's step counter -> file (nsgpu_checkpoint_save)."""
+        self._chk(lib.nsgpu_checkpoint_save(self._h, str(path).encode(), int(step)))
+
+    def checkpoint_load(self, path):
+        """Restores the state written by checkpoint_save on the same grid and slab decomposition; returns the stored step counter."""
+        step = C.c_int64(0)
+        self._chk(lib.nsgpu_checkpoint_load(self._h, str(path).encode(), C.byref(step)))
+        return int(step.value)
 
     def rhs_build(self):
         self._chk(lib.nsgpu_rhs_build(self._h))

@@ -176,6 +176,59 @@ int nsgpu_set_fields(nsgpu_ctx* ctx, const double* u, const double* v, const dou
   return 0;
 }
 
+namespace {
+struct CkptHeader { char magic[8]; int64_t nx, ny, n_cells, id0, n_local, step; double dt; };
+static_assert(sizeof(CkptHeader) == 64, "checkpoint header is 64 bytes");
+const int kCkptFields[7] = {NSGPU_U, NSGPU_V, NSGPU_PHI, NSGPU_CONV_U0, NSGPU_CONV_V0, NSGPU_GRADPHI_X, NSGPU_GRADPHI_Y};
+std::string ckpt_name(const nsgpu_ctx* ctx, const char* path) {
+  return ctx->world > 1 ? std::string(path) + "." + std::to_string(ctx->rank) : std::string(path);
+}
+}  // namespace
+
+int nsgpu_checkpoint_save(nsgpu_ctx* ctx, const char* path, int64_t step) {
+  if (!ctx || !path) return NSGPU_ERR_ARG;
+  const std::string name = ckpt_name(ctx, path), tmp = name + ".tmp";
+  FILE* f = fopen(tmp.c_str(), "wb");
+  if (!f) { ctx->err = "cannot open " + tmp + " for writing"; return NSGPU_ERR_ARG; }
+  CkptHeader h{};
+  memcpy(h.magic, "NSGPUCK1", 8);
+  h.nx = ctx->gnx; h.ny = ctx->ny; h.n_cells = ctx->n_cells_global; h.id0 = ctx->id0; h.n_local = ctx->n_local; h.step = step; h.dt = ctx->dt;
+  bool ok = fwrite(&h, sizeof h, 1, f) == 1;
+  std::vector<double> buf((size_t)ctx->n_local);
+  for (int k = 0; k < 7 && ok; k++) {
+    const int rc = nsgpu_get_array(ctx, kCkptFields[k], buf.data());
+    if (rc) { fclose(f); remove(tmp.c_str()); return rc; }
+    ok = fwrite(buf.data(), sizeof(double), buf.size(), f) == buf.size();
+  }
+  ok = (fclose(f) == 0) && ok;
+  if (ok) ok = rename(tmp.c_str(), name.c_str()) == 0;   // a crash while writing never leaves a truncated checkpoint under the final name
+  if (!ok) { remove(tmp.c_str()); ctx->err = "short write to " + name; return NSGPU_ERR_ARG; }
+  return 0;
+}
+
+int nsgpu_checkpoint_load(nsgpu_ctx* ctx, const char* path, int64_t* step) {
+  if (!ctx || !path) return NSGPU_ERR_ARG;
+  const std::string name = ckpt_name(ctx, path);
+  FILE* f = fopen(name.c_str(), "rb");
+  if (!f) { ctx->err = "cannot open " + name; return NSGPU_ERR_ARG; }
+  CkptHeader h{};
+  if (fread(&h, sizeof h, 1, f) != 1 || memcmp(h.magic, "NSGPUCK1", 8) != 0) { fclose(f); ctx->err = name + " is not an nsgpu checkpoint"; return NSGPU_ERR_ARG; }
+  if (h.nx != ctx->gnx || h.ny != ctx->ny || h.n_cells != ctx->n_cells_global || h.id0 != ctx->id0 || h.n_local != ctx->n_local) {
+    fclose(f); ctx->err = name + " was written for another grid or another slab decomposition"; return NSGPU_ERR_ARG;
+  }
+  // read everything before touching the device state: a truncated file leaves the context as it was
+  std::vector<double> buf((size_t)7 * (size_t)ctx->n_local);
+  const bool ok = fread(buf.data(), sizeof(double), buf.size(), f) == buf.size();
+  fclose(f);
+  if (!ok) { ctx->err = name + " is truncated"; return NSGPU_ERR_ARG; }
+  for (int k = 0; k < 7; k++) {
+    const int rc = nsgpu_set_array(ctx, kCkptFields[k], buf.data() + (size_t)k * (size_t)ctx->n_local);
+    if (rc) return rc;
+  }
+  if (step) *step = h.step;
+  return 0;
+}
+
 int nsgpu_rhs_build(nsgpu_ctx* ctx) {
   if (!ctx) return NSGPU_ERR_ARG;
   cudaSetDevice(ctx->device);

@@ -143,8 +143,21 @@ bool FluidSolver::createDeviceSolver() {
 }
 
 // Same loop control as FS.cpp:536-567: iter starts at 1, the first step always runs, stop when dt*iter > finalTime.
+bool FluidSolver::SaveCheckpoint(const char* path) {
+  if (!gpu || nsgpu_checkpoint_save(gpu, path, lastIter) != 0) { cout << "Checkpoint not written: " << nsgpu_last_error(gpu) << "\n"; return false; }
+  return true;
+}
+
+bool FluidSolver::LoadCheckpoint(const char* path) {
+  int64_t step = 0;
+  if (!gpu || nsgpu_checkpoint_load(gpu, path, &step) != 0) { cout << "Checkpoint not loaded: " << nsgpu_last_error(gpu) << "\n"; return false; }
+  lastIter = (int)step;
+  firstIter = lastIter + 1;
+  return true;
+}
+
 void FluidSolver::Solve() {
-  int iter = 1;
+  int iter = firstIter;
   cout << "Initiating Solver..\n";
   do {
     nsgpu_step_info info;
@@ -156,6 +169,8 @@ void FluidSolver::Solve() {
     if ((iter - 1) % 10 == 0) printf("iter\tumin\t\tumax\t\tvmin\t\tvmax\n");
     printf("%d\t%lf\t%lf\t%lf\t%lf\n", iter, info.umin, info.umax, info.vmin, info.vmax);
     if (saveIter > 0 && iter % saveIter == 0) ExportData(iter);
+    lastIter = iter;
+    if (checkpointIter > 0 && iter % checkpointIter == 0) SaveCheckpoint("checkpoint.nsgpu");
     iter++;
   } while (dt * iter <= finalTime);
   cout << "Solution Complete!\n";

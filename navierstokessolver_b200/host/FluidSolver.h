@@ -18,6 +18,8 @@ class FluidSolver {
   double finalTime;
   double re;
   int saveIter = 50;
+  int firstIter = 1;          // 1, or the step after a loaded checkpoint
+  int lastIter = 0;           // last completed step
   bool readSimulationFile(ifstream& in);
   bool checkParameters();
   void buildGhostStencils();
@@ -31,8 +33,12 @@ class FluidSolver {
   FluidSolver(char* fname, Grid* grid);
   ~FluidSolver();
   void Solve();
-  // extras (not in the reference): number of steps Solve() will take, and access for tests
+  // extras (not in the reference): access for tests, and checkpoint / restart of the time loop -- Solve() resumes after the
+  // step a loaded checkpoint was written at (nsgpu_checkpoint_save / _load, include/nsgpu.h)
   nsgpu_ctx* device() { return gpu; }
+  bool SaveCheckpoint(const char* path);
+  bool LoadCheckpoint(const char* path);
+  int checkpointIter = 0;     // > 0: Solve() writes "checkpoint.nsgpu" every checkpointIter steps
 };
 
 double minmode(double a, double b);

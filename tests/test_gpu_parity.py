@@ -245,6 +245,46 @@ def test_drop_in_main_against_reference_main(case, workdir, tmp_path):
             assert np.abs(xa[:, col] - xb[:, col]).max() <= 2e-5 * scale, (f, col)
 
 
+def test_checkpoint_restart_continues_bit_for_bit(workdir, tmp_path):
+    """nsgpu_checkpoint_save / _load: 3 steps, save, 3 more -- against a fresh context that loads the file and
+    takes the same 3 steps: identical fields; a file of another grid is refused; bin/main -checkpoint_every / -restart print the
+    same table tail as an uninterrupted run."""
+    import subprocess
+    import navierstokessolver_b200 as ns
+    g = ns.GridDesc.cavity(96, nx=160, lx=160 / 96.0)
+    a = ns.GpuFluidSolver(g, 0.002, 400.0)
+    a.step(3)
+    ck = tmp_path / "state.nsgpu"
+    a.checkpoint_save(ck, step=3)
+    a.step(3)
+    b = ns.GpuFluidSolver(g, 0.002, 400.0)
+    assert b.checkpoint_load(ck) == 3
+    b.step(3)
+    for k in (U, V, PHI, CONV_U0, CONV_V0, GRADPHI_X, GRADPHI_Y):
+        assert np.array_equal(a.get(k), b.get(k)), k
+    other = ns.GpuFluidSolver(ns.GridDesc.cavity(64), 0.002, 400.0)
+    with pytest.raises(ns.NsGpuError) as e:
+        other.checkpoint_load(ck)
+    assert e.value.code == -1
+    trunc = tmp_path / "trunc.nsgpu"
+    trunc.write_bytes(open(ck, "rb").read()[:4096])
+    before = b.get(U).copy()
+    with pytest.raises(ns.NsGpuError):
+        b.checkpoint_load(trunc)
+    assert np.array_equal(b.get(U), before)          # a truncated file leaves the state untouched
+    # the command-line driver
+    exe = f"{refapi.ROOT}/bin/main"
+    sim = tmp_path / "c.sim"
+    sim.write_text("BC {\n2 0\n2 1\n2 0\n2 0\n}\ndt 0.005\nfinal_time 0.1\nre 100\nsaveIter 1000\n")
+    d1, d2 = tmp_path / "whole", tmp_path / "parts"
+    d1.mkdir(); d2.mkdir()
+    whole = subprocess.run([exe, f"{CASES}/cavity_32.grid", str(sim)], cwd=d1, capture_output=True, text=True, timeout=300).stdout
+    subprocess.run([exe, f"{CASES}/cavity_32.grid", str(sim), "-checkpoint_every", "8"], cwd=d2, capture_output=True, text=True, timeout=300)
+    rest = subprocess.run([exe, f"{CASES}/cavity_32.grid", str(sim), "-restart", "checkpoint.nsgpu"], cwd=d2, capture_output=True, text=True, timeout=300).stdout
+    tail = lambda t: [l for l in t.splitlines() if l.split("\t")[0].isdigit() and int(l.split("\t")[0]) > 16]
+    assert len(tail(whole)) == 4 and tail(whole) == tail(rest)
+
+
 def test_zero_lid_stays_at_rest(workdir):
     import navierstokessolver_b200 as ns
     gpu = ns.GpuFluidSolver(ns.GridDesc.cavity(64, lid=0.0), 0.005, 100.0)
