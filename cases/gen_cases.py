@@ -31,6 +31,19 @@ def main(out):
         f.write("Vertices {\n0 0.5\n0 1\n4 1\n4 0\n1 0\n1 0.5\n}\nNx {\n0 1 24 -1\n1 4 72 -1\n}\nNy {\n0 0.5 16 -1\n0.5 1 16 -1\n}\n")
     with open(os.path.join(out, "step.sim"), "w") as f:
         f.write("BC {\n0 1\n2 0\n4 0\n2 0\n2 0\n2 0\n}\ndt 0.005\nfinal_time 0.1\nre 100\nsaveIter 1000000\n")
+    # outflow on the other three sides (the F_OW / F_OS / F_ON rows of LHS_phi): flow towards -x, -y and +y
+    with open(os.path.join(out, "channel_west.grid"), "w") as f:
+        f.write("Vertices {\n0 0\n0 1\n3 1\n3 0\n}\nNx {\n0 3 48 -1\n}\nNy {\n0 1 24 -1\n}\n")
+    with open(os.path.join(out, "channel_west.sim"), "w") as f:   # edges: left, top, right, bottom
+        f.write("BC {\n4 0\n2 0\n0 -1\n2 0\n}\ndt 0.01\nfinal_time 0.2\nre 100\nsaveIter 1000000\n")
+    with open(os.path.join(out, "channel_south.grid"), "w") as f:
+        f.write("Vertices {\n0 0\n0 3\n1 3\n1 0\n}\nNx {\n0 1 24 -1\n}\nNy {\n0 1 16 -1\n1 3 0 1.04\n}\n")
+    with open(os.path.join(out, "channel_south.sim"), "w") as f:
+        f.write("BC {\n2 0\n0 -1\n2 0\n4 0\n}\ndt 0.01\nfinal_time 0.2\nre 100\nsaveIter 1000000\n")
+    with open(os.path.join(out, "channel_north.grid"), "w") as f:
+        f.write("Vertices {\n0 0\n0 3\n1 3\n1 0\n}\nNx {\n0 1 24 -1\n}\nNy {\n0 3 48 -1\n}\n")
+    with open(os.path.join(out, "channel_north.sim"), "w") as f:
+        f.write("BC {\n2 0\n4 0\n2 0\n0 1\n}\ndt 0.01\nfinal_time 0.2\nre 100\nsaveIter 1000000\n")
 
 if __name__ == "__main__":
     main(sys.argv[1] if len(sys.argv) > 1 else os.path.dirname(os.path.abspath(__file__)))

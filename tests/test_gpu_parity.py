@@ -28,7 +28,8 @@ def _rel(a, b):
 
 
 CASE_LIST = [("cavity_32.grid", "cavity_re100.sim"), ("cavity_128.grid", "cavity_re1000_128.sim"),
-             ("channel.grid", "channel.sim"), ("step.grid", "step.sim")]
+             ("channel.grid", "channel.sim"), ("step.grid", "step.sim"),
+             ("channel_west.grid", "channel_west.sim"), ("channel_south.grid", "channel_south.sim"), ("channel_north.grid", "channel_north.sim")]
 
 
 @pytest.mark.parametrize("grid,sim", CASE_LIST)
@@ -121,7 +122,7 @@ def test_whole_steps_cavity(n, sim, solver, workdir):
         assert np.allclose([info.umin, info.umax, info.vmin, info.vmax], mm, rtol=0, atol=1e-8)
 
 
-@pytest.mark.parametrize("case", ["channel", "step"])
+@pytest.mark.parametrize("case", ["channel", "step", "channel_west", "channel_south", "channel_north"])
 def test_whole_steps_outflow_domains(case, workdir):
     """BASELINE configs[4]: inlet / walls / outflow (channel, backward-facing step with masked cells and stretched hx).  With a
     type-4 edge LHS_phi x = b is inconsistent; the reference's KSP converges to A x + c ILU0(A) 1 = b, mean(x) = 0

@@ -115,7 +115,9 @@ def test_minmode_matches():
 
 # ---------------------------------------------------------------------------------------------- device arithmetic, on the host
 @needs_ref
-@pytest.mark.parametrize("grid,sim", [("cavity_32.grid", "cavity_re100.sim"), ("channel.grid", "channel.sim"), ("step.grid", "step.sim")])
+@pytest.mark.parametrize("grid,sim", [("cavity_32.grid", "cavity_re100.sim"), ("channel.grid", "channel.sim"), ("step.grid", "step.sim"),
+                                      ("channel_west.grid", "channel_west.sim"), ("channel_south.grid", "channel_south.sim"),
+                                      ("channel_north.grid", "channel_north.sim")])
 def test_device_functions_match_reference_phases(grid, sim, workdir):
     """Tier A (1e-12): ns_cell.cuh compiled for the host vs the reference's ConstructRHS_V / ConstructRHS_phi /
     CorrectVelocities and the matrices ConstructLHS assembles."""
@@ -211,8 +213,11 @@ def _ilu0_times_ones(A):
     return np.array([t[i] + (a[ip[i]:diag[i]] * t[ix[ip[i]:diag[i]]]).sum() for i in range(n)])
 
 
+OUTFLOW_CASES = ["channel", "step", "channel_west", "channel_south", "channel_north"]   # outflow towards +x, +x (masked), -x, -y, +y
+
+
 @needs_ref
-@pytest.mark.parametrize("case", ["channel", "step"])
+@pytest.mark.parametrize("case", OUTFLOW_CASES)
 def test_outflow_fixed_point_of_the_reference_solve(case, workdir):
     """With a type-4 edge LHS_phi x = b has no solution; what the reference's KSPSolve (FS.cpp:551) returns is the solution of
     A x + c w = b, mean(x) = 0, w = ILU(0)(A) 1 -- pinned here on the oracle, together with the host code that builds w for the GPU."""
@@ -242,7 +247,7 @@ def test_outflow_fixed_point_of_the_reference_solve(case, workdir):
 
 
 @needs_ref
-@pytest.mark.parametrize("case", ["channel", "step"])
+@pytest.mark.parametrize("case", OUTFLOW_CASES)
 def test_outflow_whole_steps_emulation_vs_reference(case, workdir):
     """Whole time steps on inlet / wall / outflow domains: the augmented BiCGStab (same structure as csrc/ns_solver.inl) reproduces
     the reference's fields.  Tolerance 1e-6: the reference at its own rtol 1e-8 differs from itself at 1e-12 by 3e-6 there."""
