@@ -12,8 +12,10 @@ residual of 1e-8 (the reference's KSP tolerance).  Workload at N = 1: lid-driven
   value  = cells x time steps / second, state resident in HBM, device time (CUDA events on the solver's stream,
            max over ranks), in Gcell-updates/s (one cell-update = one cell advanced one time step);
            "timesteps_per_s" and "poisson_gcell_updates_per_s" (the fine-level red-black sweep alone) ride along.
-  e2e    = same metric through the C ABI with HOST buffers (nsgpu_step_host): every step uploads the full state (7 fields)
-           from pinned host memory, runs one time step and downloads the 7 fields again; the copies overlap the phases.
+  e2e    = same metric through the C ABI with HOST buffers (nsgpu_step_host): every step uploads the complete state of the
+           time loop from pinned host memory -- u, v, phi and the two convective terms; divPhi is GradP(phi) and is rebuilt on
+           the device instead of being shipped -- runs one time step and downloads the five arrays again; the copies overlap
+           the phases.  (--e2e-arrays 7 ships divPhi as well, like a caller that mirrors every reference Vec.)
 """
 import argparse
 import json
@@ -196,7 +198,7 @@ def ours(args, rank, world, local_rank):
             traffic = None
 
     # ---- end to end through the C ABI with host buffers (pinned), full state up, fields down, every step
-    fields_up = [ns.U, ns.V, ns.PHI, ns.CONV_U0, ns.CONV_V0, ns.GRADPHI_X, ns.GRADPHI_Y]
+    fields_up = [ns.U, ns.V, ns.PHI, ns.CONV_U0, ns.CONV_V0] + ([ns.GRADPHI_X, ns.GRADPHI_Y] if args.e2e_arrays == 7 else [])
     host = {k: torch.empty(s.n_local, dtype=torch.float64).pin_memory().numpy() for k in fields_up}
     for k in fields_up:
         host[k][:] = s.get(k)
@@ -204,7 +206,7 @@ def ours(args, rank, world, local_rank):
     barrier()
     t0 = time.perf_counter()
     for _ in range(e2e_steps):
-        s.step_host(host)   # 7 arrays up, one time step, 7 arrays down; copies overlap the phases (nsgpu_step_host)
+        s.step_host(host)   # the state arrays up, one time step, the same arrays down; copies overlap the phases (nsgpu_step_host)
     s.synchronize()
     e2e_wall = max_over_ranks(time.perf_counter() - t0)
     e2e_value = cells_global * e2e_steps / e2e_wall / 1e9
@@ -232,7 +234,9 @@ def ours(args, rank, world, local_rank):
                 "gpu_launches": launches,
                 "clocks": clocks,
                 "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "steps": e2e_steps,
-                        "ms_per_step": 1e3 * e2e_wall / e2e_steps},
+                        "ms_per_step": 1e3 * e2e_wall / e2e_steps,
+                        "arrays": "%d state arrays each way per step (u, v, phi, N_u, N_v%s), pinned host memory, nsgpu_step_host"
+                                  % (len(fields_up), ", divPhi x/y" if args.e2e_arrays == 7 else "; divPhi = GradP(phi) rebuilt on the device")},
                 "roofline": {"bound": "hbm", "kernel": "k_march<1,false,0> (fine-level fused red-black Poisson sweep, register-marching)", "achieved": achieved, "peak": peak,
                              "unit": "GB/s", "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
                              "bytes_per_cell_update": SWEEP_BYTES_PER_UPDATE, "us_per_launch": best * 1e3,
@@ -261,6 +265,7 @@ def main():
     ap.add_argument("--sweeps", type=int, default=100)
     ap.add_argument("--ref-n", type=int, default=256)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--e2e-arrays", type=int, default=5, choices=[5, 7])
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     rank = int(os.environ.get("RANK", "0"))

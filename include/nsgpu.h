@@ -107,7 +107,9 @@ int nsgpu_step(nsgpu_ctx* ctx, int32_t n_steps, nsgpu_step_info* last);
  * u, v, phi, convectiveDer_u0/v0, gradphi_x/y, FS.h:22-33; compact-id order, this rank's range; page-locked buffers
  * make the copies asynchronous).  The seven arrays are uploaded, the step runs, the seven arrays are overwritten with
  * the new state.  Copies overlap the phases: phi travels up while ConstructRHS_V and the velocity solves run, the
- * convective terms travel down during the solves, phi during CorrectVelocities.  Rectangular domains. */
+ * convective terms travel down during the solves, phi during CorrectVelocities.  Rectangular domains.
+ * gradphi_x = gradphi_y = NULL: divPhi is not shipped at all -- it is GradP(phi) (FS.cpp:529), so it is rebuilt on the device from
+ * the uploaded phi (same arithmetic as CorrectVelocities) and stays there: five arrays up, five down. */
 typedef struct nsgpu_host_state {
   double *u, *v, *phi, *conv_u0, *conv_v0, *gradphi_x, *gradphi_y;
 } nsgpu_host_state;

@@ -210,8 +210,11 @@ class GpuFluidSolver:
     def step_host(self, state):
         """One time step with the whole state in host arrays (nsgpu_step_host): `state` maps U, V, PHI, CONV_U0, CONV_V0,
         GRADPHI_X, GRADPHI_Y to contiguous float64 arrays of this rank's id range; they are overwritten with the new state.
+        Without the two GRADPHI entries divPhi is rebuilt on the device from PHI and not shipped (five arrays each way).
         Page-locked arrays make the copies overlap the phases."""
-        io = HostState(*[_dp(state[k]) for k in (U, V, PHI, CONV_U0, CONV_V0, GRADPHI_X, GRADPHI_Y)])
+        with_grad = GRADPHI_X in state
+        io = HostState(*[_dp(state[k]) for k in (U, V, PHI, CONV_U0, CONV_V0)],
+                       _dp(state[GRADPHI_X]) if with_grad else None, _dp(state[GRADPHI_Y]) if with_grad else None)
         info = StepInfo()
         self._chk(lib.nsgpu_step_host(self._h, C.byref(io), C.byref(info)), soft=(-5,))
         return info

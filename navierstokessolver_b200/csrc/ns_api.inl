@@ -309,16 +309,36 @@ static int step_impl(nsgpu_ctx* ctx, int32_t n_steps, nsgpu_step_info* last, con
     // upload stream: everything ConstructRHS_V reads first, phi (needed by the third solve only) behind it
     NS_CUDA(cudaEventRecord(ctx->ev_io[0], ctx->stream));          // earlier work on the solver's stream reads these arrays
     NS_CUDA(cudaStreamWaitEvent(ctx->s_in, ctx->ev_io[0], 0));
-    NS_CUDA(copy_in(ctx, ctx->u, io->u, ctx->s_in));
-    NS_CUDA(copy_in(ctx, ctx->v, io->v, ctx->s_in));
-    NS_CUDA(copy_in(ctx, ctx->conv_u, io->conv_u0, ctx->s_in));
-    NS_CUDA(copy_in(ctx, ctx->conv_v, io->conv_v0, ctx->s_in));
-    NS_CUDA(copy_in(ctx, ctx->gpx, io->gradphi_x, ctx->s_in));
-    NS_CUDA(copy_in(ctx, ctx->gpy, io->gradphi_y, ctx->s_in));
-    NS_CUDA(cudaEventRecord(ctx->ev_io[1], ctx->s_in));
-    NS_CUDA(copy_in(ctx, ctx->phi, io->phi, ctx->s_in));
-    NS_CUDA(cudaEventRecord(ctx->ev_io[2], ctx->s_in));
-    NS_CUDA(cudaStreamWaitEvent(ctx->stream, ctx->ev_io[1], 0));
+    if (io->gradphi_x) {
+      NS_CUDA(copy_in(ctx, ctx->u, io->u, ctx->s_in));
+      NS_CUDA(copy_in(ctx, ctx->v, io->v, ctx->s_in));
+      NS_CUDA(copy_in(ctx, ctx->conv_u, io->conv_u0, ctx->s_in));
+      NS_CUDA(copy_in(ctx, ctx->conv_v, io->conv_v0, ctx->s_in));
+      NS_CUDA(copy_in(ctx, ctx->gpx, io->gradphi_x, ctx->s_in));
+      NS_CUDA(copy_in(ctx, ctx->gpy, io->gradphi_y, ctx->s_in));
+      NS_CUDA(cudaEventRecord(ctx->ev_io[1], ctx->s_in));
+      NS_CUDA(copy_in(ctx, ctx->phi, io->phi, ctx->s_in));
+      NS_CUDA(cudaEventRecord(ctx->ev_io[2], ctx->s_in));
+      NS_CUDA(cudaStreamWaitEvent(ctx->stream, ctx->ev_io[1], 0));
+    } else {
+      // divPhi = GradP(phi^n) is not shipped: phi goes first and the gradient is rebuilt while u, v and the convective terms arrive
+      NS_CUDA(copy_in(ctx, ctx->phi, io->phi, ctx->s_in));
+      NS_CUDA(cudaEventRecord(ctx->ev_io[2], ctx->s_in));
+      NS_CUDA(copy_in(ctx, ctx->u, io->u, ctx->s_in));
+      NS_CUDA(copy_in(ctx, ctx->v, io->v, ctx->s_in));
+      NS_CUDA(copy_in(ctx, ctx->conv_u, io->conv_u0, ctx->s_in));
+      NS_CUDA(copy_in(ctx, ctx->conv_v, io->conv_v0, ctx->s_in));
+      NS_CUDA(cudaEventRecord(ctx->ev_io[1], ctx->s_in));
+      NS_CUDA(cudaStreamWaitEvent(ctx->stream, ctx->ev_io[2], 0));
+      const Level& L = ctx->levels[0];
+      int rc0;
+      if ((rc0 = halo_exchange(ctx, L, ctx->phi, 2))) return rc0;
+      const dim3 grid = grid_cols(L.g, 256);
+      k_gradphi<true><<<grid, 256, 0, ctx->stream>>>(L.g, ctx->phi, ctx->gpx, ctx->gpy);
+      NS_LAUNCH_CHECK();
+      ctx->halo_w.clear();
+      NS_CUDA(cudaStreamWaitEvent(ctx->stream, ctx->ev_io[1], 0));
+    }
   }
   SolveResult ru, rv, rp;
   double mm[4] = {0, 0, 0, 0};
@@ -356,8 +376,10 @@ static int step_impl(nsgpu_ctx* ctx, int32_t n_steps, nsgpu_step_info* last, con
       NS_CUDA(cudaStreamWaitEvent(ctx->s_out, ctx->ev_io[5], 0));
       NS_CUDA(copy_out(ctx, ctx->u, io->u, ctx->s_out));
       NS_CUDA(copy_out(ctx, ctx->v, io->v, ctx->s_out));
-      NS_CUDA(copy_out(ctx, ctx->gpx, io->gradphi_x, ctx->s_out));
-      NS_CUDA(copy_out(ctx, ctx->gpy, io->gradphi_y, ctx->s_out));
+      if (io->gradphi_x) {
+        NS_CUDA(copy_out(ctx, ctx->gpx, io->gradphi_x, ctx->s_out));
+        NS_CUDA(copy_out(ctx, ctx->gpy, io->gradphi_y, ctx->s_out));
+      }
     }
     if (!((ru.pending || ru.converged) && (rv.pending || rv.converged) && (rp.pending || rp.converged))) status = NSGPU_ERR_NOT_CONVERGED;   // silent in the reference
   }
@@ -399,7 +421,7 @@ extern "C" {
 int nsgpu_step(nsgpu_ctx* ctx, int32_t n_steps, nsgpu_step_info* last) { return nsgpu::step_impl(ctx, n_steps, last, nullptr); }
 
 int nsgpu_step_host(nsgpu_ctx* ctx, const nsgpu_host_state* io, nsgpu_step_info* info) {
-  if (!io || !io->u || !io->v || !io->phi || !io->conv_u0 || !io->conv_v0 || !io->gradphi_x || !io->gradphi_y) return NSGPU_ERR_ARG;
+  if (!io || !io->u || !io->v || !io->phi || !io->conv_u0 || !io->conv_v0 || ((io->gradphi_x == nullptr) != (io->gradphi_y == nullptr))) return NSGPU_ERR_ARG;
   return nsgpu::step_impl(ctx, 1, info, io);
 }
 

@@ -477,6 +477,23 @@ k_correct(LevelGeom g, StepConst sc, const double* __restrict__ phi, const doubl
   grid_reduce<4, OpMax>(acc, red, out);
 }
 
+// (gpx, gpy) = GradP(phi) alone (FS.cpp:420-456): divPhi is a pure function of phi, so a caller that keeps its state on the host
+// need not ship it (nsgpu_step_host with gradphi_x = gradphi_y = NULL)
+template <bool RECT>
+__global__ void __launch_bounds__(256)
+k_gradphi(LevelGeom g, const double* __restrict__ phi, double* __restrict__ gpx, double* __restrict__ gpy) {
+  const int j = blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= g.ny) return;
+  for (int i = chunk_lo(g.nx), i_hi = chunk_hi(g.nx); i < i_hi; i++) {
+    const unsigned f = cell_flags<RECT>(g, i, j);
+    if (f == F_OUTSIDE) continue;
+    const size_t id = cidx(g, i, j);
+    const UV gr = grad_cell(g, f, i, j, phi + id);
+    gpx[id] = gr.u;
+    gpy[id] = gr.v;
+  }
+}
+
 // ---------------------------------------------------------------------------------------------------------
 // Contiguous vector kernels over the owned columns [HX*ld, (HX+nx)*ld): padding rows and masked cells hold 0
 // in every vector, so plain linear loops are exact.

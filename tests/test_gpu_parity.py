@@ -336,6 +336,17 @@ def test_step_with_host_state_equals_resident_steps(workdir):
         for k in keys:
             assert np.array_equal(state[k], a.get(k)), k
             assert np.array_equal(b.get(k), a.get(k)), k
+    # five-array form: divPhi = GradP(phi) is rebuilt on the device instead of being shipped
+    c = ns.GpuFluidSolver(g, 0.002, 400.0)
+    five = {k: state[k].copy() for k in (U, V, PHI, CONV_U0, CONV_V0)}
+    for _ in range(2):
+        ia = a.step(1)
+        ic = c.step_host(five)
+        assert (ia.it_u, ia.it_v, ia.it_phi, ia.status) == (ic.it_u, ic.it_v, ic.it_phi, ic.status)
+        for k in keys:
+            assert np.array_equal(c.get(k), a.get(k)), k
+        for k in five:
+            assert np.array_equal(five[k], a.get(k)), k
 
 
 def test_velocity_sor_and_multigrid_agree(workdir):
