@@ -203,6 +203,7 @@ def ours(args, rank, world, local_rank):
     for k in fields_up:
         host[k][:] = s.get(k)
     e2e_steps = max(2, min(args.steps, 5))
+    s.step_host(host)   # one untimed step: copy streams, events and the solve graphs of this form are made on first use
     barrier()
     t0 = time.perf_counter()
     for _ in range(e2e_steps):

@@ -287,6 +287,17 @@ static cudaError_t copy_in(nsgpu_ctx* ctx, double* dev, const double* host, cuda
   return cudaMemcpy2DAsync(dev + cidx(g, 0, 0), (size_t)g.ld * sizeof(double), host, (size_t)g.ny * sizeof(double),
                            (size_t)g.ny * sizeof(double), (size_t)g.nx, cudaMemcpyHostToDevice, st);
 }
+// columns [c0, c1) only
+static cudaError_t copy_in_cols(nsgpu_ctx* ctx, double* dev, const double* host, int c0, int c1, cudaStream_t st) {
+  const LevelGeom& g = ctx->levels[0].g;
+  return cudaMemcpy2DAsync(dev + cidx(g, c0, 0), (size_t)g.ld * sizeof(double), host + (size_t)c0 * g.ny, (size_t)g.ny * sizeof(double),
+                           (size_t)g.ny * sizeof(double), (size_t)(c1 - c0), cudaMemcpyHostToDevice, st);
+}
+static cudaError_t copy_out_cols(nsgpu_ctx* ctx, const double* dev, double* host, int c0, int c1, cudaStream_t st) {
+  const LevelGeom& g = ctx->levels[0].g;
+  return cudaMemcpy2DAsync(host + (size_t)c0 * g.ny, (size_t)g.ny * sizeof(double), dev + cidx(g, c0, 0), (size_t)g.ld * sizeof(double),
+                           (size_t)g.ny * sizeof(double), (size_t)(c1 - c0), cudaMemcpyDeviceToHost, st);
+}
 static cudaError_t copy_out(nsgpu_ctx* ctx, const double* dev, double* host, cudaStream_t st) {
   const LevelGeom& g = ctx->levels[0].g;
   return cudaMemcpy2DAsync(host, (size_t)g.ny * sizeof(double), dev + cidx(g, 0, 0), (size_t)g.ld * sizeof(double),
@@ -297,6 +308,7 @@ static cudaError_t copy_out(nsgpu_ctx* ctx, const double* dev, double* host, cud
 static int step_impl(nsgpu_ctx* ctx, int32_t n_steps, nsgpu_step_info* last, const nsgpu_host_state* io) {
   if (!ctx || n_steps < 0) return NSGPU_ERR_ARG;
   cudaSetDevice(ctx->device);
+  int io_k = 1, nx0 = 0;   // nsgpu_step_host: number of column chunks of the pipelined upload (1: none)
   if (io) {
     if (n_steps != 1 || !ctx->rect) { ctx->err = "nsgpu_step_host: one step, rectangular domains"; return NSGPU_ERR_ARG; }
     if (!ctx->s_in) {
@@ -306,6 +318,9 @@ static int step_impl(nsgpu_ctx* ctx, int32_t n_steps, nsgpu_step_info* last, con
     }
     ctx->halo_w.clear();
     ctx->bn2_ready[0] = ctx->bn2_ready[1] = ctx->bn2_ready[2] = false;
+    // five-array form on one rank: the uploads of u, v, N_u, N_v are cut into column chunks (at least 8 columns each)
+    nx0 = ctx->levels[0].g.nx;
+    io_k = (!io->gradphi_x && ctx->world == 1 && ctx->rhs_march && nx0 >= 16) ? std::min(ctx->io_chunks, nx0 / 8) : 1;
     // upload stream: everything ConstructRHS_V reads first, phi (needed by the third solve only) behind it
     NS_CUDA(cudaEventRecord(ctx->ev_io[0], ctx->stream));          // earlier work on the solver's stream reads these arrays
     NS_CUDA(cudaStreamWaitEvent(ctx->s_in, ctx->ev_io[0], 0));
@@ -324,10 +339,26 @@ static int step_impl(nsgpu_ctx* ctx, int32_t n_steps, nsgpu_step_info* last, con
       // divPhi = GradP(phi^n) is not shipped: phi goes first and the gradient is rebuilt while u, v and the convective terms arrive
       NS_CUDA(copy_in(ctx, ctx->phi, io->phi, ctx->s_in));
       NS_CUDA(cudaEventRecord(ctx->ev_io[2], ctx->s_in));
-      NS_CUDA(copy_in(ctx, ctx->u, io->u, ctx->s_in));
-      NS_CUDA(copy_in(ctx, ctx->v, io->v, ctx->s_in));
-      NS_CUDA(copy_in(ctx, ctx->conv_u, io->conv_u0, ctx->s_in));
-      NS_CUDA(copy_in(ctx, ctx->conv_v, io->conv_v0, ctx->s_in));
+      if (io_k > 1) {   // column chunks: ConstructRHS_V follows the uploads chunk by chunk, its convective terms go home at once
+        if ((int)ctx->ev_chunk.size() < 2 * io_k) {
+          const size_t have = ctx->ev_chunk.size();
+          ctx->ev_chunk.resize((size_t)2 * io_k, nullptr);
+          for (size_t k = have; k < ctx->ev_chunk.size(); k++) NS_CUDA(cudaEventCreateWithFlags(&ctx->ev_chunk[k], cudaEventDisableTiming));
+        }
+        for (int c = 0; c < io_k; c++) {
+          const int c0 = (int)((long long)nx0 * c / io_k), c1 = (int)((long long)nx0 * (c + 1) / io_k);
+          NS_CUDA(copy_in_cols(ctx, ctx->u, io->u, c0, c1, ctx->s_in));
+          NS_CUDA(copy_in_cols(ctx, ctx->v, io->v, c0, c1, ctx->s_in));
+          NS_CUDA(copy_in_cols(ctx, ctx->conv_u, io->conv_u0, c0, c1, ctx->s_in));
+          NS_CUDA(copy_in_cols(ctx, ctx->conv_v, io->conv_v0, c0, c1, ctx->s_in));
+          NS_CUDA(cudaEventRecord(ctx->ev_chunk[c], ctx->s_in));
+        }
+      } else {
+        NS_CUDA(copy_in(ctx, ctx->u, io->u, ctx->s_in));
+        NS_CUDA(copy_in(ctx, ctx->v, io->v, ctx->s_in));
+        NS_CUDA(copy_in(ctx, ctx->conv_u, io->conv_u0, ctx->s_in));
+        NS_CUDA(copy_in(ctx, ctx->conv_v, io->conv_v0, ctx->s_in));
+      }
       NS_CUDA(cudaEventRecord(ctx->ev_io[1], ctx->s_in));
       NS_CUDA(cudaStreamWaitEvent(ctx->stream, ctx->ev_io[2], 0));
       const Level& L = ctx->levels[0];
@@ -337,7 +368,7 @@ static int step_impl(nsgpu_ctx* ctx, int32_t n_steps, nsgpu_step_info* last, con
       k_gradphi<true><<<grid, 256, 0, ctx->stream>>>(L.g, ctx->phi, ctx->gpx, ctx->gpy);
       NS_LAUNCH_CHECK();
       ctx->halo_w.clear();
-      NS_CUDA(cudaStreamWaitEvent(ctx->stream, ctx->ev_io[1], 0));
+      if (io_k <= 1) NS_CUDA(cudaStreamWaitEvent(ctx->stream, ctx->ev_io[1], 0));
     }
   }
   SolveResult ru, rv, rp;
@@ -349,9 +380,21 @@ static int step_impl(nsgpu_ctx* ctx, int32_t n_steps, nsgpu_step_info* last, con
   for (int s = 0; s < n_steps; s++) {
     const bool last = s == n_steps - 1;   // the last step of the call carries the phase timers (events are free)
     if (last) cudaEventRecord(ctx->evp[0], ctx->stream);
-    if ((rc = phase_rhs(ctx))) return rc;
+    if (io && io_k > 1) {
+      ctx->halo_w.clear();
+      ctx->bn2_ready[0] = ctx->bn2_ready[1] = false;   // |rhs|^2 is reduced by the solve heads here
+      for (int c = 0; c < io_k; c++) {
+        const int c0 = (int)((long long)nx0 * c / io_k), c1 = (int)((long long)nx0 * (c + 1) / io_k);
+        NS_CUDA(cudaStreamWaitEvent(ctx->stream, ctx->ev_chunk[std::min(c + 1, io_k - 1)], 0));   // radius-2 stencil: the next chunk too
+        if ((rc = phase_rhs_cols(ctx, c0, c1))) return rc;
+        NS_CUDA(cudaEventRecord(ctx->ev_chunk[io_k + c], ctx->stream));
+        NS_CUDA(cudaStreamWaitEvent(ctx->s_out, ctx->ev_chunk[io_k + c], 0));
+        NS_CUDA(copy_out_cols(ctx, ctx->conv_u, io->conv_u0, c0, c1, ctx->s_out));
+        NS_CUDA(copy_out_cols(ctx, ctx->conv_v, io->conv_v0, c0, c1, ctx->s_out));
+      }
+    } else if ((rc = phase_rhs(ctx))) return rc;
     if (last) cudaEventRecord(ctx->evp[1], ctx->stream);
-    if (io) {   // the convective terms are final: they go home while the solves run
+    if (io && io_k <= 1) {   // the convective terms are final: they go home while the solves run
       NS_CUDA(cudaEventRecord(ctx->ev_io[3], ctx->stream));
       NS_CUDA(cudaStreamWaitEvent(ctx->s_out, ctx->ev_io[3], 0));
       NS_CUDA(copy_out(ctx, ctx->conv_u, io->conv_u0, ctx->s_out));

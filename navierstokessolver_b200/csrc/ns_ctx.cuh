@@ -110,6 +110,8 @@ struct nsgpu_ctx {
   std::unordered_map<int, std::pair<double, long>> trace_acc;
   cudaStream_t s_in = nullptr, s_out = nullptr;  // copy streams of nsgpu_step_host (created on first use)
   cudaEvent_t ev_io[6] = {};
+  std::vector<cudaEvent_t> ev_chunk;            // nsgpu_step_host, pipelined form: upload / ConstructRHS_V events per column chunk
+  int io_chunks = 8;                             // NSGPU_IO_CHUNKS (1: no pipelining)
   int fuse_bn2 = 1;                              // NSGPU_FUSE_BN2=0: |b|^2 by a separate reduction pass over b
   bool bn2_ready[3] = {false, false, false};     // |b|^2 of the next solve of slot k is already in d_scal[30 + k] (written with b)
   double* tail_img[2] = {nullptr, nullptr};      // per operator: the launch-invariant part of the coarse tail's shared memory (k_tail_image)

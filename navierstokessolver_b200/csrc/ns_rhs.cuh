@@ -49,11 +49,12 @@ __global__ void __launch_bounds__(RHS_THREADS)
 k_rhs_march(LevelGeom g, const EdgeDev* __restrict__ edges, StepConst sc, const double* __restrict__ u,
             const double* __restrict__ v, double* __restrict__ nu0, double* __restrict__ nv0,
             const double* __restrict__ gpx, const double* __restrict__ gpy, double* __restrict__ rhs_u,
-            double* __restrict__ rhs_v, int RI, Reducer red, double* __restrict__ norms) {
+            double* __restrict__ rhs_v, int RI, Reducer red, double* __restrict__ norms, int i_begin, int i_end) {
   const int lane = threadIdx.x & 31;
   const int wj = blockIdx.x * RHS_WARPS + (threadIdx.x >> 5);
   const int j = wj * RHS_UJ + lane - 2;                  // rows -2, -1, ny, ny+1 are zero padding (PJ = 8)
-  const int ib = blockIdx.y * RI, ie = min(ib + RI, g.nx);
+  // columns [i_begin, i_end) of the slab (the whole slab, or one upload chunk of nsgpu_step_host), RI columns per CTA row
+  const int ib = i_begin + blockIdx.y * RI, ie = min(ib + RI, i_end);
   const int jc = min(j, g.ny + 1);                       // rows past the padding: clamp (never stored)
   const bool in_dom = j >= 0 && j < g.ny;
   const bool store = in_dom && lane >= 2 && lane < 30;

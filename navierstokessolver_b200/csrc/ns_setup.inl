@@ -109,6 +109,7 @@ static void destroy_ctx(nsgpu_ctx* ctx) {
   for (void* p : ctx->owned) cudaFree(p);
   for (auto& sg : ctx->sgraph) { if (sg.exec) cudaGraphExecDestroy(sg.exec); if (sg.graph) cudaGraphDestroy(sg.graph); }
   if (ctx->s_in) { cudaStreamDestroy(ctx->s_in); cudaStreamDestroy(ctx->s_out); for (auto& e : ctx->ev_io) if (e) cudaEventDestroy(e); }
+  for (auto& e : ctx->ev_chunk) if (e) cudaEventDestroy(e);
   if (ctx->h_scal) cudaFreeHost(ctx->h_scal);
   if (ctx->h_ctl) cudaFreeHost(ctx->h_ctl);
   if (ctx->h_stage) cudaFreeHost(ctx->h_stage);
@@ -172,6 +173,7 @@ static int create_impl(nsgpu_ctx* ctx, const nsgpu_grid* G, const nsgpu_params* 
   if (const char* e = getenv("NSGPU_RHS_MARCH")) ctx->rhs_march = atoi(e);
   if (const char* e = getenv("NSGPU_FUSE_BN2")) ctx->fuse_bn2 = atoi(e);
   if (const char* e = getenv("NSGPU_VEL_GUESS")) ctx->vel_guess_rhs = atoi(e);
+  if (const char* e = getenv("NSGPU_IO_CHUNKS")) ctx->io_chunks = std::max(1, atoi(e));
   if (getenv("NSGPU_TAIL_DBG")) { void* q = nullptr; if (cudaMalloc(&q, 64 * sizeof(long long)) == cudaSuccess) { cudaMemset(q, 0, 64 * sizeof(long long)); ctx->owned.push_back(q); ctx->tail_dbg = (long long*)q; } }
   if (const char* e = getenv("NSGPU_RB_MINNX")) ctx->march_rb_min_nx = atoi(e);
   if (ctx->world > 1 && ctx->world <= MAX_RANKS && ctx->use_p2p && plan.rect && plan.levels[0].gnx % ctx->world == 0) {   // equal slabs: equal arena layouts

@@ -843,7 +843,7 @@ static int phase_rhs(nsgpu_ctx* ctx) {   // ConstructRHS_V, FS.cpp:546
     const int ri = (L.g.nx + chunks - 1) / chunks;
     const dim3 grid(gx, (L.g.nx + ri - 1) / ri);
     k_rhs_march<<<grid, RHS_THREADS, 0, ctx->stream>>>(L.g, ctx->d_edges, sc, ctx->u, ctx->v, ctx->conv_u, ctx->conv_v, ctx->gpx, ctx->gpy,
-                                                       ctx->rhs_u, ctx->rhs_v, ri, ctx->red, ctx->fuse_bn2 ? ctx->d_scal + 30 : nullptr);
+                                                       ctx->rhs_u, ctx->rhs_v, ri, ctx->red, ctx->fuse_bn2 ? ctx->d_scal + 30 : nullptr, 0, L.g.nx);
     NS_LAUNCH_CHECK();
     if (ctx->fuse_bn2) {
       if ((rc = allreduce(ctx, ctx->d_scal + 30, 2, ncclSum))) return rc;
@@ -856,6 +856,20 @@ static int phase_rhs(nsgpu_ctx* ctx) {   // ConstructRHS_V, FS.cpp:546
 #define CALL(RECT) k_rhs_build<RECT><<<grid, 128, 0, ctx->stream>>>(L.g, ctx->d_edges, sc, ctx->u, ctx->v, ctx->conv_u, ctx->conv_v, ctx->gpx, ctx->gpy, ctx->rhs_u, ctx->rhs_v)
   NS_DISPATCH_RECT(ctx->rect, CALL);
 #undef CALL
+  NS_LAUNCH_CHECK();
+  return 0;
+}
+
+// ConstructRHS_V on the columns [c0, c1) only (one rank, rectangle): nsgpu_step_host runs it chunk by chunk behind the uploads
+static int phase_rhs_cols(nsgpu_ctx* ctx, int c0, int c1) {
+  const Level& L = ctx->levels[0];
+  const StepConst sc{ctx->dt, ctx->re};
+  const int gx = ((L.g.ny + RHS_UJ - 1) / RHS_UJ + RHS_WARPS - 1) / RHS_WARPS;
+  const int chunks = std::max(1, std::min(L.g.nx / 8, (148 * 10 + gx - 1) / gx));
+  const int ri = (L.g.nx + chunks - 1) / chunks;
+  const dim3 grid(gx, (c1 - c0 + ri - 1) / ri);
+  k_rhs_march<<<grid, RHS_THREADS, 0, ctx->stream>>>(L.g, ctx->d_edges, sc, ctx->u, ctx->v, ctx->conv_u, ctx->conv_v, ctx->gpx, ctx->gpy,
+                                                     ctx->rhs_u, ctx->rhs_v, ri, ctx->red, nullptr, c0, c1);
   NS_LAUNCH_CHECK();
   return 0;
 }
