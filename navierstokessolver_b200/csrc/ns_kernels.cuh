@@ -427,7 +427,7 @@ k_sub_mean(LevelGeom g, double* __restrict__ b, const double* __restrict__ sum, 
   const int j = blockIdx.x * blockDim.x + threadIdx.x;
   if (j >= g.ny) return;
   const double m = *sum * inv_n;
-  if (RECT) {   // four columns in flight per thread: one load per iteration leaves the pass latency-bound (3.7 TB/s)
+  if constexpr (RECT) {   // four columns in flight per thread: one load per iteration leaves the pass latency-bound (3.7 TB/s)
     const int i_lo = chunk_lo(g.nx), i_hi = chunk_hi(g.nx);
     const size_t ld = g.ld;
     double* p = b + cidx(g, i_lo, j);
@@ -437,10 +437,10 @@ k_sub_mean(LevelGeom g, double* __restrict__ b, const double* __restrict__ sum, 
       p[0] = a0 - m; p[ld] = a1 - m; p[2 * ld] = a2 - m; p[3 * ld] = a3 - m;
     }
     for (; i < i_hi; i++, p += ld) p[0] -= m;
-    return;
+  } else {
+    for (int i = chunk_lo(g.nx), i_hi = chunk_hi(g.nx); i < i_hi; i++)
+      if (cell_flags<RECT>(g, i, j) != F_OUTSIDE) b[cidx(g, i, j)] -= m;
   }
-  for (int i = chunk_lo(g.nx), i_hi = chunk_hi(g.nx); i < i_hi; i++)
-    if (cell_flags<RECT>(g, i, j) != F_OUTSIDE) b[cidx(g, i, j)] -= m;
 }
 
 // out[0..3] = max(-u), max(u), max(-v), max(v)

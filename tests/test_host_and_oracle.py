@@ -189,6 +189,36 @@ def test_zero_lid_oracle_stays_at_rest(workdir):
     assert not r.step(3).any() and not r.get(PHI).any()
 
 
+@needs_ref
+@pytest.mark.parametrize("grid,sim", [("cavity_32.grid", "cavity_re100.sim"), ("step.grid", "step.sim")])
+def test_oracle_linear_solves_against_sparse_direct(grid, sim, workdir):
+    """The arithmetic of the three KSPSolve calls lives in PETSc, which is not here; the stand-in's Krylov solvers are pinned against an
+    independent sparse direct solver (scipy / SuperLU) on the reference's own assembled matrices: LHS_V x = RHS_u, RHS_v directly, and
+    the singular LHS_phi system as the bordered system its null-space-projected iteration converges to (walls: c = 0 to rounding)."""
+    import scipy.sparse as sp
+    import scipy.sparse.linalg as spl
+    r = refapi.RefSolver(f"{CASES}/{grid}", f"{CASES}/{sim}")
+    r.set_rtol(1e-13)
+    r.step(2)                                  # a developed state, not the flow at rest
+    AV, AP, n = r.csr(0).tocsc(), r.csr(1).tocsr(), r.n
+    r.construct_rhs_v()
+    bu, bv = r.get(RHS_U), r.get(RHS_V)
+    r.solve_velocity()
+    lu = spl.splu(AV)
+    assert _rel(r.get(USTAR), lu.solve(bu)) <= 1e-10
+    assert _rel(r.get(VSTAR), lu.solve(bv)) <= 1e-10
+    r.construct_rhs_phi(); r.nullspace_remove()
+    b = r.get(RHS_PHI)
+    r.solve_phi()
+    w = _ilu0_times_ones(AP)
+    K = sp.bmat([[AP, w[:, None]], [np.ones((1, n)), None]]).tocsc()
+    sol = spl.spsolve(K, np.concatenate([b, [0.0]]))
+    assert _rel(r.get(PHI), sol[:n]) <= 1e-8
+    if grid.startswith("cavity"):              # consistent system: the ILU term vanishes and A phi = b holds
+        assert abs(sol[n]) * np.linalg.norm(w) <= 1e-8 * np.linalg.norm(b)
+        assert np.linalg.norm(b - AP @ r.get(PHI)) <= 1e-9 * np.linalg.norm(b)
+
+
 # ---------------------------------------------------------------------------------------------- outflow (bcType 4) domains
 def _ilu0_times_ones(A):
     """w = L (U 1) of the ILU(0) factors of a CSR matrix in natural ordering (plain Python: the domains here have ~3000 cells)."""
