@@ -3,8 +3,15 @@
  * CSR storage, ILU(0), left-preconditioned restarted GMRES and BiCGStab(l) with the
  * stopping rule PETSc uses by default (preconditioned residual norm relative to the
  * preconditioned right-hand side).  Shared by the PETSc stand-in
- * (petsc_shim/shim.cpp, which the unmodified reference sources link against) and by the
- * CPU restatement (ns_port.cpp).
+ * (petsc_shim/shim.cpp, which the unmodified reference sources link against).
+ *
+ * Pinning: the reference ships no tests, golden vectors or sample inputs, so parity is UNPINNED BY THE REFERENCE'S OWN TESTS.
+ * What pins this oracle instead: everything outside the three KSPSolve calls is the reference's own code, compiled here from
+ * /root/reference/SRC; the three solves are defined mathematically (LHS x = b; for the singular / inconsistent LHS_phi the
+ * bordered system A x + c ILU0(A) 1 = b, mean x = 0) and this file's solvers are checked against an independent sparse direct
+ * solver on the reference's assembled matrices (tests/test_host_and_oracle.py::test_oracle_linear_solves_against_sparse_direct,
+ * ::test_outflow_fixed_point_of_the_reference_solve).  Real PETSc is not installed here; its ILU(0) in natural ordering is the
+ * same unique factorisation, its Krylov paths differ from these only within the tolerance.
  */
 #ifndef NSORACLE_KRYLOV_H
 #define NSORACLE_KRYLOV_H
