@@ -28,6 +28,25 @@ import time
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
+# The JSON line is the only thing this program writes to its stdout: file descriptor 1 is pointed at stderr for everything else
+# (NCCL prints its version banner on stdout when NCCL_DEBUG is set), the line itself goes to a duplicate of the original stdout.
+_JSON_OUT = None
+
+
+def _isolate_stdout():
+    global _JSON_OUT
+    if _JSON_OUT is None:
+        sys.stdout.flush()
+        _JSON_OUT = os.fdopen(os.dup(1), "w")
+        os.dup2(2, 1)
+
+
+def emit(line):
+    out = _JSON_OUT if _JSON_OUT is not None else sys.stdout
+    out.write(json.dumps(line) + "\n")
+    out.flush()
+
+
 METRIC = "timestep_gcell_updates_per_s"
 UNIT = "Gcell-updates/s"
 SWEEP_BYTES_PER_UPDATE = 24.0     # read phi, read b, write phi
@@ -99,7 +118,7 @@ def reference_arm(args, rank):
                              "sample": "%d steps of cavity %dx%d after %d warm-up steps; the reference is strictly serial (PETSC_COMM_SELF)" % (args.steps, n, n, args.warmup)},
             "phase_seconds": dict(zip(["rhs", "helmholtz", "div", "poisson", "correct"], [float(x) for x in ph])),
             "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 def cpu_baseline_sample(n=512, steps=2):
@@ -245,7 +264,7 @@ def ours(args, rank, world, local_rank):
                 "status": int(info.status)}
         if cpu:
             line["cpu_baseline"] = cpu
-        print(json.dumps(line), flush=True)
+        emit(line)
     s.close()
     if world > 1:
         dist.destroy_process_group()
@@ -268,6 +287,7 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--e2e-arrays", type=int, default=5, choices=[5, 7])
     args = ap.parse_args()
+    _isolate_stdout()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
