@@ -134,3 +134,22 @@ def test_reference_arm_of_bench_runs_on_cpu(tmp_path):
     assert line["impl"] == "reference" and line["unit"] == "Gcell-updates/s" and line["value"] > 0
     assert line["cpu_baseline"]["kind"] == "reference" and line["cpu_baseline"]["cores"] == 1
     assert line["e2e"]["h2d_bytes_per_step"] == 0
+
+
+def test_outflow_ilu_image_is_sliced_per_slab():
+    """Several ranks on an outflow domain: every rank factors the GLOBAL ILU(0) of LHS_phi on the host (it is a sequential recurrence
+    over all ids) and keeps the slab of w = L U 1 that belongs to its id range -- the slabs of 2 and 4 ranks tile the one-rank w."""
+    import refapi
+    nx, ny = 96, 24
+    hx, hy = np.full(nx, 3.0 / nx), np.linspace(0.8, 1.2, ny) / ny
+    args = (hx, hy, [-1, 0, 1, 0], [0, 1, 0, -1], [0, 2, 4, 2], [1.0, 0.0, 0.0, 0.0], 0.01, 100.0)
+    whole, ww = refapi.Emul(*args).phi_ilu_w()
+    assert ww > 0 and np.isfinite(whole).all()
+    for world in (2, 4):
+        parts = []
+        for rank in range(world):
+            em = refapi.Emul(*args, rank=rank, world=world)
+            w, ww_r = em.phi_ilu_w()
+            assert w.size == nx * ny // world and ww_r == ww
+            parts.append(w)
+        assert np.array_equal(np.concatenate(parts), whole)
