@@ -103,6 +103,63 @@ def test_grid_parser_accepts_and_rejects_like_the_reference(name, workdir):
         assert g.N == L.nsref_n(h) and g.nx == L.nsref_nx(h)
 
 
+_BC = "BC {\n2 0\n2 1\n2 0\n2 0\n}\n"
+BAD_SIMS = {
+    "missing_file": None,
+    "unknown_keyword": _BC + "dt 0.01\nfinal_time 1\nre 100\nviscosity 3\n",
+    "bc_too_few": "BC {\n2 0\n2 1\n2 0\n}\ndt 0.01\nfinal_time 1\nre 100\n",
+    "bc_too_many": "BC {\n2 0\n2 1\n2 0\n2 0\n2 0\n}\ndt 0.01\nfinal_time 1\nre 100\n",
+    "bc_no_brace": "BC\n2 0\n2 1\n2 0\n2 0\n}\ndt 0.01\nfinal_time 1\nre 100\n",
+    "dt_negative": _BC + "dt -0.01\nfinal_time 1\nre 100\nsaveIter 50\n",
+    "dt_beyond_final_time": _BC + "dt 2\nfinal_time 1\nre 100\nsaveIter 50\n",
+    "re_zero": _BC + "dt 0.01\nfinal_time 1\nre 0\nsaveIter 50\n",
+    "save_iter_zero": _BC + "dt 0.01\nfinal_time 1\nre 100\nsaveIter 0\n",
+    "number_at_end_of_file": _BC + "dt 0.01\nfinal_time 1\nre 100",
+    "not_a_number": _BC + "dt abc\nfinal_time 1\nre 100\n",
+}
+
+
+@needs_ref
+@pytest.mark.parametrize("name", sorted(BAD_SIMS))
+def test_simulation_file_is_rejected_like_the_reference(name, workdir, tmp_path):
+    """The simulation-file parser and the parameter checks (FS.cpp:16-32, 626-669) through the two command-line drivers: whatever the
+    reference refuses, bin/main refuses with the same words on stdout, before any GPU is touched (so this runs on the CPU box)."""
+    ref_exe, gpu_exe = os.path.join(ROOT, "oracle", "_ref", "main_ref"), os.path.join(ROOT, "bin", "main")
+    if not (os.path.exists(ref_exe) and os.path.exists(gpu_exe)):
+        pytest.skip("main_ref / bin/main not built")
+    sim = tmp_path / "case.sim"
+    if BAD_SIMS[name] is not None:
+        sim.write_text(BAD_SIMS[name])
+    outs = []
+    for exe, d in ((ref_exe, tmp_path / "ref"), (gpu_exe, tmp_path / "gpu")):
+        d.mkdir()
+        r = subprocess.run([exe, f"{CASES}/cavity_16.grid", str(sim)], cwd=d, capture_output=True, text=True, timeout=120)
+        assert r.returncode == 0                       # MAIN:21 returns 0 whatever happened
+        outs.append(r.stdout)
+    assert "Solver Setup Complete!" not in outs[0]     # the reference refuses it ...
+    assert outs[1] == outs[0]                          # ... and so does the drop-in, verbatim
+
+
+@needs_ref
+@pytest.mark.parametrize("name", sorted(BAD_GRIDS))
+def test_bad_grid_file_same_stdout_as_the_reference(name, workdir, tmp_path):
+    """Grid files the reference refuses (or accepts with a count of its own): both command-line drivers print the same text."""
+    ref_exe, gpu_exe = os.path.join(ROOT, "oracle", "_ref", "main_ref"), os.path.join(ROOT, "bin", "main")
+    if not (os.path.exists(ref_exe) and os.path.exists(gpu_exe)):
+        pytest.skip("main_ref / bin/main not built")
+    g = tmp_path / "g.grid"
+    g.write_text(BAD_GRIDS[name])
+    outs = []
+    for exe, d in ((ref_exe, tmp_path / "ref"), (gpu_exe, tmp_path / "gpu")):
+        d.mkdir()
+        r = subprocess.run([exe, str(g), f"{CASES}/cavity_re100.sim"], cwd=d, capture_output=True, text=True, timeout=120)
+        assert r.returncode == 0
+        outs.append(r.stdout)
+    if "Solver Setup Complete!" in outs[0]:
+        pytest.skip("the reference accepts this grid: the GPU path would start (covered by the -m gpu tests)")
+    assert outs[1] == outs[0]
+
+
 def test_minmode_matches():
     import navierstokessolver_b200 as ns
     rng = np.random.default_rng(0)
