@@ -54,13 +54,14 @@ def test_product_never_touches_the_oracle():
 
 
 # ---------------------------------------------------------------------------------------------- host Grid / parsers
-@needs_ref
-@pytest.mark.parametrize("grid", GRIDS + ["cavity_128.grid"])
-def test_host_grid_equals_reference_grid(grid, workdir):
+def _compare_host_grid_with_reference(path):
+    """Host Grid against the reference's Grid on one file; returns False when both refuse it, asserts on any difference."""
     import navierstokessolver_b200 as ns
     L = refapi.ref_lib()
-    h = L.nsref_grid_create(f"{CASES}/{grid}".encode(), 1)
-    assert L.nsref_grid_setup(h)
+    h = L.nsref_grid_create(str(path).encode(), 1)
+    if not L.nsref_grid_setup(h):
+        assert not ns.HostGrid(str(path)).setup
+        return False
     ref_centres = open("CellCenters.csv").read()
     nx, ny, ne = L.nsref_nx(h), L.nsref_ny(h), L.nsref_n_edges(h)
     hx, hy = np.empty(nx), np.empty(ny)
@@ -70,13 +71,65 @@ def test_host_grid_equals_reference_grid(grid, workdir):
     enx, eny, et = (np.empty(ne, dtype=np.int32) for _ in range(3))
     ei, loc = np.empty(ne), np.empty(3 * ne)
     L.nsref_edges(h, enx.ctypes.data_as(ip), eny.ctypes.data_as(ip), et.ctypes.data_as(ip), ei.ctypes.data_as(dp), loc.ctypes.data_as(dp))
-    g = ns.HostGrid(f"{CASES}/{grid}")
+    g = ns.HostGrid(str(path))
     assert g.setup and (g.N, g.nx, g.ny) == (L.nsref_n(h), nx, ny)
     assert np.array_equal(g.hx, hx) and np.array_equal(g.hy, hy)          # bit-identical widths
     assert np.array_equal(g.cell_id, ids) and np.array_equal(g.cell_edges, tags)
     assert np.array_equal(g.edge_nx, enx) and np.array_equal(g.edge_ny, eny) and np.array_equal(g.edge_loc, loc)
     assert np.array_equal(g.edge_type, et) and np.array_equal(g.edge_info, ei)   # defaults -1 / 1.0 (Grid.h:25-26)
     assert open("CellCenters.csv").read() == ref_centres
+    return True
+
+
+@needs_ref
+@pytest.mark.parametrize("grid", GRIDS + ["cavity_128.grid", "channel_south.grid"])
+def test_host_grid_equals_reference_grid(grid, workdir):
+    assert _compare_host_grid_with_reference(f"{CASES}/{grid}")
+
+
+def _random_grid_file(rng):
+    """A rectilinear polygon (rectangle, or a rectangle with one corner cut out: L shapes in the four orientations), clockwise, with
+    1-3 segments per direction whose ends fall on the polygon's corners; uniform, geometric and derived-count segments (G.cpp:83-98)."""
+    def cuts(n):
+        x = np.concatenate([[0.0], np.cumsum(rng.uniform(0.5, 2.0, n))])
+        return [float(round(v, 3)) for v in x]
+    xs, ys = cuts(int(rng.integers(1, 4))), cuts(int(rng.integers(1, 4)))
+    X0, X1, Y0, Y1 = xs[0], xs[-1], ys[0], ys[-1]
+    corner = int(rng.integers(0, 5)) if len(xs) > 2 or len(ys) > 2 else 0
+    if corner and len(xs) > 2 and len(ys) > 2:
+        xm, ym = xs[int(rng.integers(1, len(xs) - 1))], ys[int(rng.integers(1, len(ys) - 1))]
+        verts = {1: [(xm, Y0), (xm, ym), (X0, ym), (X0, Y1), (X1, Y1), (X1, Y0)],      # lower-left corner removed
+                 2: [(X0, Y0), (X0, ym), (xm, ym), (xm, Y1), (X1, Y1), (X1, Y0)],      # upper-left
+                 3: [(X0, Y0), (X0, Y1), (xm, Y1), (xm, ym), (X1, ym), (X1, Y0)],      # upper-right
+                 4: [(X0, Y0), (X0, Y1), (X1, Y1), (X1, ym), (xm, ym), (xm, Y0)]}[corner]   # lower-right
+    else:
+        verts = [(X0, Y0), (X0, Y1), (X1, Y1), (X1, Y0)]
+
+    def segments(c):
+        lines = []
+        for k in range(len(c) - 1):
+            kind = int(rng.integers(0, 3))
+            if kind == 0 or (kind == 2 and k == 0):
+                lines.append("%g %g %d -1" % (c[k], c[k + 1], int(rng.integers(2, 9))))            # uniform
+            elif kind == 1:
+                lines.append("%g %g %d %.3f" % (c[k], c[k + 1], int(rng.integers(3, 9)), rng.uniform(0.8, 1.25)))   # geometric, given count
+            else:
+                lines.append("%g %g 0 %.3f" % (c[k], c[k + 1], rng.uniform(1.02, 1.2)))            # count derived from the previous spacing
+        return "\n".join(lines)
+    return ("Vertices {\n" + "\n".join("%g %g" % v for v in verts) + "\n}\nNx {\n" + segments(xs) + "\n}\nNy {\n" + segments(ys) + "\n}\n")
+
+
+@needs_ref
+def test_host_grid_equals_reference_grid_on_random_polygons(workdir):
+    """60 seeded random grid files (rectangles and L shapes, mixed segment kinds): the host Grid accepts exactly what the reference
+    accepts and then agrees with it bit for bit -- widths, compact ids, edge tags, edge list, CellCenters.csv."""
+    rng = np.random.default_rng(20240611)
+    accepted = 0
+    for k in range(60):
+        p = workdir / ("g%d.grid" % k)
+        p.write_text(_random_grid_file(rng))
+        accepted += bool(_compare_host_grid_with_reference(p))
+    assert accepted >= 30
 
 
 BAD_GRIDS = {
