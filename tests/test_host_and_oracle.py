@@ -231,7 +231,10 @@ def test_minmode_matches():
 def test_device_functions_match_reference_phases(grid, sim, workdir):
     """Tier A (1e-12): ns_cell.cuh compiled for the host vs the reference's ConstructRHS_V / ConstructRHS_phi /
     CorrectVelocities and the matrices ConstructLHS assembles."""
-    ref = refapi.RefSolver(f"{CASES}/{grid}", f"{CASES}/{sim}")
+    _check_phases_against_reference(refapi.RefSolver(f"{CASES}/{grid}", f"{CASES}/{sim}"))
+
+
+def _check_phases_against_reference(ref):
     em = refapi.Emul(dt=ref.dt, re=ref.re, **ref.desc_kwargs())
     rng = np.random.default_rng(5)
     for op in (0, 1):
@@ -259,6 +262,35 @@ def test_device_functions_match_reference_phases(grid, sim, workdir):
     em.correct()
     for k in (U, V, GRADPHI_X, GRADPHI_Y):
         assert _rel(em.get(k), ref.get(k)) <= 1e-12
+
+
+@needs_ref
+def test_device_functions_on_random_domains_and_boundary_conditions(workdir):
+    """Tier A on 30 seeded random cases: rectangles and L shapes with stretched segments, every edge an inlet (either sign) or a
+    wall (moving or not), on rectangles also one outflow edge on a random side -- rows of both operators, ConstructRHS_V,
+    ConstructRHS_phi + mean removal, CorrectVelocities of the host-compiled device functions against the reference's."""
+    rng = np.random.default_rng(77)
+    done = 0
+    for k in range(30):
+        g = workdir / ("r%d.grid" % k)
+        g.write_text(_random_grid_file(rng))
+        L = refapi.ref_lib()
+        h = L.nsref_grid_create(str(g).encode(), 1)
+        assert L.nsref_grid_setup(h)
+        ne, nx, ny = L.nsref_n_edges(h), L.nsref_nx(h), L.nsref_ny(h)
+        bc = []
+        for e in range(ne):
+            if rng.integers(0, 2):
+                bc.append("0 %.3f" % rng.uniform(-1, 1))
+            else:
+                bc.append("2 %.3f" % (rng.uniform(-1, 1) if rng.integers(0, 2) else 0.0))
+        if ne == 4 and min(nx, ny) >= 3 and rng.integers(0, 2):     # the outflow ghost reaches two cells inward (FS.cpp:100)
+            bc[int(rng.integers(0, 4))] = "4 0"
+        sim = workdir / ("r%d.sim" % k)
+        sim.write_text("BC {\n" + "\n".join(bc) + "\n}\ndt %.4f\nfinal_time 1\nre %.1f\nsaveIter 50\n" % (rng.uniform(0.001, 0.02), rng.uniform(20, 500)))
+        _check_phases_against_reference(refapi.RefSolver(str(g), str(sim)))
+        done += 1
+    assert done == 30
 
 
 @needs_ref
