@@ -44,6 +44,10 @@ def main(out):
         f.write("Vertices {\n0 0\n0 3\n1 3\n1 0\n}\nNx {\n0 1 24 -1\n}\nNy {\n0 3 48 -1\n}\n")
     with open(os.path.join(out, "channel_north.sim"), "w") as f:
         f.write("BC {\n2 0\n4 0\n2 0\n0 1\n}\ndt 0.01\nfinal_time 0.2\nre 100\nsaveIter 1000000\n")
+    # wall-refined lid-driven cavity: geometric stretching towards all four walls (ratio 1.04, h_max / h_min = 3.4)
+    with open(os.path.join(out, "cavity_stretched_64.grid"), "w") as f:
+        f.write("Vertices {\n0 0\n0 1\n1 1\n1 0\n}\nNx {\n0 0.5 32 1.04\n0.5 1 32 0.9615384615\n}\nNy {\n0 0.5 32 1.04\n0.5 1 32 0.9615384615\n}\n")
+    cavity_sim(os.path.join(out, "cavity_stretched_64.sim"), 0.005, 100, 1.0, 1000000)
 
 if __name__ == "__main__":
     main(sys.argv[1] if len(sys.argv) > 1 else os.path.dirname(os.path.abspath(__file__)))

@@ -322,6 +322,31 @@ static inline bool plan_has_outflow(const HostPlan& P) {
   return false;
 }
 
+// When is LHS_phi x = b consistent?  Without an outflow edge the left null vector of LHS_phi is the cell volumes (hx_i hy_j times row c is
+// symmetric), and the reference removes the ARITHMETIC mean from b (MatNullSpaceRemove, FS.cpp:550).  On a uniform grid that is the
+// compatibility condition, on a stretched grid it is not: a wall-refined lid-driven cavity has |vol.b| / (|vol| |b|) ~ 1e-4, and the
+// reference's KSP converges to the same bordered system as on outflow domains, A x + c w = b with c = (vol, b) / (vol, w) known in closed
+// form.  So: outflow edge -> Krylov on the augmented operator; no outflow, stretched grid -> b - c w, then the ordinary multigrid;
+// no outflow, uniform grid -> c = 0, nothing to do.
+static inline bool plan_is_uniform(const HostPlan& P) {
+  const HostLevel& H = P.levels[0];
+  for (double h : H.hx) if (std::fabs(h - H.hx[0]) > 1e-13 * H.hx[0]) return false;
+  for (double h : H.hy) if (std::fabs(h - H.hy[0]) > 1e-13 * H.hy[0]) return false;
+  return true;
+}
+
+// (vol, w) over the global domain, w in global compact-id order
+static inline double volume_dot(const nsgpu_grid* G, const HostPlan& P, const std::vector<double>& w) {
+  const HostLevel& H = P.levels[0];
+  double s = 0.0;
+  for (int i = 0; i < H.gnx; i++)
+    for (int j = 0; j < H.ny; j++) {
+      const int64_t id = P.rect ? (int64_t)i * H.ny + j : (int64_t)G->cell_id[(size_t)i * H.ny + j];
+      if (id >= 0) s += H.hx[i] * H.hy[j] * w[(size_t)id];
+    }
+  return s;
+}
+
 static inline int phi_ilu0_image_of_ones(const nsgpu_grid* G, const HostPlan& P, std::vector<double>& w, std::string& err) {
   const HostLevel& H = P.levels[0];
   const int gnx = H.gnx, ny = H.ny;

@@ -28,9 +28,10 @@ struct Emul {
   std::vector<double> f[13];   // NSGPU_* ids 0..11, 12 = tmp
   std::string err;
   // outflow domains: w = ILU(0)(LHS_phi) * 1 in the padded layout, (w, w), sum of phi before the last mean removal
-  bool aug = false;
+  bool aug = false;       // outflow edge: Krylov on the augmented operator
+  bool aug_rhs = false;   // no outflow, stretched grid: b - c w with c = (vol, b) / (vol, w), then the ordinary multigrid
   std::vector<double> aug_w;
-  double aug_ww = 0.0, aug_shift = 0.0;
+  double aug_ww = 0.0, aug_shift = 0.0, aug_yw = 0.0;
 };
 
 void bind(ELevel& L, const HostPlan& P) {
@@ -290,7 +291,8 @@ void* emul_create_rank(const nsgpu_grid* G, double dt, double re, int nu_pre, in
     if (l > 0) { L.x.assign(L.A.stride, 0.0); L.xt.assign(L.A.stride, 0.0); L.b.assign(L.A.stride, 0.0); }
   }
   for (auto& v : E->f) v.assign(E->lv[0].A.stride, 0.0);
-  if (plan_has_outflow(E->plan)) {
+  const bool outflow = plan_has_outflow(E->plan);
+  if (outflow || !plan_is_uniform(E->plan)) {
     std::vector<double> w;
     rc = phi_ilu0_image_of_ones(G, E->plan, w, E->err);
     if (rc) { if (errbuf && errlen > 0) { strncpy(errbuf, E->err.c_str(), errlen - 1); errbuf[errlen - 1] = 0; } delete E; return nullptr; }
@@ -302,7 +304,9 @@ void* emul_create_rank(const nsgpu_grid* G, double dt, double re, int nu_pre, in
         if (id >= 0) { const double wv = w[(size_t)(E->plan.id0 + id)]; E->aug_w[cidx(g, i, j)] = wv; }
       }
     for (double wv : w) E->aug_ww += wv * wv;
-    E->aug = true;
+    E->aug_yw = volume_dot(G, E->plan, w);
+    E->aug = outflow;
+    E->aug_rhs = !outflow;
   }
   return E;
 }
@@ -314,7 +318,7 @@ double emul_phi_ilu_w(void* h, double* out) {
   for (int i = 0; i < g.nx; i++)
     for (int j = 0; j < g.ny; j++) {
       const long id = E->plan.rect ? (long)i * g.ny + j : (long)E->plan.local_id[(size_t)i * g.ny + j];
-      if (id >= 0) out[id] = E->aug ? E->aug_w[cidx(g, i, j)] : 0.0;
+      if (id >= 0) out[id] = (E->aug || E->aug_rhs) ? E->aug_w[cidx(g, i, j)] : 0.0;
     }
   return E->aug_ww;
 }
@@ -365,8 +369,20 @@ void emul_apply(void* h, int op, const double* x, double* y) {
 int emul_solve(void* h, int which, double rtol, int max_cycles, double* rel) {
   Emul* E = (Emul*)h;
   if (which == 2) {
-    int n = E->aug ? solve_phi_aug(*E, E->f[NSGPU_PHI], E->f[NSGPU_RHS_PHI], rtol, max_cycles, rel)
-                   : solve_mg(*E, Coef{1, 0.0, -1.0}, E->f[NSGPU_PHI], E->f[NSGPU_RHS_PHI], rtol, max_cycles, rel);
+    int n;
+    if (E->aug) n = solve_phi_aug(*E, E->f[NSGPU_PHI], E->f[NSGPU_RHS_PHI], rtol, max_cycles, rel);
+    else if (E->aug_rhs) {   // mirrors phase_phi (csrc/ns_solver.inl): one volume-weighted sum, one axpy, then the multigrid iteration
+      const LevelGeom& g = E->lv[0].g;
+      const std::vector<double>& b = E->f[NSGPU_RHS_PHI];
+      double yb = 0.0;
+      for (int i = 0; i < g.nx; i++)
+        for (int j = 0; j < g.ny; j++)
+          if (flags_any(*E, g, i, j) != F_OUTSIDE) yb += g.hx[i + HX] * g.hy[j + PJ] * b[cidx(g, i, j)];
+      const double c = yb / E->aug_yw;
+      std::vector<double> b2(b);
+      for (size_t k = 0; k < b2.size(); k++) b2[k] -= c * E->aug_w[k];
+      n = solve_mg(*E, Coef{1, 0.0, -1.0}, E->f[NSGPU_PHI], b2, rtol, max_cycles, rel);
+    } else n = solve_mg(*E, Coef{1, 0.0, -1.0}, E->f[NSGPU_PHI], E->f[NSGPU_RHS_PHI], rtol, max_cycles, rel);
     phi_mean_zero(*E);
     return n;
   }

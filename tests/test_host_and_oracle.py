@@ -435,6 +435,40 @@ def test_outflow_whole_steps_emulation_vs_reference(case, workdir):
         assert np.allclose(me, mm, rtol=0, atol=1e-6 * np.abs(mm).max())
 
 
+@needs_ref
+def test_stretched_grid_phi_system_is_inconsistent_and_what_the_reference_returns(workdir):
+    """No outflow edge, but a stretched grid: the reference removes the ARITHMETIC mean from RHS_phi (MatNullSpaceRemove, FS.cpp:550)
+    while the left null vector of LHS_phi is the cell volumes, so LHS_phi x = b is inconsistent at the 1e-4 level on a wall-refined
+    cavity and the KSP returns the bordered solution A x + c w = b with c = (vol, b) / (vol, w) in closed form.  Pinned on the oracle;
+    the emulation of the GPU's loops (b - c w, then multigrid) then tracks the reference over whole steps."""
+    ref = refapi.RefSolver(f"{CASES}/cavity_stretched_64.grid", f"{CASES}/cavity_stretched_64.sim")
+    ref.set_rtol(1e-13)
+    ref.step(2)
+    ref.construct_rhs_v(); ref.solve_velocity(); ref.construct_rhs_phi(); ref.nullspace_remove()
+    b = ref.get(RHS_PHI)
+    ref.solve_phi()
+    phi, A = ref.get(PHI), ref.csr(1)
+    vol = np.outer(ref.hx, ref.hy).reshape(-1)
+    assert np.abs(A.T @ vol).max() <= 1e-12 * np.abs(A).max()                  # left null vector = volumes
+    assert abs(vol @ b) >= 1e-5 * np.linalg.norm(vol) * np.linalg.norm(b)      # b is not orthogonal to it ...
+    res = b - A @ phi
+    assert np.linalg.norm(res) >= 1e-5 * np.linalg.norm(b)                     # ... so the accepted phi does not solve A x = b
+    w = _ilu0_times_ones(A)
+    c = (vol @ b) / (vol @ w)
+    assert np.linalg.norm(res - c * w) <= 1e-7 * np.linalg.norm(res)           # its residual is c w
+    em = refapi.Emul(dt=ref.dt, re=ref.re, **ref.desc_kwargs())
+    w_host, _ = em.phi_ilu_w()
+    assert _rel(w_host, w) <= 1e-13
+    ref2 = refapi.RefSolver(f"{CASES}/cavity_stretched_64.grid", f"{CASES}/cavity_stretched_64.sim")
+    ref2.set_rtol(1e-12)
+    for s in range(4):
+        ref2.step(1)
+        me, worst, cyc = em.step(1, rtol=1e-10, max_cycles=80)
+        assert worst <= 1e-10, (s, worst, cyc)
+        for k in (U, V, PHI):
+            assert _rel(em.get(k), ref2.get(k)) <= 2e-8, (s, k)
+
+
 def test_golden_fixture_matches_oracle_or_emulation(workdir):
     """tests/golden/cavity32_re100_5steps.npz was written by tests/golden/make_golden.py from the oracle in exact mode."""
     z = np.load(os.path.join(ROOT, "tests", "golden", "cavity32_re100_5steps.npz"))
