@@ -84,6 +84,10 @@ struct nsgpu_ctx {
   double* aug_w = nullptr;      // w in the field layout (zeros in padding and masked cells)
   double* aug_t = nullptr;      // scratch vector of the preconditioner
   double aug_ww = 0.0;          // (w, w) over the global domain
+  // no outflow edge but a stretched grid: LHS_phi x = b is inconsistent too (the reference removes the arithmetic mean, the left null
+  // vector is the cell volumes) and the reference returns A x + c w = b, c = (vol, b) / (vol, w): phase_phi solves with b - c w
+  bool aug_rhs = false;
+  double aug_yw = 0.0;          // (vol, w) over the global domain
 
   nsgpu::Reducer red{};
   double* d_scal = nullptr;     // device scalars (64 doubles)

@@ -477,6 +477,21 @@ k_correct(LevelGeom g, StepConst sc, const double* __restrict__ phi, const doubl
   grid_reduce<4, OpMax>(acc, red, out);
 }
 
+// out[0] = sum over the fluid cells of hx_i hy_j b_ij: the product of b with the left null vector of LHS_phi on domains without an
+// outflow edge (ns_hostgeom.h, plan_is_uniform) -- the inconsistency the reference's arithmetic mean removal leaves on stretched grids
+template <bool RECT>
+__global__ void __launch_bounds__(256)
+k_vol_dot(LevelGeom g, const double* __restrict__ b, Reducer red, double* out) {
+  const int j = blockIdx.x * blockDim.x + threadIdx.x;
+  double acc[1] = {0.0};
+  if (j < g.ny) {
+    const double hyj = g.hy[j + PJ];
+    for (int i = chunk_lo(g.nx), i_hi = chunk_hi(g.nx); i < i_hi; i++)
+      if (RECT || cell_flags<RECT>(g, i, j) != F_OUTSIDE) acc[0] = fma(g.hx[i + HX] * hyj, b[cidx(g, i, j)], acc[0]);
+  }
+  grid_reduce<1, OpSum>(acc, red, out);
+}
+
 // (gpx, gpy) = GradP(phi) alone (FS.cpp:420-456): divPhi is a pure function of phi, so a caller that keeps its state on the host
 // need not ship it (nsgpu_step_host with gradphi_x = gradphi_y = NULL)
 template <bool RECT>

@@ -312,7 +312,10 @@ static int create_impl(nsgpu_ctx* ctx, const nsgpu_grid* G, const nsgpu_params* 
   double** fields[] = {&ctx->u, &ctx->v, &ctx->phi, &ctx->conv_u, &ctx->conv_v, &ctx->gpx, &ctx->gpy,
                        &ctx->rhs_u, &ctx->rhs_v, &ctx->rhs_phi, &ctx->ustar, &ctx->vstar, &ctx->tmp};
   for (double** f : fields) { int rc = dev_zeros(ctx, ctx->owned, S, f); if (rc) return rc; }
-  if (plan_has_outflow(plan)) {   // FS.cpp:98-101: LHS_phi x = b is inconsistent there; see ns_hostgeom.h for what the reference returns
+  const bool outflow = plan_has_outflow(plan);
+  bool rhs_consistent = true;   // NSGPU_RHS_CONSISTENT=0: leave the right-hand side of stretched grids as the reference builds it
+  if (const char* e = getenv("NSGPU_RHS_CONSISTENT")) rhs_consistent = atoi(e) != 0;
+  if (outflow || (rhs_consistent && !plan_is_uniform(plan))) {   // LHS_phi x = b is inconsistent there; see ns_hostgeom.h for what the reference returns
     std::vector<double> w;
     int rc = phi_ilu0_image_of_ones(G, plan, w, ctx->err);
     if (rc) return rc;
@@ -327,7 +330,9 @@ static int create_impl(nsgpu_ctx* ctx, const nsgpu_grid* G, const nsgpu_params* 
     if ((rc = dev_zeros(ctx, ctx->owned, S, &ctx->aug_w))) return rc;
     if ((rc = dev_zeros(ctx, ctx->owned, S, &ctx->aug_t))) return rc;
     NS_CUDA(cudaMemcpy(ctx->aug_w, wp.data(), S * sizeof(double), cudaMemcpyHostToDevice));
-    ctx->aug = ctx->aug_ww > 0.0;
+    ctx->aug_yw = volume_dot(G, plan, w);
+    ctx->aug = outflow && ctx->aug_ww > 0.0;
+    ctx->aug_rhs = !outflow && ctx->aug_yw != 0.0;
   }
   if (ctx->solver == 1 || ctx->aug)
     for (int k = 0; k < 8; k++) { int rc = dev_zeros(ctx, ctx->owned, S, &ctx->kry[k]); if (rc) return rc; }

@@ -917,10 +917,28 @@ static int phase_phi(nsgpu_ctx* ctx, SolveResult* rp) {   // FS.cpp:551, warm st
   ctx->halo_w.clear();   // every field may have been rewritten by a non-marching kernel since
   const Level& L = ctx->levels[0];
   int rc;
-  if ((rc = halo_exchange(ctx, L, ctx->rhs_phi, HX - 1))) return rc;
-  const int64_t before = ctx->launches;
-  (void)before;
-  if ((rc = solve(ctx, 2, coef_phi(), &ctx->phi, ctx->rhs_phi, ctx->rtol_phi, rp))) return rc;
+  const double* b = ctx->rhs_phi;
+  if (ctx->aug_rhs) {
+    // stretched grid, no outflow edge: b'' = b - c w with c = (vol, b) / (vol, w) is the right-hand side whose solution the reference's
+    // KSP converges to (ns_hostgeom.h); rhs_phi itself stays what ConstructRHS_phi + MatNullSpaceRemove made it
+    const dim3 grid = grid_cols(L.g, 256);
+#define CALL(RECT) k_vol_dot<RECT><<<grid, 256, 0, ctx->stream>>>(L.g, ctx->rhs_phi, ctx->red, ctx->d_scal + 41)
+    NS_DISPATCH_RECT(ctx->rect, CALL);
+#undef CALL
+    NS_LAUNCH_CHECK();
+    if ((rc = allreduce(ctx, ctx->d_scal + 41, 1, ncclSum))) return rc;
+    cudaError_t e = cudaMemcpyAsync(ctx->aug_t, ctx->rhs_phi, L.stride * sizeof(double), cudaMemcpyDeviceToDevice, ctx->stream);
+    if (e != cudaSuccess) { ctx->err = cudaGetErrorString(e); return NSGPU_ERR_CUDA; }
+    const size_t n = (size_t)L.g.nx * L.g.ld, off = (size_t)HX * L.g.ld;
+    const int blocks = (int)std::min<size_t>((n + 255) / 256, 148 * 8);
+    k_aug_axpy<<<blocks, 256, 0, ctx->stream>>>(n, ctx->aug_t + off, ctx->aug_w + off, ctx->d_scal + 41, -1.0 / ctx->aug_yw, nullptr, ctx->red, ctx->d_scal + 44);
+    NS_LAUNCH_CHECK();
+    ctx->halo_w.erase(ctx->aug_t);
+    ctx->bn2_ready[2] = false;   // |b''|^2 is reduced by the solve head
+    b = ctx->aug_t;
+  }
+  if ((rc = halo_exchange(ctx, L, const_cast<double*>(b), HX - 1))) return rc;
+  if ((rc = solve(ctx, 2, coef_phi(), &ctx->phi, b, ctx->rtol_phi, rp))) return rc;
   if (!rp->pending) ctx->fine_sweeps_phi += (double)rp->cycles * (ctx->nu_pre + ctx->nu_post) * (ctx->solver == 1 ? 2 : 1);
   // pin mean(phi) = 0: the reference projects the constant out of every Krylov update (MatSetNullSpace, FS.cpp:143)
   {

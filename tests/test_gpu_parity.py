@@ -395,3 +395,21 @@ def test_two_gpus_equal_one_gpu(workdir):
     out = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr", "127.0.0.1",
                           "--master-port", "29533", f"{refapi.ROOT}/tools/mgpu_check.py", "256", "128", "4"], capture_output=True, text=True, timeout=600)
     assert out.returncode == 0, out.stdout[-2000:] + out.stderr[-2000:]
+
+
+@pytest.mark.xfail(strict=False, reason="written after the round's GPU minutes were spent: the branch (k_vol_dot + one axpy in phase_phi) is "
+                   "verified on the host emulation (tests/test_host_and_oracle.py::test_stretched_grid_phi_system_...) but this test has "
+                   "not run on a B200 yet -- XPASS is the expected outcome; kept last in the file")
+def test_whole_steps_stretched_cavity(workdir):
+    """Wall-refined lid-driven cavity (geometric stretching, h_max / h_min = 3.4): LHS_phi x = b is inconsistent at 2.4e-4 there and
+    the reference returns A x + c w = b with c = (vol, b) / (vol, w); the GPU solves with b - c w.  Tier B tolerance."""
+    ref = refapi.RefSolver(f"{CASES}/cavity_stretched_64.grid", f"{CASES}/cavity_stretched_64.sim")
+    ref.set_rtol(1e-12)
+    gpu = _gpu(ref, rtol_u=1e-10, rtol_phi=1e-10)
+    for s in range(4):
+        mm = ref.step(1)
+        info = gpu.step(1)
+        assert info.status == 0, (s, info.status, info.res_phi, info.it_phi)
+        for k in (U, V, PHI):
+            assert _rel(gpu.get(k), ref.get(k)) <= 2e-8, (s, k, _rel(gpu.get(k), ref.get(k)))
+        assert np.allclose([info.umin, info.umax, info.vmin, info.vmax], mm, rtol=0, atol=1e-8)
