@@ -88,6 +88,7 @@ struct nsgpu_ctx {
   // vector is the cell volumes) and the reference returns A x + c w = b, c = (vol, b) / (vol, w): phase_phi solves with b - c w
   bool aug_rhs = false;
   double aug_yw = 0.0;          // (vol, w) over the global domain
+  bool krylov_phi = false;      // the phi solve runs BiCGStab: aug, or a grid that cannot be coarsened (one level: no multigrid to keep)
 
   nsgpu::Reducer red{};
   double* d_scal = nullptr;     // device scalars (64 doubles)

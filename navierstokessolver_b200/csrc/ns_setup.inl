@@ -331,10 +331,12 @@ static int create_impl(nsgpu_ctx* ctx, const nsgpu_grid* G, const nsgpu_params* 
     if ((rc = dev_zeros(ctx, ctx->owned, S, &ctx->aug_t))) return rc;
     NS_CUDA(cudaMemcpy(ctx->aug_w, wp.data(), S * sizeof(double), cudaMemcpyHostToDevice));
     ctx->aug_yw = volume_dot(G, plan, w);
-    ctx->aug = outflow && ctx->aug_ww > 0.0;
-    ctx->aug_rhs = !outflow && ctx->aug_yw != 0.0;
+    // a grid that cannot be coarsened at all has no multigrid to keep: Krylov on the augmented operator there as well
+    ctx->aug = (outflow || ctx->levels.size() == 1) && ctx->aug_ww > 0.0;
+    ctx->aug_rhs = !ctx->aug && ctx->aug_yw != 0.0;
   }
-  if (ctx->solver == 1 || ctx->aug)
+  ctx->krylov_phi = ctx->aug || ctx->levels.size() == 1;   // uniform and uncoarsenable: plain preconditioned BiCGStab on the consistent system
+  if (ctx->solver == 1 || ctx->krylov_phi)
     for (int k = 0; k < 8; k++) { int rc = dev_zeros(ctx, ctx->owned, S, &ctx->kry[k]); if (rc) return rc; }
   { const EdgeDev* p; int rc = dev_upload(ctx, ctx->owned, plan.edges, &p); if (rc) return rc; ctx->d_edges = const_cast<EdgeDev*>(p); }
   { int rc = dev_zeros(ctx, ctx->owned, (size_t)4 * RED_MAX_BLOCKS, &ctx->red.partials); if (rc) return rc; }

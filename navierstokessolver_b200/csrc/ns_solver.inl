@@ -809,14 +809,15 @@ static inline bool dev_solve_ok(const nsgpu_ctx* ctx, OpCoef c) {
 
 // slot: 0 = u, 1 = v, 2 = phi.  On the device-controlled path the result is pending until finish_results().
 static int solve(nsgpu_ctx* ctx, int slot, OpCoef c, double** x, const double* b, double rtol, SolveResult* out, double* x0 = nullptr) {
-  if (dev_solve_ok(ctx, c)) { out->pending = true; return solve_mg_dev(ctx, slot, c, x, &ctx->tmp, x0, b, rtol); }
+  const bool krylov = ctx->solver == 1 || (ctx->krylov_phi && c.op == 1);
+  if (!krylov && dev_solve_ok(ctx, c)) { out->pending = true; return solve_mg_dev(ctx, slot, c, x, &ctx->tmp, x0, b, rtol); }
   out->pending = false;
   ctx->bn2_ready[slot] = false;
   if (x0 && x0 != *x) {   // host-driven solvers iterate in place
     cudaError_t e = cudaMemcpyAsync(*x, x0, ctx->levels[0].stride * sizeof(double), cudaMemcpyDeviceToDevice, ctx->stream);
     if (e != cudaSuccess) { ctx->err = cudaGetErrorString(e); return NSGPU_ERR_CUDA; }
   }
-  if (ctx->solver == 1 || (ctx->aug && c.op == 1)) return solve_bicgstab(ctx, c, x, &ctx->tmp, b, rtol, out);
+  if (krylov) return solve_bicgstab(ctx, c, x, &ctx->tmp, b, rtol, out);
   return solve_mg(ctx, c, x, &ctx->tmp, b, rtol, out);
 }
 

@@ -29,6 +29,7 @@ struct Emul {
   std::string err;
   // outflow domains: w = ILU(0)(LHS_phi) * 1 in the padded layout, (w, w), sum of phi before the last mean removal
   bool aug = false;       // outflow edge: Krylov on the augmented operator
+  bool krylov_phi = false;   // phi solve by BiCGStab (aug, or a single-level grid)
   bool aug_rhs = false;   // no outflow, stretched grid: b - c w with c = (vol, b) / (vol, w), then the ordinary multigrid
   std::vector<double> aug_w;
   double aug_ww = 0.0, aug_shift = 0.0, aug_yw = 0.0;
@@ -152,16 +153,16 @@ void aug_apply(const Emul& E, const std::vector<double>& x, std::vector<double>&
   std::fill(y.begin(), y.end(), 0.0);
   for (int i = 0; i < g.nx; i++)
     for (int j = 0; j < g.ny; j++)
-      if (flags_any(E, g, i, j) != F_OUTSIDE) { const size_t id = cidx(g, i, j); y[id] = apply_any(E, g, c, i, j, x) + m * E.aug_w[id]; }
+      if (flags_any(E, g, i, j) != F_OUTSIDE) { const size_t id = cidx(g, i, j); y[id] = apply_any(E, g, c, i, j, x) + (E.aug ? m * E.aug_w[id] : 0.0); }
 }
 void aug_precond(Emul& E, const std::vector<double>& v, std::vector<double>& z) {
   const double n = (double)E.plan.n_cells_global;
-  double vw = 0; for (size_t k = 0; k < v.size(); k++) vw += v[k] * E.aug_w[k];
+  double vw = 0; if (E.aug) for (size_t k = 0; k < v.size(); k++) vw += v[k] * E.aug_w[k];
   std::vector<double> t(v);
   add_const(E, t, -fluid_sum(E, v) / n);
   std::fill(z.begin(), z.end(), 0.0);
   vcycle(E, 0, Coef{2, 0.0, -1.0}, z, E.f[12], t);
-  add_const(E, z, -fluid_sum(E, z) / n + vw / E.aug_ww);
+  add_const(E, z, -fluid_sum(E, z) / n + (E.aug ? vw / E.aug_ww : 0.0));
 }
 double dotv(const std::vector<double>& a, const std::vector<double>& b) { double s = 0; for (size_t k = 0; k < a.size(); k++) s += a[k] * b[k]; return s; }
 
@@ -305,9 +306,11 @@ void* emul_create_rank(const nsgpu_grid* G, double dt, double re, int nu_pre, in
       }
     for (double wv : w) E->aug_ww += wv * wv;
     E->aug_yw = volume_dot(G, E->plan, w);
-    E->aug = outflow;
-    E->aug_rhs = !outflow;
+    // a grid that cannot be coarsened at all has no multigrid to keep: Krylov on the augmented operator there as well
+    E->aug = outflow || E->lv.size() == 1;
+    E->aug_rhs = !E->aug;
   }
+  E->krylov_phi = E->aug || E->lv.size() == 1;   // uniform and uncoarsenable: plain preconditioned BiCGStab on the consistent system
   return E;
 }
 void emul_destroy(void* h) { delete (Emul*)h; }
@@ -370,7 +373,7 @@ int emul_solve(void* h, int which, double rtol, int max_cycles, double* rel) {
   Emul* E = (Emul*)h;
   if (which == 2) {
     int n;
-    if (E->aug) n = solve_phi_aug(*E, E->f[NSGPU_PHI], E->f[NSGPU_RHS_PHI], rtol, max_cycles, rel);
+    if (E->krylov_phi) n = solve_phi_aug(*E, E->f[NSGPU_PHI], E->f[NSGPU_RHS_PHI], rtol, max_cycles, rel);
     else if (E->aug_rhs) {   // mirrors phase_phi (csrc/ns_solver.inl): one volume-weighted sum, one axpy, then the multigrid iteration
       const LevelGeom& g = E->lv[0].g;
       const std::vector<double>& b = E->f[NSGPU_RHS_PHI];

@@ -270,27 +270,9 @@ def test_device_functions_on_random_domains_and_boundary_conditions(workdir):
     wall (moving or not), on rectangles also one outflow edge on a random side -- rows of both operators, ConstructRHS_V,
     ConstructRHS_phi + mean removal, CorrectVelocities of the host-compiled device functions against the reference's."""
     rng = np.random.default_rng(77)
-    done = 0
     for k in range(30):
-        g = workdir / ("r%d.grid" % k)
-        g.write_text(_random_grid_file(rng))
-        L = refapi.ref_lib()
-        h = L.nsref_grid_create(str(g).encode(), 1)
-        assert L.nsref_grid_setup(h)
-        ne, nx, ny = L.nsref_n_edges(h), L.nsref_nx(h), L.nsref_ny(h)
-        bc = []
-        for e in range(ne):
-            if rng.integers(0, 2):
-                bc.append("0 %.3f" % rng.uniform(-1, 1))
-            else:
-                bc.append("2 %.3f" % (rng.uniform(-1, 1) if rng.integers(0, 2) else 0.0))
-        if ne == 4 and min(nx, ny) >= 3 and rng.integers(0, 2):     # the outflow ghost reaches two cells inward (FS.cpp:100)
-            bc[int(rng.integers(0, 4))] = "4 0"
-        sim = workdir / ("r%d.sim" % k)
-        sim.write_text("BC {\n" + "\n".join(bc) + "\n}\ndt %.4f\nfinal_time 1\nre %.1f\nsaveIter 50\n" % (rng.uniform(0.001, 0.02), rng.uniform(20, 500)))
-        _check_phases_against_reference(refapi.RefSolver(str(g), str(sim)))
-        done += 1
-    assert done == 30
+        g, sim = _random_case(rng, workdir, k)
+        _check_phases_against_reference(refapi.RefSolver(g, sim))
 
 
 @needs_ref
@@ -467,6 +449,70 @@ def test_stretched_grid_phi_system_is_inconsistent_and_what_the_reference_return
         assert worst <= 1e-10, (s, worst, cyc)
         for k in (U, V, PHI):
             assert _rel(em.get(k), ref2.get(k)) <= 2e-8, (s, k)
+
+
+def _random_case(rng, workdir, k):
+    """One random grid file plus a random simulation file: every edge an inlet (either sign) or a wall (moving or not), on rectangles
+    with at least 3 cells across also one outflow edge on a random side (its ghost reaches two cells inward, FS.cpp:100)."""
+    g = workdir / ("r%d.grid" % k)
+    g.write_text(_random_grid_file(rng))
+    L = refapi.ref_lib()
+    h = L.nsref_grid_create(str(g).encode(), 1)
+    assert L.nsref_grid_setup(h)
+    ne, nx, ny = L.nsref_n_edges(h), L.nsref_nx(h), L.nsref_ny(h)
+    bc = []
+    for e in range(ne):
+        if rng.integers(0, 2):
+            bc.append("0 %.3f" % rng.uniform(-1, 1))
+        else:
+            bc.append("2 %.3f" % (rng.uniform(-1, 1) if rng.integers(0, 2) else 0.0))
+    if ne == 4 and min(nx, ny) >= 3 and rng.integers(0, 2):
+        bc[int(rng.integers(0, 4))] = "4 0"
+    sim = workdir / ("r%d.sim" % k)
+    sim.write_text("BC {\n" + "\n".join(bc) + "\n}\ndt %.4f\nfinal_time 1\nre %.1f\nsaveIter 50\n" % (rng.uniform(0.001, 0.02), rng.uniform(20, 500)))
+    return str(g), str(sim)
+
+
+@needs_ref
+def test_whole_steps_on_random_domains_emulation_vs_reference(workdir):
+    """The solver the GPU runs (host emulation of the same loops), whole time steps on 24 seeded random cases -- rectangles and L shapes,
+    stretched segments, grids that cannot be coarsened, inlets / walls / one outflow edge: every phi system is the bordered system the
+    reference's KSP converges to (multigrid on b - c w, or BiCGStab on the augmented operator), every solve converges and the fields
+    follow the reference.  Before the bordered formulation 21 of 30 such cases did not converge."""
+    rng = np.random.default_rng(123)
+    kinds = set()
+    for k in range(24):
+        g, sim = _random_case(rng, workdir, k)
+        ref = refapi.RefSolver(g, sim)
+        ref.set_rtol(1e-12)
+        em = refapi.Emul(dt=ref.dt, re=ref.re, **ref.desc_kwargs())
+        kinds.add((em.num_levels == 1, bool((ref.edge_type == 4).any()), em.rect))
+        for s in range(2):
+            ref.step(1)
+            me, worst, cyc = em.step(1, rtol=1e-10, max_cycles=200)
+            assert worst <= 1e-9, (k, s, worst, cyc)
+            vel = max(np.abs(ref.get(U)).max(), np.abs(ref.get(V)).max())      # one scale for both components: one of them can vanish
+            for q in (U, V):
+                assert np.abs(em.get(q) - ref.get(q)).max() <= 1e-6 * vel, (k, s, q)
+            assert _rel(em.get(PHI), ref.get(PHI)) <= 1e-6, (k, s)
+    assert len(kinds) >= 4          # single- and multi-level, with and without outflow, rectangles and L shapes all occurred
+
+
+@needs_ref
+def test_uncoarsenable_uniform_cavity_uses_the_krylov_fallback(workdir):
+    """33 x 33 cells: no level below the fine one, so the phi solve is BiCGStab preconditioned by the smoother instead of a multigrid
+    iteration that would need thousands of sweeps."""
+    (workdir / "c.grid").write_text("Vertices {\n0 0\n0 1\n1 1\n1 0\n}\nNx {\n0 1 33 -1\n}\nNy {\n0 1 33 -1\n}\n")
+    ref = refapi.RefSolver(str(workdir / "c.grid"), f"{CASES}/cavity_re100.sim")
+    ref.set_rtol(1e-12)
+    em = refapi.Emul(dt=ref.dt, re=ref.re, **ref.desc_kwargs())
+    assert em.num_levels == 1
+    for s in range(3):
+        ref.step(1)
+        me, worst, cyc = em.step(1, rtol=1e-10, max_cycles=200)
+        assert worst <= 1e-10 and cyc[2] <= 60, (s, worst, cyc)
+        for q in (U, V, PHI):
+            assert _rel(em.get(q), ref.get(q)) <= 2e-8, (s, q)
 
 
 def test_golden_fixture_matches_oracle_or_emulation(workdir):
