@@ -335,6 +335,16 @@ static inline bool plan_is_uniform(const HostPlan& P) {
   return true;
 }
 
+// max(h) / min(h), the larger of the two directions.  Point-smoothed multigrid with rediscretised coarse operators degrades quickly with it
+// (host emulation, wall-refined 64 x 64 cavity: 7 V(2,2) cycles at 1.8, 30 at 3.4, divergence at 6), BiCGStab preconditioned by the same
+// V-cycle does not (10 iterations at 3.4, 17 at 6, 37 at 19).
+static inline double plan_stretch(const HostPlan& P) {
+  const HostLevel& H = P.levels[0];
+  const auto mmx = std::minmax_element(H.hx.begin(), H.hx.end());
+  const auto mmy = std::minmax_element(H.hy.begin(), H.hy.end());
+  return std::max(*mmx.second / *mmx.first, *mmy.second / *mmy.first);
+}
+
 // (vol, w) over the global domain, w in global compact-id order
 static inline double volume_dot(const nsgpu_grid* G, const HostPlan& P, const std::vector<double>& w) {
   const HostLevel& H = P.levels[0];

@@ -313,9 +313,12 @@ static int create_impl(nsgpu_ctx* ctx, const nsgpu_grid* G, const nsgpu_params* 
                        &ctx->rhs_u, &ctx->rhs_v, &ctx->rhs_phi, &ctx->ustar, &ctx->vstar, &ctx->tmp};
   for (double** f : fields) { int rc = dev_zeros(ctx, ctx->owned, S, f); if (rc) return rc; }
   const bool outflow = plan_has_outflow(plan);
-  bool rhs_consistent = true;   // NSGPU_RHS_CONSISTENT=0: leave the right-hand side of stretched grids as the reference builds it
-  if (const char* e = getenv("NSGPU_RHS_CONSISTENT")) rhs_consistent = atoi(e) != 0;
-  if (outflow || (rhs_consistent && !plan_is_uniform(plan))) {   // LHS_phi x = b is inconsistent there; see ns_hostgeom.h for what the reference returns
+  // NSGPU_RHS_CONSISTENT: -1 treats a stretched grid like a uniform one (the pre-round-1 behaviour: the solve stagnates at the level of the
+  // inconsistency); 0 (default): stretched grids take the Krylov solve on the augmented operator; 1: mildly stretched grids (<= 2) keep the
+  // multigrid iteration, on b - c w; 2: every stretched grid does
+  int rhs_mode = 0;
+  if (const char* e = getenv("NSGPU_RHS_CONSISTENT")) rhs_mode = atoi(e);
+  if (outflow || (rhs_mode >= 0 && !plan_is_uniform(plan))) {   // LHS_phi x = b is inconsistent there; see ns_hostgeom.h for what the reference returns
     std::vector<double> w;
     int rc = phi_ilu0_image_of_ones(G, plan, w, ctx->err);
     if (rc) return rc;
@@ -331,9 +334,12 @@ static int create_impl(nsgpu_ctx* ctx, const nsgpu_grid* G, const nsgpu_params* 
     if ((rc = dev_zeros(ctx, ctx->owned, S, &ctx->aug_t))) return rc;
     NS_CUDA(cudaMemcpy(ctx->aug_w, wp.data(), S * sizeof(double), cudaMemcpyHostToDevice));
     ctx->aug_yw = volume_dot(G, plan, w);
-    // a grid that cannot be coarsened at all has no multigrid to keep: Krylov on the augmented operator there as well
-    ctx->aug = (outflow || ctx->levels.size() == 1) && ctx->aug_ww > 0.0;
-    ctx->aug_rhs = !ctx->aug && ctx->aug_yw != 0.0;
+    // stretched grids go to the Krylov solve as well (plain multigrid diverges beyond a stretch of ~5, ns_hostgeom.h plan_stretch), and so
+    // does a grid that cannot be coarsened at all
+    const bool mg_on_corrected_rhs = rhs_mode >= 1 && !outflow && ctx->levels.size() > 1 && ctx->aug_yw != 0.0 &&
+                                     (rhs_mode >= 2 || plan_stretch(plan) <= 2.0);
+    ctx->aug = !mg_on_corrected_rhs && ctx->aug_ww > 0.0;
+    ctx->aug_rhs = mg_on_corrected_rhs;
   }
   ctx->krylov_phi = ctx->aug || ctx->levels.size() == 1;   // uniform and uncoarsenable: plain preconditioned BiCGStab on the consistent system
   if (ctx->solver == 1 || ctx->krylov_phi)

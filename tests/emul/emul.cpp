@@ -4,6 +4,7 @@
 // libnsgpu.so links, loads or calls this file; it is not a fallback path.  The loops below mirror the kernel
 // launch structure of csrc/ns_solver.inl one to one (same red-black order, same restriction/prolongation).
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
 #include <vector>
 #include <string>
@@ -306,9 +307,13 @@ void* emul_create_rank(const nsgpu_grid* G, double dt, double re, int nu_pre, in
       }
     for (double wv : w) E->aug_ww += wv * wv;
     E->aug_yw = volume_dot(G, E->plan, w);
-    // a grid that cannot be coarsened at all has no multigrid to keep: Krylov on the augmented operator there as well
-    E->aug = outflow || E->lv.size() == 1;
-    E->aug_rhs = !E->aug;
+    // Stretched grids go to the Krylov solve on the augmented operator as well (plain multigrid diverges beyond a stretch of ~5), and so
+    // does a grid that cannot be coarsened at all.  EMUL_RHS_CONSISTENT=1 (NSGPU_RHS_CONSISTENT=1 in the library) keeps the multigrid
+    // iteration on b - c w for mildly stretched grids (stretch <= 2).
+    const bool mg_on_corrected_rhs = getenv("EMUL_RHS_CONSISTENT") && atoi(getenv("EMUL_RHS_CONSISTENT")) && !outflow && E->lv.size() > 1 &&
+                                     (plan_stretch(E->plan) <= 2.0 || atoi(getenv("EMUL_RHS_CONSISTENT")) > 1);
+    E->aug = !mg_on_corrected_rhs;
+    E->aug_rhs = mg_on_corrected_rhs;
   }
   E->krylov_phi = E->aug || E->lv.size() == 1;   // uniform and uncoarsenable: plain preconditioned BiCGStab on the consistent system
   return E;

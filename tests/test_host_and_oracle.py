@@ -418,7 +418,7 @@ def test_outflow_whole_steps_emulation_vs_reference(case, workdir):
 
 
 @needs_ref
-def test_stretched_grid_phi_system_is_inconsistent_and_what_the_reference_returns(workdir):
+def test_stretched_grid_phi_system_is_inconsistent_and_what_the_reference_returns(workdir, monkeypatch):
     """No outflow edge, but a stretched grid: the reference removes the ARITHMETIC mean from RHS_phi (MatNullSpaceRemove, FS.cpp:550)
     while the left null vector of LHS_phi is the cell volumes, so LHS_phi x = b is inconsistent at the 1e-4 level on a wall-refined
     cavity and the KSP returns the bordered solution A x + c w = b with c = (vol, b) / (vol, w) in closed form.  Pinned on the oracle;
@@ -441,14 +441,36 @@ def test_stretched_grid_phi_system_is_inconsistent_and_what_the_reference_return
     em = refapi.Emul(dt=ref.dt, re=ref.re, **ref.desc_kwargs())
     w_host, _ = em.phi_ilu_w()
     assert _rel(w_host, w) <= 1e-13
+    # default: BiCGStab on the augmented operator; opt-in (NSGPU_RHS_CONSISTENT=2 in the library): multigrid on b - c w
+    monkeypatch.setenv("EMUL_RHS_CONSISTENT", "2")
+    em_mg = refapi.Emul(dt=ref.dt, re=ref.re, **ref.desc_kwargs())
     ref2 = refapi.RefSolver(f"{CASES}/cavity_stretched_64.grid", f"{CASES}/cavity_stretched_64.sim")
     ref2.set_rtol(1e-12)
     for s in range(4):
         ref2.step(1)
-        me, worst, cyc = em.step(1, rtol=1e-10, max_cycles=80)
-        assert worst <= 1e-10, (s, worst, cyc)
+        for solver, cap in ((em, 20), (em_mg, 60)):
+            me, worst, cyc = solver.step(1, rtol=1e-10, max_cycles=80)
+            assert worst <= 1e-10 and cyc[2] <= cap, (s, worst, cyc)
+            for k in (U, V, PHI):
+                assert _rel(solver.get(k), ref2.get(k)) <= 2e-8, (s, k)
+
+
+@needs_ref
+def test_strongly_stretched_cavity_whole_steps(workdir):
+    """Wall refinement with ratio 1.1 (h_max / h_min = 19): the plain multigrid iteration diverges there, BiCGStab preconditioned by the
+    same V-cycle converges and follows the reference."""
+    r, inv = 1.1, 1.0 / 1.1
+    (workdir / "s.grid").write_text("Vertices {\n0 0\n0 1\n1 1\n1 0\n}\nNx {\n0 0.5 32 %.10f\n0.5 1 32 %.10f\n}\nNy {\n0 0.5 32 %.10f\n0.5 1 32 %.10f\n}\n" % (r, inv, r, inv))
+    ref = refapi.RefSolver(str(workdir / "s.grid"), f"{CASES}/cavity_stretched_64.sim")
+    ref.set_rtol(1e-12)
+    assert ref.hx.max() / ref.hx.min() > 15
+    em = refapi.Emul(dt=ref.dt, re=ref.re, **ref.desc_kwargs())
+    for s in range(2):
+        ref.step(1)
+        me, worst, cyc = em.step(1, rtol=1e-10, max_cycles=200)
+        assert worst <= 1e-9 and cyc[2] <= 80, (s, worst, cyc)
         for k in (U, V, PHI):
-            assert _rel(em.get(k), ref2.get(k)) <= 2e-8, (s, k)
+            assert _rel(em.get(k), ref.get(k)) <= 2e-8, (s, k)
 
 
 def _random_case(rng, workdir, k):
