@@ -143,6 +143,124 @@ def cpu_baseline_sample(n=512, steps=2):
             "timesteps_per_s": steps / dt}
 
 
+def timed_case(ns, torch, dist, rank, world, local_rank, nccl_id, ny, nxl, args, steps, warmup, e2e=False, fixed_cycles=0):
+    """One more cavity (Re 1000 from rest, dt = 0.25/ny, ny rows, nxl columns per rank) timed like the headline: `warmup` untimed
+    steps, `steps` timed ones, device time, max over ranks.  fixed_cycles > 0: every solve runs exactly that many iterations."""
+    import numpy as np
+    gnx = nxl * world
+    try:
+        grid = ns.GridDesc.cavity(ny, nx=gnx, lx=gnx / float(ny))
+        kw = dict(device=local_rank, rank=rank, world=world, nccl_id=nccl_id, solver=args.solver, use_graph=0 if args.graph else -1)
+        if fixed_cycles:
+            kw.update(rtol_u=1e-300, rtol_phi=1e-300, max_cycles=fixed_cycles)
+        else:
+            kw.update(rtol_u=args.rtol, rtol_phi=args.rtol)
+        s = ns.GpuFluidSolver(grid, 0.25 / ny, args.re, **kw)
+    except ns.NsGpuError as e:
+        return {"ny": ny, "nx": gnx, "unavailable": str(e)}
+
+    def sync_all():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def mx(x):
+        if world == 1:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    s.step(warmup)
+    sync_all()
+    info = s.step(steps)
+    ms = mx(info.ms_total) / steps
+    rec = {"ny": ny, "nx": gnx, "columns_per_gpu": nxl, "n_gpus": world, "steps": steps, "warmup": warmup, "ms_per_step": ms,
+           "gcell_updates_per_s": gnx * ny / (ms * 1e-3) / 1e9, "timesteps_per_s": 1e3 / ms,
+           "iterations_last_step": {"u": info.it_u, "v": info.it_v, "phi": info.it_phi},
+           "phase_ms_last_step": dict(zip(["rhs_build", "velocity_solves", "div_rhs", "phi_solve", "correct"], s.phase_ms())),
+           "status": int(info.status), "levels": s.num_levels}
+    if fixed_cycles:
+        rec["fixed_iterations_per_solve"] = fixed_cycles
+        rec["fine_sweeps_per_step"] = {"phi": 4 * fixed_cycles, "u": 4 * fixed_cycles, "v": 4 * fixed_cycles}
+        rec["note"] = "status -5 (NOT_CONVERGED) is expected: the tolerance is unreachable on purpose"
+    if e2e:
+        keys = [ns.U, ns.V, ns.PHI, ns.CONV_U0, ns.CONV_V0]
+        host = {k: torch.empty(s.n_local, dtype=torch.float64).pin_memory().numpy() for k in keys}
+        for k in keys:
+            host[k][:] = s.get(k)
+        s.step_host(host)
+        sync_all()
+        t0 = time.perf_counter()
+        for _ in range(steps):
+            s.step_host(host)
+        s.synchronize()
+        rec["e2e_ms_per_step"] = 1e3 * mx(time.perf_counter() - t0) / steps
+        rec["e2e_gcell_updates_per_s"] = gnx * ny / (rec["e2e_ms_per_step"] * 1e-3) / 1e9
+    s.close()
+    torch.cuda.empty_cache()
+    return rec
+
+
+def parity_vs_one_rank(ns, capi, torch, dist, rank, world, local_rank, nccl_id, args):
+    """N x-slabs against ONE rank on the same problems (4 steps, bench tolerances, graphs as in the timed run): the driver's test box
+    has one GPU, so this is where N-rank correctness is checked under the driver's clock.  Every rank needs its own NCCL id per
+    context: the id of the timed context is reused (a communicator per context, created and destroyed in the same order on all ranks)."""
+    import numpy as np
+    out = {"cases": [], "steps": 4}
+    worst = {"u": 0.0, "v": 0.0, "phi": 0.0}
+    its_equal = True
+    for ny, nxl in ((256, 128), (130, 66), (512, 256)):
+        gnx = nxl * world
+        grid = ns.GridDesc.cavity(ny, nx=gnx, lx=gnx / float(ny))
+        box = [capi.nccl_unique_id() if rank == 0 else None]
+        dist.broadcast_object_list(box, src=0)
+        kw = dict(rtol_u=args.rtol, rtol_phi=args.rtol, use_graph=0 if args.graph else -1)
+        s, err = None, ""
+        try:
+            s = ns.GpuFluidSolver(grid, 0.25 / ny, args.re, device=local_rank, rank=rank, world=world, nccl_id=box[0], **kw)
+        except ns.NsGpuError as e:   # deterministic (plan / arguments): every rank sees it; the flag below keeps the collectives in step anyway
+            err = str(e)
+        okt = torch.tensor([1 if s is not None else 0], dtype=torch.int32, device="cuda")
+        dist.all_reduce(okt, op=dist.ReduceOp.MIN)
+        if int(okt.item()) == 0:
+            if s is not None:
+                s.close()
+            if rank == 0:
+                out["cases"].append({"grid": [gnx, ny], "unavailable": err or "context creation failed on another rank"})
+            continue
+        info = s.step(4)
+        mine = {k: torch.from_numpy(s.get(k)).cuda() for k in (ns.U, ns.V, ns.PHI)}
+        full = {}
+        for k, t in mine.items():
+            parts = [torch.empty_like(t) for _ in range(world)] if rank == 0 else None
+            dist.gather(t, parts, dst=0)
+            if rank == 0:
+                full[k] = torch.cat(parts).cpu().numpy()
+        flags = int(info.flags)
+        s.close()
+        if rank == 0:
+            one = ns.GpuFluidSolver(grid, 0.25 / ny, args.re, device=local_rank, **kw)
+            i1 = one.step(4)
+            gaps = {}
+            for k, name in ((ns.U, "u"), (ns.V, "v"), (ns.PHI, "phi")):
+                ref = one.get(k)
+                gaps[name] = float(np.abs(full[k] - ref).max() / max(np.abs(ref).max(), 1e-300))
+                worst[name] = max(worst[name], gaps[name])
+            same = [info.it_u, info.it_v, info.it_phi] == [i1.it_u, i1.it_v, i1.it_phi]
+            its_equal = its_equal and same
+            out["cases"].append({"grid": [gnx, ny], "gaps": gaps, "iterations": [info.it_u, info.it_v, info.it_phi],
+                                 "iterations_1gpu": [i1.it_u, i1.it_v, i1.it_phi], "status": [int(info.status), int(i1.status)],
+                                 "p2p": bool(flags & 4), "graph_fallback": bool(flags & 1)})
+            one.close()
+        dist.barrier()
+    out.update(worst)
+    out["iterations_equal"] = its_equal
+    out["tolerance"] = "relative max-norm gap of u, v, phi after 4 steps, rtol %g on both sides; summation order is the only difference" % args.rtol
+    return out
+
+
 def ours(args, rank, world, local_rank):
     import numpy as np
     import navierstokessolver_b200 as ns
@@ -208,13 +326,48 @@ def ours(args, rank, world, local_rank):
     sweep_gcups = cells_global / (best * 1e-3) / 1e9
     peak, peak_src = measured_peak_gbs()
     achieved = cells_local * SWEEP_BYTES_PER_UPDATE / (best * 1e-3) / 1e9
+    # dram bytes per launch from the committed ncu capture -- only when the timed launch IS the captured configuration
+    # (one rank, 4096 x 4096, non-pushing kernel variant); any other grid or rank count reports null
     traffic = None
     tpath = os.path.join(ROOT, "profiles", "sweep_traffic.json")
-    if os.path.exists(tpath):
+    if world == 1 and ny == 4096 and nxl == 4096 and os.path.exists(tpath):
         try:
             traffic = json.load(open(tpath)).get("dram_bytes_per_launch")
         except Exception:
             traffic = None
+
+    # ---- the passes the time step really runs on the fine level, each timed alone the same way (nsgpu_time_passes)
+    inloop = {}
+    if s.num_levels >= 2:
+        names = {1: "k_march<2,false,1,*> first pass of a phi V-cycle: 2 fused red-black sweeps + residual restricted to level 1",
+                 2: "k_march<2,true,2,*> last pass of a phi V-cycle: coarse correction added, 2 fused sweeps, |r|^2 reduced",
+                 3: "k_march<2,false,0,*,SOR> red-black SOR double sweep of LHS_V (velocity solves)"}
+        # algorithmic bytes per fine cell and pass: read x, read b, write x = 24; the restriction writes / the prolongation reads
+        # one coarse double per 4 fine cells (+2)
+        bpc = {1: 26.0, 2: 26.0, 3: 24.0}
+        try:
+            for kind in (1, 2, 3):
+                s.time_passes(kind, 10)
+                b_ = None
+                for _ in range(3):
+                    barrier()
+                    t_ = max_over_ranks(s.time_passes(kind, 50)) / 50
+                    b_ = t_ if b_ is None else min(b_, t_)
+                ach = cells_local * bpc[kind] / (b_ * 1e-3) / 1e9
+                inloop[str(kind)] = {"kernel": names[kind], "us_per_launch": b_ * 1e3, "bytes_per_cell": bpc[kind], "cell_updates_per_launch": 2 * cells_local,
+                                     "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
+                                     "gcell_updates_per_s": 2 * cells_global / (b_ * 1e-3) / 1e9}
+        except ns.NsGpuError as e:
+            inloop = {"unavailable": str(e)}
+    # ncu DRAM bytes of the in-loop passes, same rule as `traffic`
+    ipath = os.path.join(ROOT, "profiles", "inloop_traffic.json")
+    if world == 1 and ny == 4096 and nxl == 4096 and os.path.exists(ipath) and "unavailable" not in inloop:
+        try:
+            for k_, v_ in json.load(open(ipath)).items():
+                if k_ in inloop:
+                    inloop[k_]["traffic"] = v_.get("dram_bytes_per_launch")
+        except Exception:
+            pass
 
     # ---- end to end through the C ABI with host buffers (pinned), full state up, fields down, every step
     fields_up = [ns.U, ns.V, ns.PHI, ns.CONV_U0, ns.CONV_V0] + ([ns.GRADPHI_X, ns.GRADPHI_Y] if args.e2e_arrays == 7 else [])
@@ -233,6 +386,26 @@ def ours(args, rank, world, local_rank):
     h2d = 8 * s.n_local * len(fields_up)
     d2h = 8 * s.n_local * len(fields_up)
 
+    n_levels = s.num_levels
+    s.close()
+    del host
+    torch.cuda.empty_cache()
+
+    extras = {}
+    if not args.no_extras:
+        # ---- (a) several ranks: the same small problems on N slabs and on ONE rank (rank 0's GPU), fields compared
+        if world > 1:
+            extras["parity_vs_1gpu"] = parity_vs_one_rank(ns, capi, torch, dist, rank, world, local_rank, nccl_id, args)
+        # ---- (b) north-star configuration: 16384 x 16384, strong scaling (16384 / N columns per GPU), one code state
+        extras["strong_16384"] = timed_case(ns, torch, dist, rank, world, local_rank, nccl_id, 16384, 16384 // world, args, steps=5, warmup=3)
+        if world == 1:
+            # ---- (c) the reference arm's own inputs (like for like), and the other size SURVEY 8(d) asks a time-step line for
+            extras["same_config"] = [timed_case(ns, torch, dist, rank, world, local_rank, nccl_id, n_, n_, args, steps=args.steps, warmup=args.warmup, e2e=True)
+                                     for n_ in (256, 512)]
+            extras["size_1024"] = timed_case(ns, torch, dist, rank, world, local_rank, nccl_id, 1024, 1024, args, steps=args.steps, warmup=args.warmup)
+            # ---- (d) fixed work: exactly 4 phi V-cycles and 4 x 4 SOR sweeps per velocity solve every step, whatever the residuals
+            extras["fixed_work_4096"] = timed_case(ns, torch, dist, rank, world, local_rank, nccl_id, ny, nxl, args, steps=args.steps, warmup=3, fixed_cycles=4)
+
     cpu = cpu_baseline_sample() if (rank == 0 and world == 1 and not args.no_cpu_baseline) else None
 
     if rank == 0:
@@ -243,7 +416,7 @@ def ours(args, rank, world, local_rank):
                            "parallelism": ("x-slabs, %d rank(s); solves: halo columns, norms and the replicated coarse rhs through NVLink peer memory from inside the kernels (NCCL only outside the solves)" % world) if world > 1 else "1 rank (no exchange)",
                            "solver": ("BiCGStab + V(2,2)" if args.solver else "phi: multigrid V(2,2), fused red-black GS passes; u*, v*: red-black SOR or multigrid (auto)")
                                      + ", true-residual rtol %g all solves, %s" % (args.rtol, "one CUDA graph per solve (device-side WHILE)" if args.graph else "direct launches"),
-                           "levels": s.num_levels, "cache": "inputs larger than L2 (13 resident fields x %.0f MB per GPU)" % (cells_local * 8 / 1e6)},
+                           "levels": n_levels, "cache": "inputs larger than L2 (13 resident fields x %.0f MB per GPU)" % (cells_local * 8 / 1e6)},
                 "timesteps_per_s": args.steps / (ms * 1e-3),
                 "poisson_gcell_updates_per_s": sweep_gcups,
                 "solver_iterations_last_step": {"u": info.it_u, "v": info.it_v, "phi": info.it_phi},
@@ -260,12 +433,14 @@ def ours(args, rank, world, local_rank):
                 "roofline": {"bound": "hbm", "kernel": "k_march<1,false,0> (fine-level fused red-black Poisson sweep, register-marching)", "achieved": achieved, "peak": peak,
                              "unit": "GB/s", "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
                              "bytes_per_cell_update": SWEEP_BYTES_PER_UPDATE, "us_per_launch": best * 1e3,
-                             "cells_per_launch": cells_local, "timing": "CUDA events on the solver stream around %d back-to-back launches, best of 5" % args.sweeps},
-                "status": int(info.status)}
+                             "cells_per_launch": cells_local, "timing": "CUDA events on the solver stream around %d back-to-back launches, best of 5" % args.sweeps,
+                             "rhs": "physically shaped: phi and RHS_phi are the state after %d cavity time steps" % (args.warmup + args.steps)},
+                "status": int(info.status), "flags": int(info.flags)}
+        line["roofline_inloop"] = inloop
+        line.update(extras)
         if cpu:
             line["cpu_baseline"] = cpu
         emit(line)
-    s.close()
     if world > 1:
         dist.destroy_process_group()
 
@@ -286,6 +461,7 @@ def main():
     ap.add_argument("--ref-n", type=int, default=256)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--e2e-arrays", type=int, default=5, choices=[5, 7])
+    ap.add_argument("--no-extras", action="store_true", help="skip the sub-records (parity_vs_1gpu, strong_16384, same_config, size_1024, fixed_work_4096)")
     args = ap.parse_args()
     _isolate_stdout()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup

@@ -78,7 +78,15 @@ typedef struct {
   float ms_total;                  /* device time of the call, CUDA events on the ctx stream    */
   int32_t kernel_launches;         /* kernels launched by this call                             */
   int32_t status;
+  int32_t flags;                   /* NSGPU_FLAG_* bits                                         */
+  int32_t krylov_restarts;         /* BiCGStab restarts from the recomputed true residual       */
 } nsgpu_step_info;
+enum {
+  NSGPU_FLAG_GRAPH_FALLBACK = 1,   /* CUDA graphs were requested but the solves ran as direct launches (capture failed, or a  */
+                                   /* solve needs NCCL inside its loop): same results, about twice the launch latency        */
+  NSGPU_FLAG_KRYLOV_PHI = 2,       /* the phi solve took the Krylov route (outflow / stretched / uncoarsenable grid)         */
+  NSGPU_FLAG_P2P = 4               /* several ranks: halo columns travel through NVLink peer memory from inside the kernels  */
+};
 
 /* ids for nsgpu_get_array / nsgpu_set_array (FluidSolver private state, FS.h:22-33) */
 enum {
@@ -127,12 +135,30 @@ int nsgpu_correct(nsgpu_ctx* ctx, nsgpu_step_info* info);      /* CorrectVelocit
  * time of the sweeps alone (CUDA events on the ctx stream). */
 int nsgpu_poisson_sweeps(nsgpu_ctx* ctx, int32_t n_sweeps, double* residual_l2, float* ms);
 
+/* The fine-level passes the time step really runs, timed alone (n back-to-back launches, CUDA events on the ctx stream): kind 0 = plain
+ * sweep (as nsgpu_poisson_sweeps), 1 = first pass of a phi V-cycle (two fused sweeps + residual restricted to the next level), 2 = its
+ * last pass (coarse correction added while loading, two fused sweeps, |r|^2 reduced), 3 = red-black SOR double sweep of LHS_V on
+ * (u*, RHS_u).  Smooths phi / u* in place: for benchmark contexts, not inside a time loop.  Rectangles with >= 2 levels. */
+int nsgpu_time_passes(nsgpu_ctx* ctx, int32_t kind, int32_t n, float* ms);
+
 /* y = LHS x for op 0 = LHS_V, 1 = LHS_phi (the operators ConstructLHS assembles, FS.cpp:105-145);
  * x, y are host arrays of n_local doubles. */
 int nsgpu_apply_operator(nsgpu_ctx* ctx, int32_t op, const double* x, double* y);
 
 /* physical pressure Pr = phi - dt/(2Re) LHS_phi phi (ExportData, FS.cpp:577-581) and lapPhi */
 int nsgpu_pressure(nsgpu_ctx* ctx, double* pr, double* lap_phi);
+
+/* ExportData without stalling the time loop (FS.cpp:561, 569-615).  nsgpu_export_begin takes a snapshot of u, v, phi, Pr and
+ * lapPhi = LHS_phi phi on the device (one kernel on the solver's stream) and starts their copy into page-locked host memory on a
+ * separate stream; it returns at once, further nsgpu_step calls overlap the copy.  nsgpu_export_wait blocks until the OLDEST
+ * pending snapshot is on the host and returns pointers to its five arrays (n_local doubles each, compact-id order; owned by the
+ * context, valid until the second nsgpu_export_begin after this snapshot's) and the tag given to begin.  At most two snapshots
+ * may be pending.  Any output pointer may be NULL. */
+int nsgpu_export_begin(nsgpu_ctx* ctx, int64_t tag);
+int nsgpu_export_wait(nsgpu_ctx* ctx, const double** u, const double** v, const double** phi, const double** pr,
+                      const double** lap_phi, int64_t* tag);
+
+int nsgpu_export_last_ms(const nsgpu_ctx* ctx, float* ms);   /* device time of the snapshot kernel of the snapshot last waited for */
 
 int nsgpu_get_array(nsgpu_ctx* ctx, int32_t which, double* out);       /* n_local doubles, compact-id order */
 int nsgpu_set_array(nsgpu_ctx* ctx, int32_t which, const double* in);
@@ -141,10 +167,10 @@ int nsgpu_set_fields(nsgpu_ctx* ctx, const double* u, const double* v, const dou
 
 /* Checkpoint / restart.  The reference has none (its state lives and dies with the process, FS.h:22-33); SURVEY.md section 8(f) lists
  * it for the long runs to steady state.  The file holds the complete state of the time loop for this rank's id range -- the seven
- * arrays of nsgpu_host_state -- plus the caller's step counter, so a restarted run continues bit for bit (outflow domains: to
- * the solver tolerance, the Krylov warm-start shift is not part of the state).  Little-endian binary: 64-byte header
- * ("NSGPUCK1", nx, ny, n_cells, id0, n_local, step, dt) then 7 x n_local doubles.  Several ranks: each rank writes "<path>.<rank>".
- * load refuses a file whose grid extents or id range differ from the context's (NSGPU_ERR_ARG). */
+ * arrays of nsgpu_host_state -- plus the caller's step counter, dt, re and the warm-start shift of the augmented phi solve of outflow /
+ * stretched domains, so a restarted run continues bit for bit on every domain.  Little-endian binary: 88-byte header
+ * ("NSGPUCK2", nx, ny, n_cells, id0, n_local, step, dt, re, shift, reserved) then 7 x n_local doubles.  Several ranks: each rank writes
+ * "<path>.<rank>".  load refuses a file whose grid extents, id range, dt or re differ from the context's (NSGPU_ERR_ARG). */
 int nsgpu_checkpoint_save(nsgpu_ctx* ctx, const char* path, int64_t step);
 int nsgpu_checkpoint_load(nsgpu_ctx* ctx, const char* path, int64_t* step);
 

@@ -43,7 +43,7 @@ class StepInfo(C.Structure):
                 ("it_u", C.c_int32), ("it_v", C.c_int32), ("it_phi", C.c_int32),
                 ("res_u", C.c_double), ("res_v", C.c_double), ("res_phi", C.c_double),
                 ("fine_sweeps", C.c_double), ("ms_total", C.c_float), ("kernel_launches", C.c_int32),
-                ("status", C.c_int32)]
+                ("status", C.c_int32), ("flags", C.c_int32), ("krylov_restarts", C.c_int32)]
 
     def as_dict(self):
         return {k: getattr(self, k) for k, _ in self._fields_}
@@ -84,7 +84,11 @@ def _load():
     L.nsgpu_correct.argtypes = [P, C.POINTER(StepInfo)]
     L.nsgpu_poisson_sweeps.argtypes = [P, C.c_int32, dp, C.POINTER(C.c_float)]
     L.nsgpu_apply_operator.argtypes = [P, C.c_int32, dp, dp]
+    L.nsgpu_time_passes.argtypes = [P, C.c_int32, C.c_int32, C.POINTER(C.c_float)]
     L.nsgpu_pressure.argtypes = [P, dp, dp]
+    L.nsgpu_export_begin.argtypes = [P, C.c_int64]
+    L.nsgpu_export_wait.argtypes = [P] + [C.POINTER(dp)] * 5 + [C.POINTER(C.c_int64)]
+    L.nsgpu_export_last_ms.argtypes = [P, C.POINTER(C.c_float)]
     L.nsgpu_get_array.argtypes = [P, C.c_int32, dp]
     L.nsgpu_set_array.argtypes = [P, C.c_int32, dp]
     L.nsgpu_get_fields.argtypes = [P, dp, dp, dp]
@@ -104,7 +108,8 @@ EXPORTED = ["nsgpu_nccl_unique_id", "nsgpu_create", "nsgpu_destroy", "nsgpu_last
             "nsgpu_step", "nsgpu_rhs_build", "nsgpu_solve_velocity", "nsgpu_div_rhs", "nsgpu_solve_phi",
             "nsgpu_correct", "nsgpu_poisson_sweeps", "nsgpu_apply_operator", "nsgpu_pressure", "nsgpu_get_array",
             "nsgpu_set_array", "nsgpu_get_fields", "nsgpu_set_fields", "nsgpu_num_levels", "nsgpu_kernel_launches",
-            "nsgpu_synchronize", "nsgpu_phase_ms", "nsgpu_step_host", "nsgpu_checkpoint_save", "nsgpu_checkpoint_load"]
+            "nsgpu_synchronize", "nsgpu_phase_ms", "nsgpu_step_host", "nsgpu_checkpoint_save", "nsgpu_checkpoint_load",
+            "nsgpu_export_begin", "nsgpu_export_wait", "nsgpu_time_passes", "nsgpu_export_last_ms"]
 
 
 def _dp(a):
@@ -255,6 +260,12 @@ class GpuFluidSolver:
         self._chk(lib.nsgpu_poisson_sweeps(self._h, n, C.byref(r) if want_residual else None, C.byref(ms)))
         return r.value, ms.value
 
+    def time_passes(self, kind, n):
+        """device ms of n back-to-back fine-level passes of `kind` (nsgpu_time_passes)"""
+        ms = C.c_float(0.0)
+        self._chk(lib.nsgpu_time_passes(self._h, kind, n, C.byref(ms)))
+        return ms.value
+
     def apply_operator(self, op, x):
         x = np.ascontiguousarray(x, dtype=np.float64)
         y = np.empty(self.n_local, dtype=np.float64)
@@ -265,6 +276,18 @@ class GpuFluidSolver:
         pr, lap = np.empty(self.n_local), np.empty(self.n_local)
         self._chk(lib.nsgpu_pressure(self._h, _dp(pr), _dp(lap)))
         return pr, lap
+
+    def export_begin(self, tag=0):
+        """Snapshot of u, v, phi, Pr, lapPhi on the device + asynchronous copy home (nsgpu_export_begin); returns at once."""
+        self._chk(lib.nsgpu_export_begin(self._h, int(tag)))
+
+    def export_wait(self):
+        """Oldest pending snapshot: (tag, {"u", "v", "phi", "pr", "lap"}) as copies of the context's pinned arrays."""
+        ptr = [C.POINTER(C.c_double)() for _ in range(5)]
+        tag = C.c_int64(0)
+        self._chk(lib.nsgpu_export_wait(self._h, *[C.byref(q) for q in ptr], C.byref(tag)))
+        names = ("u", "v", "phi", "pr", "lap")
+        return int(tag.value), {k: np.ctypeslib.as_array(q, shape=(self.n_local,)).copy() for k, q in zip(names, ptr)}
 
     @property
     def num_levels(self):

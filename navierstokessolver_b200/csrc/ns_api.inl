@@ -177,8 +177,10 @@ int nsgpu_set_fields(nsgpu_ctx* ctx, const double* u, const double* v, const dou
 }
 
 namespace {
-struct CkptHeader { char magic[8]; int64_t nx, ny, n_cells, id0, n_local, step; double dt; };
-static_assert(sizeof(CkptHeader) == 64, "checkpoint header is 64 bytes");
+// version 2: dt, re and the warm-start shift of the augmented phi solve (d_scal[46] = n * mean(x), outflow / stretched domains) are part
+// of the state, so a restarted run continues bit for bit there too
+struct CkptHeader { char magic[8]; int64_t nx, ny, n_cells, id0, n_local, step; double dt, re, aug_c, reserved; };
+static_assert(sizeof(CkptHeader) == 88, "checkpoint header is 88 bytes");
 const int kCkptFields[7] = {NSGPU_U, NSGPU_V, NSGPU_PHI, NSGPU_CONV_U0, NSGPU_CONV_V0, NSGPU_GRADPHI_X, NSGPU_GRADPHI_Y};
 std::string ckpt_name(const nsgpu_ctx* ctx, const char* path) {
   return ctx->world > 1 ? std::string(path) + "." + std::to_string(ctx->rank) : std::string(path);
@@ -187,12 +189,18 @@ std::string ckpt_name(const nsgpu_ctx* ctx, const char* path) {
 
 int nsgpu_checkpoint_save(nsgpu_ctx* ctx, const char* path, int64_t step) {
   if (!ctx || !path) return NSGPU_ERR_ARG;
+  cudaSetDevice(ctx->device);
   const std::string name = ckpt_name(ctx, path), tmp = name + ".tmp";
   FILE* f = fopen(tmp.c_str(), "wb");
   if (!f) { ctx->err = "cannot open " + tmp + " for writing"; return NSGPU_ERR_ARG; }
   CkptHeader h{};
-  memcpy(h.magic, "NSGPUCK1", 8);
-  h.nx = ctx->gnx; h.ny = ctx->ny; h.n_cells = ctx->n_cells_global; h.id0 = ctx->id0; h.n_local = ctx->n_local; h.step = step; h.dt = ctx->dt;
+  memcpy(h.magic, "NSGPUCK2", 8);
+  h.nx = ctx->gnx; h.ny = ctx->ny; h.n_cells = ctx->n_cells_global; h.id0 = ctx->id0; h.n_local = ctx->n_local; h.step = step;
+  h.dt = ctx->dt; h.re = ctx->re;
+  if (cudaStreamSynchronize(ctx->stream) != cudaSuccess ||
+      cudaMemcpy(&h.aug_c, ctx->d_scal + 46, sizeof(double), cudaMemcpyDeviceToHost) != cudaSuccess) {
+    fclose(f); remove(tmp.c_str()); ctx->err = "checkpoint: device read failed"; return NSGPU_ERR_CUDA;
+  }
   bool ok = fwrite(&h, sizeof h, 1, f) == 1;
   std::vector<double> buf((size_t)ctx->n_local);
   for (int k = 0; k < 7 && ok; k++) {
@@ -208,13 +216,17 @@ int nsgpu_checkpoint_save(nsgpu_ctx* ctx, const char* path, int64_t step) {
 
 int nsgpu_checkpoint_load(nsgpu_ctx* ctx, const char* path, int64_t* step) {
   if (!ctx || !path) return NSGPU_ERR_ARG;
+  cudaSetDevice(ctx->device);
   const std::string name = ckpt_name(ctx, path);
   FILE* f = fopen(name.c_str(), "rb");
   if (!f) { ctx->err = "cannot open " + name; return NSGPU_ERR_ARG; }
   CkptHeader h{};
-  if (fread(&h, sizeof h, 1, f) != 1 || memcmp(h.magic, "NSGPUCK1", 8) != 0) { fclose(f); ctx->err = name + " is not an nsgpu checkpoint"; return NSGPU_ERR_ARG; }
+  if (fread(&h, sizeof h, 1, f) != 1 || memcmp(h.magic, "NSGPUCK2", 8) != 0) { fclose(f); ctx->err = name + " is not an nsgpu checkpoint (version 2)"; return NSGPU_ERR_ARG; }
   if (h.nx != ctx->gnx || h.ny != ctx->ny || h.n_cells != ctx->n_cells_global || h.id0 != ctx->id0 || h.n_local != ctx->n_local) {
     fclose(f); ctx->err = name + " was written for another grid or another slab decomposition"; return NSGPU_ERR_ARG;
+  }
+  if (h.dt != ctx->dt || h.re != ctx->re) {   // the history terms and divPhi in the file belong to that dt and re
+    fclose(f); ctx->err = name + " was written with another dt or re"; return NSGPU_ERR_ARG;
   }
   // read everything before touching the device state: a truncated file leaves the context as it was
   std::vector<double> buf((size_t)7 * (size_t)ctx->n_local);
@@ -225,6 +237,7 @@ int nsgpu_checkpoint_load(nsgpu_ctx* ctx, const char* path, int64_t* step) {
     const int rc = nsgpu_set_array(ctx, kCkptFields[k], buf.data() + (size_t)k * (size_t)ctx->n_local);
     if (rc) return rc;
   }
+  NS_CUDA(cudaMemcpy(ctx->d_scal + 46, &h.aug_c, sizeof(double), cudaMemcpyHostToDevice));
   if (step) *step = h.step;
   return 0;
 }
@@ -375,6 +388,7 @@ static int step_impl(nsgpu_ctx* ctx, int32_t n_steps, nsgpu_step_info* last, con
   double mm[4] = {0, 0, 0, 0};
   const int64_t l0 = ctx->launches;
   const double s0 = ctx->fine_sweeps_phi;
+  ctx->krylov_restarts = 0;
   int status = 0, rc;
   NS_CUDA(cudaEventRecord(ctx->ev0, ctx->stream));
   for (int s = 0; s < n_steps; s++) {
@@ -453,6 +467,9 @@ static int step_impl(nsgpu_ctx* ctx, int32_t n_steps, nsgpu_step_info* last, con
     last->ms_total = ms;
     last->kernel_launches = (int32_t)(ctx->launches - l0);
     last->status = status;
+    last->flags = (ctx->graph_fallback ? NSGPU_FLAG_GRAPH_FALLBACK : 0) | (ctx->krylov_phi ? NSGPU_FLAG_KRYLOV_PHI : 0) |
+                  ((ctx->world > 1 && ctx->use_p2p && ctx->d_pt) ? NSGPU_FLAG_P2P : 0);
+    last->krylov_restarts = ctx->krylov_restarts;
   }
   return status;
 }
@@ -489,6 +506,39 @@ int nsgpu_poisson_sweeps(nsgpu_ctx* ctx, int32_t n_sweeps, double* residual_l2, 
   return 0;
 }
 
+// The passes the time step really runs on the fine level, timed alone (bench.py "roofline_inloop"): kind 1 = first pass of a phi V-cycle
+// (two fused sweeps + residual restricted to level 1), 2 = last pass (coarse correction added, two fused sweeps, |r|^2 reduced),
+// 3 = one red-black SOR double sweep of LHS_V on (u*, RHS_u); kind 0 = the plain sweep of nsgpu_poisson_sweeps.  Work on copies of
+// nothing: phi / u* are smoothed in place n times (harmless for a benchmark context, wrong inside a time loop).
+int nsgpu_time_passes(nsgpu_ctx* ctx, int32_t kind, int32_t n, float* ms) {
+  if (!ctx || n < 0 || kind < 0 || kind > 3) return NSGPU_ERR_ARG;
+  cudaSetDevice(ctx->device);
+  if (kind == 0) return nsgpu_poisson_sweeps(ctx, n, nullptr, ms);
+  const Level& L = ctx->levels[0];
+  const OpCoef c = kind == 3 ? coef_v(ctx) : coef_phi();
+  if (!march_level_ok(ctx, L, c) || (kind != 3 && ctx->levels.size() < 2)) { ctx->err = "nsgpu_time_passes: rectangle fast path with at least two levels only"; return NSGPU_ERR_ARG; }
+  int rc;
+  ctx->halo_w.clear();
+  double** x = kind == 3 ? &ctx->ustar : &ctx->phi;
+  const double* b = kind == 3 ? ctx->rhs_u : ctx->rhs_phi;
+  if ((rc = halo_exchange(ctx, L, const_cast<double*>(b), HX - 1))) return rc;
+  if ((rc = halo_exchange(ctx, L, *x, HX - 1))) return rc;
+  ctx->halo_w[*x] = std::min(HX - 1, L.g.nx);
+  NS_CUDA(cudaEventRecord(ctx->ev0, ctx->stream));
+  for (int k = 0; k < n; k++) {
+    if (kind == 1) rc = march_pass(ctx, L, c, 2, *x, b, ctx->tmp, nullptr, nullptr, &ctx->levels[1], nullptr, nullptr);
+    else if (kind == 2) rc = march_pass(ctx, L, c, 2, *x, b, ctx->tmp, &ctx->levels[1], ctx->levels[1].x, nullptr, ctx->d_scal + 24, nullptr);
+    else rc = march_pass(ctx, L, c, 2, *x, b, ctx->tmp, nullptr, nullptr, nullptr, nullptr, nullptr, ctx->vel_omega > 0 ? ctx->vel_omega : 1.0);
+    if (rc) return rc;
+    std::swap(*x, ctx->tmp);
+  }
+  NS_CUDA(cudaEventRecord(ctx->ev1, ctx->stream));
+  if ((rc = sync_check(ctx))) return rc;
+  if (ms) NS_CUDA(cudaEventElapsedTime(ms, ctx->ev0, ctx->ev1));
+  ctx->halo_w.clear();
+  return 0;
+}
+
 int nsgpu_apply_operator(nsgpu_ctx* ctx, int32_t op, const double* x, double* y) {
   if (!ctx || !x || !y || (op != 0 && op != 1)) return NSGPU_ERR_ARG;
   cudaSetDevice(ctx->device);
@@ -503,19 +553,104 @@ int nsgpu_apply_operator(nsgpu_ctx* ctx, int32_t op, const double* x, double* y)
   return download_field(ctx, ctx->kry[1], y);
 }
 
+// ExportData without stalling the loop (FS.cpp:561, 569-615).  begin: one kernel on the solver's stream takes the snapshot (u, v, phi,
+// Pr, lapPhi), a copy stream brings it into one of two pinned buffers; the call returns at once and the next time steps run under the
+// copy.  wait: blocks until the OLDEST pending snapshot is home and hands out pointers into the pinned buffer (valid until the second
+// nsgpu_export_begin after it).
+int nsgpu_export_begin(nsgpu_ctx* ctx, int64_t tag) {
+  if (!ctx) return NSGPU_ERR_ARG;
+  cudaSetDevice(ctx->device);
+  if (ctx->exp_pending >= 2) { ctx->err = "nsgpu_export_begin: two snapshots are already pending (call nsgpu_export_wait)"; return NSGPU_ERR_ARG; }
+  const Level& L = ctx->levels[0];
+  const size_t n_host = ctx->rect ? (size_t)ctx->n_local : L.stride;
+  if (!ctx->s_exp) {
+    NS_CUDA(cudaStreamCreateWithFlags(&ctx->s_exp, cudaStreamNonBlocking));
+    NS_CUDA(cudaEventCreateWithFlags(&ctx->exp_snap, cudaEventDisableTiming));
+    for (auto& e : ctx->exp_home) NS_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+    for (auto& e : ctx->exp_t0) NS_CUDA(cudaEventCreate(&e));
+    for (auto& e : ctx->exp_t1) NS_CUDA(cudaEventCreate(&e));
+    for (auto& q : ctx->exp_dev) { void* p = nullptr; NS_CUDA(cudaMalloc(&p, L.stride * sizeof(double))); ctx->owned.push_back(p); NS_CUDA(cudaMemset(p, 0, L.stride * sizeof(double))); q = (double*)p; }
+    for (auto& q : ctx->exp_host) NS_CUDA(cudaMallocHost((void**)&q, 5 * n_host * sizeof(double)));
+    for (auto& e : ctx->exp_home) NS_CUDA(cudaEventRecord(e, ctx->s_exp));
+  }
+  int rc;
+  if ((rc = halo_exchange(ctx, L, ctx->phi, 2))) return rc;
+  ctx->halo_w.clear();
+  // the device staging arrays are reused by every snapshot: the previous copies must have left them
+  NS_CUDA(cudaStreamWaitEvent(ctx->stream, ctx->exp_home[(ctx->exp_head + 1) & 1], 0));
+  const dim3 grid = grid_cols(L.g, 256);
+  const double half = ctx->dt / (2.0 * ctx->re);
+  NS_CUDA(cudaEventRecord(ctx->exp_t0[ctx->exp_head], ctx->stream));
+#define CALL(RECT) k_export_snapshot<RECT><<<grid, 256, 0, ctx->stream>>>(L.g, half, ctx->u, ctx->v, ctx->phi, ctx->exp_dev[0], ctx->exp_dev[1], ctx->exp_dev[2], ctx->exp_dev[3], ctx->exp_dev[4])
+  NS_DISPATCH_RECT(ctx->rect, CALL);
+#undef CALL
+  NS_LAUNCH_CHECK();
+  NS_CUDA(cudaEventRecord(ctx->exp_t1[ctx->exp_head], ctx->stream));
+  NS_CUDA(cudaEventRecord(ctx->exp_snap, ctx->stream));
+  NS_CUDA(cudaStreamWaitEvent(ctx->s_exp, ctx->exp_snap, 0));
+  const int slot = ctx->exp_head;
+  double* h = ctx->exp_host[slot];
+  for (int k = 0; k < 5; k++) {
+    if (ctx->rect) {
+      const LevelGeom& g = L.g;
+      NS_CUDA(cudaMemcpy2DAsync(h + (size_t)k * n_host, (size_t)g.ny * sizeof(double), ctx->exp_dev[k] + cidx(g, 0, 0), (size_t)g.ld * sizeof(double),
+                                (size_t)g.ny * sizeof(double), (size_t)g.nx, cudaMemcpyDeviceToHost, ctx->s_exp));
+    } else {
+      NS_CUDA(cudaMemcpyAsync(h + (size_t)k * n_host, ctx->exp_dev[k], L.stride * sizeof(double), cudaMemcpyDeviceToHost, ctx->s_exp));
+    }
+  }
+  NS_CUDA(cudaEventRecord(ctx->exp_home[slot], ctx->s_exp));
+  ctx->exp_tag[slot] = tag;
+  ctx->exp_head ^= 1;
+  ctx->exp_pending++;
+  return 0;
+}
+
+int nsgpu_export_wait(nsgpu_ctx* ctx, const double** u, const double** v, const double** phi, const double** pr, const double** lap_phi, int64_t* tag) {
+  if (!ctx) return NSGPU_ERR_ARG;
+  if (ctx->exp_pending <= 0) { ctx->err = "nsgpu_export_wait: no snapshot pending"; return NSGPU_ERR_ARG; }
+  cudaSetDevice(ctx->device);
+  const int slot = (ctx->exp_head + 2 - ctx->exp_pending) & 1;
+  NS_CUDA(cudaEventSynchronize(ctx->exp_home[slot]));
+  ctx->exp_pending--;
+  if (cudaEventElapsedTime(&ctx->exp_last_ms, ctx->exp_t0[slot], ctx->exp_t1[slot]) != cudaSuccess) { ctx->exp_last_ms = 0.0f; cudaGetLastError(); }
+  const Level& L = ctx->levels[0];
+  const double* base = ctx->exp_host[slot];
+  size_t n_host = (size_t)ctx->n_local;
+  if (!ctx->rect) {   // general domains: padded layout -> compact ids on the host
+    const LevelGeom& g = L.g;
+    std::vector<double>& c = ctx->exp_compact[slot];
+    c.assign((size_t)5 * (size_t)ctx->n_local, 0.0);
+    for (int k = 0; k < 5; k++)
+      for (int i = 0; i < g.nx; i++)
+        for (int j = 0; j < g.ny; j++) {
+          const int32_t id = ctx->local_id[(size_t)i * g.ny + j];
+          if (id >= 0) c[(size_t)k * ctx->n_local + id] = base[(size_t)k * L.stride + cidx(g, i, j)];
+        }
+    base = c.data();
+  }
+  const double** outp[5] = {u, v, phi, pr, lap_phi};
+  for (int k = 0; k < 5; k++) if (outp[k]) *outp[k] = base + (size_t)k * n_host;
+  if (tag) *tag = ctx->exp_tag[slot];
+  return 0;
+}
+
+int nsgpu_export_last_ms(const nsgpu_ctx* ctx, float* ms) {
+  if (!ctx || !ms) return NSGPU_ERR_ARG;
+  *ms = ctx->exp_last_ms;
+  return 0;
+}
+
+// physical pressure, synchronous form (kept for callers that want it now): one snapshot, waited for at once
 int nsgpu_pressure(nsgpu_ctx* ctx, double* pr, double* lap_phi) {
   if (!ctx || !pr) return NSGPU_ERR_ARG;
-  cudaSetDevice(ctx->device);
-  const Level& L = ctx->levels[0];
-  if (!ctx->kry[0]) for (int k = 0; k < 2; k++) { int rc = dev_zeros(ctx, ctx->owned, L.stride, &ctx->kry[k]); if (rc) return rc; }
-  int rc;
-  if ((rc = apply_op(ctx, L, coef_phi(), ctx->phi, ctx->kry[1], nullptr, nullptr))) return rc;
-  if ((rc = sync_check(ctx))) return rc;
-  std::vector<double> lap((size_t)ctx->n_local), ph((size_t)ctx->n_local);
-  if ((rc = download_field(ctx, ctx->kry[1], lap.data()))) return rc;
-  if ((rc = download_field(ctx, ctx->phi, ph.data()))) return rc;
-  const double f = ctx->dt / (2.0 * ctx->re);
-  for (size_t k = 0; k < lap.size(); k++) { pr[k] = ph[k] - f * lap[k]; if (lap_phi) lap_phi[k] = lap[k]; }   // FS.cpp:579-581
+  if (ctx->exp_pending) { ctx->err = "nsgpu_pressure: an asynchronous export is pending"; return NSGPU_ERR_ARG; }
+  int rc = nsgpu_export_begin(ctx, -1);
+  if (rc) return rc;
+  const double *p = nullptr, *l = nullptr;
+  if ((rc = nsgpu_export_wait(ctx, nullptr, nullptr, nullptr, &p, &l, nullptr))) return rc;
+  memcpy(pr, p, (size_t)ctx->n_local * sizeof(double));
+  if (lap_phi) memcpy(lap_phi, l, (size_t)ctx->n_local * sizeof(double));
   return 0;
 }
 

@@ -133,6 +133,19 @@ struct nsgpu_ctx {
   int tail_start = 0, use_tail = 1;
   double vel_rho = 0.0, vel_omega = 0.0;   // Jacobi radius bound of LHS_V; SOR factor (0: velocity solves use multigrid)
   nsgpu::TailDesc tail[2];
+  // non-blocking export (nsgpu_export_begin / _wait): a device snapshot of u, v, phi, Pr, L_phi phi taken on the solver's stream, brought
+  // home by a copy stream into one of two pinned buffers while the time loop goes on
+  double* exp_dev[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
+  double* exp_host[2] = {nullptr, nullptr};      // 5 * n_host doubles each (n_host = n_local, or the padded stride on general domains)
+  std::vector<double> exp_compact[2];            // general domains: compacted copies handed to the caller
+  cudaStream_t s_exp = nullptr;
+  cudaEvent_t exp_snap = nullptr, exp_home[2] = {nullptr, nullptr};
+  cudaEvent_t exp_t0[2] = {nullptr, nullptr}, exp_t1[2] = {nullptr, nullptr};   // around the snapshot kernel (nsgpu_export_last_ms)
+  float exp_last_ms = 0.0f;
+  int64_t exp_tag[2] = {0, 0};
+  int exp_head = 0, exp_pending = 0;             // next slot to fill; snapshots begun and not yet waited for (<= 2)
+  bool graph_fallback = false;                   // graphs were asked for but a solve had to fall back to direct launches
+  int krylov_restarts = 0;                       // BiCGStab restarts from the true residual during the last call
   int64_t launches = 0;
   double fine_sweeps_phi = 0;
   std::vector<void*> owned;

@@ -509,6 +509,29 @@ k_gradphi(LevelGeom g, const double* __restrict__ phi, double* __restrict__ gpx,
   }
 }
 
+// Snapshot for ExportData (FS.cpp:569-615): copies of u, v, phi plus lapPhi = LHS_phi phi (MatMult, FS.cpp:577) and the physical
+// pressure Pr = phi - dt/(2Re) lapPhi (FS.cpp:579-581) in one pass, so the time loop can go on while the copies travel home.
+template <bool RECT>
+__global__ void __launch_bounds__(256)
+k_export_snapshot(LevelGeom g, double half, const double* __restrict__ u, const double* __restrict__ v, const double* __restrict__ phi,
+                  double* __restrict__ su, double* __restrict__ sv, double* __restrict__ sphi, double* __restrict__ spr,
+                  double* __restrict__ slap) {
+  const int j = blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= g.ny) return;
+  for (int i = chunk_lo(g.nx), i_hi = chunk_hi(g.nx); i < i_hi; i++) {
+    const unsigned f = cell_flags<RECT>(g, i, j);
+    if (f == F_OUTSIDE) continue;
+    const size_t id = cidx(g, i, j);
+    const double lap = apply_cell<1>(g, f, i, j, phi + id, 0.0, -1.0);
+    const double pc = phi[id];
+    su[id] = u[id];
+    sv[id] = v[id];
+    sphi[id] = pc;
+    slap[id] = lap;
+    spr[id] = pc - half * lap;
+  }
+}
+
 // ---------------------------------------------------------------------------------------------------------
 // Contiguous vector kernels over the owned columns [HX*ld, (HX+nx)*ld): padding rows and masked cells hold 0
 // in every vector, so plain linear loops are exact.

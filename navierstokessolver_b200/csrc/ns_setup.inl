@@ -110,6 +110,12 @@ static void destroy_ctx(nsgpu_ctx* ctx) {
   for (auto& sg : ctx->sgraph) { if (sg.exec) cudaGraphExecDestroy(sg.exec); if (sg.graph) cudaGraphDestroy(sg.graph); }
   if (ctx->s_in) { cudaStreamDestroy(ctx->s_in); cudaStreamDestroy(ctx->s_out); for (auto& e : ctx->ev_io) if (e) cudaEventDestroy(e); }
   for (auto& e : ctx->ev_chunk) if (e) cudaEventDestroy(e);
+  for (auto& q : ctx->exp_host) if (q) cudaFreeHost(q);
+  if (ctx->s_exp) cudaStreamDestroy(ctx->s_exp);
+  if (ctx->exp_snap) cudaEventDestroy(ctx->exp_snap);
+  for (auto& e : ctx->exp_home) if (e) cudaEventDestroy(e);
+  for (auto& e : ctx->exp_t0) if (e) cudaEventDestroy(e);
+  for (auto& e : ctx->exp_t1) if (e) cudaEventDestroy(e);
   if (ctx->h_scal) cudaFreeHost(ctx->h_scal);
   if (ctx->h_ctl) cudaFreeHost(ctx->h_ctl);
   if (ctx->h_stage) cudaFreeHost(ctx->h_stage);
@@ -177,11 +183,19 @@ static int create_impl(nsgpu_ctx* ctx, const nsgpu_grid* G, const nsgpu_params* 
   if (getenv("NSGPU_TAIL_DBG")) { void* q = nullptr; if (cudaMalloc(&q, 64 * sizeof(long long)) == cudaSuccess) { cudaMemset(q, 0, 64 * sizeof(long long)); ctx->owned.push_back(q); ctx->tail_dbg = (long long*)q; } }
   if (const char* e = getenv("NSGPU_RB_MINNX")) ctx->march_rb_min_nx = atoi(e);
   if (ctx->world > 1 && ctx->world <= MAX_RANKS && ctx->use_p2p && plan.rect && plan.levels[0].gnx % ctx->world == 0) {   // equal slabs: equal arena layouts
+    // Everything a marching pass may write has to lie inside the arena (the pass pushes `xout + neighbour offset`): the 13 state
+    // fields, and on the Krylov routes (solver == 1, outflow / stretched / uncoarsenable grids -- decided below from the same plan)
+    // the 8 BiCGStab vectors plus aug_w, aug_t.  march_pass checks the range again before it enables the push.
+    int rhs_mode_a = 0;
+    if (const char* e = getenv("NSGPU_RHS_CONSISTENT")) rhs_mode_a = atoi(e);
+    const bool need_aug = plan_has_outflow(plan) || (rhs_mode_a >= 0 && !plan_is_uniform(plan));
+    const bool need_kry = ctx->solver == 1 || need_aug || plan.levels.size() == 1;
+    const size_t fine_fields = 13 + (need_kry ? 8 : 0) + (need_aug ? 2 : 0);
     size_t doubles = 0;
     for (size_t l = 0; l < plan.levels.size(); l++) {
       const size_t ld = ((plan.levels[l].ny + 3) / 4) * 4 + 2 * PJ;
       const size_t stride = (size_t)(plan.lnx[l] + 2 * HX + SLACK_COLS) * ld + 32;
-      doubles += (l == 0 ? 13 + (ctx->solver == 1 ? 8 : 0) : 3) * stride;
+      doubles += (l == 0 ? fine_fields : 3) * stride + 64;   // + 256-byte rounding of every allocation
     }
     ctx->arena_bytes = doubles * sizeof(double) + (1 << 20);
     NS_CUDA(cudaMalloc((void**)&ctx->arena, ctx->arena_bytes));

@@ -161,7 +161,10 @@ static int march_pass(nsgpu_ctx* ctx, const Level& L, OpCoef c, int nsw, double*
   const int uj = march_uj(nsw, res);
   // several ranks: push the boundary columns into the neighbours' halos from inside the pass (peer memory over NVLink)
   static const bool nopush = getenv("NSGPU_NOPUSH") != nullptr;   // debugging: arena mapped, halo columns through NCCL
-  const bool push = ctx->world > 1 && ctx->use_p2p && ctx->arena && !L.replicated && (ctx->peerL || ctx->peerR) && !nopush;
+  // (a buffer outside the arena has no image on the neighbour: `xout + offset` would be a wild peer pointer -- NCCL then)
+  auto in_arena = [&](const double* q) { return (const char*)q >= ctx->arena && (const char*)q < ctx->arena + ctx->arena_bytes; };
+  const bool push = ctx->world > 1 && ctx->use_p2p && ctx->arena && !L.replicated && (ctx->peerL || ctx->peerR) && !nopush &&
+                    in_arena(xout) && (!Cr || in_arena(Cr->b));
   const bool push_b = push && Cr && !Cr->replicated;
   MarchKernel kern = nullptr;
 #define NS_MARCH(NSW, PRO, RES, PF) do { if (push) kern = k_march<NSW, PRO, RES, PF, false, true>; else kern = k_march<NSW, PRO, RES, PF, false, false>; } while (0)
@@ -409,7 +412,13 @@ static int norm2_vec(nsgpu_ctx* ctx, const Level& L, const double* a, double* d_
 
 // V-cycle for the host-driven solvers: fused marching passes where every level supports them, generic kernels otherwise.
 static int vcycle_any(nsgpu_ctx* ctx, OpCoef c, double** x, double** xt, const double* b, bool xzero) {
-  if (all_levels_march(ctx, c)) return vcycle_fused(ctx, 0, c, x, xt, b, xzero, nullptr, nullptr);
+  if (all_levels_march(ctx, c)) {
+    // the fused passes recompute halo columns and read b there: a right-hand side written by a vector kernel (owned columns only,
+    // the Krylov recurrences) gets its halo columns first, or the preconditioner would differ from the one-rank one at the slab edges
+    int rc = halo_exchange(ctx, ctx->levels[0], const_cast<double*>(b), HX - 1);
+    if (rc) return rc;
+    return vcycle_fused(ctx, 0, c, x, xt, b, xzero, nullptr, nullptr);
+  }
   if (xzero) {
     cudaError_t e = cudaMemsetAsync(*x, 0, ctx->levels[0].stride * sizeof(double), ctx->stream);
     if (e != cudaSuccess) { ctx->err = cudaGetErrorString(e); return NSGPU_ERR_CUDA; }
@@ -547,61 +556,69 @@ static int solve_bicgstab(nsgpu_ctx* ctx, OpCoef c, double** xp, double** xtp, c
   out->cycles = 0;
   if (bn == 0.0) { cudaMemsetAsync(x, 0, L.stride * sizeof(double), ctx->stream); out->rel = 0; out->converged = true; return 0; }
   if (rn <= rtol * bn) { out->rel = rn / bn; out->converged = true; return 0; }
-  cudaMemcpyAsync(r0, r, L.stride * sizeof(double), cudaMemcpyDeviceToDevice, ctx->stream);
-  cudaMemsetAsync(p, 0, L.stride * sizeof(double), ctx->stream);
-  cudaMemsetAsync(v, 0, L.stride * sizeof(double), ctx->stream);
-  const double init[4] = {h[0], 1.0, 1.0, 1.0};   // rho_new = (r0, r) = (r, r); rho_old = alpha = omega = 1
-  cudaMemcpyAsync(S, init, sizeof init, cudaMemcpyHostToDevice, ctx->stream);
-  cudaStreamSynchronize(ctx->stream);
   double* tmpA = ctx->tmp;   // ping-pong partner for the preconditioner's fine level
-  while (out->cycles < ctx->max_cycles) {
-    k_bicg_p<<<blocks, 256, 0, ctx->stream>>>(n, r + off, p + off, v + off, S);
-    NS_LAUNCH_CHECK();
-    // ph = M^-1 p
-    { double *a = ph, *bq = tmpA; if ((rc = aug ? aug_precond(ctx, L, p, &a, &bq) : vcycle_any(ctx, c, &a, &bq, p, true))) return rc; ph = a; tmpA = bq; }
+  // The recurrence residual can drift from the true one.  After the recurrence says "converged" the true residual is recomputed; if
+  // it misses rtol the iteration restarts from the current x (r0 = r = true residual) -- at most MAX_RESTARTS times; a solve is
+  // reported as converged only when the TRUE residual meets rtol (the stopping rule stated in include/nsgpu.h).
+  constexpr int MAX_RESTARTS = 3;
+  for (int restart = 0;; restart++) {
+    cudaMemcpyAsync(r0, r, L.stride * sizeof(double), cudaMemcpyDeviceToDevice, ctx->stream);
+    cudaMemsetAsync(p, 0, L.stride * sizeof(double), ctx->stream);
+    cudaMemsetAsync(v, 0, L.stride * sizeof(double), ctx->stream);
+    const double init[4] = {rn * rn, 1.0, 1.0, 1.0};   // rho_new = (r0, r) = (r, r); rho_old = alpha = omega = 1
+    cudaMemcpyAsync(S, init, sizeof init, cudaMemcpyHostToDevice, ctx->stream);
+    cudaStreamSynchronize(ctx->stream);
+    while (out->cycles < ctx->max_cycles) {
+      k_bicg_p<<<blocks, 256, 0, ctx->stream>>>(n, r + off, p + off, v + off, S);
+      NS_LAUNCH_CHECK();
+      // ph = M^-1 p
+      { double *a = ph, *bq = tmpA; if ((rc = aug ? aug_precond(ctx, L, p, &a, &bq) : vcycle_any(ctx, c, &a, &bq, p, true))) return rc; ph = a; tmpA = bq; }
+      if (aug) {
+        if ((rc = apply_op(ctx, L, c, ph, v, nullptr, nullptr))) return rc;
+        if ((rc = aug_rank_one(ctx, L, ph, v, 1.0, r0, S + 4))) return rc;
+      } else if ((rc = apply_op(ctx, L, c, ph, v, r0, S + 4))) return rc;
+      k_scalar_div<<<1, 1, 0, ctx->stream>>>(S + 2, S + 0, S + 4);   // alpha = rho / (r0, v)
+      NS_LAUNCH_CHECK();
+      k_bicg_s<<<blocks, 256, 0, ctx->stream>>>(n, r + off, v + off, s + off, S + 2, ctx->red, S + 8);
+      NS_LAUNCH_CHECK();
+      if ((rc = allreduce(ctx, S + 8, 1, ncclSum))) return rc;
+      // sh = M^-1 s
+      { double *a = sh, *bq = tmpA; if ((rc = aug ? aug_precond(ctx, L, s, &a, &bq) : vcycle_any(ctx, c, &a, &bq, s, true))) return rc; sh = a; tmpA = bq; }
+      if (aug) {
+        if ((rc = apply_op(ctx, L, c, sh, t, nullptr, nullptr))) return rc;
+        if ((rc = aug_rank_one(ctx, L, sh, t, 1.0, s, S + 6))) return rc;
+      } else if ((rc = apply_op(ctx, L, c, sh, t, s, S + 6))) return rc;
+      k_scalar_div<<<1, 1, 0, ctx->stream>>>(S + 3, S + 6, S + 7);   // omega = (t,s)/(t,t)
+      NS_LAUNCH_CHECK();
+      k_scalar_copy<<<1, 1, 0, ctx->stream>>>(S + 1, S + 0);         // rho_old = rho_new
+      NS_LAUNCH_CHECK();
+      k_bicg_xr<<<blocks, 256, 0, ctx->stream>>>(n, x + off, ph + off, sh + off, r + off, s + off, t + off, r0 + off, S + 2, S + 3,
+                                                 ctx->red, S + 9);
+      NS_LAUNCH_CHECK();
+      if ((rc = allreduce(ctx, S + 9, 2, ncclSum))) return rc;
+      k_scalar_copy<<<1, 1, 0, ctx->stream>>>(S + 0, S + 10);        // rho_new = (r0, r)
+      NS_LAUNCH_CHECK();
+      out->cycles++;
+      if ((rc = read_scalars(ctx, S + 9, 1, h))) return rc;
+      rn = std::sqrt(h[0]);
+      if (!(rn == rn) || rn <= rtol * bn) break;
+    }
+    // the true residual (into r: it is the restart vector if one is needed)
+    if ((rc = residual_vec(ctx, L, c, x, b, r, S + 9))) return rc;
     if (aug) {
-      if ((rc = apply_op(ctx, L, c, ph, v, nullptr, nullptr))) return rc;
-      if ((rc = aug_rank_one(ctx, L, ph, v, 1.0, r0, S + 4))) return rc;
-    } else if ((rc = apply_op(ctx, L, c, ph, v, r0, S + 4))) return rc;
-    k_scalar_div<<<1, 1, 0, ctx->stream>>>(S + 2, S + 0, S + 4);   // alpha = rho / (r0, v)
-    NS_LAUNCH_CHECK();
-    k_bicg_s<<<blocks, 256, 0, ctx->stream>>>(n, r + off, v + off, s + off, S + 2, ctx->red, S + 8);
-    NS_LAUNCH_CHECK();
-    if ((rc = allreduce(ctx, S + 8, 1, ncclSum))) return rc;
-    // sh = M^-1 s
-    { double *a = sh, *bq = tmpA; if ((rc = aug ? aug_precond(ctx, L, s, &a, &bq) : vcycle_any(ctx, c, &a, &bq, s, true))) return rc; sh = a; tmpA = bq; }
-    if (aug) {
-      if ((rc = apply_op(ctx, L, c, sh, t, nullptr, nullptr))) return rc;
-      if ((rc = aug_rank_one(ctx, L, sh, t, 1.0, s, S + 6))) return rc;
-    } else if ((rc = apply_op(ctx, L, c, sh, t, s, S + 6))) return rc;
-    k_scalar_div<<<1, 1, 0, ctx->stream>>>(S + 3, S + 6, S + 7);   // omega = (t,s)/(t,t)
-    NS_LAUNCH_CHECK();
-    k_scalar_copy<<<1, 1, 0, ctx->stream>>>(S + 1, S + 0);         // rho_old = rho_new
-    NS_LAUNCH_CHECK();
-    k_bicg_xr<<<blocks, 256, 0, ctx->stream>>>(n, x + off, ph + off, sh + off, r + off, s + off, t + off, r0 + off, S + 2, S + 3,
-                                               ctx->red, S + 9);
-    NS_LAUNCH_CHECK();
-    if ((rc = allreduce(ctx, S + 9, 2, ncclSum))) return rc;
-    k_scalar_copy<<<1, 1, 0, ctx->stream>>>(S + 0, S + 10);        // rho_new = (r0, r)
-    NS_LAUNCH_CHECK();
-    out->cycles++;
+      if ((rc = aug_rank_one(ctx, L, x, r, -1.0, nullptr, S + 44))) return rc;
+      k_scalar_copy<<<1, 1, 0, ctx->stream>>>(S + 9, S + 45);
+      NS_LAUNCH_CHECK();
+    }
     if ((rc = read_scalars(ctx, S + 9, 1, h))) return rc;
     rn = std::sqrt(h[0]);
-    if (!(rn == rn) || rn <= rtol * bn) break;
+    if (!(rn == rn) || rn <= rtol * bn || out->cycles >= ctx->max_cycles || restart >= MAX_RESTARTS) break;
+    ctx->krylov_restarts++;
   }
   ctx->kry[6] = ph; ctx->kry[7] = sh; ctx->tmp = tmpA;
-  // the recurrence residual can drift from the true one: report the true residual
-  if (aug) {
-    if ((rc = residual_vec(ctx, L, c, x, b, r, S + 9))) return rc;
-    if ((rc = aug_rank_one(ctx, L, x, r, -1.0, nullptr, S + 44))) return rc;
-    k_scalar_copy<<<1, 1, 0, ctx->stream>>>(S + 9, S + 45);
-    NS_LAUNCH_CHECK();
-    if ((rc = vec_sum(ctx, L, x, S + 46))) return rc;   // mean(x) * n: next step's warm start (phase_phi removes it from phi)
-  } else if ((rc = residual_norm2(ctx, L, c, x, b, S + 9))) return rc;
-  if ((rc = read_scalars(ctx, S + 9, 1, h))) return rc;
-  rn = std::sqrt(h[0]);
+  if (aug && (rc = vec_sum(ctx, L, x, S + 46))) return rc;   // mean(x) * n: next step's warm start (phase_phi removes it from phi)
   out->rel = rn / bn;
-  out->converged = rn <= rtol * bn * 1.0001 || rn <= 10 * rtol * bn;
+  out->converged = rn <= rtol * bn;
   return 0;
 }
 
@@ -764,6 +781,7 @@ static int solve_mg_dev(nsgpu_ctx* ctx, int slot, OpCoef c, double** x, double**
         if (st != cudaStreamCaptureStatusNone) { cudaGraph_t g = nullptr; cudaStreamEndCapture(ctx->stream, &g); }
         cudaGetLastError();
         ctx->use_graph = 0;
+        ctx->graph_fallback = true;   // reported in nsgpu_step_info.flags
       }
     }
     if (ctx->use_graph) {

@@ -29,6 +29,7 @@ FluidSolver::FluidSolver(char* fname, Grid* g) : grid(g) {
 }
 
 FluidSolver::~FluidSolver() {
+  if (writer.joinable()) writer.join();
   if (gpu) nsgpu_destroy(gpu);
 }
 
@@ -159,6 +160,10 @@ bool FluidSolver::LoadCheckpoint(const char* path) {
 void FluidSolver::Solve() {
   int iter = firstIter;
   cout << "Initiating Solver..\n";
+  if (firstIter > 1 && dt * iter > finalTime) {   // restarted from a checkpoint of the last step: nothing left to do
+    cout << "Solution Complete!\n";
+    return;
+  }
   do {
     nsgpu_step_info info;
     int rc = nsgpu_step(gpu, 1, &info);
@@ -173,6 +178,7 @@ void FluidSolver::Solve() {
     if (checkpointIter > 0 && iter % checkpointIter == 0) SaveCheckpoint("checkpoint.nsgpu");
     iter++;
   } while (dt * iter <= finalTime);
+  if (writer.joinable()) writer.join();   // the last export is on disk before "Solution Complete!"
   cout << "Solution Complete!\n";
 }
 
@@ -191,30 +197,46 @@ double FluidSolver::ghostPhi(const double* P, int i, int j, int e) {            
 }
 
 // FlowData_<iter>.csv: one row per cell centre followed by one row per adjacent boundary face (FS.cpp:588-605).
+// The reference computes lapPhi and Pr on the host and writes the file inside the time loop (FS.cpp:561, 569-615).  Here the snapshot
+// (u, v, phi, Pr, lapPhi) is taken by one kernel, travels home on a copy stream and is formatted by a writer thread while the next
+// time steps run (nsgpu_export_begin / nsgpu_export_wait); NSGPU_EXPORT_SYNC=1 writes the file before the loop goes on.
 void FluidSolver::ExportData(int iter) {
-  const size_t n = (size_t)grid->N;
-  vector<double> u(n), v(n), phi(n), pr(n), lap(n);
-  if (nsgpu_get_fields(gpu, u.data(), v.data(), phi.data()) != 0 || nsgpu_pressure(gpu, pr.data(), lap.data()) != 0) {
+  if (writer.joinable()) writer.join();   // one file at a time; its pinned buffer is free again for the snapshot after this one
+  if (nsgpu_export_begin(gpu, iter) != 0) {
+    cout << "GPU export failed: " << nsgpu_last_error(gpu) << "\n";
+    return;
+  }
+  writer = std::thread([this] { writeSnapshot(); });
+  if (env_int("NSGPU_EXPORT_SYNC", 0)) writer.join();
+}
+
+void FluidSolver::writeSnapshot() {
+  const double *u, *v, *phi, *pr, *lap;
+  int64_t iter = 0;
+  if (nsgpu_export_wait(gpu, &u, &v, &phi, &pr, &lap, &iter) != 0) {
     cout << "GPU export failed: " << nsgpu_last_error(gpu) << "\n";
     return;
   }
   char name[255];
-  snprintf(name, sizeof name, "FlowData_%d.csv", iter);
-  ofstream out{name};
+  snprintf(name, sizeof name, "FlowData_%d.csv", (int)iter);
+  vector<char> iobuf(1 << 20);
+  ofstream out;
+  out.rdbuf()->pubsetbuf(iobuf.data(), (std::streamsize)iobuf.size());
+  out.open(name);
   out << "Point_X,Point_Y,Point_Z,U,V,Pr\n";
   const double half = dt / (2 * re);
   for (size_t i = 0; i < grid->cells.size(); i++)
     for (size_t j = 0; j < grid->cells[i].size(); j++) {
       const Cell& c = grid->cells[i][j];
       if (c.id < 0) continue;
-      out << c.x << "," << c.y << "," << 0.0 << "," << u[c.id] << "," << v[c.id] << "," << pr[c.id] << endl;
+      out << c.x << "," << c.y << "," << 0.0 << "," << u[c.id] << "," << v[c.id] << "," << pr[c.id] << "\n";
       for (int k : c.edges) {
         if (k < 0) continue;
         const Edge& e = grid->edges[k];
         out << c.x + e.nx * grid->hx[i] / 2 << "," << c.y + e.ny * grid->hy[j] / 2 << "," << 0.0 << ","
-            << 0.5 * (u[c.id] + ghostVelocity(u.data(), (int)i, (int)j, k, 0)) << ","
-            << 0.5 * (v[c.id] + ghostVelocity(v.data(), (int)i, (int)j, k, 1)) << ","
-            << 0.5 * (phi[c.id] + ghostPhi(phi.data(), (int)i, (int)j, k)) - half * lap[c.id] << endl;
+            << 0.5 * (u[c.id] + ghostVelocity(u, (int)i, (int)j, k, 0)) << ","
+            << 0.5 * (v[c.id] + ghostVelocity(v, (int)i, (int)j, k, 1)) << ","
+            << 0.5 * (phi[c.id] + ghostPhi(phi, (int)i, (int)j, k)) - half * lap[c.id] << "\n";
       }
     }
   out.close();

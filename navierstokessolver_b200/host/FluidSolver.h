@@ -9,6 +9,7 @@
 #include "compat/petsc.h"   // the reference header pulls in petsc.h (FS.h:3); MAIN_Solver.cpp relies on it
 #include "Grid.h"
 #include "nsgpu.h"
+#include <thread>
 
 class FluidSolver {
  private:
@@ -27,6 +28,8 @@ class FluidSolver {
   double ghostVelocity(const double* V, int i, int j, int e, int d);
   double ghostPhi(const double* P, int i, int j, int e);
   void ExportData(int iter);
+  void writeSnapshot();       // formats the oldest pending device snapshot into FlowData_<iter>.csv (runs on `writer`)
+  std::thread writer;         // ExportData does not stall the loop: the CSV of step n is written while steps n+1... run
 
  public:
   bool setup = false;

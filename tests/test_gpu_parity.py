@@ -397,9 +397,6 @@ def test_two_gpus_equal_one_gpu(workdir):
     assert out.returncode == 0, out.stdout[-2000:] + out.stderr[-2000:]
 
 
-@pytest.mark.xfail(strict=False, reason="written after the round's GPU minutes were spent: stretched grids are routed to the Krylov solve on "
-                   "the augmented operator (every kernel of that route has run on a B200 for the outflow domains; the routing itself and this "
-                   "test have not) -- verified on the host emulation, XPASS is the expected outcome; kept last in the file")
 def test_whole_steps_stretched_cavity(workdir):
     """Wall-refined lid-driven cavity (geometric stretching, h_max / h_min = 3.4): LHS_phi x = b is inconsistent at 2.4e-4 there and
     the reference returns A x + c w = b with c = (vol, b) / (vol, w); the GPU solves that bordered system (BiCGStab on the augmented
