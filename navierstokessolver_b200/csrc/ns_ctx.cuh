@@ -11,6 +11,7 @@
 #include "../../include/nsgpu.h"
 #include "ns_kernels.cuh"
 #include "ns_rhs.cuh"
+#include "ns_phys.cuh"
 #include "ns_march.cuh"
 #include "ns_tail.cuh"
 #include "ns_hostgeom.h"
@@ -121,6 +122,7 @@ struct nsgpu_ctx {
   bool bn2_ready[3] = {false, false, false};     // |b|^2 of the next solve of slot k is already in d_scal[30 + k] (written with b)
   double* tail_img[2] = {nullptr, nullptr};      // per operator: the launch-invariant part of the coarse tail's shared memory (k_tail_image)
   long long* tail_dbg = nullptr;                 // NSGPU_TAIL_DBG=1: clock64 stamps of the coarse tail's phases (printed at destroy)
+  int phys_march = 1;                            // ConstructRHS_phi / CorrectVelocities on rectangles through k_div_march / k_correct_march (NSGPU_PHYS_MARCH=0: row kernels)
   int rhs_march = 1;                             // ConstructRHS_V on rectangles through k_rhs_march (NSGPU_RHS_MARCH=0: cell kernel)
   int vel_guess_rhs = 0;                         // initial guess of the u*, v* solves: 0 = u^n, v^n; 1 = the right-hand side (LHS_V = I - dt/(2Re) L is close to I)
   int march_rb_min_nx = 0;                       // levels with fewer columns keep uniform chunks (NSGPU_RB_MINNX)
@@ -133,9 +135,10 @@ struct nsgpu_ctx {
   int tail_start = 0, use_tail = 1;
   double vel_rho = 0.0, vel_omega = 0.0;   // Jacobi radius bound of LHS_V; SOR factor (0: velocity solves use multigrid)
   nsgpu::TailDesc tail[2];
-  // non-blocking export (nsgpu_export_begin / _wait): a device snapshot of u, v, phi, Pr, L_phi phi taken on the solver's stream, brought
-  // home by a copy stream into one of two pinned buffers while the time loop goes on
-  double* exp_dev[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
+  // non-blocking export (nsgpu_export_begin / _wait): Pr and L_phi phi by one kernel on the solver's stream; a copy stream brings u, v, phi
+  // (live arrays: the next step waits for those reads before it overwrites them) and Pr, lapPhi into one of two pinned buffers
+  double* exp_dev[2] = {nullptr, nullptr};       // staging of Pr and lapPhi (u, v, phi are copied from the live arrays, fenced by events)
+  cudaEvent_t exp_phi_read = nullptr, exp_uv_read = nullptr;   // the copy stream has read phi / u, v of the last snapshot
   double* exp_host[2] = {nullptr, nullptr};      // 5 * n_host doubles each (n_host = n_local, or the padded stride on general domains)
   std::vector<double> exp_compact[2];            // general domains: compacted copies handed to the caller
   cudaStream_t s_exp = nullptr;
@@ -144,6 +147,13 @@ struct nsgpu_ctx {
   float exp_last_ms = 0.0f;
   int64_t exp_tag[2] = {0, 0};
   int exp_head = 0, exp_pending = 0;             // next slot to fill; snapshots begun and not yet waited for (<= 2)
+  // MatSetNullSpace semantics (mean(phi) = 0 after the solve, FS.cpp:143) without a pass of its own: the marching solves reduce sum(phi) with
+  // the residual norm of their last pass (SolveCtl::xsum); phi stays as it is in memory (only its differences enter CorrectVelocities) and
+  // the FIRST pass of the next phi solve subtracts the mean while it loads the warm start.  Whoever needs phi's values (downloads, export,
+  // checkpoints, nsgpu_step_host, the host-driven solvers) calls phi_normalize() first.  NSGPU_LAZY_MEAN=0: explicit k_sum + k_sub_mean.
+  int lazy_mean = 1;
+  bool phi_shift = false;                        // phi in memory still contains the mean xsum / n
+  const double* next_pass_shift = nullptr;       // consumed by the next march_pass (set by the head of the phi solve)
   bool graph_fallback = false;                   // graphs were asked for but a solve had to fall back to direct launches
   int krylov_restarts = 0;                       // BiCGStab restarts from the true residual during the last call
   int64_t launches = 0;

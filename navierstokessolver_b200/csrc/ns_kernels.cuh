@@ -23,6 +23,7 @@ constexpr int RED_MAX_BLOCKS = 1 << 16;
 struct Reducer {
   double* partials;   // [NV * RED_MAX_BLOCKS]
   unsigned* counter;  // zero between launches
+  double* tmp;        // 8 doubles: where a reduction lands when its epilogue distributes the values itself
 };
 
 struct OpSum { __device__ static double f(double a, double b) { return a + b; } __device__ static double id() { return 0.0; } };
@@ -102,7 +103,9 @@ struct SolveCtl {
   int total_cycles;  // cumulative over the life of the context (never reset on the device)
   int fails;         // cumulative number of solves that stopped at max_cycles above the tolerance
   unsigned long long handle;   // cudaGraphConditionalHandle of the WHILE node (0: none)
+  double xsum;       // sum of the iterate over all cells after the last cycle (marching solves): phi's mean is removed lazily from it
 };
+static_assert(sizeof(SolveCtl) == 64, "SolveCtl is one 64-byte block");
 
 // ---------------------------------------------------------------------------------------------------------
 // Several ranks (one process per GPU): every rank's arena is mapped into every other rank's address space (CUDA IPC).
@@ -110,7 +113,7 @@ struct SolveCtl {
 // arena to rank r's, so `local_pointer + off[r]` is the same object on rank r.
 constexpr int MAX_RANKS = 8;
 enum : int { HDR_ARR_L = 0, HDR_ARR_R = 1, HDR_TAIL_ARR = 2, HDR_SENT_L = 3, HDR_SENT_R = 4, HDR_TICKET = 5, HDR_TAIL_NEED = 6,
-             HDR_XSEQ = 7, HDR_XSLOTS = 16, HDR_WORDS = 512 };
+             HDR_XSEQ = 7, HDR_XSLOTS = 16 /* 4 buffers x MAX_RANKS x 3 words */, HDR_WORDS = 512 };
 struct PeerTable {
   int world, rank;
   long long off[MAX_RANKS];
@@ -133,27 +136,37 @@ __device__ __forceinline__ void wait_word(const unsigned long long* p, unsigned 
   }
 }
 
-// Sum of one double over all ranks, called by ONE thread per rank; every rank adds the contributions in rank order,
+// Sum of two doubles over all ranks, called by ONE thread per rank; every rank adds the contributions in rank order,
 // so all ranks get the same bits.  Four slot buffers: a rank can be at most one reduction ahead of the slowest one.
-__device__ inline double xreduce_sum(const PeerTable* pt, double mine) {
+// Slot of (buffer, rank): three words {value a, value b, sequence}.
+__device__ inline void xreduce_sum2(const PeerTable* pt, double a, double b, double* ra, double* rb) {
   unsigned long long* hdr = pt->hdr;
   const unsigned long long s = hdr[HDR_XSEQ] + 1;
   hdr[HDR_XSEQ] = s;
   const int buf = (int)(s & 3);
-  unsigned long long* my_slot = hdr + HDR_XSLOTS + 2 * (buf * MAX_RANKS + pt->rank);
-  for (int r = 0; r < pt->world; r++) reinterpret_cast<double*>(my_slot + pt->off[r])[0] = mine;
+  unsigned long long* my_slot = hdr + HDR_XSLOTS + 3 * (buf * MAX_RANKS + pt->rank);
+  for (int r = 0; r < pt->world; r++) {
+    reinterpret_cast<double*>(my_slot + pt->off[r])[0] = a;
+    reinterpret_cast<double*>(my_slot + pt->off[r])[1] = b;
+  }
   __threadfence_system();
   for (int r = 0; r < pt->world; r++) {
-    unsigned long long* q = my_slot + pt->off[r] + 1;
+    unsigned long long* q = my_slot + pt->off[r] + 2;
     asm volatile("st.relaxed.sys.global.u64 [%0], %1;" :: "l"(q), "l"(s) : "memory");   // ordered after the values by the fence
   }
-  double sum = 0.0;
+  double sa = 0.0, sb = 0.0;
   for (int r = 0; r < pt->world; r++) {
-    const unsigned long long* q = hdr + HDR_XSLOTS + 2 * (buf * MAX_RANKS + r);
-    wait_word(q + 1, s, true, pt->err);
-    sum += reinterpret_cast<const volatile double*>(q)[0];
+    const unsigned long long* q = hdr + HDR_XSLOTS + 3 * (buf * MAX_RANKS + r);
+    wait_word(q + 2, s, true, pt->err);
+    sa += reinterpret_cast<const volatile double*>(q)[0];
+    sb += reinterpret_cast<const volatile double*>(q)[1];
   }
-  return sum;
+  *ra = sa; *rb = sb;
+}
+__device__ inline double xreduce_sum(const PeerTable* pt, double mine) {
+  double a, b;
+  xreduce_sum2(pt, mine, 0.0, &a, &b);
+  return a;
 }
 
 // Several ranks: the slabs of a replicated right-hand side are stored by every rank's restriction pass (peer memory);
@@ -174,17 +187,19 @@ struct CtlEpilogue {
   SolveCtl* c;
   const PeerTable* pt;
   double* out_w;
+  bool with_sum = false;   // out[1] = sum of the iterate (marching passes)
   __device__ void operator()(const double* out) const {
-    if (!c && !pt) return;
-    double rn2 = out[0];
-    if (pt) { rn2 = xreduce_sum(pt, rn2); if (out_w) out_w[0] = rn2; }
+    double rn2 = out[0], xs = with_sum ? out[1] : 0.0;
+    if (pt) xreduce_sum2(pt, rn2, xs, &rn2, &xs);
+    if (out_w && (pt || with_sum)) out_w[0] = rn2;   // (otherwise `out` is out_w already)
     if (!c) return;
     c->rn2 = rn2;
+    if (with_sum) c->xsum = xs;
     c->cycles += 1;
     if (c->cycles > 0) c->total_cycles += 1;
     const bool zero = !(c->bn2 > 0.0);
     c->zero_rhs = zero ? 1 : 0;
-    if (zero) c->cycles = 0;   // x = 0 is the answer, whatever ran before
+    if (zero) { c->cycles = 0; c->xsum = 0.0; }   // x = 0 is the answer, whatever ran before
     const bool go = !zero && (rn2 > c->tol2 * c->bn2) && (c->cycles < c->max_cycles) && (rn2 == rn2);
     c->go = go ? 1 : 0;
     if (!go && !zero && !(rn2 <= c->tol2 * c->bn2)) c->fails += 1;
@@ -199,7 +214,10 @@ __global__ void k_ctl_init(SolveCtl* c, double tol2, int max_cycles, unsigned lo
   c->tol2 = tol2; c->max_cycles = max_cycles; c->cycles = cycles0; c->go = 0; c->zero_rhs = 0; c->handle = handle; c->rn2 = 0.0;
 }
 // x <- 0 when the right-hand side was identically zero (KSPSolve returns x = 0 for b = 0)
-__global__ void __launch_bounds__(256) k_zero_if(size_t n, double* __restrict__ x, const SolveCtl* __restrict__ c) {
+// Also publishes the control block to the host: `pub` is page-locked host memory mapped into the device's address space, written by
+// one thread -- no copy-engine transfer, so the readback never queues behind the field copies of nsgpu_step_host / nsgpu_export_begin.
+__global__ void __launch_bounds__(256) k_zero_if(size_t n, double* __restrict__ x, const SolveCtl* __restrict__ c, SolveCtl* pub) {
+  if (pub && blockIdx.x == 0 && threadIdx.x == 0) *pub = *c;
   if (!c->zero_rhs) return;
   for (size_t k = blockIdx.x * (size_t)blockDim.x + threadIdx.x; k < n; k += (size_t)gridDim.x * blockDim.x) x[k] = 0.0;
 }
@@ -509,13 +527,11 @@ k_gradphi(LevelGeom g, const double* __restrict__ phi, double* __restrict__ gpx,
   }
 }
 
-// Snapshot for ExportData (FS.cpp:569-615): copies of u, v, phi plus lapPhi = LHS_phi phi (MatMult, FS.cpp:577) and the physical
-// pressure Pr = phi - dt/(2Re) lapPhi (FS.cpp:579-581) in one pass, so the time loop can go on while the copies travel home.
+// Pressure recovery for ExportData (FS.cpp:577-581): lapPhi = LHS_phi phi (the reference's MatMult) and the physical pressure
+// Pr = phi - dt/(2Re) lapPhi in one pass over phi, into two staging arrays (streaming stores: nothing reads them but the copy engine).
 template <bool RECT>
 __global__ void __launch_bounds__(256)
-k_export_snapshot(LevelGeom g, double half, const double* __restrict__ u, const double* __restrict__ v, const double* __restrict__ phi,
-                  double* __restrict__ su, double* __restrict__ sv, double* __restrict__ sphi, double* __restrict__ spr,
-                  double* __restrict__ slap) {
+k_pressure(LevelGeom g, double half, const double* __restrict__ phi, double* __restrict__ spr, double* __restrict__ slap) {
   const int j = blockIdx.x * blockDim.x + threadIdx.x;
   if (j >= g.ny) return;
   for (int i = chunk_lo(g.nx), i_hi = chunk_hi(g.nx); i < i_hi; i++) {
@@ -523,12 +539,8 @@ k_export_snapshot(LevelGeom g, double half, const double* __restrict__ u, const 
     if (f == F_OUTSIDE) continue;
     const size_t id = cidx(g, i, j);
     const double lap = apply_cell<1>(g, f, i, j, phi + id, 0.0, -1.0);
-    const double pc = phi[id];
-    su[id] = u[id];
-    sv[id] = v[id];
-    sphi[id] = pc;
-    slap[id] = lap;
-    spr[id] = pc - half * lap;
+    __stcs(slap + id, lap);
+    __stcs(spr + id, phi[id] - half * lap);
   }
 }
 
@@ -605,9 +617,16 @@ __global__ void __launch_bounds__(256) k_aug_axpy(size_t n, double* __restrict__
   }
   grid_reduce<2, OpSum>(acc, red, out);
 }
+// n doubles (n <= 32) from device memory to mapped page-locked host memory, in place of a cudaMemcpyAsync: a copy-engine transfer would wait
+// behind every field copy already queued in that direction
+__global__ void k_publish(double* __restrict__ host_mapped, const double* __restrict__ src, int n) {
+  if ((int)threadIdx.x < n) host_mapped[threadIdx.x] = src[threadIdx.x];
+}
+__global__ void k_publish_ctl(SolveCtl* host_mapped, const SolveCtl* src) { *host_mapped = *src; }
 // tiny scalar kernels of the Krylov recurrences: dst = num/den
 __global__ void k_scalar_div(double* dst, const double* num, const double* den) { *dst = *num / *den; }
 __global__ void k_scalar_copy(double* dst, const double* src) { *dst = *src; }
+__global__ void k_scalar_set(double* dst, double v) { *dst = v; }
 // |b - mean|^2 from s = {sum b, sum b^2} over n cells (inv_n = 1 / n; 0: the mean stays in)
 __global__ void k_bn2_from_sums(double* dst, const double* s, double inv_n) { *dst = fmax(s[1] - s[0] * s[0] * inv_n, 0.0); }
 

@@ -115,6 +115,8 @@ struct MarchXfer {
   unsigned incL, incR;                       // CTAs of this launch that signal leftwards / rightwards (the same on every rank)
   int rb;                                    // > 0: the first two chunks are the short boundary chunks [0, rb) and [nx - rb, nx)
   int gather;                                // RES == 1 onto a replicated coarse level: store the slab on every rank
+  const double* shift;                       // != nullptr: xin - *shift * shift_scale is what the pass smooths (phi's lazily removed mean)
+  double shift_scale;
 };
 
 // Per-thread state of the march: one ring of columns (PF prefetched ones ahead of the K being worked on) and
@@ -137,7 +139,8 @@ struct Marcher {
   bool useful, jstore2, jstore1, pushL, pushR;
   MarchXfer xf;
   double2 racc;
-  double acc;
+  double acc, accx;                                 // RES == 2: |r|^2 and the sum of the iterate
+  double xshift;                                    // subtracted from every loaded x (0 unless the pass removes phi's mean)
 
   // Unconditional loads (no branch, so they can be scheduled early).  Lanes past the column end read the zero
   // padding (their row offset is clamped); columns past the chunk exist (SLACK_COLS extra columns are allocated
@@ -151,7 +154,7 @@ struct Marcher {
       if (px) asm volatile("prefetch.global.L2 [%0];" :: "l"(px + pfo));
       asm volatile("prefetch.global.L2 [%0];" :: "l"(pb + pfo));
     }
-    if (px) { vx = *reinterpret_cast<const double2*>(px); px += ld; }
+    if (px) { vx = *reinterpret_cast<const double2*>(px); px += ld; vx.x -= xshift; vx.y -= xshift; }
     vb = *reinterpret_cast<const double2*>(pb);
     pb += ld;
     if (PROLONG) {
@@ -178,6 +181,7 @@ struct Marcher {
     if ((unsigned)(rs - ib) < (unsigned)(ie - ib)) {
       if (jstore2) *reinterpret_cast<double2*>(po) = X[PF + L];
       else if (jstore1) *po = X[PF + L].x;
+      if (RES == 2) accx += (jstore2 || jstore1 ? X[PF + L].x : 0.0) + (jstore2 ? X[PF + L].y : 0.0);
       if (PUSH && pushL && rs < xf.pushw) {                    // first columns of the slab -> left neighbour's right halo
         if (jstore2) *reinterpret_cast<double2*>(po + xf.dL) = X[PF + L];
         else if (jstore1) po[xf.dL] = X[PF + L].x;
@@ -311,7 +315,8 @@ k_march(LevelGeom g, const double* __restrict__ mcx, const double* __restrict__ 
   m.pxc = nullptr;
   if (PROLONG) m.pxc = xf.xc + (size_t)((xf.pcy == 2 ? ((jl + 2 * PJ) >> 1) - PJ : jl) + PJ);
   m.racc = make_double2(0.0, 0.0);
-  m.acc = 0.0;
+  m.acc = 0.0; m.accx = 0.0;
+  m.xshift = xf.shift ? *xf.shift * xf.shift_scale : 0.0;
 #pragma unroll
   for (int q = 0; q < M::RL; q++) { m.X[q] = make_double2(0.0, 0.0); m.Bq[q] = make_double2(0.0, 0.0); }
 #pragma unroll
@@ -346,8 +351,8 @@ k_march(LevelGeom g, const double* __restrict__ mcx, const double* __restrict__ 
     }
   }
   if (RES == 2) {
-    double acc[1] = {m.acc};
-    grid_reduce<1, OpSum>(acc, xf.red, xf.out, CtlEpilogue{xf.ctl, xf.pt, xf.out});
+    double acc[2] = {m.acc, m.accx};
+    grid_reduce<2, OpSum>(acc, xf.red, xf.red.tmp, CtlEpilogue{xf.ctl, xf.pt, xf.out, true});
   }
 }
 

@@ -113,6 +113,8 @@ static void destroy_ctx(nsgpu_ctx* ctx) {
   for (auto& q : ctx->exp_host) if (q) cudaFreeHost(q);
   if (ctx->s_exp) cudaStreamDestroy(ctx->s_exp);
   if (ctx->exp_snap) cudaEventDestroy(ctx->exp_snap);
+  if (ctx->exp_phi_read) cudaEventDestroy(ctx->exp_phi_read);
+  if (ctx->exp_uv_read) cudaEventDestroy(ctx->exp_uv_read);
   for (auto& e : ctx->exp_home) if (e) cudaEventDestroy(e);
   for (auto& e : ctx->exp_t0) if (e) cudaEventDestroy(e);
   for (auto& e : ctx->exp_t1) if (e) cudaEventDestroy(e);
@@ -177,6 +179,8 @@ static int create_impl(nsgpu_ctx* ctx, const nsgpu_grid* G, const nsgpu_params* 
   if (const char* e = getenv("NSGPU_TRACE")) ctx->trace = atoi(e);
   if (const char* e = getenv("NSGPU_RB")) ctx->march_rb = atoi(e);
   if (const char* e = getenv("NSGPU_RHS_MARCH")) ctx->rhs_march = atoi(e);
+  if (const char* e = getenv("NSGPU_PHYS_MARCH")) ctx->phys_march = atoi(e);
+  if (const char* e = getenv("NSGPU_LAZY_MEAN")) ctx->lazy_mean = atoi(e);
   if (const char* e = getenv("NSGPU_FUSE_BN2")) ctx->fuse_bn2 = atoi(e);
   if (const char* e = getenv("NSGPU_VEL_GUESS")) ctx->vel_guess_rhs = atoi(e);
   if (const char* e = getenv("NSGPU_IO_CHUNKS")) ctx->io_chunks = std::max(1, atoi(e));
@@ -361,6 +365,7 @@ static int create_impl(nsgpu_ctx* ctx, const nsgpu_grid* G, const nsgpu_params* 
   { const EdgeDev* p; int rc = dev_upload(ctx, ctx->owned, plan.edges, &p); if (rc) return rc; ctx->d_edges = const_cast<EdgeDev*>(p); }
   { int rc = dev_zeros(ctx, ctx->owned, (size_t)4 * RED_MAX_BLOCKS, &ctx->red.partials); if (rc) return rc; }
   { double* c; int rc = dev_zeros(ctx, ctx->owned, 2, &c); if (rc) return rc; ctx->red.counter = (unsigned*)c; }
+  { int rc = dev_zeros(ctx, ctx->owned, 8, &ctx->red.tmp); if (rc) return rc; }
   { int rc = dev_zeros(ctx, ctx->owned, 64, &ctx->d_scal); if (rc) return rc; }
   ctx->d_errflag = (int*)(ctx->d_scal + 48);
   NS_CUDA(cudaMallocHost((void**)&ctx->h_scal, 64 * sizeof(double)));

@@ -158,6 +158,8 @@ static int march_pass(nsgpu_ctx* ctx, const Level& L, OpCoef c, int nsw, double*
   if (Cr) { xf.bc = Cr->b + rep_off_r; xf.ldbc = Cr->g.ld; xf.rcx = L.cx; xf.rcy = L.cy; xf.rscale = 1.0 / (double)(L.cx * L.cy); }
   if (res == 2) { xf.red = ctx->red; xf.out = norm_out; xf.ctl = ctl; }
   xf.omega = omega;
+  if (ctx->next_pass_shift && xin) { xf.shift = ctx->next_pass_shift; xf.shift_scale = 1.0 / (double)ctx->n_cells_global; }
+  ctx->next_pass_shift = nullptr;
   const int uj = march_uj(nsw, res);
   // several ranks: push the boundary columns into the neighbours' halos from inside the pass (peer memory over NVLink)
   static const bool nopush = getenv("NSGPU_NOPUSH") != nullptr;   // debugging: arena mapped, halo columns through NCCL
@@ -393,8 +395,11 @@ static int vcycle(nsgpu_ctx* ctx, int l, OpCoef c, double** x, double** xt, cons
   return smooth(ctx, L, c, x, xt, b, ctx->nu_post);
 }
 
+// n <= 32 device scalars -> host.  Written into mapped page-locked memory by a one-warp kernel (k_publish) rather than copied: the copy
+// engines may be busy with hundreds of megabytes of field copies (nsgpu_step_host, nsgpu_export_begin) that a small copy would queue behind.
 static int read_scalars(nsgpu_ctx* ctx, const double* d, int n, double* h) {
-  cudaError_t e = cudaMemcpyAsync(ctx->h_scal, d, n * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream);
+  k_publish<<<1, 32, 0, ctx->stream>>>(ctx->h_scal, d, n);
+  cudaError_t e = cudaGetLastError();
   if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
   if (e != cudaSuccess) { ctx->err = std::string("scalar readback: ") + cudaGetErrorString(e); return NSGPU_ERR_CUDA; }
   for (int k = 0; k < n; k++) h[k] = ctx->h_scal[k];
@@ -658,6 +663,7 @@ static int solve_head(nsgpu_ctx* ctx, int slot, OpCoef c, double* x, double* xt,
   if (!bn2_pre && (rc = norm2_vec(ctx, L, b, &ctl->bn2))) return rc;
   if (iterate) {
     double *xa = x, *xb = xt;
+    if (slot == 2 && ctx->lazy_mean) ctx->next_pass_shift = &ctl->xsum;   // the first pass removes the mean the last solve left in phi
     if ((rc = solve_body(ctx, slot, c, &xa, &xb, b, x0 && x0 != x ? x0 : nullptr))) return rc;
     if (xa != x) { ctx->err = "internal: an iteration does not return to its buffer"; return NSGPU_ERR_ARG; }
     return 0;
@@ -672,10 +678,8 @@ static int solve_head(nsgpu_ctx* ctx, int slot, OpCoef c, double* x, double* xt,
 static int solve_tail(nsgpu_ctx* ctx, int slot, double* x) {
   const Level& L = ctx->levels[0];
   ctx->halo_w.erase(x);
-  k_zero_if<<<148 * 4, 256, 0, ctx->stream>>>(L.stride, x, ctx->d_ctl + slot);
+  k_zero_if<<<148 * 4, 256, 0, ctx->stream>>>(L.stride, x, ctx->d_ctl + slot, ctx->h_ctl + slot);   // h_ctl: mapped host memory
   NS_LAUNCH_CHECK();
-  cudaError_t e = cudaMemcpyAsync(ctx->h_ctl + slot, ctx->d_ctl + slot, sizeof(SolveCtl), cudaMemcpyDeviceToHost, ctx->stream);
-  if (e != cudaSuccess) { ctx->err = std::string("ctl readback: ") + cudaGetErrorString(e); return NSGPU_ERR_CUDA; }
   return 0;
 }
 
@@ -794,7 +798,8 @@ static int solve_mg_dev(nsgpu_ctx* ctx, int slot, OpCoef c, double** x, double**
   }
   if ((rc = solve_head(ctx, slot, c, *x, *xt, x0, b, rtol, 0ull, bn2_pre))) return rc;
   for (;;) {
-    cudaError_t e = cudaMemcpyAsync(ctx->h_ctl + slot, ctx->d_ctl + slot, sizeof(SolveCtl), cudaMemcpyDeviceToHost, ctx->stream);
+    k_publish_ctl<<<1, 1, 0, ctx->stream>>>(ctx->h_ctl + slot, ctx->d_ctl + slot);
+    cudaError_t e = cudaGetLastError();
     if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
     if (e != cudaSuccess) { ctx->err = std::string("ctl readback: ") + cudaGetErrorString(e); return NSGPU_ERR_CUDA; }
     if (!ctx->h_ctl[slot].go) break;
@@ -825,12 +830,31 @@ static inline bool dev_solve_ok(const nsgpu_ctx* ctx, OpCoef c) {
   return all_levels_march(ctx, c);
 }
 
+// phi <- phi - mean(phi) now, if the marching solve left it pending (ctx->phi_shift); see nsgpu_ctx::lazy_mean
+static int phi_normalize(nsgpu_ctx* ctx) {
+  if (!ctx->phi_shift) return 0;
+  const Level& L = ctx->levels[0];
+  const dim3 grid = grid_cols(L.g, 256);
+  const double inv_n = 1.0 / (double)ctx->n_cells_global;
+  double* xsum = &ctx->d_ctl[2].xsum;
+#define CALL(RECT) k_sub_mean<RECT><<<grid, 256, 0, ctx->stream>>>(L.g, ctx->phi, xsum, inv_n)
+  NS_DISPATCH_RECT(ctx->rect, CALL);
+#undef CALL
+  NS_LAUNCH_CHECK();
+  k_scalar_set<<<1, 1, 0, ctx->stream>>>(xsum, 0.0);
+  NS_LAUNCH_CHECK();
+  ctx->phi_shift = false;
+  ctx->halo_w.clear();
+  return 0;
+}
+
 // slot: 0 = u, 1 = v, 2 = phi.  On the device-controlled path the result is pending until finish_results().
 static int solve(nsgpu_ctx* ctx, int slot, OpCoef c, double** x, const double* b, double rtol, SolveResult* out, double* x0 = nullptr) {
   const bool krylov = ctx->solver == 1 || (ctx->krylov_phi && c.op == 1);
   if (!krylov && dev_solve_ok(ctx, c)) { out->pending = true; return solve_mg_dev(ctx, slot, c, x, &ctx->tmp, x0, b, rtol); }
   out->pending = false;
   ctx->bn2_ready[slot] = false;
+  if (slot == 2) { int rcn = phi_normalize(ctx); if (rcn) return rcn; }
   if (x0 && x0 != *x) {   // host-driven solvers iterate in place
     cudaError_t e = cudaMemcpyAsync(*x, x0, ctx->levels[0].stride * sizeof(double), cudaMemcpyDeviceToDevice, ctx->stream);
     if (e != cudaSuccess) { ctx->err = cudaGetErrorString(e); return NSGPU_ERR_CUDA; }
@@ -847,6 +871,43 @@ static void finish_results(nsgpu_ctx* ctx, SolveResult* ru, SolveResult* rv, Sol
 
 // ---------------------------------------------------------------------------------------------------------
 // Phases of one time step
+
+// A pending nsgpu_export_begin reads phi, u, v from the live arrays on its copy stream: whoever overwrites them waits for that read
+// (an event wait on the solver's stream, no host synchronisation; a no-op when no export was ever begun).
+static inline void export_fence(nsgpu_ctx* ctx, bool phi, bool uv) {
+  if (!ctx->s_exp) return;
+  if (phi) cudaStreamWaitEvent(ctx->stream, ctx->exp_phi_read, 0);
+  if (uv) cudaStreamWaitEvent(ctx->stream, ctx->exp_uv_read, 0);
+}
+
+// Launch shape of the projection kernels of ns_phys.cuh: gx CTAs of 4 warps cover the rows, the columns are cut into chunks of *ri
+// so that the CTAs fill whole waves (same estimate as march_chunk: waves x (columns per chunk + start-up)).
+static dim3 phys_grid(const void* kern, const Level& L, int* ri, size_t* smem) {
+  static std::vector<std::pair<const void*, int>> cache;
+  int wave = 0;
+  for (auto& e : cache) if (e.first == kern) wave = e.second;
+  if (!wave) {
+    int per_sm = 0, dev = 0, sms = 148;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, PH_THREADS, 3 * 256 * sizeof(double)) != cudaSuccess || per_sm < 1) per_sm = 4;
+    wave = per_sm * sms;
+    cache.push_back({kern, wave});
+  }
+  const int gx = ((L.g.ny + PH_UJ - 1) / PH_UJ + PH_WARPS - 1) / PH_WARPS;
+  long long best = -1;
+  int r_best = L.g.nx;
+  for (int r = 8; r <= std::min(L.g.nx, 1024); r += 4) {
+    const long long ctas = (long long)gx * ((L.g.nx + r - 1) / r);
+    const long long cost = ((ctas + wave - 1) / wave) * (r + 2 * PH_PF);
+    if (best < 0 || cost < best) { best = cost; r_best = r; }
+  }
+  if (L.g.nx < 8) r_best = L.g.nx;
+  while ((long long)gx * ((L.g.nx + r_best - 1) / r_best) > RED_MAX_BLOCKS) r_best *= 2;
+  *ri = r_best;
+  *smem = (size_t)3 * r_best * sizeof(double);
+  return dim3(gx, (L.g.nx + r_best - 1) / r_best);
+}
 
 static int phase_rhs(nsgpu_ctx* ctx) {   // ConstructRHS_V, FS.cpp:546
   ctx->halo_w.clear();   // every field may have been rewritten by a non-marching kernel since
@@ -914,9 +975,15 @@ static int phase_div(nsgpu_ctx* ctx, bool remove_mean) {   // FS.cpp:549-550
   if ((rc = halo_exchange(ctx, L, ctx->vstar, 1))) return rc;
   const StepConst sc{ctx->dt, ctx->re};
   const dim3 grid = grid_cols(L.g, 256);
+  if (ctx->rect && ctx->phys_march) {
+    int ri; size_t sh;
+    const dim3 pg = phys_grid((const void*)k_div_march, L, &ri, &sh);
+    k_div_march<<<pg, PH_THREADS, sh, ctx->stream>>>(L.g, ctx->d_edges, sc, ctx->ustar, ctx->vstar, ctx->rhs_phi, ri, ctx->red, ctx->d_scal + 28);
+  } else {
 #define CALL(RECT) k_div_rhs<RECT><<<grid, 256, 0, ctx->stream>>>(L.g, ctx->d_edges, sc, ctx->ustar, ctx->vstar, ctx->rhs_phi, ctx->red, ctx->d_scal + 28)
-  NS_DISPATCH_RECT(ctx->rect, CALL);
+    NS_DISPATCH_RECT(ctx->rect, CALL);
 #undef CALL
+  }
   NS_LAUNCH_CHECK();
   if ((rc = allreduce(ctx, ctx->d_scal + 28, 2, ncclSum))) return rc;
   k_bn2_from_sums<<<1, 1, 0, ctx->stream>>>(ctx->d_scal + 32, ctx->d_scal + 28, remove_mean ? 1.0 / (double)ctx->n_cells_global : 0.0);
@@ -933,6 +1000,7 @@ static int phase_div(nsgpu_ctx* ctx, bool remove_mean) {   // FS.cpp:549-550
 }
 
 static int phase_phi(nsgpu_ctx* ctx, SolveResult* rp) {   // FS.cpp:551, warm start from phi^n (FS.cpp:54)
+  export_fence(ctx, true, false);
   ctx->halo_w.clear();   // every field may have been rewritten by a non-marching kernel since
   const Level& L = ctx->levels[0];
   int rc;
@@ -960,7 +1028,9 @@ static int phase_phi(nsgpu_ctx* ctx, SolveResult* rp) {   // FS.cpp:551, warm st
   if ((rc = solve(ctx, 2, coef_phi(), &ctx->phi, b, ctx->rtol_phi, rp))) return rc;
   if (!rp->pending) ctx->fine_sweeps_phi += (double)rp->cycles * (ctx->nu_pre + ctx->nu_post) * (ctx->solver == 1 ? 2 : 1);
   // pin mean(phi) = 0: the reference projects the constant out of every Krylov update (MatSetNullSpace, FS.cpp:143)
-  {
+  const bool lazy = rp->pending && ctx->lazy_mean && (ctx->nu_pre >= 1 || ctx->levels.size() == 1);   // the solve head iterates (solve_head)
+  if (lazy) ctx->phi_shift = true;   // sum(phi) is in the solve's control block; removed by the next solve's first pass, or by phi_normalize()
+  else {
     const size_t n = (size_t)L.g.nx * L.g.ld;
     const int blocks = (int)std::min<size_t>((n + 255) / 256, 148 * 8);
     ctx->halo_w.clear();
@@ -978,15 +1048,22 @@ static int phase_phi(nsgpu_ctx* ctx, SolveResult* rp) {   // FS.cpp:551, warm st
 }
 
 static int phase_correct(nsgpu_ctx* ctx, double mm[4]) {   // FS.cpp:552-557
+  export_fence(ctx, false, true);
   ctx->halo_w.clear();   // every field may have been rewritten by a non-marching kernel since
   const Level& L = ctx->levels[0];
   int rc;
   if ((rc = halo_exchange(ctx, L, ctx->phi, 2))) return rc;
   const StepConst sc{ctx->dt, ctx->re};
-  const dim3 grid = grid_cols(L.g, 256);
+  if (ctx->rect && ctx->phys_march) {
+    int ri; size_t sh;
+    const dim3 pg = phys_grid((const void*)k_correct_march, L, &ri, &sh);
+    k_correct_march<<<pg, PH_THREADS, sh, ctx->stream>>>(L.g, sc, ctx->phi, ctx->ustar, ctx->vstar, ctx->u, ctx->v, ctx->gpx, ctx->gpy, ri, ctx->red, ctx->d_scal + 20);
+  } else {
+    const dim3 grid = grid_cols(L.g, 256);
 #define CALL(RECT) k_correct<RECT><<<grid, 256, 0, ctx->stream>>>(L.g, sc, ctx->phi, ctx->ustar, ctx->vstar, ctx->u, ctx->v, ctx->gpx, ctx->gpy, ctx->red, ctx->d_scal + 20)
-  NS_DISPATCH_RECT(ctx->rect, CALL);
+    NS_DISPATCH_RECT(ctx->rect, CALL);
 #undef CALL
+  }
   NS_LAUNCH_CHECK();
   if ((rc = allreduce(ctx, ctx->d_scal + 20, 4, ncclMax))) return rc;
   if (mm) {
