@@ -3,6 +3,7 @@
 //   PROLONG   the coarse-grid correction is added while the column is loaded      (x <- x + P xc)
 //   RES == 1  the residual of the smoothed iterate is restricted to the coarse rhs (bc <- R (b - A x))
 //   RES == 2  the squared residual norm of the smoothed iterate is reduced         (out <- |b - A x|^2)
+//   RES == 3  as 2, plus the sum of the smoothed iterate (phi solves: the mean is removed lazily, ns_ctx.cuh)
 // so that one V(2,2) cycle touches every level exactly twice.  Rectangle fast path (1-D folded coefficients).
 //
 // Replaces the inner iterations of KSPSolve(phiSolver) / KSPSolve(uSolver) (reference FS.cpp:547-551) on the
@@ -154,15 +155,25 @@ struct Marcher {
       if (px) asm volatile("prefetch.global.L2 [%0];" :: "l"(px + pfo));
       asm volatile("prefetch.global.L2 [%0];" :: "l"(pb + pfo));
     }
-    if (px) { vx = *reinterpret_cast<const double2*>(px); px += ld; vx.x -= xshift; vx.y -= xshift; }
+    if (px) { vx = *reinterpret_cast<const double2*>(px); px += ld; }
     vb = *reinterpret_cast<const double2*>(pb);
     pb += ld;
     if (PROLONG) {
+      // (measured: adding the correction when the column enters the working set instead, with the coarse value loaded one step
+      // ahead, is slower -- 126 us against 96 us at 4096^2: the fine level's 400 MB per pass push the coarse array out of L2 and one
+      // step does not cover a DRAM access; a coarse register ring as deep as the fine one costs the third resident CTA)
       const int ic = (xf.pcx == 2 ? ((n + 2 * HX) >> 1) : n + HX);
       const double* pc = pxc + (size_t)ic * xf.ldc;
       if (xf.pcy == 2) { const double c0 = *pc; vx.x += c0; vx.y += c0; }
       else { const double2 c2 = *reinterpret_cast<const double2*>(pc); vx.x += c2.x; vx.y += c2.y; }
     }
+  }
+
+  // column n (loaded PF steps ago, now X[PF]) enters the working set.  phi's lazily removed mean is subtracted HERE, not behind the load:
+  // an instruction that consumes a load's result right away waits for it and the register prefetch is gone (every pass 20-50 % slower).
+  // Only the restricting passes carry the code: the first pass of a phi solve is one (solve_head), everywhere else the shift is 0.
+  __device__ __forceinline__ void arrive(int n) {
+    if (RES == 1 && px) { X[PF].x -= xshift; X[PF].y -= xshift; }
   }
 
   // column n enters the pipeline; TA: this step's half-sweeps all update the .x cell (they do: the colour of
@@ -172,6 +183,7 @@ struct Marcher {
 #pragma unroll
     for (int q = RL - 1; q > 0; q--) { X[q] = X[q - 1]; Bq[q] = Bq[q - 1]; }
     load_col(n + PF, X[0], Bq[0]);
+    arrive(n);
 #pragma unroll
     for (int s = 0; s < L; s++) {
       const double* c3 = cc - 3 * (1 + s);
@@ -181,7 +193,7 @@ struct Marcher {
     if ((unsigned)(rs - ib) < (unsigned)(ie - ib)) {
       if (jstore2) *reinterpret_cast<double2*>(po) = X[PF + L];
       else if (jstore1) *po = X[PF + L].x;
-      if (RES == 2) accx += (jstore2 || jstore1 ? X[PF + L].x : 0.0) + (jstore2 ? X[PF + L].y : 0.0);
+      if (RES == 3) accx += (jstore2 || jstore1 ? X[PF + L].x : 0.0) + (jstore2 ? X[PF + L].y : 0.0);
       if (PUSH && pushL && rs < xf.pushw) {                    // first columns of the slab -> left neighbour's right halo
         if (jstore2) *reinterpret_cast<double2*>(po + xf.dL) = X[PF + L];
         else if (jstore1) po[xf.dL] = X[PF + L].x;
@@ -197,7 +209,7 @@ struct Marcher {
       const double* c3 = cc - 3 * (L + 1);
       const double2 res = pair_residual(X[PF + L + 1], X[PF + L + 2], X[PF + L], Bq[PF + L + 1], c3[0], c3[1], c3[2], k);
       if ((unsigned)(rr - ib) < (unsigned)(ie - ib)) {
-        if (RES == 2) {
+        if (RES >= 2) {
           acc += (jstore2 || jstore1 ? res.x * res.x : 0.0) + (jstore2 ? res.y * res.y : 0.0);   // branch-free
         } else {
           // chunks start on even columns, so a coarse pair never straddles two chunks
@@ -351,6 +363,10 @@ k_march(LevelGeom g, const double* __restrict__ mcx, const double* __restrict__ 
     }
   }
   if (RES == 2) {
+    double acc[1] = {m.acc};
+    grid_reduce<1, OpSum>(acc, xf.red, xf.out, CtlEpilogue{xf.ctl, xf.pt, xf.out});
+  }
+  if (RES == 3) {
     double acc[2] = {m.acc, m.accx};
     grid_reduce<2, OpSum>(acc, xf.red, xf.red.tmp, CtlEpilogue{xf.ctl, xf.pt, xf.out, true});
   }

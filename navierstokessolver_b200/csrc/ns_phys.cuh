@@ -4,26 +4,37 @@
 // The one-thread-per-row versions (k_div_rhs, k_correct in ns_kernels.cuh; kept for general domains) have one column in flight per
 // thread and run at 55-61 % of the HBM peak, latency-bound.  Here, as in ns_march.cuh, a lane owns the pair of rows (j0, j0 + 1) as one
 // double2 -- every load and store is 16 bytes per lane, 512 contiguous bytes per warp -- and marches over the columns of its chunk with
-// the next PF columns of every input already on their way (register prefetch, statically indexed: the column loop is unrolled by PF);
+// the next PH_D columns of every input already on their way: one lane issues a 512-byte bulk copy (cp.async.bulk, TMA engine) per field
+// column into the warp's own ring of column slots in shared memory, completion is signalled through one mbarrier per slot (ns_tma.cuh),
+// so the prefetch costs no registers (the register-ring version needed 130 and, held to 96, spilled the prefetched columns -- which
+// waits for the loads and is no prefetch at all: 1.3-1.9 us per column step, long-scoreboard bound);
 // x neighbours come from a three-column register ring, y neighbours from the pair partner or the adjacent lane (one halo pair per side
 // of the warp: 60 useful rows of 64).  Interior cells take a straight-line path whose expressions are div_cell's / grad_cell's
-// (ns_cell.cuh); cells that touch an edge go through div_cell / grad_cell themselves (first / last column: the whole warp, first / last
-// row: one lane), so every boundary-condition type keeps its one implementation.
+// (ns_cell.cuh); cells that touch an edge go through div_cell / grad_cell themselves after the march (for_edge_cells), so every
+// boundary-condition type keeps its one implementation.
 #pragma once
 #include <cuda_runtime.h>
 #include "ns_cell.cuh"
 #include "ns_kernels.cuh"
+#include "ns_tma.cuh"
 
 namespace nsgpu {
 
 constexpr int PH_WARPS = 4;
 constexpr int PH_THREADS = 32 * PH_WARPS;
 constexpr int PH_UJ = 60;      // useful rows per warp
-constexpr int PH_PF = 4;       // columns in flight per input array (PF <= SLACK_COLS)
+#ifndef NS_PH_D
+#define NS_PH_D 6
+#endif
+constexpr int PH_D = NS_PH_D;  // ring depth: columns in flight per field and warp (PH_D + 1 <= SLACK_COLS)
 #ifndef NS_PH_MIN_CTAS
 #define NS_PH_MIN_CTAS 5
 #endif
 constexpr int PH_MIN_CTAS = NS_PH_MIN_CTAS;   // resident CTAs per SM the register allocation is held to (5 x 4 warps)
+// dynamic shared memory of a CTA: x coefficients of the chunk (3 doubles per column) | PH_WARPS rings of PH_D slots x A fields x 512 B | barriers
+__host__ __device__ constexpr size_t phys_smem(int ri, int fields) {
+  return (size_t)(((3 * ri * 8 + 127) / 128) * 128) + (size_t)PH_WARPS * PH_D * fields * 512 + (size_t)PH_WARPS * PH_D * 8;
+}
 
 struct PhysLane {
   int j0, ld;
@@ -69,62 +80,142 @@ __device__ __forceinline__ void st_pair(double* p, const double2& v, bool st2, b
   else if (st1) *p = v.x;
 }
 
+// Cells that touch an edge are not computed in the marching loop at all: inlined there, the general cell functions (ghost closures of
+// every boundary type) were copied into every unrolled step and the loop body outgrew the instruction caches (32 KB: slower than the
+// row kernels).  The loop stores interior cells only; afterwards every warp visits the edge cells of its (strip, chunk) -- first / last
+// row: one lane per column, first / last column: one lane per row -- through div_cell / grad_cell, once.
+struct EdgeWalk {
+  int jlo, jhi;   // useful rows of this warp: [jlo, jhi)
+};
+__device__ __forceinline__ EdgeWalk edge_walk(const LevelGeom& g, int wj) {
+  EdgeWalk w;
+  w.jlo = wj * PH_UJ;
+  w.jhi = min(w.jlo + PH_UJ, g.ny);
+  return w;
+}
+// calls f(i, j) for every edge cell of the chunk [ib, ie) x rows [jlo, jhi), each exactly once, lanes in parallel
+template <class F>
+__device__ __forceinline__ void for_edge_cells(const LevelGeom& g, int ib, int ie, const EdgeWalk& w, int lane, F f) {
+  if (w.jlo >= w.jhi) return;
+#pragma unroll 1
+  for (int side = 0; side < 2; side++) {                         // first / last row
+    const int j = side ? g.ny - 1 : 0;
+    if (side && g.ny == 1) break;
+    if (j < w.jlo || j >= w.jhi) continue;
+#pragma unroll 1
+    for (int i = ib + lane; i < ie; i += 32) f(i, j);
+  }
+#pragma unroll 1
+  for (int side = 0; side < 2; side++) {                         // first / last column of the domain, rows 1 .. ny - 2
+    const int ig = side ? g.gnx - 1 : 0;
+    if (side && g.gnx == 1) break;
+    const int i = ig - g.gi0;
+    if (i < ib || i >= ie) continue;
+#pragma unroll 1
+    for (int j = max(w.jlo, 1) + lane; j < min(w.jhi, g.ny - 1); j += 32) f(i, j);
+  }
+}
+
+// x / d for a divisor that is the same for every cell (dt): q = x * (1/d) corrected by one fused step, q + (x - q d) * (1/d).  With
+// 1/d correctly rounded this is the correctly rounded quotient (Markstein), i.e. the bits of the reference's `/ dt` (FS.cpp:374), in
+// 3 instructions instead of the ~30 of a general double division (two per column step were a third of the kernel's instructions).
+__device__ __forceinline__ double div_invariant(double x, double d, double rd) {
+  const double q = x * rd;
+  return fma(fma(-q, d, x), rd, q);
+}
+
+// stores the interior cells of a pair: both, only a = (i, j0), or only b = (i, j0 + 1)
+__device__ __forceinline__ void st_interior(double* p, const double2& v, bool sa, bool sb) {
+  if (sa && sb) *reinterpret_cast<double2*>(p) = v;
+  else if (sa) p[0] = v.x;
+  else if (sb) p[1] = v.y;
+}
+
 // ---------------------------------------------------------------------------------------------------------
 // b = Div_V(u*, v*) / dt ; out = {sum b, sum b^2}
 __global__ void __launch_bounds__(PH_THREADS, PH_MIN_CTAS)
 k_div_march(LevelGeom g, const EdgeDev* __restrict__ edges, StepConst sc, const double* __restrict__ u, const double* __restrict__ v,
             double* __restrict__ b, int RI, Reducer red, double* __restrict__ out) {
-  extern __shared__ double s_x[];
-  const int lane = threadIdx.x & 31, wj = blockIdx.x * PH_WARPS + (threadIdx.x >> 5);
+  extern __shared__ __align__(128) unsigned char s_raw[];
+  double* s_x = reinterpret_cast<double*>(s_raw);
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5, wj = blockIdx.x * PH_WARPS + wid;
   const int ib = blockIdx.y * RI, ie = min(ib + RI, g.nx);
+  constexpr int A = 2;                                              // fields in a slot: u (column i + 1), v (column i)
+  double2* ring = reinterpret_cast<double2*>(s_raw + ((3 * RI * 8 + 127) / 128) * 128) + (size_t)wid * PH_D * A * 32;
+  uint64_t* bar = reinterpret_cast<uint64_t*>(s_raw + ((3 * RI * 8 + 127) / 128) * 128 + (size_t)PH_WARPS * PH_D * A * 512) + wid * PH_D;
   phys_stage_x(g, ib, ie, s_x);
   const PhysLane L = phys_lane(g, lane, wj);
   const int ld = L.ld;
-  const double rdt = sc.dt;
-  const double* pu = u + (size_t)(ib + HX) * ld + L.row;          // column ib
-  const double* pv = v + (size_t)(ib + HX) * ld + L.row;
-  double* pb = b + (size_t)(ib + HX) * ld + L.row;
-  double2 um = ld2(pu - ld), uc = ld2(pu);
-  double2 Fu[PH_PF], Fv[PH_PF];                                    // Fu[p]: column i + 1 + p of u; Fv[p]: column i + p of v
-#pragma unroll
-  for (int p = 0; p < PH_PF; p++) { Fu[p] = ld2(pu + (size_t)(1 + p) * ld); Fv[p] = ld2(pv + (size_t)p * ld); }
+  const bool active = wj * PH_UJ < g.ny;                            // warps past the last strip only take part in the reduction
+  const bool sa = (L.st2 || L.st1) && L.inA, sb = L.st2 && L.inB;   // interior cells this lane stores
+  const double rdt = 1.0 / sc.dt;
   double acc[2] = {0.0, 0.0};
-  for (int i0 = ib; i0 < ie; i0 += PH_PF) {
+  if (active) {
+    // the warp's 64 rows start at row wj * 60 - 2 (+ PJ padding rows): 512 contiguous bytes of every column
+    const size_t wrow = (size_t)(wj * PH_UJ - 2 + PJ);
+    const double* gu = u + (size_t)(ib + 1 + HX) * ld + wrow;       // column ib + 1 of u, column ib of v: slot of step ib
+    const double* gv = v + (size_t)(ib + HX) * ld + wrow;
+    if (lane == 0) {
 #pragma unroll
-    for (int p = 0; p < PH_PF; p++) {
-      const int i = i0 + p;
-      if (i < ie) {                                                // uniform
-        const double2 up = Fu[p], vc = Fv[p];
-        Fu[p] = ld2(pu + (size_t)(1 + PH_PF) * ld);               // columns i + 1 + PF, i + PF: SLACK_COLS columns exist behind every field
-        Fv[p] = ld2(pv + (size_t)PH_PF * ld);
-        const double vS = __shfl_up_sync(0xffffffffu, vc.y, 1), vN = __shfl_down_sync(0xffffffffu, vc.x, 1);
-        const int ig = g.gi0 + i;
-        const bool xin = ig > 0 && ig < g.gnx - 1;
-        const double* c3 = s_x + 3 * (i - ib);
-        const double rW = c3[0], rE = c3[1], rhx = c3[2];
-        double2 d;
-        {
-          const double VW = um.x * rW + uc.x * (1.0 - rW), VE = up.x * rE + uc.x * (1.0 - rE);
-          const double VS = vS * L.rSa + vc.x * (1.0 - L.rSa), VN = vc.y * L.rNa + vc.x * (1.0 - L.rNa);
-          d.x = ((VE - VW) * rhx + (VN - VS) * L.rhya) / rdt;
+      for (int p = 0; p < PH_D; p++) mbar_init(bar + p, 1);
+      mbar_init_fence();
+#pragma unroll
+      for (int p = 0; p < PH_D; p++)
+        if (ib + p < ie) {
+          mbar_expect_tx(bar + p, A * 512);
+          bulk_g2s(ring + (p * A + 0) * 32, gu + (size_t)p * ld, 512, bar + p);
+          bulk_g2s(ring + (p * A + 1) * 32, gv + (size_t)p * ld, 512, bar + p);
         }
-        {
-          const double VW = um.y * rW + uc.y * (1.0 - rW), VE = up.y * rE + uc.y * (1.0 - rE);
-          const double VS = vc.x * L.rSb + vc.y * (1.0 - L.rSb), VN = vN * L.rNb + vc.y * (1.0 - L.rNb);
-          d.y = ((VE - VW) * rhx + (VN - VS) * L.rhyb) / rdt;
+    }
+    __syncwarp();
+    double* pb = b + (size_t)(ib + HX) * ld + L.row;
+    double2 um = ld2(u + (size_t)(ib - 1 + HX) * ld + L.row), uc = ld2(u + (size_t)(ib + HX) * ld + L.row);
+    uint32_t parity = 0;
+#pragma unroll 1
+    for (int i0 = ib; i0 < ie; i0 += PH_D, parity ^= 1) {
+#pragma unroll
+      for (int p = 0; p < PH_D; p++) {
+        const int i = i0 + p;
+        if (i < ie) {                                                // uniform
+          mbar_wait(bar + p, parity);
+          const double2 up = ring[(p * A + 0) * 32 + lane], vc = ring[(p * A + 1) * 32 + lane];
+          __syncwarp();                                              // every lane has read the slot: refill it with step i + PH_D
+          if (lane == 0 && i + PH_D < ie) {
+            mbar_expect_tx(bar + p, A * 512);
+            bulk_g2s(ring + (p * A + 0) * 32, gu + (size_t)(i - ib + PH_D) * ld, 512, bar + p);
+            bulk_g2s(ring + (p * A + 1) * 32, gv + (size_t)(i - ib + PH_D) * ld, 512, bar + p);
+          }
+          const double vS = __shfl_up_sync(0xffffffffu, vc.y, 1), vN = __shfl_down_sync(0xffffffffu, vc.x, 1);
+          const int ig = g.gi0 + i;
+          if (ig > 0 && ig < g.gnx - 1) {                            // uniform: first / last column belong to the edge walk
+            const double* c3 = s_x + 3 * (i - ib);
+            const double rW = c3[0], rE = c3[1], rhx = c3[2];
+            double2 d;
+            {
+              const double VW = um.x * rW + uc.x * (1.0 - rW), VE = up.x * rE + uc.x * (1.0 - rE);
+              const double VS = vS * L.rSa + vc.x * (1.0 - L.rSa), VN = vc.y * L.rNa + vc.x * (1.0 - L.rNa);
+              d.x = div_invariant((VE - VW) * rhx + (VN - VS) * L.rhya, sc.dt, rdt);
+            }
+            {
+              const double VW = um.y * rW + uc.y * (1.0 - rW), VE = up.y * rE + uc.y * (1.0 - rE);
+              const double VS = vc.x * L.rSb + vc.y * (1.0 - L.rSb), VN = vN * L.rNb + vc.y * (1.0 - L.rNb);
+              d.y = div_invariant((VE - VW) * rhx + (VN - VS) * L.rhyb, sc.dt, rdt);
+            }
+            st_interior(pb, d, sa, sb);
+            if (sa) { acc[0] += d.x; acc[1] = fma(d.x, d.x, acc[1]); }
+            if (sb) { acc[0] += d.y; acc[1] = fma(d.y, d.y, acc[1]); }
+          }
+          um = uc; uc = up;
+          pb += ld;
         }
-        if (L.st2 || L.st1) {                                      // cells on an edge: the general cell function (reads its neighbours from memory)
-          const size_t off = (size_t)(i + HX) * ld + L.row;
-          if (!(xin && L.inA)) d.x = div_cell<true>(g, edges, sc, i, L.j0, u + off, v + off);
-          if (L.st2 && !(xin && L.inB)) d.y = div_cell<true>(g, edges, sc, i, L.j0 + 1, u + off + 1, v + off + 1);
-        }
-        st_pair(pb, d, L.st2, L.st1);
-        if (L.st2 || L.st1) { acc[0] += d.x; acc[1] = fma(d.x, d.x, acc[1]); }
-        if (L.st2) { acc[0] += d.y; acc[1] = fma(d.y, d.y, acc[1]); }
-        um = uc; uc = up;
-        pu += ld; pv += ld; pb += ld;
       }
     }
+    for_edge_cells(g, ib, ie, edge_walk(g, wj), lane, [&](int i, int j) {
+      const size_t id = cidx(g, i, j);
+      const double d = div_cell<true>(g, edges, sc, i, j, u + id, v + id);
+      b[id] = d;
+      acc[0] += d; acc[1] = fma(d, d, acc[1]);
+    });
   }
   grid_reduce<2, OpSum>(acc, red, out);
 }
@@ -132,76 +223,104 @@ k_div_march(LevelGeom g, const EdgeDev* __restrict__ edges, StepConst sc, const 
 // ---------------------------------------------------------------------------------------------------------
 // divPhi = GradP(phi); u = u* - dt divPhi_x; v = v* - dt divPhi_y; out[0..3] = max(-u), max(u), max(-v), max(v) (NaN-propagating)
 // phi may carry a constant offset (the mean is removed lazily, ns_solver.inl): only differences of phi enter.
+__device__ __forceinline__ void minmax_acc(double (&acc)[4], double un, double vn) {
+  const bool bad = !(isfinite(un) && isfinite(vn));   // fmax drops NaNs: map a non-finite value to +inf on all four
+  const double inf = 1.0 / 0.0;
+  acc[0] = fmax(acc[0], bad ? inf : -un); acc[1] = fmax(acc[1], bad ? inf : un);
+  acc[2] = fmax(acc[2], bad ? inf : -vn); acc[3] = fmax(acc[3], bad ? inf : vn);
+}
+
 __global__ void __launch_bounds__(PH_THREADS, PH_MIN_CTAS)
 k_correct_march(LevelGeom g, StepConst sc, const double* __restrict__ phi, const double* __restrict__ us, const double* __restrict__ vs,
                 double* __restrict__ u, double* __restrict__ v, double* __restrict__ gpx, double* __restrict__ gpy, int RI, Reducer red,
                 double* __restrict__ out) {
-  extern __shared__ double s_x[];
-  const int lane = threadIdx.x & 31, wj = blockIdx.x * PH_WARPS + (threadIdx.x >> 5);
+  extern __shared__ __align__(128) unsigned char s_raw[];
+  double* s_x = reinterpret_cast<double*>(s_raw);
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5, wj = blockIdx.x * PH_WARPS + wid;
   const int ib = blockIdx.y * RI, ie = min(ib + RI, g.nx);
+  constexpr int A = 3;                                              // fields in a slot: phi (column i + 1), u*, v* (column i)
+  double2* ring = reinterpret_cast<double2*>(s_raw + ((3 * RI * 8 + 127) / 128) * 128) + (size_t)wid * PH_D * A * 32;
+  uint64_t* bar = reinterpret_cast<uint64_t*>(s_raw + ((3 * RI * 8 + 127) / 128) * 128 + (size_t)PH_WARPS * PH_D * A * 512) + wid * PH_D;
   phys_stage_x(g, ib, ie, s_x);
   const PhysLane L = phys_lane(g, lane, wj);
   const int ld = L.ld;
-  const size_t base = (size_t)(ib + HX) * ld + L.row;
-  const double* pp = phi + base;
-  const double* pus = us + base;
-  const double* pvs = vs + base;
-  size_t o = base;                                                 // running offset of the output pair
-  double2 pm = ld2(pp - ld), pc = ld2(pp);
-  double2 Fp[PH_PF], Fu[PH_PF], Fv[PH_PF];                         // Fp[p]: column i + 1 + p of phi; Fu / Fv[p]: column i + p of u*, v*
-#pragma unroll
-  for (int p = 0; p < PH_PF; p++) { Fp[p] = ld2(pp + (size_t)(1 + p) * ld); Fu[p] = ld2(pus + (size_t)p * ld); Fv[p] = ld2(pvs + (size_t)p * ld); }
+  const bool active = wj * PH_UJ < g.ny;
+  const bool sa = (L.st2 || L.st1) && L.inA, sb = L.st2 && L.inB;
   double acc[4] = {OpMax::id(), OpMax::id(), OpMax::id(), OpMax::id()};
-  const double inf = 1.0 / 0.0;
-  for (int i0 = ib; i0 < ie; i0 += PH_PF) {
+  if (active) {
+    const size_t wrow = (size_t)(wj * PH_UJ - 2 + PJ);
+    const double* gp = phi + (size_t)(ib + 1 + HX) * ld + wrow;
+    const double* gus = us + (size_t)(ib + HX) * ld + wrow;
+    const double* gvs = vs + (size_t)(ib + HX) * ld + wrow;
+    if (lane == 0) {
 #pragma unroll
-    for (int p = 0; p < PH_PF; p++) {
-      const int i = i0 + p;
-      if (i < ie) {                                                // uniform
-        const double2 pn = Fp[p], usc = Fu[p], vsc = Fv[p];
-        Fp[p] = ld2(pp + (size_t)(1 + PH_PF) * ld);
-        Fu[p] = ld2(pus + (size_t)PH_PF * ld);
-        Fv[p] = ld2(pvs + (size_t)PH_PF * ld);
-        const double pS = __shfl_up_sync(0xffffffffu, pc.y, 1), pN = __shfl_down_sync(0xffffffffu, pc.x, 1);
-        const int ig = g.gi0 + i;
-        const bool xin = ig > 0 && ig < g.gnx - 1;
-        const double* c3 = s_x + 3 * (i - ib);
-        const double rW = c3[0], rE = c3[1], rhx = c3[2];
-        double2 gx, gy;
-        {
-          const double VW = pm.x * rW + pc.x * (1.0 - rW), VE = pn.x * rE + pc.x * (1.0 - rE);
-          const double VS = pS * L.rSa + pc.x * (1.0 - L.rSa), VN = pc.y * L.rNa + pc.x * (1.0 - L.rNa);
-          gx.x = (VE - VW) * rhx; gy.x = (VN - VS) * L.rhya;
+      for (int p = 0; p < PH_D; p++) mbar_init(bar + p, 1);
+      mbar_init_fence();
+#pragma unroll
+      for (int p = 0; p < PH_D; p++)
+        if (ib + p < ie) {
+          mbar_expect_tx(bar + p, A * 512);
+          bulk_g2s(ring + (p * A + 0) * 32, gp + (size_t)p * ld, 512, bar + p);
+          bulk_g2s(ring + (p * A + 1) * 32, gus + (size_t)p * ld, 512, bar + p);
+          bulk_g2s(ring + (p * A + 2) * 32, gvs + (size_t)p * ld, 512, bar + p);
         }
-        {
-          const double VW = pm.y * rW + pc.y * (1.0 - rW), VE = pn.y * rE + pc.y * (1.0 - rE);
-          const double VS = pc.x * L.rSb + pc.y * (1.0 - L.rSb), VN = pN * L.rNb + pc.y * (1.0 - L.rNb);
-          gx.y = (VE - VW) * rhx; gy.y = (VN - VS) * L.rhyb;
+    }
+    __syncwarp();
+    size_t o = (size_t)(ib + HX) * ld + L.row;                       // running offset of the output pair
+    double2 pm = ld2(phi + o - ld), pc = ld2(phi + o);
+    uint32_t parity = 0;
+#pragma unroll 1
+    for (int i0 = ib; i0 < ie; i0 += PH_D, parity ^= 1) {
+#pragma unroll
+      for (int p = 0; p < PH_D; p++) {
+        const int i = i0 + p;
+        if (i < ie) {                                                // uniform
+          mbar_wait(bar + p, parity);
+          const double2 pn = ring[(p * A + 0) * 32 + lane], usc = ring[(p * A + 1) * 32 + lane], vsc = ring[(p * A + 2) * 32 + lane];
+          __syncwarp();
+          if (lane == 0 && i + PH_D < ie) {
+            mbar_expect_tx(bar + p, A * 512);
+            bulk_g2s(ring + (p * A + 0) * 32, gp + (size_t)(i - ib + PH_D) * ld, 512, bar + p);
+            bulk_g2s(ring + (p * A + 1) * 32, gus + (size_t)(i - ib + PH_D) * ld, 512, bar + p);
+            bulk_g2s(ring + (p * A + 2) * 32, gvs + (size_t)(i - ib + PH_D) * ld, 512, bar + p);
+          }
+          const double pS = __shfl_up_sync(0xffffffffu, pc.y, 1), pN = __shfl_down_sync(0xffffffffu, pc.x, 1);
+          const int ig = g.gi0 + i;
+          if (ig > 0 && ig < g.gnx - 1) {                            // uniform
+            const double* c3 = s_x + 3 * (i - ib);
+            const double rW = c3[0], rE = c3[1], rhx = c3[2];
+            double2 gx, gy;
+            {
+              const double VW = pm.x * rW + pc.x * (1.0 - rW), VE = pn.x * rE + pc.x * (1.0 - rE);
+              const double VS = pS * L.rSa + pc.x * (1.0 - L.rSa), VN = pc.y * L.rNa + pc.x * (1.0 - L.rNa);
+              gx.x = (VE - VW) * rhx; gy.x = (VN - VS) * L.rhya;
+            }
+            {
+              const double VW = pm.y * rW + pc.y * (1.0 - rW), VE = pn.y * rE + pc.y * (1.0 - rE);
+              const double VS = pc.x * L.rSb + pc.y * (1.0 - L.rSb), VN = pN * L.rNb + pc.y * (1.0 - L.rNb);
+              gx.y = (VE - VW) * rhx; gy.y = (VN - VS) * L.rhyb;
+            }
+            const double2 un = make_double2(usc.x - sc.dt * gx.x, usc.y - sc.dt * gx.y);
+            const double2 vn = make_double2(vsc.x - sc.dt * gy.x, vsc.y - sc.dt * gy.y);
+            st_interior(gpx + o, gx, sa, sb);
+            st_interior(gpy + o, gy, sa, sb);
+            st_interior(u + o, un, sa, sb);
+            st_interior(v + o, vn, sa, sb);
+            if (sa) minmax_acc(acc, un.x, vn.x);
+            if (sb) minmax_acc(acc, un.y, vn.y);
+          }
+          pm = pc; pc = pn;
+          o += ld;
         }
-        if (L.st2 || L.st1) {                                      // cells on an edge: grad_cell itself (wall and outflow closures)
-          if (!(xin && L.inA)) { const UV gr = grad_cell(g, cell_flags<true>(g, i, L.j0), i, L.j0, phi + o); gx.x = gr.u; gy.x = gr.v; }
-          if (L.st2 && !(xin && L.inB)) { const UV gr = grad_cell(g, cell_flags<true>(g, i, L.j0 + 1), i, L.j0 + 1, phi + o + 1); gx.y = gr.u; gy.y = gr.v; }
-        }
-        const double2 un = make_double2(usc.x - sc.dt * gx.x, usc.y - sc.dt * gx.y);
-        const double2 vn = make_double2(vsc.x - sc.dt * gy.x, vsc.y - sc.dt * gy.y);
-        st_pair(gpx + o, gx, L.st2, L.st1);
-        st_pair(gpy + o, gy, L.st2, L.st1);
-        st_pair(u + o, un, L.st2, L.st1);
-        st_pair(v + o, vn, L.st2, L.st1);
-        if (L.st2 || L.st1) {
-          const bool bad = !(isfinite(un.x) && isfinite(vn.x));
-          acc[0] = fmax(acc[0], bad ? inf : -un.x); acc[1] = fmax(acc[1], bad ? inf : un.x);
-          acc[2] = fmax(acc[2], bad ? inf : -vn.x); acc[3] = fmax(acc[3], bad ? inf : vn.x);
-        }
-        if (L.st2) {
-          const bool bad = !(isfinite(un.y) && isfinite(vn.y));
-          acc[0] = fmax(acc[0], bad ? inf : -un.y); acc[1] = fmax(acc[1], bad ? inf : un.y);
-          acc[2] = fmax(acc[2], bad ? inf : -vn.y); acc[3] = fmax(acc[3], bad ? inf : vn.y);
-        }
-        pm = pc; pc = pn;
-        pp += ld; pus += ld; pvs += ld; o += ld;
       }
     }
+    for_edge_cells(g, ib, ie, edge_walk(g, wj), lane, [&](int i, int j) {
+      const size_t id = cidx(g, i, j);
+      const UV gr = grad_cell(g, cell_flags<true>(g, i, j), i, j, phi + id);
+      const double un = us[id] - sc.dt * gr.u, vn = vs[id] - sc.dt * gr.v;
+      gpx[id] = gr.u; gpy[id] = gr.v; u[id] = un; v[id] = vn;
+      minmax_acc(acc, un, vn);
+    });
   }
   grid_reduce<4, OpMax>(acc, red, out);
 }

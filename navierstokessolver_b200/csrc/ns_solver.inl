@@ -145,7 +145,7 @@ static inline int march_chunk(const nsgpu_ctx* ctx, const Level& L, int uj, int 
 //   xin == nullptr: zero initial guess;  Cp/xc: prolong from;  Cr: restrict the residual to Cr->b;  norm_out/ctl: |r|^2
 static int march_pass(nsgpu_ctx* ctx, const Level& L, OpCoef c, int nsw, double* xin, const double* b, double* xout,
                       const Level* Cp, double* xc, const Level* Cr, double* norm_out, SolveCtl* ctl, double omega = 0.0) {
-  const int res = Cr ? 1 : (norm_out ? 2 : 0);
+  const int res = Cr ? 1 : (norm_out ? (c.op == 0 ? 2 : 3) : 0);   // 3: the phi operators also reduce the sum of the iterate
   const int lead = march_lead(nsw, res);
   int rc;
   if (xin && (rc = halo_exchange(ctx, L, xin, lead, true))) return rc;
@@ -156,9 +156,10 @@ static int march_pass(nsgpu_ctx* ctx, const Level& L, OpCoef c, int nsw, double*
   const size_t rep_off_r = (Cr && Cr->replicated && !L.replicated) ? (size_t)(L.g.gi0 / L.cx) * Cr->g.ld : 0;
   if (Cp) { xf.xc = xc + rep_off_p; xf.ldc = Cp->g.ld; xf.pcx = L.cx; xf.pcy = L.cy; }
   if (Cr) { xf.bc = Cr->b + rep_off_r; xf.ldbc = Cr->g.ld; xf.rcx = L.cx; xf.rcy = L.cy; xf.rscale = 1.0 / (double)(L.cx * L.cy); }
-  if (res == 2) { xf.red = ctx->red; xf.out = norm_out; xf.ctl = ctl; }
+  if (res >= 2) { xf.red = ctx->red; xf.out = norm_out; xf.ctl = ctl; }
   xf.omega = omega;
-  if (ctx->next_pass_shift && xin) { xf.shift = ctx->next_pass_shift; xf.shift_scale = 1.0 / (double)ctx->n_cells_global; }
+  if (ctx->next_pass_shift && xin && res == 1) { xf.shift = ctx->next_pass_shift; xf.shift_scale = 1.0 / (double)ctx->n_cells_global; }
+  else if (ctx->next_pass_shift) { ctx->err = "internal: phi's pending mean has to be removed by a restricting pass"; return NSGPU_ERR_ARG; }
   ctx->next_pass_shift = nullptr;
   const int uj = march_uj(nsw, res);
   // several ranks: push the boundary columns into the neighbours' halos from inside the pass (peer memory over NVLink)
@@ -170,7 +171,7 @@ static int march_pass(nsgpu_ctx* ctx, const Level& L, OpCoef c, int nsw, double*
   const bool push_b = push && Cr && !Cr->replicated;
   MarchKernel kern = nullptr;
 #define NS_MARCH(NSW, PRO, RES, PF) do { if (push) kern = k_march<NSW, PRO, RES, PF, false, true>; else kern = k_march<NSW, PRO, RES, PF, false, false>; } while (0)
-#define NS_MARCH_RES(NSW, PRO) do { if (res == 0) NS_MARCH(NSW, PRO, 0, MARCH_PF); else if (res == 1) NS_MARCH(NSW, PRO, 1, MARCH_PF); else NS_MARCH(NSW, PRO, 2, MARCH_PF); } while (0)
+#define NS_MARCH_RES(NSW, PRO) do { if (res == 0) NS_MARCH(NSW, PRO, 0, MARCH_PF); else if (res == 1) NS_MARCH(NSW, PRO, 1, MARCH_PF); else if (res == 2) NS_MARCH(NSW, PRO, 2, MARCH_PF); else NS_MARCH(NSW, PRO, 3, MARCH_PF); } while (0)
   if (omega > 0.0) {                   // red-black SOR double sweep (velocity solves)
     if (nsw != 2 || Cp || res == 1) { ctx->err = "SOR passes are double sweeps without transfers"; return NSGPU_ERR_ARG; }
     if (res == 0) kern = push ? k_march<2, false, 0, MARCH_PF, true, true> : k_march<2, false, 0, MARCH_PF, true, false>;
@@ -223,7 +224,7 @@ static int march_pass(nsgpu_ctx* ctx, const Level& L, OpCoef c, int nsw, double*
       xf.incR = grid.x * (unsigned)(gy - (L.g.nx - zone) / ri);
     }
     if (gather) ctx->last_gather_ctas = grid.x * grid.y;
-  } else if (res == 2 && ctx->d_pt) xf.pt = ctx->d_pt;   // the residual norm is summed over the ranks in the epilogue
+  } else if (res >= 2 && ctx->d_pt) xf.pt = ctx->d_pt;   // the residual norm is summed over the ranks in the epilogue
   trace_begin(ctx, (int)(&L - ctx->levels.data()) * 1000 + nsw * 100 + res * 10 + (Cp ? 2 : 0) + (push ? 1 : 0) + (omega > 0 ? 50000 : 0));
   kern<<<grid, MARCH_THREADS, sh, ctx->stream>>>(L.g, L.mcx[op_tab(c)], L.mcy[op_tab(c)], xin, b, xout, ri, xf);
   trace_end(ctx);
@@ -663,7 +664,7 @@ static int solve_head(nsgpu_ctx* ctx, int slot, OpCoef c, double* x, double* xt,
   if (!bn2_pre && (rc = norm2_vec(ctx, L, b, &ctl->bn2))) return rc;
   if (iterate) {
     double *xa = x, *xb = xt;
-    if (slot == 2 && ctx->lazy_mean) ctx->next_pass_shift = &ctl->xsum;   // the first pass removes the mean the last solve left in phi
+    if (slot == 2 && ctx->lazy_mean && ctx->levels.size() > 1 && ctx->nu_pre >= 1) ctx->next_pass_shift = &ctl->xsum;   // the first pass (a restricting one) removes the mean the last solve left in phi
     if ((rc = solve_body(ctx, slot, c, &xa, &xb, b, x0 && x0 != x ? x0 : nullptr))) return rc;
     if (xa != x) { ctx->err = "internal: an iteration does not return to its buffer"; return NSGPU_ERR_ARG; }
     return 0;
@@ -882,7 +883,7 @@ static inline void export_fence(nsgpu_ctx* ctx, bool phi, bool uv) {
 
 // Launch shape of the projection kernels of ns_phys.cuh: gx CTAs of 4 warps cover the rows, the columns are cut into chunks of *ri
 // so that the CTAs fill whole waves (same estimate as march_chunk: waves x (columns per chunk + start-up)).
-static dim3 phys_grid(const void* kern, const Level& L, int* ri, size_t* smem) {
+static dim3 phys_grid(const void* kern, int fields, const Level& L, int* ri, size_t* smem) {
   static std::vector<std::pair<const void*, int>> cache;
   int wave = 0;
   for (auto& e : cache) if (e.first == kern) wave = e.second;
@@ -890,7 +891,8 @@ static dim3 phys_grid(const void* kern, const Level& L, int* ri, size_t* smem) {
     int per_sm = 0, dev = 0, sms = 148;
     cudaGetDevice(&dev);
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, PH_THREADS, 3 * 256 * sizeof(double)) != cudaSuccess || per_sm < 1) per_sm = 4;
+    cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)phys_smem(1024, fields));
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, PH_THREADS, phys_smem(128, fields)) != cudaSuccess || per_sm < 1) per_sm = 4;
     wave = per_sm * sms;
     cache.push_back({kern, wave});
   }
@@ -899,13 +901,13 @@ static dim3 phys_grid(const void* kern, const Level& L, int* ri, size_t* smem) {
   int r_best = L.g.nx;
   for (int r = 8; r <= std::min(L.g.nx, 1024); r += 4) {
     const long long ctas = (long long)gx * ((L.g.nx + r - 1) / r);
-    const long long cost = ((ctas + wave - 1) / wave) * (r + 2 * PH_PF);
+    const long long cost = ((ctas + wave - 1) / wave) * (r + 2 * PH_D);
     if (best < 0 || cost < best) { best = cost; r_best = r; }
   }
   if (L.g.nx < 8) r_best = L.g.nx;
   while ((long long)gx * ((L.g.nx + r_best - 1) / r_best) > RED_MAX_BLOCKS) r_best *= 2;
   *ri = r_best;
-  *smem = (size_t)3 * r_best * sizeof(double);
+  *smem = phys_smem(r_best, fields);
   return dim3(gx, (L.g.nx + r_best - 1) / r_best);
 }
 
@@ -977,7 +979,7 @@ static int phase_div(nsgpu_ctx* ctx, bool remove_mean) {   // FS.cpp:549-550
   const dim3 grid = grid_cols(L.g, 256);
   if (ctx->rect && ctx->phys_march) {
     int ri; size_t sh;
-    const dim3 pg = phys_grid((const void*)k_div_march, L, &ri, &sh);
+    const dim3 pg = phys_grid((const void*)k_div_march, 2, L, &ri, &sh);
     k_div_march<<<pg, PH_THREADS, sh, ctx->stream>>>(L.g, ctx->d_edges, sc, ctx->ustar, ctx->vstar, ctx->rhs_phi, ri, ctx->red, ctx->d_scal + 28);
   } else {
 #define CALL(RECT) k_div_rhs<RECT><<<grid, 256, 0, ctx->stream>>>(L.g, ctx->d_edges, sc, ctx->ustar, ctx->vstar, ctx->rhs_phi, ctx->red, ctx->d_scal + 28)
@@ -1028,7 +1030,7 @@ static int phase_phi(nsgpu_ctx* ctx, SolveResult* rp) {   // FS.cpp:551, warm st
   if ((rc = solve(ctx, 2, coef_phi(), &ctx->phi, b, ctx->rtol_phi, rp))) return rc;
   if (!rp->pending) ctx->fine_sweeps_phi += (double)rp->cycles * (ctx->nu_pre + ctx->nu_post) * (ctx->solver == 1 ? 2 : 1);
   // pin mean(phi) = 0: the reference projects the constant out of every Krylov update (MatSetNullSpace, FS.cpp:143)
-  const bool lazy = rp->pending && ctx->lazy_mean && (ctx->nu_pre >= 1 || ctx->levels.size() == 1);   // the solve head iterates (solve_head)
+  const bool lazy = rp->pending && ctx->lazy_mean && ctx->nu_pre >= 1 && ctx->levels.size() > 1;   // the next solve's head starts with a restricting pass (solve_head)
   if (lazy) ctx->phi_shift = true;   // sum(phi) is in the solve's control block; removed by the next solve's first pass, or by phi_normalize()
   else {
     const size_t n = (size_t)L.g.nx * L.g.ld;
@@ -1056,7 +1058,7 @@ static int phase_correct(nsgpu_ctx* ctx, double mm[4]) {   // FS.cpp:552-557
   const StepConst sc{ctx->dt, ctx->re};
   if (ctx->rect && ctx->phys_march) {
     int ri; size_t sh;
-    const dim3 pg = phys_grid((const void*)k_correct_march, L, &ri, &sh);
+    const dim3 pg = phys_grid((const void*)k_correct_march, 3, L, &ri, &sh);
     k_correct_march<<<pg, PH_THREADS, sh, ctx->stream>>>(L.g, sc, ctx->phi, ctx->ustar, ctx->vstar, ctx->u, ctx->v, ctx->gpx, ctx->gpy, ri, ctx->red, ctx->d_scal + 20);
   } else {
     const dim3 grid = grid_cols(L.g, 256);

@@ -321,10 +321,22 @@ def test_graph_solves_equal_direct_launches(n, sim, workdir):
     assert ia.kernel_launches == ib.kernel_launches
 
 
-def test_step_with_host_state_equals_resident_steps(workdir):
+def _same(a, b, exact):
+    if exact:
+        return np.array_equal(a, b)
+    return np.abs(a - b).max() <= 1e-12 * max(np.abs(b).max(), 1e-300)
+
+
+@pytest.mark.parametrize("lazy", ["1", "0"])
+def test_step_with_host_state_equals_resident_steps(lazy, workdir, monkeypatch):
     """nsgpu_step_host (state streamed from / to host arrays, copies overlapped with the phases) against the same steps
-    with the state resident on the device: identical fields, three steps in a row."""
+    with the state resident on the device, three steps in a row: same iteration counts, fields equal to rounding (1e-12).  Not bit for
+    bit since round 2: a resident phi keeps its mean until the next solve's first pass removes it (nsgpu_ctx::lazy_mean) while a phi that
+    travels to the host is normalised first -- CorrectVelocities sees phi + const in one run and phi in the other, and GradP of a
+    constant is zero only up to rounding.  NSGPU_LAZY_MEAN=0 restores the bit-identical behaviour (checked below)."""
     import navierstokessolver_b200 as ns
+    monkeypatch.setenv("NSGPU_LAZY_MEAN", lazy)
+    exact = lazy == "0"
     g = ns.GridDesc.cavity(96, nx=160, lx=160 / 96.0)
     a = ns.GpuFluidSolver(g, 0.002, 400.0)
     b = ns.GpuFluidSolver(g, 0.002, 400.0)
@@ -337,8 +349,8 @@ def test_step_with_host_state_equals_resident_steps(workdir):
         ib = b.step_host(state)
         assert (ia.it_u, ia.it_v, ia.it_phi, ia.status) == (ib.it_u, ib.it_v, ib.it_phi, ib.status)
         for k in keys:
-            assert np.array_equal(state[k], a.get(k)), k
-            assert np.array_equal(b.get(k), a.get(k)), k
+            assert _same(state[k], a.get(k), exact), k
+            assert _same(b.get(k), a.get(k), exact), k
     # five-array form: divPhi = GradP(phi) is rebuilt on the device instead of being shipped
     c = ns.GpuFluidSolver(g, 0.002, 400.0)
     five = {k: state[k].copy() for k in (U, V, PHI, CONV_U0, CONV_V0)}
@@ -347,9 +359,9 @@ def test_step_with_host_state_equals_resident_steps(workdir):
         ic = c.step_host(five)
         assert (ia.it_u, ia.it_v, ia.it_phi, ia.status) == (ic.it_u, ic.it_v, ic.it_phi, ic.status)
         for k in keys:
-            assert np.array_equal(c.get(k), a.get(k)), k
+            assert _same(c.get(k), a.get(k), exact), k
         for k in five:
-            assert np.array_equal(five[k], a.get(k)), k
+            assert _same(five[k], a.get(k), exact), k
 
 
 def test_velocity_sor_and_multigrid_agree(workdir):

@@ -295,8 +295,8 @@ def test_export_every_step_costs_little_device_time(workdir):
           % (dev_a / 30, dev_b / 30, snap_ms / 30, 1e3 * wall_a / 30, 1e3 * wall_b / 30))
     assert dev_b + snap_ms <= 1.10 * dev_a + 0.5
     assert wall_b <= 1.5 * wall_a + 0.01
-    for k in (U, V, PHI):
-        assert np.array_equal(a.get(k), b.get(k))
+    for k in (U, V, PHI):      # equal to rounding: an exported phi is normalised at once, a resident one lazily (nsgpu_ctx::lazy_mean)
+        assert _rel(a.get(k), b.get(k)) <= 1e-12
 
 
 def test_direct_launch_step_lists_the_solver_kernels(workdir):
