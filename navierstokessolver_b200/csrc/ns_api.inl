@@ -30,7 +30,6 @@ static int ensure_stage(nsgpu_ctx* ctx) {
 
 // host compact-id order -> padded device layout
 static int upload_field(nsgpu_ctx* ctx, double* dev, const double* host) {
-  export_fence(ctx, true, true);
   if (dev == ctx->phi) {   // a new phi replaces whatever mean was pending
     ctx->phi_shift = false;
     k_scalar_set<<<1, 1, 0, ctx->stream>>>(&ctx->d_ctl[2].xsum, 0.0);
@@ -336,8 +335,7 @@ static int step_impl(nsgpu_ctx* ctx, int32_t n_steps, nsgpu_step_info* last, con
       NS_CUDA(cudaStreamCreateWithFlags(&ctx->s_out, cudaStreamNonBlocking));
       for (auto& e : ctx->ev_io) NS_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
     }
-    export_fence(ctx, true, true);
-    ctx->halo_w.clear();
+      ctx->halo_w.clear();
     ctx->bn2_ready[0] = ctx->bn2_ready[1] = ctx->bn2_ready[2] = false;
     ctx->phi_shift = false;   // phi arrives from the host
     k_scalar_set<<<1, 1, 0, ctx->stream>>>(&ctx->d_ctl[2].xsum, 0.0);
@@ -505,7 +503,6 @@ int nsgpu_poisson_sweeps(nsgpu_ctx* ctx, int32_t n_sweeps, double* residual_l2, 
   cudaSetDevice(ctx->device);
   const Level& L = ctx->levels[0];
   int rc;
-  export_fence(ctx, true, true);
   if ((rc = phi_normalize(ctx))) return rc;
   ctx->halo_w.clear();
   if ((rc = halo_exchange(ctx, L, ctx->rhs_phi, 1))) return rc;
@@ -535,7 +532,6 @@ int nsgpu_time_passes(nsgpu_ctx* ctx, int32_t kind, int32_t n, float* ms) {
   const OpCoef c = kind == 3 ? coef_v(ctx) : coef_phi();
   if (!march_level_ok(ctx, L, c) || (kind != 3 && ctx->levels.size() < 2)) { ctx->err = "nsgpu_time_passes: rectangle fast path with at least two levels only"; return NSGPU_ERR_ARG; }
   int rc;
-  export_fence(ctx, true, true);
   if ((rc = phi_normalize(ctx))) return rc;
   ctx->halo_w.clear();
   double** x = kind == 3 ? &ctx->ustar : &ctx->phi;
@@ -572,11 +568,12 @@ int nsgpu_apply_operator(nsgpu_ctx* ctx, int32_t op, const double* x, double* y)
   return download_field(ctx, ctx->kry[1], y);
 }
 
-// ExportData without stalling the loop (FS.cpp:561, 569-615).  begin: k_pressure on the solver's stream forms lapPhi and Pr; a copy
-// stream then reads phi, u, v straight from the live arrays and Pr, lapPhi from the staging arrays into one of two pinned buffers.  The
-// call returns at once and the next time steps run under the copies: the solver's stream waits for "phi has been read" before the next
-// phi solve and for "u, v have been read" before the next projection (export_fence), nothing else.  wait: blocks until the OLDEST
-// pending snapshot is home and hands out pointers into the pinned buffer (valid until the second nsgpu_export_begin after it).
+// ExportData without stalling the loop (FS.cpp:561, 569-615).  begin: one kernel on the solver's stream takes the snapshot -- copies of
+// u, v, phi, plus lapPhi = LHS_phi phi and Pr = phi - dt/(2Re) lapPhi -- into five staging arrays, a copy stream brings them into one of
+// two pinned buffers.  The call returns at once and the next time steps run under the copies with no dependence on them (an earlier
+// version copied u, v, phi from the live arrays behind event fences: at 1024^2 the next step then waited for PCIe, 0.84 -> 1.12 ms).
+// wait: blocks until the OLDEST pending snapshot is home and hands out pointers into the pinned buffer (valid until the second
+// nsgpu_export_begin after it).
 int nsgpu_export_begin(nsgpu_ctx* ctx, int64_t tag) {
   if (!ctx) return NSGPU_ERR_ARG;
   cudaSetDevice(ctx->device);
@@ -586,8 +583,6 @@ int nsgpu_export_begin(nsgpu_ctx* ctx, int64_t tag) {
   if (!ctx->s_exp) {
     NS_CUDA(cudaStreamCreateWithFlags(&ctx->s_exp, cudaStreamNonBlocking));
     NS_CUDA(cudaEventCreateWithFlags(&ctx->exp_snap, cudaEventDisableTiming));
-    NS_CUDA(cudaEventCreateWithFlags(&ctx->exp_phi_read, cudaEventDisableTiming));
-    NS_CUDA(cudaEventCreateWithFlags(&ctx->exp_uv_read, cudaEventDisableTiming));
     for (auto& e : ctx->exp_home) NS_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
     for (auto& e : ctx->exp_t0) NS_CUDA(cudaEventCreate(&e));
     for (auto& e : ctx->exp_t1) NS_CUDA(cudaEventCreate(&e));
@@ -599,12 +594,12 @@ int nsgpu_export_begin(nsgpu_ctx* ctx, int64_t tag) {
   if ((rc = phi_normalize(ctx))) return rc;
   if ((rc = halo_exchange(ctx, L, ctx->phi, 2))) return rc;
   ctx->halo_w.clear();
-  // the two staging arrays are reused by every snapshot: the previous snapshot's copies must have left them
+  // the staging arrays are reused by every snapshot: the previous snapshot's copies must have left them
   NS_CUDA(cudaStreamWaitEvent(ctx->stream, ctx->exp_home[(ctx->exp_head + 1) & 1], 0));
   const dim3 grid = grid_cols(L.g, 256);
   const double half = ctx->dt / (2.0 * ctx->re);
   NS_CUDA(cudaEventRecord(ctx->exp_t0[ctx->exp_head], ctx->stream));
-#define CALL(RECT) k_pressure<RECT><<<grid, 256, 0, ctx->stream>>>(L.g, half, ctx->phi, ctx->exp_dev[0], ctx->exp_dev[1])
+#define CALL(RECT) k_export_snapshot<RECT><<<grid, 256, 0, ctx->stream>>>(L.g, half, ctx->u, ctx->v, ctx->phi, ctx->exp_dev[0], ctx->exp_dev[1], ctx->exp_dev[2], ctx->exp_dev[3], ctx->exp_dev[4])
   NS_DISPATCH_RECT(ctx->rect, CALL);
 #undef CALL
   NS_LAUNCH_CHECK();
@@ -613,20 +608,14 @@ int nsgpu_export_begin(nsgpu_ctx* ctx, int64_t tag) {
   NS_CUDA(cudaStreamWaitEvent(ctx->s_exp, ctx->exp_snap, 0));
   const int slot = ctx->exp_head;
   double* h = ctx->exp_host[slot];
-  // host order: u, v, phi, Pr, lapPhi; copy order: phi first (the next step needs it back first), then u, v, then the staging arrays
-  const double* src[5] = {ctx->u, ctx->v, ctx->phi, ctx->exp_dev[0], ctx->exp_dev[1]};
-  const int order[5] = {2, 0, 1, 3, 4};
-  for (int q = 0; q < 5; q++) {
-    const int k = order[q];
+  for (int k = 0; k < 5; k++) {   // host order: u, v, phi, Pr, lapPhi
     if (ctx->rect) {
       const LevelGeom& g = L.g;
-      NS_CUDA(cudaMemcpy2DAsync(h + (size_t)k * n_host, (size_t)g.ny * sizeof(double), src[k] + cidx(g, 0, 0), (size_t)g.ld * sizeof(double),
+      NS_CUDA(cudaMemcpy2DAsync(h + (size_t)k * n_host, (size_t)g.ny * sizeof(double), ctx->exp_dev[k] + cidx(g, 0, 0), (size_t)g.ld * sizeof(double),
                                 (size_t)g.ny * sizeof(double), (size_t)g.nx, cudaMemcpyDeviceToHost, ctx->s_exp));
     } else {
-      NS_CUDA(cudaMemcpyAsync(h + (size_t)k * n_host, src[k], L.stride * sizeof(double), cudaMemcpyDeviceToHost, ctx->s_exp));
+      NS_CUDA(cudaMemcpyAsync(h + (size_t)k * n_host, ctx->exp_dev[k], L.stride * sizeof(double), cudaMemcpyDeviceToHost, ctx->s_exp));
     }
-    if (q == 0) NS_CUDA(cudaEventRecord(ctx->exp_phi_read, ctx->s_exp));
-    if (q == 2) NS_CUDA(cudaEventRecord(ctx->exp_uv_read, ctx->s_exp));
   }
   NS_CUDA(cudaEventRecord(ctx->exp_home[slot], ctx->s_exp));
   ctx->exp_tag[slot] = tag;

@@ -135,10 +135,9 @@ struct nsgpu_ctx {
   int tail_start = 0, use_tail = 1;
   double vel_rho = 0.0, vel_omega = 0.0;   // Jacobi radius bound of LHS_V; SOR factor (0: velocity solves use multigrid)
   nsgpu::TailDesc tail[2];
-  // non-blocking export (nsgpu_export_begin / _wait): Pr and L_phi phi by one kernel on the solver's stream; a copy stream brings u, v, phi
-  // (live arrays: the next step waits for those reads before it overwrites them) and Pr, lapPhi into one of two pinned buffers
-  double* exp_dev[2] = {nullptr, nullptr};       // staging of Pr and lapPhi (u, v, phi are copied from the live arrays, fenced by events)
-  cudaEvent_t exp_phi_read = nullptr, exp_uv_read = nullptr;   // the copy stream has read phi / u, v of the last snapshot
+  // non-blocking export (nsgpu_export_begin / _wait): a device snapshot of u, v, phi, Pr, L_phi phi taken on the solver's stream, brought
+  // home by a copy stream into one of two pinned buffers while the time loop goes on
+  double* exp_dev[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};   // device staging: u, v, phi, Pr, lapPhi
   double* exp_host[2] = {nullptr, nullptr};      // 5 * n_host doubles each (n_host = n_local, or the padded stride on general domains)
   std::vector<double> exp_compact[2];            // general domains: compacted copies handed to the caller
   cudaStream_t s_exp = nullptr;
@@ -147,12 +146,13 @@ struct nsgpu_ctx {
   float exp_last_ms = 0.0f;
   int64_t exp_tag[2] = {0, 0};
   int exp_head = 0, exp_pending = 0;             // next slot to fill; snapshots begun and not yet waited for (<= 2)
-  // MatSetNullSpace semantics (mean(phi) = 0 after the solve, FS.cpp:143) without a pass of its own: the marching solves reduce sum(phi) with
-  // the residual norm of their last pass (SolveCtl::xsum); phi stays as it is in memory (only its differences enter CorrectVelocities) and
+  // MatSetNullSpace semantics (mean(phi) = 0 after the solve, FS.cpp:143) without a pass of its own: CorrectVelocities, which reads phi anyway, reduces sum(phi)
+  // with its four maxima (SolveCtl::xsum of the phi slot); phi stays as it is in memory (only its differences enter CorrectVelocities) and
   // the FIRST pass of the next phi solve subtracts the mean while it loads the warm start.  Whoever needs phi's values (downloads, export,
   // checkpoints, nsgpu_step_host, the host-driven solvers) calls phi_normalize() first.  NSGPU_LAZY_MEAN=0: explicit k_sum + k_sub_mean.
   int lazy_mean = 1;
-  bool phi_shift = false;                        // phi in memory still contains the mean xsum / n
+  bool phi_shift = false;                        // phi in memory still contains its mean
+  bool phi_sum_known = false;                    // ... and SolveCtl::xsum of the phi slot holds sum(phi) (written by k_correct_march)
   const double* next_pass_shift = nullptr;       // consumed by the next march_pass (set by the head of the phi solve)
   bool graph_fallback = false;                   // graphs were asked for but a solve had to fall back to direct launches
   int krylov_restarts = 0;                       // BiCGStab restarts from the true residual during the last call

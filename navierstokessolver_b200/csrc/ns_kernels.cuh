@@ -26,17 +26,22 @@ struct Reducer {
   double* tmp;        // 8 doubles: where a reduction lands when its epilogue distributes the values itself
 };
 
-struct OpSum { __device__ static double f(double a, double b) { return a + b; } __device__ static double id() { return 0.0; } };
-struct OpMax { __device__ static double f(double a, double b) { return fmax(a, b); } __device__ static double id() { return -1.79769313486231570e308; } };
+// reduction operators; the index k is the position in the reduced vector (OpMax4Sum: four maxima and one sum in one reduction)
+struct OpSum { __device__ static double f(int, double a, double b) { return a + b; } __device__ static double id(int = 0) { return 0.0; } };
+struct OpMax { __device__ static double f(int, double a, double b) { return fmax(a, b); } __device__ static double id(int = 0) { return -1.79769313486231570e308; } };
+struct OpMax4Sum {
+  __device__ static double f(int k, double a, double b) { return k < 4 ? fmax(a, b) : a + b; }
+  __device__ static double id(int k = 0) { return k < 4 ? -1.79769313486231570e308 : 0.0; }
+};
 
 // blockIdx.y owns a contiguous run of columns, so the x-neighbour columns a block re-reads are still in its L1
 __device__ __forceinline__ int chunk_lo(int nx) { return (int)(((long long)nx * blockIdx.y) / gridDim.y); }
 __device__ __forceinline__ int chunk_hi(int nx) { return (int)(((long long)nx * (blockIdx.y + 1)) / gridDim.y); }
 
 template <class OP>
-__device__ __forceinline__ double warp_red(double v) {
+__device__ __forceinline__ double warp_red(int k, double v) {
 #pragma unroll
-  for (int o = 16; o > 0; o >>= 1) v = OP::f(v, __shfl_down_sync(0xffffffffu, v, o));
+  for (int o = 16; o > 0; o >>= 1) v = OP::f(k, v, __shfl_down_sync(0xffffffffu, v, o));
   return v;
 }
 
@@ -53,7 +58,7 @@ __device__ void grid_reduce(double (&v)[NV], Reducer red, double* out, EPI epi =
   const int lane = tid & 31, wid = tid >> 5, nw = (nth + 31) >> 5;
 #pragma unroll
   for (int k = 0; k < NV; k++) {
-    double w = warp_red<OP>(v[k]);
+    double w = warp_red<OP>(k, v[k]);
     if (lane == 0) sm[k][wid] = w;
   }
   __syncthreads();
@@ -62,8 +67,8 @@ __device__ void grid_reduce(double (&v)[NV], Reducer red, double* out, EPI epi =
   if (wid == 0) {
 #pragma unroll
     for (int k = 0; k < NV; k++) {
-      double w = (lane < nw) ? sm[k][lane] : OP::id();
-      w = warp_red<OP>(w);
+      double w = (lane < nw) ? sm[k][lane] : OP::id(k);
+      w = warp_red<OP>(k, w);
       if (lane == 0) red.partials[(size_t)k * RED_MAX_BLOCKS + bid] = w;
     }
     if (lane == 0) {
@@ -77,15 +82,15 @@ __device__ void grid_reduce(double (&v)[NV], Reducer red, double* out, EPI epi =
   __threadfence();
 #pragma unroll
   for (int k = 0; k < NV; k++) {
-    double w = OP::id();
-    for (unsigned b = tid; b < nb; b += nth) w = OP::f(w, __ldcg(&red.partials[(size_t)k * RED_MAX_BLOCKS + b]));
-    w = warp_red<OP>(w);
+    double w = OP::id(k);
+    for (unsigned b = tid; b < nb; b += nth) w = OP::f(k, w, __ldcg(&red.partials[(size_t)k * RED_MAX_BLOCKS + b]));
+    w = warp_red<OP>(k, w);
     __syncthreads();
     if (lane == 0) sm[k][wid] = w;
     __syncthreads();
     if (wid == 0) {
-      double z = (lane < nw) ? sm[k][lane] : OP::id();
-      z = warp_red<OP>(z);
+      double z = (lane < nw) ? sm[k][lane] : OP::id(k);
+      z = warp_red<OP>(k, z);
       if (lane == 0) out[k] = z;
     }
   }
@@ -103,7 +108,7 @@ struct SolveCtl {
   int total_cycles;  // cumulative over the life of the context (never reset on the device)
   int fails;         // cumulative number of solves that stopped at max_cycles above the tolerance
   unsigned long long handle;   // cudaGraphConditionalHandle of the WHILE node (0: none)
-  double xsum;       // sum of the iterate over all cells after the last cycle (marching solves): phi's mean is removed lazily from it
+  double xsum;       // phi slot: sum of phi over all cells, reduced by the projection kernel that reads phi anyway (lazy mean removal)
 };
 static_assert(sizeof(SolveCtl) == 64, "SolveCtl is one 64-byte block");
 
@@ -163,6 +168,37 @@ __device__ inline void xreduce_sum2(const PeerTable* pt, double a, double b, dou
   }
   *ra = sa; *rb = sb;
 }
+// Exchange of a small vector (N <= XV_MAX doubles) between all ranks, called by ONE thread per rank: all[r * N + k] = value k of rank r,
+// the same bits on every rank; the caller combines them in rank order with whatever operator each entry needs.  Own slot region
+// behind the sum slots: four buffers x MAX_RANKS x (XV_MAX + 1) words.
+constexpr int XV_MAX = 6;
+constexpr int HDR_XVSLOTS = HDR_XSLOTS + 4 * MAX_RANKS * 3;   // = 112
+constexpr int HDR_XVSEQ = 8;
+static_assert(HDR_XVSLOTS + 4 * MAX_RANKS * (XV_MAX + 1) <= HDR_WORDS, "control header too small");
+template <int N>
+__device__ inline void xexchange(const PeerTable* pt, const double (&mine)[N], double* all) {
+  static_assert(N <= XV_MAX, "vector too long");
+  unsigned long long* hdr = pt->hdr;
+  const unsigned long long s = hdr[HDR_XVSEQ] + 1;
+  hdr[HDR_XVSEQ] = s;
+  const int buf = (int)(s & 3);
+  unsigned long long* my_slot = hdr + HDR_XVSLOTS + (XV_MAX + 1) * (buf * MAX_RANKS + pt->rank);
+  for (int r = 0; r < pt->world; r++)
+#pragma unroll
+    for (int k = 0; k < N; k++) reinterpret_cast<double*>(my_slot + pt->off[r])[k] = mine[k];
+  __threadfence_system();
+  for (int r = 0; r < pt->world; r++) {
+    unsigned long long* q = my_slot + pt->off[r] + XV_MAX;
+    asm volatile("st.relaxed.sys.global.u64 [%0], %1;" :: "l"(q), "l"(s) : "memory");
+  }
+  for (int r = 0; r < pt->world; r++) {
+    const unsigned long long* q = hdr + HDR_XVSLOTS + (XV_MAX + 1) * (buf * MAX_RANKS + r);
+    wait_word(q + XV_MAX, s, true, pt->err);
+#pragma unroll
+    for (int k = 0; k < N; k++) all[r * N + k] = reinterpret_cast<const volatile double*>(q)[k];
+  }
+}
+
 __device__ inline double xreduce_sum(const PeerTable* pt, double mine) {
   double a, b;
   xreduce_sum2(pt, mine, 0.0, &a, &b);
@@ -183,23 +219,42 @@ struct SumEpilogue {   // out[0] <- sum over ranks
   __device__ void operator()(const double* out) const { if (pt) out_w[0] = xreduce_sum(pt, out[0]); }
 };
 
+// projection kernel: out[0..3] = the four maxima, out[4] = sum(phi) of this rank; over all ranks when pt != nullptr
+struct CorrectEpilogue {
+  const PeerTable* pt;
+  double* xsum;    // SolveCtl::xsum of the phi slot (may be nullptr)
+  __device__ void operator()(const double* out_c) const {
+    double* out = const_cast<double*>(out_c);
+    double s = out[4];
+    if (pt) {
+      double all[MAX_RANKS * 5];
+      const double mine[5] = {out[0], out[1], out[2], out[3], out[4]};
+      xexchange<5>(pt, mine, all);
+      s = 0.0;
+      for (int r = 0; r < pt->world; r++) {
+        for (int k = 0; k < 4; k++) out[k] = r == 0 ? all[k] : fmax(out[k], all[r * 5 + k]);
+        s += all[r * 5 + 4];
+      }
+    }
+    if (xsum) *xsum = s;
+  }
+};
+
 struct CtlEpilogue {
   SolveCtl* c;
   const PeerTable* pt;
   double* out_w;
-  bool with_sum = false;   // out[1] = sum of the iterate (marching passes)
   __device__ void operator()(const double* out) const {
-    double rn2 = out[0], xs = with_sum ? out[1] : 0.0;
-    if (pt) xreduce_sum2(pt, rn2, xs, &rn2, &xs);
-    if (out_w && (pt || with_sum)) out_w[0] = rn2;   // (otherwise `out` is out_w already)
+    if (!c && !pt) return;
+    double rn2 = out[0];
+    if (pt) { rn2 = xreduce_sum(pt, rn2); if (out_w) out_w[0] = rn2; }
     if (!c) return;
     c->rn2 = rn2;
-    if (with_sum) c->xsum = xs;
     c->cycles += 1;
     if (c->cycles > 0) c->total_cycles += 1;
     const bool zero = !(c->bn2 > 0.0);
     c->zero_rhs = zero ? 1 : 0;
-    if (zero) { c->cycles = 0; c->xsum = 0.0; }   // x = 0 is the answer, whatever ran before
+    if (zero) c->cycles = 0;   // x = 0 is the answer, whatever ran before
     const bool go = !zero && (rn2 > c->tol2 * c->bn2) && (c->cycles < c->max_cycles) && (rn2 == rn2);
     c->go = go ? 1 : 0;
     if (!go && !zero && !(rn2 <= c->tol2 * c->bn2)) c->fails += 1;
@@ -527,11 +582,14 @@ k_gradphi(LevelGeom g, const double* __restrict__ phi, double* __restrict__ gpx,
   }
 }
 
-// Pressure recovery for ExportData (FS.cpp:577-581): lapPhi = LHS_phi phi (the reference's MatMult) and the physical pressure
-// Pr = phi - dt/(2Re) lapPhi in one pass over phi, into two staging arrays (streaming stores: nothing reads them but the copy engine).
+// Snapshot for ExportData (FS.cpp:569-615): copies of u, v, phi plus lapPhi = LHS_phi phi (the reference's MatMult, FS.cpp:577) and the
+// physical pressure Pr = phi - dt/(2Re) lapPhi (FS.cpp:579-581) in one pass, into five staging arrays (streaming stores: nothing reads
+// them but the copy engine), so the time loop can go on while the copies travel home.
 template <bool RECT>
 __global__ void __launch_bounds__(256)
-k_pressure(LevelGeom g, double half, const double* __restrict__ phi, double* __restrict__ spr, double* __restrict__ slap) {
+k_export_snapshot(LevelGeom g, double half, const double* __restrict__ u, const double* __restrict__ v, const double* __restrict__ phi,
+                  double* __restrict__ su, double* __restrict__ sv, double* __restrict__ sphi, double* __restrict__ spr,
+                  double* __restrict__ slap) {
   const int j = blockIdx.x * blockDim.x + threadIdx.x;
   if (j >= g.ny) return;
   for (int i = chunk_lo(g.nx), i_hi = chunk_hi(g.nx); i < i_hi; i++) {
@@ -539,8 +597,12 @@ k_pressure(LevelGeom g, double half, const double* __restrict__ phi, double* __r
     if (f == F_OUTSIDE) continue;
     const size_t id = cidx(g, i, j);
     const double lap = apply_cell<1>(g, f, i, j, phi + id, 0.0, -1.0);
+    const double pc = phi[id];
+    __stcs(su + id, u[id]);
+    __stcs(sv + id, v[id]);
+    __stcs(sphi + id, pc);
     __stcs(slap + id, lap);
-    __stcs(spr + id, phi[id] - half * lap);
+    __stcs(spr + id, pc - half * lap);
   }
 }
 

@@ -3,7 +3,6 @@
 //   PROLONG   the coarse-grid correction is added while the column is loaded      (x <- x + P xc)
 //   RES == 1  the residual of the smoothed iterate is restricted to the coarse rhs (bc <- R (b - A x))
 //   RES == 2  the squared residual norm of the smoothed iterate is reduced         (out <- |b - A x|^2)
-//   RES == 3  as 2, plus the sum of the smoothed iterate (phi solves: the mean is removed lazily, ns_ctx.cuh)
 // so that one V(2,2) cycle touches every level exactly twice.  Rectangle fast path (1-D folded coefficients).
 //
 // Replaces the inner iterations of KSPSolve(phiSolver) / KSPSolve(uSolver) (reference FS.cpp:547-551) on the
@@ -140,7 +139,7 @@ struct Marcher {
   bool useful, jstore2, jstore1, pushL, pushR;
   MarchXfer xf;
   double2 racc;
-  double acc, accx;                                 // RES == 2: |r|^2 and the sum of the iterate
+  double acc;                                       // RES == 2: |r|^2
   double xshift;                                    // subtracted from every loaded x (0 unless the pass removes phi's mean)
 
   // Unconditional loads (no branch, so they can be scheduled early).  Lanes past the column end read the zero
@@ -193,7 +192,6 @@ struct Marcher {
     if ((unsigned)(rs - ib) < (unsigned)(ie - ib)) {
       if (jstore2) *reinterpret_cast<double2*>(po) = X[PF + L];
       else if (jstore1) *po = X[PF + L].x;
-      if (RES == 3) accx += (jstore2 || jstore1 ? X[PF + L].x : 0.0) + (jstore2 ? X[PF + L].y : 0.0);
       if (PUSH && pushL && rs < xf.pushw) {                    // first columns of the slab -> left neighbour's right halo
         if (jstore2) *reinterpret_cast<double2*>(po + xf.dL) = X[PF + L];
         else if (jstore1) po[xf.dL] = X[PF + L].x;
@@ -209,7 +207,7 @@ struct Marcher {
       const double* c3 = cc - 3 * (L + 1);
       const double2 res = pair_residual(X[PF + L + 1], X[PF + L + 2], X[PF + L], Bq[PF + L + 1], c3[0], c3[1], c3[2], k);
       if ((unsigned)(rr - ib) < (unsigned)(ie - ib)) {
-        if (RES >= 2) {
+        if (RES == 2) {
           acc += (jstore2 || jstore1 ? res.x * res.x : 0.0) + (jstore2 ? res.y * res.y : 0.0);   // branch-free
         } else {
           // chunks start on even columns, so a coarse pair never straddles two chunks
@@ -327,7 +325,7 @@ k_march(LevelGeom g, const double* __restrict__ mcx, const double* __restrict__ 
   m.pxc = nullptr;
   if (PROLONG) m.pxc = xf.xc + (size_t)((xf.pcy == 2 ? ((jl + 2 * PJ) >> 1) - PJ : jl) + PJ);
   m.racc = make_double2(0.0, 0.0);
-  m.acc = 0.0; m.accx = 0.0;
+  m.acc = 0.0;
   m.xshift = xf.shift ? *xf.shift * xf.shift_scale : 0.0;
 #pragma unroll
   for (int q = 0; q < M::RL; q++) { m.X[q] = make_double2(0.0, 0.0); m.Bq[q] = make_double2(0.0, 0.0); }
@@ -365,10 +363,6 @@ k_march(LevelGeom g, const double* __restrict__ mcx, const double* __restrict__ 
   if (RES == 2) {
     double acc[1] = {m.acc};
     grid_reduce<1, OpSum>(acc, xf.red, xf.out, CtlEpilogue{xf.ctl, xf.pt, xf.out});
-  }
-  if (RES == 3) {
-    double acc[2] = {m.acc, m.accx};
-    grid_reduce<2, OpSum>(acc, xf.red, xf.red.tmp, CtlEpilogue{xf.ctl, xf.pt, xf.out, true});
   }
 }
 

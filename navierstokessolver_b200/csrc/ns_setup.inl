@@ -113,8 +113,6 @@ static void destroy_ctx(nsgpu_ctx* ctx) {
   for (auto& q : ctx->exp_host) if (q) cudaFreeHost(q);
   if (ctx->s_exp) cudaStreamDestroy(ctx->s_exp);
   if (ctx->exp_snap) cudaEventDestroy(ctx->exp_snap);
-  if (ctx->exp_phi_read) cudaEventDestroy(ctx->exp_phi_read);
-  if (ctx->exp_uv_read) cudaEventDestroy(ctx->exp_uv_read);
   for (auto& e : ctx->exp_home) if (e) cudaEventDestroy(e);
   for (auto& e : ctx->exp_t0) if (e) cudaEventDestroy(e);
   for (auto& e : ctx->exp_t1) if (e) cudaEventDestroy(e);
@@ -363,7 +361,7 @@ static int create_impl(nsgpu_ctx* ctx, const nsgpu_grid* G, const nsgpu_params* 
   if (ctx->solver == 1 || ctx->krylov_phi)
     for (int k = 0; k < 8; k++) { int rc = dev_zeros(ctx, ctx->owned, S, &ctx->kry[k]); if (rc) return rc; }
   { const EdgeDev* p; int rc = dev_upload(ctx, ctx->owned, plan.edges, &p); if (rc) return rc; ctx->d_edges = const_cast<EdgeDev*>(p); }
-  { int rc = dev_zeros(ctx, ctx->owned, (size_t)4 * RED_MAX_BLOCKS, &ctx->red.partials); if (rc) return rc; }
+  { int rc = dev_zeros(ctx, ctx->owned, (size_t)5 * RED_MAX_BLOCKS, &ctx->red.partials); if (rc) return rc; }
   { double* c; int rc = dev_zeros(ctx, ctx->owned, 2, &c); if (rc) return rc; ctx->red.counter = (unsigned*)c; }
   { int rc = dev_zeros(ctx, ctx->owned, 8, &ctx->red.tmp); if (rc) return rc; }
   { int rc = dev_zeros(ctx, ctx->owned, 64, &ctx->d_scal); if (rc) return rc; }

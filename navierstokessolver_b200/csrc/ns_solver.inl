@@ -145,7 +145,7 @@ static inline int march_chunk(const nsgpu_ctx* ctx, const Level& L, int uj, int 
 //   xin == nullptr: zero initial guess;  Cp/xc: prolong from;  Cr: restrict the residual to Cr->b;  norm_out/ctl: |r|^2
 static int march_pass(nsgpu_ctx* ctx, const Level& L, OpCoef c, int nsw, double* xin, const double* b, double* xout,
                       const Level* Cp, double* xc, const Level* Cr, double* norm_out, SolveCtl* ctl, double omega = 0.0) {
-  const int res = Cr ? 1 : (norm_out ? (c.op == 0 ? 2 : 3) : 0);   // 3: the phi operators also reduce the sum of the iterate
+  const int res = Cr ? 1 : (norm_out ? 2 : 0);
   const int lead = march_lead(nsw, res);
   int rc;
   if (xin && (rc = halo_exchange(ctx, L, xin, lead, true))) return rc;
@@ -156,7 +156,7 @@ static int march_pass(nsgpu_ctx* ctx, const Level& L, OpCoef c, int nsw, double*
   const size_t rep_off_r = (Cr && Cr->replicated && !L.replicated) ? (size_t)(L.g.gi0 / L.cx) * Cr->g.ld : 0;
   if (Cp) { xf.xc = xc + rep_off_p; xf.ldc = Cp->g.ld; xf.pcx = L.cx; xf.pcy = L.cy; }
   if (Cr) { xf.bc = Cr->b + rep_off_r; xf.ldbc = Cr->g.ld; xf.rcx = L.cx; xf.rcy = L.cy; xf.rscale = 1.0 / (double)(L.cx * L.cy); }
-  if (res >= 2) { xf.red = ctx->red; xf.out = norm_out; xf.ctl = ctl; }
+  if (res == 2) { xf.red = ctx->red; xf.out = norm_out; xf.ctl = ctl; }
   xf.omega = omega;
   if (ctx->next_pass_shift && xin && res == 1) { xf.shift = ctx->next_pass_shift; xf.shift_scale = 1.0 / (double)ctx->n_cells_global; }
   else if (ctx->next_pass_shift) { ctx->err = "internal: phi's pending mean has to be removed by a restricting pass"; return NSGPU_ERR_ARG; }
@@ -171,7 +171,7 @@ static int march_pass(nsgpu_ctx* ctx, const Level& L, OpCoef c, int nsw, double*
   const bool push_b = push && Cr && !Cr->replicated;
   MarchKernel kern = nullptr;
 #define NS_MARCH(NSW, PRO, RES, PF) do { if (push) kern = k_march<NSW, PRO, RES, PF, false, true>; else kern = k_march<NSW, PRO, RES, PF, false, false>; } while (0)
-#define NS_MARCH_RES(NSW, PRO) do { if (res == 0) NS_MARCH(NSW, PRO, 0, MARCH_PF); else if (res == 1) NS_MARCH(NSW, PRO, 1, MARCH_PF); else if (res == 2) NS_MARCH(NSW, PRO, 2, MARCH_PF); else NS_MARCH(NSW, PRO, 3, MARCH_PF); } while (0)
+#define NS_MARCH_RES(NSW, PRO) do { if (res == 0) NS_MARCH(NSW, PRO, 0, MARCH_PF); else if (res == 1) NS_MARCH(NSW, PRO, 1, MARCH_PF); else NS_MARCH(NSW, PRO, 2, MARCH_PF); } while (0)
   if (omega > 0.0) {                   // red-black SOR double sweep (velocity solves)
     if (nsw != 2 || Cp || res == 1) { ctx->err = "SOR passes are double sweeps without transfers"; return NSGPU_ERR_ARG; }
     if (res == 0) kern = push ? k_march<2, false, 0, MARCH_PF, true, true> : k_march<2, false, 0, MARCH_PF, true, false>;
@@ -224,7 +224,7 @@ static int march_pass(nsgpu_ctx* ctx, const Level& L, OpCoef c, int nsw, double*
       xf.incR = grid.x * (unsigned)(gy - (L.g.nx - zone) / ri);
     }
     if (gather) ctx->last_gather_ctas = grid.x * grid.y;
-  } else if (res >= 2 && ctx->d_pt) xf.pt = ctx->d_pt;   // the residual norm is summed over the ranks in the epilogue
+  } else if (res == 2 && ctx->d_pt) xf.pt = ctx->d_pt;   // the residual norm is summed over the ranks in the epilogue
   trace_begin(ctx, (int)(&L - ctx->levels.data()) * 1000 + nsw * 100 + res * 10 + (Cp ? 2 : 0) + (push ? 1 : 0) + (omega > 0 ? 50000 : 0));
   kern<<<grid, MARCH_THREADS, sh, ctx->stream>>>(L.g, L.mcx[op_tab(c)], L.mcy[op_tab(c)], xin, b, xout, ri, xf);
   trace_end(ctx);
@@ -664,7 +664,7 @@ static int solve_head(nsgpu_ctx* ctx, int slot, OpCoef c, double* x, double* xt,
   if (!bn2_pre && (rc = norm2_vec(ctx, L, b, &ctl->bn2))) return rc;
   if (iterate) {
     double *xa = x, *xb = xt;
-    if (slot == 2 && ctx->lazy_mean && ctx->levels.size() > 1 && ctx->nu_pre >= 1) ctx->next_pass_shift = &ctl->xsum;   // the first pass (a restricting one) removes the mean the last solve left in phi
+    if (slot == 2 && ctx->lazy_mean && ctx->levels.size() > 1 && ctx->nu_pre >= 1 && ctx->rect && ctx->phys_march) ctx->next_pass_shift = &ctl->xsum;   // the first pass (a restricting one) removes the mean the last solve left in phi
     if ((rc = solve_body(ctx, slot, c, &xa, &xb, b, x0 && x0 != x ? x0 : nullptr))) return rc;
     if (xa != x) { ctx->err = "internal: an iteration does not return to its buffer"; return NSGPU_ERR_ARG; }
     return 0;
@@ -838,6 +838,14 @@ static int phi_normalize(nsgpu_ctx* ctx) {
   const dim3 grid = grid_cols(L.g, 256);
   const double inv_n = 1.0 / (double)ctx->n_cells_global;
   double* xsum = &ctx->d_ctl[2].xsum;
+  if (!ctx->phi_sum_known) {   // the projection that reduces sum(phi) has not run since the solve
+    const size_t n = (size_t)L.g.nx * L.g.ld;
+    const int blocks = (int)std::min<size_t>((n + 255) / 256, 148 * 8);
+    k_sum<<<blocks, 256, 0, ctx->stream>>>(n, ctx->phi + (size_t)HX * L.g.ld, ctx->red, xsum);
+    NS_LAUNCH_CHECK();
+    int rc = allreduce(ctx, xsum, 1, ncclSum);
+    if (rc) return rc;
+  }
 #define CALL(RECT) k_sub_mean<RECT><<<grid, 256, 0, ctx->stream>>>(L.g, ctx->phi, xsum, inv_n)
   NS_DISPATCH_RECT(ctx->rect, CALL);
 #undef CALL
@@ -845,6 +853,7 @@ static int phi_normalize(nsgpu_ctx* ctx) {
   k_scalar_set<<<1, 1, 0, ctx->stream>>>(xsum, 0.0);
   NS_LAUNCH_CHECK();
   ctx->phi_shift = false;
+  ctx->phi_sum_known = false;
   ctx->halo_w.clear();
   return 0;
 }
@@ -872,14 +881,6 @@ static void finish_results(nsgpu_ctx* ctx, SolveResult* ru, SolveResult* rv, Sol
 
 // ---------------------------------------------------------------------------------------------------------
 // Phases of one time step
-
-// A pending nsgpu_export_begin reads phi, u, v from the live arrays on its copy stream: whoever overwrites them waits for that read
-// (an event wait on the solver's stream, no host synchronisation; a no-op when no export was ever begun).
-static inline void export_fence(nsgpu_ctx* ctx, bool phi, bool uv) {
-  if (!ctx->s_exp) return;
-  if (phi) cudaStreamWaitEvent(ctx->stream, ctx->exp_phi_read, 0);
-  if (uv) cudaStreamWaitEvent(ctx->stream, ctx->exp_uv_read, 0);
-}
 
 // Launch shape of the projection kernels of ns_phys.cuh: gx CTAs of 4 warps cover the rows, the columns are cut into chunks of *ri
 // so that the CTAs fill whole waves (same estimate as march_chunk: waves x (columns per chunk + start-up)).
@@ -1002,7 +1003,7 @@ static int phase_div(nsgpu_ctx* ctx, bool remove_mean) {   // FS.cpp:549-550
 }
 
 static int phase_phi(nsgpu_ctx* ctx, SolveResult* rp) {   // FS.cpp:551, warm start from phi^n (FS.cpp:54)
-  export_fence(ctx, true, false);
+  if (ctx->phi_shift && !ctx->phi_sum_known) { int rcn = phi_normalize(ctx); if (rcn) return rcn; }   // two phi solves without a projection in between
   ctx->halo_w.clear();   // every field may have been rewritten by a non-marching kernel since
   const Level& L = ctx->levels[0];
   int rc;
@@ -1030,8 +1031,8 @@ static int phase_phi(nsgpu_ctx* ctx, SolveResult* rp) {   // FS.cpp:551, warm st
   if ((rc = solve(ctx, 2, coef_phi(), &ctx->phi, b, ctx->rtol_phi, rp))) return rc;
   if (!rp->pending) ctx->fine_sweeps_phi += (double)rp->cycles * (ctx->nu_pre + ctx->nu_post) * (ctx->solver == 1 ? 2 : 1);
   // pin mean(phi) = 0: the reference projects the constant out of every Krylov update (MatSetNullSpace, FS.cpp:143)
-  const bool lazy = rp->pending && ctx->lazy_mean && ctx->nu_pre >= 1 && ctx->levels.size() > 1;   // the next solve's head starts with a restricting pass (solve_head)
-  if (lazy) ctx->phi_shift = true;   // sum(phi) is in the solve's control block; removed by the next solve's first pass, or by phi_normalize()
+  const bool lazy = rp->pending && ctx->lazy_mean && ctx->nu_pre >= 1 && ctx->levels.size() > 1 && ctx->rect && ctx->phys_march;   // the next solve's head starts with a restricting pass (solve_head), k_correct_march reduces the sum
+  if (lazy) { ctx->phi_shift = true; ctx->phi_sum_known = false; }   // sum(phi) is in the solve's control block; removed by the next solve's first pass, or by phi_normalize()
   else {
     const size_t n = (size_t)L.g.nx * L.g.ld;
     const int blocks = (int)std::min<size_t>((n + 255) / 256, 148 * 8);
@@ -1050,7 +1051,6 @@ static int phase_phi(nsgpu_ctx* ctx, SolveResult* rp) {   // FS.cpp:551, warm st
 }
 
 static int phase_correct(nsgpu_ctx* ctx, double mm[4]) {   // FS.cpp:552-557
-  export_fence(ctx, false, true);
   ctx->halo_w.clear();   // every field may have been rewritten by a non-marching kernel since
   const Level& L = ctx->levels[0];
   int rc;
@@ -1059,7 +1059,22 @@ static int phase_correct(nsgpu_ctx* ctx, double mm[4]) {   // FS.cpp:552-557
   if (ctx->rect && ctx->phys_march) {
     int ri; size_t sh;
     const dim3 pg = phys_grid((const void*)k_correct_march, 3, L, &ri, &sh);
-    k_correct_march<<<pg, PH_THREADS, sh, ctx->stream>>>(L.g, sc, ctx->phi, ctx->ustar, ctx->vstar, ctx->u, ctx->v, ctx->gpx, ctx->gpy, ri, ctx->red, ctx->d_scal + 20);
+    // sum(phi) rides along when phi's mean is pending; with the peer map the four maxima and the sum are combined over the ranks in the
+    // kernel's epilogue (no NCCL call in this phase)
+    k_correct_march<<<pg, PH_THREADS, sh, ctx->stream>>>(L.g, sc, ctx->phi, ctx->ustar, ctx->vstar, ctx->u, ctx->v, ctx->gpx, ctx->gpy, ri, ctx->red,
+                                                         ctx->d_scal + 20, ctx->d_pt, ctx->phi_shift ? &ctx->d_ctl[2].xsum : nullptr);
+    NS_LAUNCH_CHECK();
+    if (ctx->phi_shift) {
+      ctx->phi_sum_known = true;
+      if (!ctx->d_pt && (rc = allreduce(ctx, &ctx->d_ctl[2].xsum, 1, ncclSum))) return rc;
+    }
+    if (!ctx->d_pt && (rc = allreduce(ctx, ctx->d_scal + 20, 4, ncclMax))) return rc;
+    if (mm) {
+      double h[4];
+      if ((rc = read_scalars(ctx, ctx->d_scal + 20, 4, h))) return rc;
+      mm[0] = -h[0]; mm[1] = h[1]; mm[2] = -h[2]; mm[3] = h[3];
+    }
+    return 0;
   } else {
     const dim3 grid = grid_cols(L.g, 256);
 #define CALL(RECT) k_correct<RECT><<<grid, 256, 0, ctx->stream>>>(L.g, sc, ctx->phi, ctx->ustar, ctx->vstar, ctx->u, ctx->v, ctx->gpx, ctx->gpy, ctx->red, ctx->d_scal + 20)
