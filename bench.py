@@ -148,6 +148,11 @@ def timed_case(ns, torch, dist, rank, world, local_rank, nccl_id, ny, nxl, args,
     steps, `steps` timed ones, device time, max over ranks.  fixed_cycles > 0: every solve runs exactly that many iterations."""
     import numpy as np
     gnx = nxl * world
+    if world > 1:   # every context has its own communicator: a fresh NCCL id, agreed on by all ranks
+        from navierstokessolver_b200 import capi
+        box = [capi.nccl_unique_id() if rank == 0 else None]
+        dist.broadcast_object_list(box, src=0)
+        nccl_id = box[0]
     try:
         grid = ns.GridDesc.cavity(ny, nx=gnx, lx=gnx / float(ny))
         kw = dict(device=local_rank, rank=rank, world=world, nccl_id=nccl_id, solver=args.solver, use_graph=0 if args.graph else -1)
