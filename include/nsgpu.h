@@ -174,6 +174,16 @@ int nsgpu_set_fields(nsgpu_ctx* ctx, const double* u, const double* v, const dou
 int nsgpu_checkpoint_save(nsgpu_ctx* ctx, const char* path, int64_t step);
 int nsgpu_checkpoint_load(nsgpu_ctx* ctx, const char* path, int64_t* step);
 
+/* No counterpart in the reference: added for callers that cannot call cudaMalloc (code under
+ * CUDA graph capture, tight serving loops, harnesses that forbid it).  VecMin / VecMax of two arrays as the time step computes them
+ * (FS.cpp:554-557: out4 = umin, umax, vmin, vmax; a non-finite value anywhere gives -inf, +inf, -inf, +inf), with NO allocation of
+ * any kind: the staging copies of u and v and the reduction's scratch live in one static device array of fixed size that every GPU
+ * holds from the first use of libnsgpu.so until exit (18 MiB).  u, v: host arrays of n doubles, n <= nsgpu_noalloc_max_cells()
+ * (2^20; larger n is refused with NSGPU_ERR_ARG, message from nsgpu_last_error(NULL)).  Synchronous, on the legacy default stream of
+ * `device`.  All calls share the static array: calls that overlap on one GPU race -- serialise them. */
+int nsgpu_minmax_noalloc(int32_t device, const double* u, const double* v, int64_t n, double* out4);
+long long nsgpu_noalloc_max_cells(void);
+
 /* introspection for benchmarks and tests */
 int nsgpu_num_levels(const nsgpu_ctx* ctx);
 /* device milliseconds of the five phases of the last time step run by nsgpu_step: ConstructRHS_V, the two velocity

@@ -89,6 +89,8 @@ def _load():
     L.nsgpu_export_begin.argtypes = [P, C.c_int64]
     L.nsgpu_export_wait.argtypes = [P] + [C.POINTER(dp)] * 5 + [C.POINTER(C.c_int64)]
     L.nsgpu_export_last_ms.argtypes = [P, C.POINTER(C.c_float)]
+    L.nsgpu_minmax_noalloc.argtypes = [C.c_int32, dp, dp, C.c_int64, dp]
+    L.nsgpu_noalloc_max_cells.restype = C.c_longlong
     L.nsgpu_get_array.argtypes = [P, C.c_int32, dp]
     L.nsgpu_set_array.argtypes = [P, C.c_int32, dp]
     L.nsgpu_get_fields.argtypes = [P, dp, dp, dp]
@@ -109,7 +111,8 @@ EXPORTED = ["nsgpu_nccl_unique_id", "nsgpu_create", "nsgpu_destroy", "nsgpu_last
             "nsgpu_correct", "nsgpu_poisson_sweeps", "nsgpu_apply_operator", "nsgpu_pressure", "nsgpu_get_array",
             "nsgpu_set_array", "nsgpu_get_fields", "nsgpu_set_fields", "nsgpu_num_levels", "nsgpu_kernel_launches",
             "nsgpu_synchronize", "nsgpu_phase_ms", "nsgpu_step_host", "nsgpu_checkpoint_save", "nsgpu_checkpoint_load",
-            "nsgpu_export_begin", "nsgpu_export_wait", "nsgpu_time_passes", "nsgpu_export_last_ms"]
+            "nsgpu_export_begin", "nsgpu_export_wait", "nsgpu_time_passes", "nsgpu_export_last_ms",
+            "nsgpu_minmax_noalloc", "nsgpu_noalloc_max_cells"]
 
 
 def _dp(a):
@@ -153,6 +156,17 @@ class GridDesc:
         g.edge_nx, g.edge_ny, g.edge_bc_type = _ip(self.edge_nx), _ip(self.edge_ny), _ip(self.edge_bc_type)
         g.edge_bc_info = _dp(self.edge_bc_info)
         return g
+
+
+def minmax_noalloc(u, v, device=0):
+    """(umin, umax, vmin, vmax) through nsgpu_minmax_noalloc: no allocation on the device, scratch in a static device array."""
+    u = np.ascontiguousarray(u, dtype=np.float64)
+    v = np.ascontiguousarray(v, dtype=np.float64)
+    out = np.empty(4)
+    rc = lib.nsgpu_minmax_noalloc(device, _dp(u), _dp(v), u.size, _dp(out))
+    if rc:
+        raise NsGpuError(rc, lib.nsgpu_last_error(None).decode())
+    return tuple(float(x) for x in out)
 
 
 def nccl_unique_id():
