@@ -10,10 +10,11 @@
 #include <cmath>
 #include "../../include/nsgpu.h"
 #include "ns_kernels.cuh"
-#include "ns_rhs.cuh"
 #include "ns_phys.cuh"
+#include "ns_rhs.cuh"
 #include "ns_march.cuh"
 #include "ns_tail.cuh"
+#include "ns_ctail.cuh"
 #include "ns_hostgeom.h"
 
 namespace nsgpu {
@@ -135,6 +136,10 @@ struct nsgpu_ctx {
   int tail_start = 0, use_tail = 1;
   double vel_rho = 0.0, vel_omega = 0.0;   // Jacobi radius bound of LHS_V; SOR factor (0: velocity solves use multigrid)
   nsgpu::TailDesc tail[2];
+  // cluster tail (ns_ctail.cuh): levels >= ctail_start run in one 8-CTA cluster kernel (takes precedence over the one-CTA tail); 0 = off
+  int ctail_start = 0, use_ctail = 1;
+  nsgpu::CtDesc ctail[2];
+  double* ctail_img[2] = {nullptr, nullptr};
   // non-blocking export (nsgpu_export_begin / _wait): a device snapshot of u, v, phi, Pr, L_phi phi taken on the solver's stream, brought
   // home by a copy stream into one of two pinned buffers while the time loop goes on
   double* exp_dev[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};   // device staging: u, v, phi, Pr, lapPhi

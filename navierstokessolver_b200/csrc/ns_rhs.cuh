@@ -1,180 +1,235 @@
 // ns_rhs.cuh -- ConstructRHS_V (FS.cpp:183-363, 458-510) on rectangles as a register-marching kernel.
 //
-// k_rhs_build (ns_kernels.cuh) follows the reference cell by cell: every cell evaluates its own MUSCL slopes AND
-// those of its four neighbours, and every face flux is evaluated by both cells that share the face: 6 slope pairs
-// and 8 Roe fluxes per cell, ~650 us at 4096^2 (64 B/cell would take 165 us).  Here a lane owns one row and marches
-// over the columns of its chunk:
-//   * x direction: u, v of columns i-1 .. i+2 and the slopes of columns i, i+1 stay in registers; the east-face
-//     fluxes of cell i are carried to cell i+1 as its west-face fluxes;
-//   * y direction: the neighbours' values, slopes and the south-face fluxes come from the adjacent lanes by shuffle
-//     (2 halo lanes per side of the warp, 28 useful rows);
-// so a cell costs 2 slope pairs and 4 fluxes, and u, v are read once per column.  The arithmetic of every quantity is
-// the expression rhs_cell uses (ns_cell.cuh), evaluated once instead of twice.
+// k_rhs_build (ns_kernels.cuh) follows the reference cell by cell: every cell evaluates its own MUSCL slopes AND those of its four
+// neighbours, and every face flux is evaluated by both cells that share the face: 6 slope pairs and 8 Roe fluxes per cell, ~650 us at
+// 4096^2 (64 B/cell would take 165 us).  Round 1's marching version (one row per lane, ghost closures inline) brought that to 2 slope
+// pairs and 4 fluxes per cell but stayed instruction-bound: 290 M warp instructions, 0.53 ms.  This version
+//   * gives a lane the PAIR of rows (j0, j0 + 1) as one double2 (16-byte loads and stores, one shuffle serves two cells; one halo pair
+//     per side of the warp: 60 useful rows of 64);
+//   * reads u, v (two columns ahead: the slope of column i + 1 needs column i + 2) and the two history terms through a per-warp ring
+//     of column slots in shared memory, filled by bulk copies (cp.async.bulk + mbarrier, ns_tma.cuh): no prefetch registers;
+//   * keeps u, v of columns i - 1 .. i + 1, the x slopes of columns i, i + 1 and the east-face fluxes of cell i - 1 (= west-face fluxes
+//     of cell i) in registers; y neighbours, y slopes and the south-face fluxes come from the partner cell or the adjacent lane;
+//   * computes INTERIOR cells only in the marching loop -- no ghost values, no flag tests, no edge records; the slopes of the first /
+//     last column and row (which interior faces need, and which involve ghost values) come from slope_x / slope_y of ns_cell.cuh;
+//   * finishes the cells that touch an edge afterwards, one lane per cell, through rhs_cell itself (for_edge_cells, ns_phys.cuh), so
+//     every boundary-condition type keeps its one implementation;
+//   * runs ONE column step per loop iteration with the ring slot as a run-time index: unrolled over the slots the loop body was 38 KB
+//     of code and the top stall reason `no_instruction` (instruction-cache misses; ncu, profiles/r2_*_rhs_*).
+// The arithmetic of every quantity is the expression rhs_cell uses (ns_cell.cuh), evaluated once instead of twice.
 #pragma once
 #include <cuda_runtime.h>
 #include "ns_cell.cuh"
 #include "ns_kernels.cuh"
+#include "ns_tma.cuh"
+#include "ns_phys.cuh"
 
 namespace nsgpu {
 
-constexpr int RHS_WARPS = 4;
-constexpr int RHS_THREADS = 32 * RHS_WARPS;
-constexpr int RHS_UJ = 28;   // useful rows per warp
-
-__device__ __forceinline__ double shfl_up1(double v) { return __shfl_up_sync(0xffffffffu, v, 1); }
-__device__ __forceinline__ double shfl_dn1(double v) { return __shfl_down_sync(0xffffffffu, v, 1); }
-
-// Ghost value behind side k (W, E, S, N) of a cell with value c: w * c + constant (EvaluateGhostStencil_V, FS.cpp:166-173).
-// Only boundary cells come here, so the edge record is read where it is needed instead of living in registers.
-struct GhostUV { double u, v; };
-__device__ __forceinline__ GhostUV ghost_uv(const LevelGeom& g, const EdgeDev* __restrict__ edges, int k, double uc, double vc) {
-  const EdgeDev e = edges[g.side_edge[k]];
-  const double w = e.outflow ? 1.0 : -1.0;
-  return GhostUV{w * uc + e.cu, w * vc + e.cv};
+constexpr int RHS_WARPS = PH_WARPS;
+constexpr int RHS_THREADS = PH_THREADS;
+constexpr int RHS_UJ = PH_UJ;        // useful rows per warp
+#ifndef NS_RHS_D
+#define NS_RHS_D 6
+#endif
+constexpr int RHS_D = NS_RHS_D;      // ring depth (columns in flight per field and warp)
+constexpr int RHS_A = 4;             // fields in a slot: u, v (column s + 2), N_u, N_v of the last step (column s)
+// dynamic shared memory of a CTA: x geometry of the chunk (6 doubles per column, RI + 3 columns) | rings | barriers
+__host__ __device__ constexpr size_t rhs_smem(int ri) {
+  return (size_t)(((6 * (ri + 3) * 8 + 127) / 128) * 128) + (size_t)RHS_WARPS * RHS_D * RHS_A * 512 + (size_t)RHS_WARPS * RHS_D * 8;
 }
 
-// minmod slopes of (u, v) along one direction; k_hi / k_lo: the sides towards the higher / lower index
-__device__ __forceinline__ GhostUV slope_uv(const LevelGeom& g, const EdgeDev* __restrict__ edges, bool has_hi, bool has_lo, int k_hi,
-                                            int k_lo, double uc, double vc, double uhi, double vhi, double ulo, double vlo,
-                                            double s_hi, double s_lo, double rh) {
-  double au, av, bu, bv;
-  if (has_hi) { au = (uhi - uc) * s_hi; av = (vhi - vc) * s_hi; }
-  else { const GhostUV gh = ghost_uv(g, edges, k_hi, uc, vc); au = (gh.u - uc) * rh; av = (gh.v - vc) * rh; }
-  if (has_lo) { bu = (uc - ulo) * s_lo; bv = (vc - vlo) * s_lo; }
-  else { const GhostUV gl = ghost_uv(g, edges, k_lo, uc, vc); bu = (uc - gl.u) * rh; bv = (vc - gl.v) * rh; }
-  return GhostUV{minmod(au, bu), minmod(av, bv)};
+struct D2 { double2 u, v; };   // (u, v) of the two rows of a lane
+
+__device__ __forceinline__ double2 minmod2(const double2& a, const double2& b) { return make_double2(minmod(a.x, b.x), minmod(a.y, b.y)); }
+// minmod slope of the pair along x from the columns lo, c, hi with the scales sW (towards lo) and sE (towards hi)
+__device__ __forceinline__ double2 slope2(const double2& lo, const double2& c, const double2& hi, double sW, double sE) {
+  return minmod2(make_double2((hi.x - c.x) * sE, (hi.y - c.y) * sE), make_double2((c.x - lo.x) * sW, (c.y - lo.y) * sW));
 }
 
-__global__ void __launch_bounds__(RHS_THREADS)
+__global__ void __launch_bounds__(RHS_THREADS, 3)
 k_rhs_march(LevelGeom g, const EdgeDev* __restrict__ edges, StepConst sc, const double* __restrict__ u,
             const double* __restrict__ v, double* __restrict__ nu0, double* __restrict__ nv0,
             const double* __restrict__ gpx, const double* __restrict__ gpy, double* __restrict__ rhs_u,
             double* __restrict__ rhs_v, int RI, Reducer red, double* __restrict__ norms, int i_begin, int i_end) {
-  const int lane = threadIdx.x & 31;
-  const int wj = blockIdx.x * RHS_WARPS + (threadIdx.x >> 5);
-  const int j = wj * RHS_UJ + lane - 2;                  // rows -2, -1, ny, ny+1 are zero padding (PJ = 8)
+  extern __shared__ __align__(128) unsigned char s_raw[];
+  double* s_x = reinterpret_cast<double*>(s_raw);
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5, wj = blockIdx.x * RHS_WARPS + wid;
   // columns [i_begin, i_end) of the slab (the whole slab, or one upload chunk of nsgpu_step_host), RI columns per CTA row
   const int ib = i_begin + blockIdx.y * RI, ie = min(ib + RI, i_end);
-  const int jc = min(j, g.ny + 1);                       // rows past the padding: clamp (never stored)
-  const bool in_dom = j >= 0 && j < g.ny;
-  const bool store = in_dom && lane >= 2 && lane < 30;
-  const int ld = g.ld;
+  const size_t xbytes = ((6 * (RI + 3) * 8 + 127) / 128) * 128;
+  double2* ring = reinterpret_cast<double2*>(s_raw + xbytes) + (size_t)wid * RHS_D * RHS_A * 32;
+  uint64_t* bar = reinterpret_cast<uint64_t*>(s_raw + xbytes + (size_t)RHS_WARPS * RHS_D * RHS_A * 512) + wid * RHS_D;
+  // per column c in [ib - 1, ie + 1]: 2 rsx[c-1], 2 rsx[c] (slope scales), hx/2, 1/hx, ire rsx[c-1], ire rsx[c] (diffusive scales)
   const double ire = 1.0 / sc.re;
-
-  // y geometry and y-side ghost constants of this lane's row
-  const int ja = max(min(jc, g.ny - 1), 0) + PJ;
-  const double hyj = g.hy[ja], rhy = g.rhy[ja], rsym = g.rsy[ja - 1], rsyp = g.rsy[ja];
-  const double hyN = 0.5 * g.hy[ja + 1];
-  const bool fS = j > 0, fN = j < g.ny - 1;
-
-  const size_t row = (size_t)(jc + PJ);
-  const double* pu = u + (size_t)(ib - 2 + HX) * ld + row;   // next column to load: ib - 2 (then ib - 1, ...)
-  const double* pv = v + (size_t)(ib - 2 + HX) * ld + row;
-  auto col_ok = [&](int n) { const int ng = g.gi0 + n; return ng >= 0 && ng < g.gnx && n >= -HX && n < g.nx + HX; };
-  double uF = col_ok(ib - 2) ? *pu : 0.0, vF = col_ok(ib - 2) ? *pv : 0.0;   // prefetched column
-
-  // ring: columns i-1, i, i+1, i+2 while cell i is finished
-  double uM = 0, uC = 0, uP = 0, uQ = 0, vM = 0, vC = 0, vP = 0, vQ = 0;
-  double sxCu = 0, sxCv = 0, sxPu = 0, sxPv = 0;   // x slopes of columns i and i+1
-  double cWsq = 0, cWuv = 0;                       // east-face fluxes of cell i-1 = west-face fluxes of cell i
-  double nrm[2] = {0.0, 0.0};                      // |rhs_u|^2, |rhs_v|^2 of the cells this thread stores
-
-  // n: column entering the ring; cell i = n - 2 is finished; the first finished cell is ib - 1 (its east face only)
-  for (int n = ib - 2; n < ie + 2; n++) {
-    uM = uC; uC = uP; uP = uQ; vM = vC; vC = vP; vP = vQ;
-    uQ = uF; vQ = vF;
-    pu += ld; pv += ld;
-    { const bool ok = col_ok(n + 1) && n + 1 < ie + 2; uF = ok ? *pu : 0.0; vF = ok ? *pv : 0.0; }   // next column, one step ahead
-    const int ic = n - 2;   // history terms of the cell that is finished in this step
-    const bool ld_hist = store && ic >= ib;
-    const size_t idc = (size_t)(ic + HX) * ld + row;
-    const double hu = ld_hist ? nu0[idc] : 0.0, hv = ld_hist ? nv0[idc] : 0.0;
-    sxCu = sxPu; sxCv = sxPv;
-    {  // x slope of column n - 1 (needs columns n - 2, n - 1, n)
-      const int i1 = n - 1, ig = g.gi0 + i1;
-      if (ig >= 0 && ig < g.gnx && i1 >= -HX + 1) {
-        const bool hW = ig > 0, hE = ig < g.gnx - 1;
-        const int a = i1 + HX;
-        const double sE = 2.0 * g.rsx[a], sW = 2.0 * g.rsx[a - 1], rh = g.rhx[a];
-        const GhostUV sl = slope_uv(g, edges, hE, hW, 1, 0, uP, vP, uQ, vQ, uC, vC, sE, sW, rh);
-        sxPu = sl.u; sxPv = sl.v;
-      } else { sxPu = 0.0; sxPv = 0.0; }
+  for (int q = threadIdx.x; q < ie - ib + 3; q += RHS_THREADS) {
+    const int a = ib - 1 + q + HX;
+    s_x[6 * q] = 2.0 * g.rsx[a - 1];
+    s_x[6 * q + 1] = 2.0 * g.rsx[a];
+    s_x[6 * q + 2] = 0.5 * g.hx[a];
+    s_x[6 * q + 3] = g.rhx[a];
+    s_x[6 * q + 4] = ire * g.rsx[a - 1];
+    s_x[6 * q + 5] = ire * g.rsx[a];
+  }
+  __syncthreads();
+  const PhysLane L = phys_lane(g, lane, wj);
+  const int ld = L.ld;
+  const bool active = wj * RHS_UJ < g.ny;
+  const bool sa = (L.st2 || L.st1) && L.inA, sb = L.st2 && L.inB;   // interior cells this lane stores
+  double nrm[2] = {0.0, 0.0};                                       // |rhs_u|^2, |rhs_v|^2 of the cells this thread stores
+  if (active) {
+    // y geometry of the lane's rows a = j0, b = j0 + 1 and of the row above b
+    const int ja = min(max(L.j0, 0), g.ny - 1) + PJ, jb = min(max(L.j0 + 1, 0), g.ny - 1) + PJ, jc = min(max(L.j0 + 2, 0), g.ny - 1) + PJ;
+    const double sSa = 2.0 * g.rsy[ja - 1], sNa = 2.0 * g.rsy[ja], sNb = 2.0 * g.rsy[jb];        // slope scales (sSb = sNa)
+    const double hya = 0.5 * g.hy[ja], hyb = 0.5 * g.hy[jb], hyc = 0.5 * g.hy[jc];
+    const double rhya = g.rhy[ja], rhyb = g.rhy[jb];
+    const double dSa = ire * g.rsy[ja - 1], dNa = ire * g.rsy[ja], dNb = ire * g.rsy[jb];        // diffusive scales (dSb = dNa)
+    const bool edge_a = L.j0 == 0 || L.j0 == g.ny - 1, edge_b = L.j0 + 1 == g.ny - 1;           // rows whose y slope involves a ghost value
+    const bool row_a = L.j0 >= 0 && L.j0 < g.ny, row_b = L.j0 + 1 < g.ny;                       // (j0 + 1 >= 0 always)
+    const size_t wrow = (size_t)(wj * RHS_UJ - 2 + PJ);
+    const double* gu = u + (size_t)(ib + 1 + HX) * ld + wrow;        // slot of step s (s = ib - 1, ib, ...): u, v of column s + 2, history of column s
+    const double* gv = v + (size_t)(ib + 1 + HX) * ld + wrow;
+    const double* ghu = nu0 + (size_t)(ib - 1 + HX) * ld + wrow;
+    const double* ghv = nv0 + (size_t)(ib - 1 + HX) * ld + wrow;
+    const int nsteps = ie - ib + 1;                                  // steps s = ib - 1 (warm-up: east face of column ib - 1 only) .. ie - 1
+    if (lane == 0) {
+#pragma unroll
+      for (int p = 0; p < RHS_D; p++) mbar_init(bar + p, 1);
+      mbar_init_fence();
+#pragma unroll
+      for (int p = 0; p < RHS_D; p++)
+        if (p < nsteps) {
+          mbar_expect_tx(bar + p, RHS_A * 512);
+          bulk_g2s(ring + (p * RHS_A + 0) * 32, gu + (size_t)p * ld, 512, bar + p);
+          bulk_g2s(ring + (p * RHS_A + 1) * 32, gv + (size_t)p * ld, 512, bar + p);
+          bulk_g2s(ring + (p * RHS_A + 2) * 32, ghu + (size_t)p * ld, 512, bar + p);
+          bulk_g2s(ring + (p * RHS_A + 3) * 32, ghv + (size_t)p * ld, 512, bar + p);
+        }
     }
-    const int i = n - 2, ig = g.gi0 + i;
-    if (i < ib - 1) continue;
-    if (ig < 0 || ig >= g.gnx) { cWsq = 0.0; cWuv = 0.0; continue; }   // uniform over the block
-    const bool fW = ig > 0, fE = ig < g.gnx - 1;
-    const int a = i + HX;
-    const double hxi = g.hx[a], rhx = g.rhx[a];
-    // east face (FS.cpp:232-237)
-    double cEsq, cEuv;
-    {
-      const double u1 = uC + 0.5 * hxi * sxCu, v1 = vC + 0.5 * hxi * sxCv;
-      double u2, v2;
-      if (fE) { const double h = 0.5 * g.hx[a + 1]; u2 = uP - h * sxPu; v2 = vP - h * sxPv; }
-      else { const GhostUV gh = ghost_uv(g, edges, 1, uC, vC); u2 = 0.5 * (uC + gh.u); v2 = 0.5 * (vC + gh.v); }
-      cEsq = flux_sq(u1, u2); cEuv = flux_uv(u1, v1, u2, v2);
-    }
-    if (i < ib) { cWsq = cEsq; cWuv = cEuv; continue; }   // warm-up column: only its east face is needed
-
-    // y neighbours of (i, j) from the adjacent lanes
-    const double uS = shfl_up1(uC), uN = shfl_dn1(uC), vS = shfl_up1(vC), vN = shfl_dn1(vC);
-    double syu = 0.0, syv = 0.0;
-    if (in_dom) { const GhostUV sl = slope_uv(g, edges, fN, fS, 3, 2, uC, vC, uN, vN, uS, vS, 2.0 * rsyp, 2.0 * rsym, rhy); syu = sl.u; syv = sl.v; }
-    const double syNu = shfl_dn1(syu), syNv = shfl_dn1(syv);
-    // north face (FS.cpp:246-251); the south face is the north face of the lane below
-    double cNsq, cNuv;
-    {
-      const double u1 = uC + 0.5 * hyj * syu, v1 = vC + 0.5 * hyj * syv;
-      double u2, v2;
-      if (fN) { u2 = uN - hyN * syNu; v2 = vN - hyN * syNv; }
-      else { const GhostUV gh = ghost_uv(g, edges, 3, uC, vC); u2 = 0.5 * (uC + gh.u); v2 = 0.5 * (vC + gh.v); }
-      cNsq = flux_sq(v1, v2); cNuv = flux_uv(u1, v1, u2, v2);
-    }
-    double cSsq = shfl_up1(cNsq), cSuv = shfl_up1(cNuv);
-    if (!fS) {   // south side is an edge (FS.cpp:239-244)
-      const double u2 = uC - 0.5 * hyj * syu, v2 = vC - 0.5 * hyj * syv;
-      const GhostUV gh = ghost_uv(g, edges, 2, uC, vC);
-      const double u1 = 0.5 * (uC + gh.u), v1 = 0.5 * (vC + gh.v);
-      cSsq = flux_sq(v1, v2); cSuv = flux_uv(u1, v1, u2, v2);
-    }
-    if (!fW) {   // west side is an edge (FS.cpp:225-230)
-      const double u2 = uC - 0.5 * hxi * sxCu, v2 = vC - 0.5 * hxi * sxCv;
-      const GhostUV gh = ghost_uv(g, edges, 0, uC, vC);
-      const double u1 = 0.5 * (uC + gh.u), v1 = 0.5 * (vC + gh.v);
-      cWsq = flux_sq(u1, u2); cWuv = flux_uv(u1, v1, u2, v2);
-    }
-    if (store) {
-      // DiffusiveFlux (FS.cpp:183-203)
-      double DuW, DuE, DuS, DuN, DvW, DvE, DvS, DvN;
-      if (fW) { const double s = ire * g.rsx[a - 1]; DuW = s * (uC - uM); DvW = s * (vC - vM); }
-      else { const double s = 0.5 * ire * rhx; const GhostUV gh = ghost_uv(g, edges, 0, uC, vC); DuW = s * (uC - gh.u); DvW = s * (vC - gh.v); }
-      if (fE) { const double s = ire * g.rsx[a]; DuE = s * (uP - uC); DvE = s * (vP - vC); }
-      else { const double s = -0.5 * ire * rhx; const GhostUV gh = ghost_uv(g, edges, 1, uC, vC); DuE = s * (uC - gh.u); DvE = s * (vC - gh.v); }
-      if (fS) { const double s = ire * rsym; DuS = s * (uC - uS); DvS = s * (vC - vS); }
-      else { const double s = 0.5 * ire * rhy; const GhostUV gh = ghost_uv(g, edges, 2, uC, vC); DuS = s * (uC - gh.u); DvS = s * (vC - gh.v); }
-      if (fN) { const double s = ire * rsyp; DuN = s * (uN - uC); DvN = s * (vN - vC); }
-      else { const double s = -0.5 * ire * rhy; const GhostUV gh = ghost_uv(g, edges, 3, uC, vC); DuN = s * (uC - gh.u); DvN = s * (vC - gh.v); }
-      const double diff_u = sc.dt * ((DuE - DuW) * rhx + (DuN - DuS) * rhy);
-      const double diff_v = sc.dt * ((DvE - DvW) * rhx + (DvN - DvS) * rhy);
-      const size_t id = (size_t)a * ld + row;
-      const double nu = (cEsq - cWsq) * rhx + (cNuv - cSuv) * rhy;   // FS.cpp:352
-      const double nv = (cEuv - cWuv) * rhx + (cNsq - cSsq) * rhy;   // FS.cpp:356
-      double ru = uC + 0.5 * sc.dt * hu + diff_u - 1.5 * sc.dt * nu;   // FS.cpp:335-359
-      double rv = vC + 0.5 * sc.dt * hv + diff_v - 1.5 * sc.dt * nv;
-      if (!(fW && fE && fS && fN)) {
-        const unsigned f = (fW ? F_W : (g.side_out[0] ? F_OW : 0u)) | (fE ? F_E : (g.side_out[1] ? F_OE : 0u)) |
-                           (fS ? F_S : (g.side_out[2] ? F_OS : 0u)) | (fN ? F_N : (g.side_out[3] ? F_ON : 0u));
-        rhs_boundary_terms<true>(g, edges, sc, f, i, j, gpx + id, gpy + id, ru, rv);
+    __syncwarp();
+    // register ring at step s: columns s - 1 (M), s (C), s + 1 (P) of u, v; x slopes of columns s (sC) and s + 1 (sP); column s + 2 (Q)
+    // arrives from the ring.  First step: s = ib - 1.
+    const size_t o0 = (size_t)(ib - 2 + HX) * ld + L.row;
+    D2 M, C, P, sC, sP;
+    M.u = ld2(u + o0); M.v = ld2(v + o0);                                         // column ib - 2
+    C.u = ld2(u + o0 + ld); C.v = ld2(v + o0 + ld);                               // column ib - 1
+    P.u = ld2(u + o0 + 2 * (size_t)ld); P.v = ld2(v + o0 + 2 * (size_t)ld);       // column ib
+    {  // x slope of column ib - 1
+      const int c = ib - 1, cgl = g.gi0 + c;
+      sC.u = slope2(M.u, C.u, P.u, s_x[0], s_x[1]);
+      sC.v = slope2(M.v, C.v, P.v, s_x[0], s_x[1]);
+      if (cgl == 0 || cgl == g.gnx - 1) {   // a column on the domain edge: its slope involves the ghost value (uniform branch)
+        const size_t id = (size_t)(c + HX) * ld + L.row;
+        if (row_a) { const UV t = slope_x<true>(g, edges, cell_flags<true>(g, c, L.j0), c, L.j0, u + id, v + id); sC.u.x = t.u; sC.v.x = t.v; }
+        if (row_b) { const UV t = slope_x<true>(g, edges, cell_flags<true>(g, c, L.j0 + 1), c, L.j0 + 1, u + id + 1, v + id + 1); sC.u.y = t.u; sC.v.y = t.v; }
       }
-      rhs_u[id] = ru;
-      rhs_v[id] = rv;
-      nrm[0] = fma(ru, ru, nrm[0]);
-      nrm[1] = fma(rv, rv, nrm[1]);
-      nu0[id] = nu;
-      nv0[id] = nv;
     }
-    cWsq = cEsq; cWuv = cEuv;
+    sP = sC;
+    double2 cWsq = make_double2(0.0, 0.0), cWuv = make_double2(0.0, 0.0);
+    int sink = 0;                                                                 // see ring_refill_point (ns_phys.cuh)
+    size_t o = (size_t)(ib - 1 + HX) * ld + L.row;                                // output pair of cell s
+    uint32_t parity = 0;
+    int p = 0;                                                                    // ring slot of this step
+#pragma unroll 1
+    for (int s = ib - 1; s < ie; s++) {
+      mbar_wait(bar + p, parity);
+      D2 Q;
+      Q.u = ring[(p * RHS_A + 0) * 32 + lane]; Q.v = ring[(p * RHS_A + 1) * 32 + lane];
+      const double2 hu = ring[(p * RHS_A + 2) * 32 + lane], hv = ring[(p * RHS_A + 3) * 32 + lane];
+      sink ^= __double2hiint(Q.u.x) ^ __double2hiint(Q.v.x) ^ __double2hiint(hu.x) ^ __double2hiint(hv.x);
+      const double* k6 = s_x + 6 * (s - ib + 1);                 // column s; k6 + 6: column s + 1
+      {  // x slope of column s + 1 from columns s (C), s + 1 (P), s + 2 (Q)
+        sP.u = slope2(C.u, P.u, Q.u, k6[6], k6[7]);
+        sP.v = slope2(C.v, P.v, Q.v, k6[6], k6[7]);
+        const int c = s + 1, cgl = g.gi0 + c;
+        if (cgl == 0 || cgl == g.gnx - 1) {                      // uniform: slope at a domain edge column involves the ghost value
+          const size_t id = (size_t)(c + HX) * ld + L.row;
+          if (row_a) { const UV t = slope_x<true>(g, edges, cell_flags<true>(g, c, L.j0), c, L.j0, u + id, v + id); sP.u.x = t.u; sP.v.x = t.v; }
+          if (row_b) { const UV t = slope_x<true>(g, edges, cell_flags<true>(g, c, L.j0 + 1), c, L.j0 + 1, u + id + 1, v + id + 1); sP.u.y = t.u; sP.v.y = t.v; }
+        }
+      }
+      // east face of cell s (FS.cpp:232-237): low state from cell s, high state from cell s + 1
+      double2 cEsq, cEuv;
+      {
+        const double hC = k6[2], hP = k6[8];
+        const double u1a = C.u.x + hC * sC.u.x, v1a = C.v.x + hC * sC.v.x, u2a = P.u.x - hP * sP.u.x, v2a = P.v.x - hP * sP.v.x;
+        const double u1b = C.u.y + hC * sC.u.y, v1b = C.v.y + hC * sC.v.y, u2b = P.u.y - hP * sP.u.y, v2b = P.v.y - hP * sP.v.y;
+        cEsq = make_double2(flux_sq(u1a, u2a), flux_sq(u1b, u2b));
+        cEuv = make_double2(flux_uv(u1a, v1a, u2a, v2a), flux_uv(u1b, v1b, u2b, v2b));
+      }
+      const int ig = g.gi0 + s;
+      if (s >= ib && ig > 0 && ig < g.gnx - 1) {                 // uniform: interior column; the first / last one belongs to the edge walk
+        // y neighbours of the pair from the adjacent lanes
+        const double uSa = __shfl_up_sync(0xffffffffu, C.u.y, 1), vSa = __shfl_up_sync(0xffffffffu, C.v.y, 1);
+        const double uNb = __shfl_down_sync(0xffffffffu, C.u.x, 1), vNb = __shfl_down_sync(0xffffffffu, C.v.x, 1);
+        // y slopes of rows a, b (FS.cpp:306-325)
+        double2 syu, syv;
+        syu.x = minmod((C.u.y - C.u.x) * sNa, (C.u.x - uSa) * sSa); syv.x = minmod((C.v.y - C.v.x) * sNa, (C.v.x - vSa) * sSa);
+        syu.y = minmod((uNb - C.u.y) * sNb, (C.u.y - C.u.x) * sNa); syv.y = minmod((vNb - C.v.y) * sNb, (C.v.y - C.v.x) * sNa);
+        if (edge_a && row_a) { const UV t = slope_y<true>(g, edges, cell_flags<true>(g, s, L.j0), s, L.j0, u + o, v + o); syu.x = t.u; syv.x = t.v; }
+        if (edge_b) { const UV t = slope_y<true>(g, edges, cell_flags<true>(g, s, L.j0 + 1), s, L.j0 + 1, u + o + 1, v + o + 1); syu.y = t.u; syv.y = t.v; }
+        const double syuN = __shfl_down_sync(0xffffffffu, syu.x, 1), syvN = __shfl_down_sync(0xffffffffu, syv.x, 1);   // slopes of row j0 + 2
+        // north faces (FS.cpp:246-251): of row a (between a and b) and of row b (between b and the next lane's a)
+        double2 cNsq, cNuv;
+        {
+          const double u1 = C.u.x + hya * syu.x, v1 = C.v.x + hya * syv.x, u2 = C.u.y - hyb * syu.y, v2 = C.v.y - hyb * syv.y;
+          cNsq.x = flux_sq(v1, v2); cNuv.x = flux_uv(u1, v1, u2, v2);
+        }
+        {
+          const double u1 = C.u.y + hyb * syu.y, v1 = C.v.y + hyb * syv.y, u2 = uNb - hyc * syuN, v2 = vNb - hyc * syvN;
+          cNsq.y = flux_sq(v1, v2); cNuv.y = flux_uv(u1, v1, u2, v2);
+        }
+        // south faces: of row a = north face of the previous lane's row b; of row b = north face of row a
+        const double cSsq_a = __shfl_up_sync(0xffffffffu, cNsq.y, 1), cSuv_a = __shfl_up_sync(0xffffffffu, cNuv.y, 1);
+        const double rhx = k6[3], dW = k6[4], dE = k6[5];
+        double2 ru, rv, nu, nv;
+        {  // row a
+          const double DuW = dW * (C.u.x - M.u.x), DvW = dW * (C.v.x - M.v.x), DuE = dE * (P.u.x - C.u.x), DvE = dE * (P.v.x - C.v.x);
+          const double DuS = dSa * (C.u.x - uSa), DvS = dSa * (C.v.x - vSa), DuN = dNa * (C.u.y - C.u.x), DvN = dNa * (C.v.y - C.v.x);
+          const double diff_u = sc.dt * ((DuE - DuW) * rhx + (DuN - DuS) * rhya), diff_v = sc.dt * ((DvE - DvW) * rhx + (DvN - DvS) * rhya);
+          nu.x = (cEsq.x - cWsq.x) * rhx + (cNuv.x - cSuv_a) * rhya;   // FS.cpp:352
+          nv.x = (cEuv.x - cWuv.x) * rhx + (cNsq.x - cSsq_a) * rhya;   // FS.cpp:356
+          ru.x = C.u.x + 0.5 * sc.dt * hu.x + diff_u - 1.5 * sc.dt * nu.x;   // FS.cpp:335-359
+          rv.x = C.v.x + 0.5 * sc.dt * hv.x + diff_v - 1.5 * sc.dt * nv.x;
+        }
+        {  // row b
+          const double DuW = dW * (C.u.y - M.u.y), DvW = dW * (C.v.y - M.v.y), DuE = dE * (P.u.y - C.u.y), DvE = dE * (P.v.y - C.v.y);
+          const double DuS = dNa * (C.u.y - C.u.x), DvS = dNa * (C.v.y - C.v.x), DuN = dNb * (uNb - C.u.y), DvN = dNb * (vNb - C.v.y);
+          const double diff_u = sc.dt * ((DuE - DuW) * rhx + (DuN - DuS) * rhyb), diff_v = sc.dt * ((DvE - DvW) * rhx + (DvN - DvS) * rhyb);
+          nu.y = (cEsq.y - cWsq.y) * rhx + (cNuv.y - cNuv.x) * rhyb;
+          nv.y = (cEuv.y - cWuv.y) * rhx + (cNsq.y - cNsq.x) * rhyb;
+          ru.y = C.u.y + 0.5 * sc.dt * hu.y + diff_u - 1.5 * sc.dt * nu.y;
+          rv.y = C.v.y + 0.5 * sc.dt * hv.y + diff_v - 1.5 * sc.dt * nv.y;
+        }
+        st_interior(rhs_u + o, ru, sa, sb);
+        st_interior(rhs_v + o, rv, sa, sb);
+        st_interior(nu0 + o, nu, sa, sb);
+        st_interior(nv0 + o, nv, sa, sb);
+        if (sa) { nrm[0] = fma(ru.x, ru.x, nrm[0]); nrm[1] = fma(rv.x, rv.x, nrm[1]); }
+        if (sb) { nrm[0] = fma(ru.y, ru.y, nrm[0]); nrm[1] = fma(rv.y, rv.y, nrm[1]); }
+      }
+      cWsq = cEsq; cWuv = cEuv;
+      M = C; C = P; P = Q; sC = sP;
+      o += ld;
+      ring_refill_point(sink);
+      if (lane == 0 && s - (ib - 1) + RHS_D < nsteps) {
+        const size_t q = (size_t)(s - (ib - 1) + RHS_D) * ld;
+        mbar_expect_tx(bar + p, RHS_A * 512);
+        bulk_g2s(ring + (p * RHS_A + 0) * 32, gu + q, 512, bar + p);
+        bulk_g2s(ring + (p * RHS_A + 1) * 32, gv + q, 512, bar + p);
+        bulk_g2s(ring + (p * RHS_A + 2) * 32, ghu + q, 512, bar + p);
+        bulk_g2s(ring + (p * RHS_A + 3) * 32, ghv + q, 512, bar + p);
+      }
+      if (++p == RHS_D) { p = 0; parity ^= 1; }
+    }
+    // cells that touch an edge: the reference's cell function, once per cell (reads the OLD history term of its own cell only)
+    for_edge_cells(g, ib, ie, edge_walk(g, wj), lane, [&](int i, int j) {
+      const size_t id = cidx(g, i, j);
+      const RhsOut r = rhs_cell<true>(g, edges, sc, i, j, u + id, v + id, nu0[id], nv0[id], gpx + id, gpy + id);
+      rhs_u[id] = r.rhs_u; rhs_v[id] = r.rhs_v; nu0[id] = r.nu; nv0[id] = r.nv;
+      nrm[0] = fma(r.rhs_u, r.rhs_u, nrm[0]); nrm[1] = fma(r.rhs_v, r.rhs_v, nrm[1]);
+    });
+    if (sink == 0x7fc0ffee && RI < 0) nrm[0] += 1.0;                 // never true: keeps `sink` alive (ring_refill_point)
   }
   if (norms) grid_reduce<2, OpSum>(nrm, red, norms);   // the velocity solves' |b|^2 (uniform branch)
 }

@@ -323,6 +323,66 @@ static int create_impl(nsgpu_ctx* ctx, const nsgpu_grid* G, const nsgpu_params* 
     }
   }
 
+  // ---- cluster tail: every level from the first one of at most CT_FIRST_CELLS cells down, in one kernel on a cluster of CT_C CTAs
+  if (const char* e = getenv("NSGPU_CTAIL")) ctx->use_ctail = atoi(e);
+  ctx->ctail_start = 0;
+  if (ctx->use_ctail && ctx->rect && (ctx->world == 1 || plan.rep_start > 0)) {
+    long long first_cells = CT_FIRST_CELLS;
+    if (const char* e = getenv("NSGPU_CTAIL_CELLS")) first_cells = atoll(e);
+    const int nl = (int)ctx->levels.size();
+    int ts = 0;
+    for (int l = 1; l < nl; l++)
+      if ((long long)ctx->levels[l].g.gnx * ctx->levels[l].g.ny <= first_cells) { ts = l; break; }
+    bool ok = ts > 0 && nl - ts <= CT_MAX_LEVELS && (plan.rep_start == 0 || ts >= plan.rep_start);
+    for (int op = 0; op < 2 && ok; op++) {
+      CtDesc& T = ctx->ctail[op];
+      T.nlev = nl - ts; T.nu_pre = ctx->nu_pre; T.nu_post = ctx->nu_post;
+      T.coarse_sweeps = ctx->levels.back().coarse_sweeps;
+      T.coarse_omega = 1.0;
+      if (op == 1) {   // as for the one-CTA tail: optimal SOR for the Neumann problem on the long coarsest grid
+        const int n = std::max(ctx->levels.back().g.gnx, ctx->levels.back().g.ny);
+        if (n >= 4) T.coarse_omega = 2.0 / (1.0 + std::sin(3.14159265358979323846 / n));
+        if (const char* e = getenv("NSGPU_COARSE_OMEGA")) T.coarse_omega = atof(e);
+      }
+      int off = 0;
+      bool dist = true;
+      for (int k = 0; k < T.nlev; k++) {
+        const Level& L = ctx->levels[ts + k];
+        CtLevel& t = T.lv[k];
+        t.nx = L.g.nx; t.ny = L.g.ny; t.cx = L.cx; t.cy = L.cy; t.ld = L.g.ld;
+        t.mcx = L.mcx[op]; t.mcy = L.mcy[op];
+        // a level stays distributed while its columns split evenly and every coarse column has both children in one CTA
+        const bool last = k == T.nlev - 1;
+        dist = dist && t.nx % CT_C == 0 && (last || t.cx == 1 || (t.nx / CT_C) % 2 == 0);
+        t.dist = dist ? 1 : 0;
+        t.nc = dist ? t.nx / CT_C : t.nx;
+        if ((long long)t.nc * ((t.ny + 1) / 2) > (long long)CT_KC * CT_THREADS) ok = false;
+        t.xoff = off; off += (t.nc + 2) * (t.ny + 2);
+        t.boff = off; off += t.nc * t.ny;
+        t.rdoff = off; off += t.nc * t.ny;
+        t.sxoff = off; off += 3 * t.nc;
+        t.syoff = off; off += 3 * t.ny;
+      }
+      if (!T.lv[0].dist) ok = false;
+      T.smem_doubles = off + (off & 1);
+      if ((size_t)T.smem_doubles * sizeof(double) > 200 * 1024) ok = false;
+    }
+    if (ok) {
+      const size_t bytes = (size_t)ctx->ctail[0].smem_doubles * sizeof(double);
+      ok = cudaFuncSetAttribute(k_cluster_tail, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes) == cudaSuccess;
+      for (int op = 0; op < 2 && ok; op++) {
+        void* q = nullptr;
+        NS_CUDA(cudaMalloc(&q, bytes * CT_C));
+        ctx->owned.push_back(q);
+        ctx->ctail_img[op] = (double*)q;
+        k_ctail_image<<<CT_C, CT_THREADS, 0, ctx->stream>>>(ctx->ctail[op], ctx->ctail_img[op]);
+        NS_CUDA(cudaGetLastError());
+      }
+      cudaGetLastError();
+      if (ok) ctx->ctail_start = ts;
+    }
+  }
+
   // ---- fields
   const size_t S = ctx->levels[0].stride;
   double** fields[] = {&ctx->u, &ctx->v, &ctx->phi, &ctx->conv_u, &ctx->conv_v, &ctx->gpx, &ctx->gpy,

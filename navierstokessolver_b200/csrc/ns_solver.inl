@@ -269,6 +269,23 @@ static int march_sweeps(nsgpu_ctx* ctx, const Level& L, OpCoef c, int n, double*
 static int vcycle_fused(nsgpu_ctx* ctx, int l, OpCoef c, double** x, double** xt, const double* b, bool xzero, double* norm_out,
                         SolveCtl* ctl, double* src0 = nullptr) {
   Level& L = ctx->levels[l];
+  if (ctx->ctail_start > 0 && l == ctx->ctail_start && march_tab_ok(L, c)) {   // the rest of the cycle in one kernel on a cluster of CT_C CTAs
+    const CtDesc& T = ctx->ctail[op_tab(c)];
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(CT_C); cfg.blockDim = dim3(CT_THREADS);
+    cfg.dynamicSmemBytes = (size_t)T.smem_doubles * sizeof(double);
+    cfg.stream = ctx->stream;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeClusterDimension;
+    at[0].val.clusterDim.x = CT_C; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+    cfg.attrs = at; cfg.numAttrs = 1;
+    trace_begin(ctx, 99998);
+    cudaError_t e = cudaLaunchKernelEx(&cfg, k_cluster_tail, T, (const double*)ctx->ctail_img[op_tab(c)], b, *x, ctx->tail_dbg);
+    trace_end(ctx);
+    if (e != cudaSuccess) { ctx->err = std::string("cluster tail launch: ") + cudaGetErrorString(e); return NSGPU_ERR_CUDA; }
+    NS_LAUNCH_CHECK();
+    return 0;
+  }
   if (ctx->tail_start > 0 && l == ctx->tail_start && march_tab_ok(L, c)) {   // the rest of the cycle in one single-CTA kernel
     const TailDesc& T = ctx->tail[op_tab(c)];
     trace_begin(ctx, 99999);
@@ -912,6 +929,32 @@ static dim3 phys_grid(const void* kern, int fields, const Level& L, int* ri, siz
   return dim3(gx, (L.g.nx + r_best - 1) / r_best);
 }
 
+// launch shape of k_rhs_march over `ncols` columns: whole waves of CTAs, like phys_grid
+static dim3 rhs_grid(const Level& L, int ncols, int* ri, size_t* smem) {
+  static int wave = 0;
+  if (!wave) {
+    int per_sm = 0, dev = 0, sms = 148;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    cudaFuncSetAttribute(k_rhs_march, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)rhs_smem(1024));
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_rhs_march, RHS_THREADS, rhs_smem(128)) != cudaSuccess || per_sm < 1) per_sm = 2;
+    wave = per_sm * sms;
+  }
+  const int gx = ((L.g.ny + RHS_UJ - 1) / RHS_UJ + RHS_WARPS - 1) / RHS_WARPS;
+  long long best = -1;
+  int r_best = ncols;
+  for (int r = 8; r <= std::min(ncols, 1024); r += 4) {
+    const long long ctas = (long long)gx * ((ncols + r - 1) / r);
+    const long long cost = ((ctas + wave - 1) / wave) * (r + RHS_D + 4);
+    if (best < 0 || cost < best) { best = cost; r_best = r; }
+  }
+  if (ncols < 8) r_best = ncols;
+  while ((long long)gx * ((ncols + r_best - 1) / r_best) > RED_MAX_BLOCKS) r_best *= 2;
+  *ri = r_best;
+  *smem = rhs_smem(r_best);
+  return dim3(gx, (ncols + r_best - 1) / r_best);
+}
+
 static int phase_rhs(nsgpu_ctx* ctx) {   // ConstructRHS_V, FS.cpp:546
   ctx->halo_w.clear();   // every field may have been rewritten by a non-marching kernel since
   const Level& L = ctx->levels[0];
@@ -921,12 +964,10 @@ static int phase_rhs(nsgpu_ctx* ctx) {   // ConstructRHS_V, FS.cpp:546
   if ((rc = halo_exchange(ctx, L, ctx->gpy, 1))) return rc;
   const StepConst sc{ctx->dt, ctx->re};
   if (ctx->rect && ctx->rhs_march && L.g.nx >= 2) {   // rectangles: marching kernel, every slope and face flux once
-    const int gx = ((L.g.ny + RHS_UJ - 1) / RHS_UJ + RHS_WARPS - 1) / RHS_WARPS;
-    const int chunks = std::max(1, std::min(L.g.nx / 8, (148 * 10 + gx - 1) / gx));
-    const int ri = (L.g.nx + chunks - 1) / chunks;
-    const dim3 grid(gx, (L.g.nx + ri - 1) / ri);
-    k_rhs_march<<<grid, RHS_THREADS, 0, ctx->stream>>>(L.g, ctx->d_edges, sc, ctx->u, ctx->v, ctx->conv_u, ctx->conv_v, ctx->gpx, ctx->gpy,
-                                                       ctx->rhs_u, ctx->rhs_v, ri, ctx->red, ctx->fuse_bn2 ? ctx->d_scal + 30 : nullptr, 0, L.g.nx);
+    int ri; size_t sh;
+    const dim3 grid = rhs_grid(L, L.g.nx, &ri, &sh);
+    k_rhs_march<<<grid, RHS_THREADS, sh, ctx->stream>>>(L.g, ctx->d_edges, sc, ctx->u, ctx->v, ctx->conv_u, ctx->conv_v, ctx->gpx, ctx->gpy,
+                                                        ctx->rhs_u, ctx->rhs_v, ri, ctx->red, ctx->fuse_bn2 ? ctx->d_scal + 30 : nullptr, 0, L.g.nx);
     NS_LAUNCH_CHECK();
     if (ctx->fuse_bn2) {
       if ((rc = allreduce(ctx, ctx->d_scal + 30, 2, ncclSum))) return rc;
@@ -947,12 +988,10 @@ static int phase_rhs(nsgpu_ctx* ctx) {   // ConstructRHS_V, FS.cpp:546
 static int phase_rhs_cols(nsgpu_ctx* ctx, int c0, int c1) {
   const Level& L = ctx->levels[0];
   const StepConst sc{ctx->dt, ctx->re};
-  const int gx = ((L.g.ny + RHS_UJ - 1) / RHS_UJ + RHS_WARPS - 1) / RHS_WARPS;
-  const int chunks = std::max(1, std::min(L.g.nx / 8, (148 * 10 + gx - 1) / gx));
-  const int ri = (L.g.nx + chunks - 1) / chunks;
-  const dim3 grid(gx, (c1 - c0 + ri - 1) / ri);
-  k_rhs_march<<<grid, RHS_THREADS, 0, ctx->stream>>>(L.g, ctx->d_edges, sc, ctx->u, ctx->v, ctx->conv_u, ctx->conv_v, ctx->gpx, ctx->gpy,
-                                                     ctx->rhs_u, ctx->rhs_v, ri, ctx->red, nullptr, c0, c1);
+  int ri; size_t sh;
+  const dim3 grid = rhs_grid(L, c1 - c0, &ri, &sh);
+  k_rhs_march<<<grid, RHS_THREADS, sh, ctx->stream>>>(L.g, ctx->d_edges, sc, ctx->u, ctx->v, ctx->conv_u, ctx->conv_v, ctx->gpx, ctx->gpy,
+                                                      ctx->rhs_u, ctx->rhs_v, ri, ctx->red, nullptr, c0, c1);
   NS_LAUNCH_CHECK();
   return 0;
 }
