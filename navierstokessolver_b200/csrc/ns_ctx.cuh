@@ -129,6 +129,8 @@ struct nsgpu_ctx {
   int march_rb_min_nx = 0;                       // levels with fewer columns keep uniform chunks (NSGPU_RB_MINNX)
   int march_rb = 0;                              // width of the short boundary chunks of pushing passes (NSGPU_RB, 0 = off)
   unsigned last_gather_ctas = 0;                 // CTAs of the last restriction pass that gathered onto the replicated level
+  unsigned long long* selfpush_hdr = nullptr;
+  int selfpush = 0;                              // PROFILING ONLY (NSGPU_SELFPUSH=1, one rank): run the pushing kernel variants with this rank as its own neighbour
   int* d_errflag = nullptr;
   int use_p2p = 1;
   std::unordered_map<const double*, int> halo_w; // valid halo width of a buffer since its last write

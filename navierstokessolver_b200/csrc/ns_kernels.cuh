@@ -124,6 +124,7 @@ struct PeerTable {
   long long off[MAX_RANKS];
   unsigned long long* hdr;   // this rank's header
   int* err;                  // set when a wait times out (instead of hanging the GPU)
+  int nowait;                // TIMING EXPERIMENT ONLY (NSGPU_XRED_NOWAIT=1): cross-rank reductions return world x the local value without waiting
 };
 
 __device__ __forceinline__ unsigned long long ld_acquire_sys(const unsigned long long* p) {
@@ -131,8 +132,11 @@ __device__ __forceinline__ unsigned long long ld_acquire_sys(const unsigned long
   asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
   return v;
 }
+// TIMING EXPERIMENTS ONLY (NSGPU_NOWAIT=1, set at nsgpu_create): no device-side wait waits -- results are wrong, kernel times are the pure execution times
+static __device__ int g_ns_nowait = 0;
 // spin until *p >= need (exact == false) or *p == need (exact == true); gives up after ~3 s and raises the error flag
 __device__ __forceinline__ void wait_word(const unsigned long long* p, unsigned long long need, bool exact, int* err) {
+  if (g_ns_nowait) return;
   const long long t0 = clock64();
   for (;;) {
     const unsigned long long v = ld_acquire_sys(p);
@@ -145,6 +149,7 @@ __device__ __forceinline__ void wait_word(const unsigned long long* p, unsigned 
 // so all ranks get the same bits.  Four slot buffers: a rank can be at most one reduction ahead of the slowest one.
 // Slot of (buffer, rank): three words {value a, value b, sequence}.
 __device__ inline void xreduce_sum2(const PeerTable* pt, double a, double b, double* ra, double* rb) {
+  if (pt->nowait) { *ra = a * pt->world; *rb = b * pt->world; return; }
   unsigned long long* hdr = pt->hdr;
   const unsigned long long s = hdr[HDR_XSEQ] + 1;
   hdr[HDR_XSEQ] = s;

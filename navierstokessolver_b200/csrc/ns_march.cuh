@@ -251,6 +251,62 @@ struct Marcher {
   }
 };
 
+// The march of one warp over its chunk: sets the Marcher up, runs the pipelined column loop, returns the warp lane's share of |r|^2
+// (RES == 2).  P: this CTA stores boundary columns into a neighbour's halo (peer memory).  A kernel of the pushing family holds BOTH
+// instances and picks one per CTA (uniform branch): the conditional peer stores in the loop body cost every CTA 50 % (the loads of the
+// register prefetch are no longer hoisted over them: 148 us against 100 us per fine-level pass at 4096^2, long-scoreboard stalls
+// doubled -- profiles/r2_t_up_push_ncu_raw.csv), so only the two short boundary chunks of a slab run the pushing loop.
+template <int NSW, bool PROLONG, int RES, int PF, bool SOR, bool P>
+__device__ __forceinline__ double march_run(const LevelGeom& g, const double* __restrict__ mcy, const double* __restrict__ xin,
+                                            const double* __restrict__ b, double* __restrict__ xout, const MarchXfer& xf, const double* s_c,
+                                            int ib, int ie, int n0, int nend, int r0, int lane, int wj) {
+  using M = Marcher<NSW, PROLONG, RES, PF, SOR, P>;
+  constexpr int L = M::L;
+  constexpr int HJ = march_halo(NSW, RES);
+  constexpr int UJ = 64 - 2 * HJ;
+  constexpr int HL = HJ / 2;
+  // warps past the last strip run with every predicate false (no divergent exit: the shuffles stay convergent)
+  M m;
+  m.xf = xf;
+  m.ld = g.ld; m.ny = g.ny; m.ib = ib; m.ie = ie; m.nxl = g.nx;
+  m.pfo = (size_t)MARCH_PFD * g.ld;
+  m.pushL = P && xf.dL != 0 && ib < xf.zone;
+  m.pushR = P && xf.dR != 0 && ie > g.nx - xf.zone;
+  m.j0 = wj * UJ - HJ + 2 * lane;                            // even, >= -HJ >= -PJ
+  const int jl = min(m.j0, (g.ny + PJ - 2) & ~1);            // lanes past the column end: an even (16-byte aligned) zero pair
+  {
+    const int a = jl + PJ;                                   // entries outside the domain have cs = cn = 0
+    m.k.csa = mcy[3 * a]; m.k.cna = mcy[3 * a + 1]; m.k.dya = mcy[3 * a + 2];
+    m.k.csb = mcy[3 * a + 3]; m.k.cnb = mcy[3 * a + 4]; m.k.dyb = mcy[3 * a + 5];
+  }
+  const size_t joff = (size_t)(jl + PJ);
+  m.useful = lane >= HL && lane < 32 - HL;
+  m.jstore2 = m.useful && (m.j0 + 1 < g.ny);
+  m.jstore1 = m.useful && (m.j0 < g.ny) && !m.jstore2;
+  m.cc = s_c + 3 * (n0 - r0);
+  m.px = xin ? xin + (size_t)(n0 + HX) * g.ld + joff : nullptr;
+  m.pb = b + (size_t)(n0 + HX) * g.ld + joff;
+  m.po = xout + (size_t)(n0 - L + HX) * g.ld + joff;        // only dereferenced inside [ib, ie)
+  m.pbc = nullptr;
+  if (RES == 1) m.pbc = xf.bc + (size_t)((xf.rcx == 2 ? (ib >> 1) : ib) + HX) * xf.ldbc + (xf.rcy == 2 ? (size_t)((m.j0 >> 1) + PJ) : joff);
+  m.pxc = nullptr;
+  if (PROLONG) m.pxc = xf.xc + (size_t)((xf.pcy == 2 ? ((jl + 2 * PJ) >> 1) - PJ : jl) + PJ);
+  m.racc = make_double2(0.0, 0.0);
+  m.acc = 0.0;
+  m.xshift = xf.shift ? *xf.shift * xf.shift_scale : 0.0;
+#pragma unroll
+  for (int q = 0; q < M::RL; q++) { m.X[q] = make_double2(0.0, 0.0); m.Bq[q] = make_double2(0.0, 0.0); }
+#pragma unroll
+  for (int p = 0; p < PF; p++) m.load_col(n0 + p, m.X[PF - 1 - p], m.Bq[PF - 1 - p]);
+
+#pragma unroll 2
+  for (int n = n0; n < nend; n += 2) {
+    m.template step<true>(n);
+    m.template step<false>(n + 1);
+  }
+  return m.acc;
+}
+
 // NOTE: no minBlocksPerSM here -- naming one (even 1) makes ptxas spend 15-40 more registers on every variant.
 template <int NSW, bool PROLONG, int RES, int PF, bool SOR = false, bool PUSH = false>
 __global__ void __launch_bounds__(MARCH_THREADS)
@@ -260,8 +316,6 @@ k_march(LevelGeom g, const double* __restrict__ mcx, const double* __restrict__ 
   constexpr int L = M::L;
   constexpr int HJ = march_halo(NSW, RES);   // halo cells per side of the strip
   constexpr int LL = march_lead(NSW, RES);   // halo columns per side of the chunk
-  constexpr int UJ = 64 - 2 * HJ;
-  constexpr int HL = HJ / 2;                 // halo lanes per side
   extern __shared__ double s_c[];            // (cw, ce, dx) of columns [r0, r0 + nrows)
   const int lane = threadIdx.x & 31;
   const int wj = blockIdx.x * MARCH_WARPS + (threadIdx.x >> 5);
@@ -299,44 +353,11 @@ k_march(LevelGeom g, const double* __restrict__ mcx, const double* __restrict__ 
   __syncthreads();
 
   // warps past the last strip run with every predicate false (no divergent exit: the shuffles stay convergent)
-  M m;
-  m.xf = xf;
-  m.ld = g.ld; m.ny = g.ny; m.ib = ib; m.ie = ie; m.nxl = g.nx;
-  m.pfo = (size_t)MARCH_PFD * g.ld;
-  m.pushL = PUSH && xf.dL != 0 && ib < xf.zone;
-  m.pushR = PUSH && xf.dR != 0 && ie > g.nx - xf.zone;
-  m.j0 = wj * UJ - HJ + 2 * lane;                            // even, >= -HJ >= -PJ
-  const int jl = min(m.j0, (g.ny + PJ - 2) & ~1);            // lanes past the column end: an even (16-byte aligned) zero pair
-  {
-    const int a = jl + PJ;                                   // entries outside the domain have cs = cn = 0
-    m.k.csa = mcy[3 * a]; m.k.cna = mcy[3 * a + 1]; m.k.dya = mcy[3 * a + 2];
-    m.k.csb = mcy[3 * a + 3]; m.k.cnb = mcy[3 * a + 4]; m.k.dyb = mcy[3 * a + 5];
-  }
-  const size_t joff = (size_t)(jl + PJ);
-  m.useful = lane >= HL && lane < 32 - HL;
-  m.jstore2 = m.useful && (m.j0 + 1 < g.ny);
-  m.jstore1 = m.useful && (m.j0 < g.ny) && !m.jstore2;
-  m.cc = s_c + 3 * (n0 - r0);
-  m.px = xin ? xin + (size_t)(n0 + HX) * g.ld + joff : nullptr;
-  m.pb = b + (size_t)(n0 + HX) * g.ld + joff;
-  m.po = xout + (size_t)(n0 - L + HX) * g.ld + joff;        // only dereferenced inside [ib, ie)
-  m.pbc = nullptr;
-  if (RES == 1) m.pbc = xf.bc + (size_t)((xf.rcx == 2 ? (ib >> 1) : ib) + HX) * xf.ldbc + (xf.rcy == 2 ? (size_t)((m.j0 >> 1) + PJ) : joff);
-  m.pxc = nullptr;
-  if (PROLONG) m.pxc = xf.xc + (size_t)((xf.pcy == 2 ? ((jl + 2 * PJ) >> 1) - PJ : jl) + PJ);
-  m.racc = make_double2(0.0, 0.0);
-  m.acc = 0.0;
-  m.xshift = xf.shift ? *xf.shift * xf.shift_scale : 0.0;
-#pragma unroll
-  for (int q = 0; q < M::RL; q++) { m.X[q] = make_double2(0.0, 0.0); m.Bq[q] = make_double2(0.0, 0.0); }
-#pragma unroll
-  for (int p = 0; p < PF; p++) m.load_col(n0 + p, m.X[PF - 1 - p], m.Bq[PF - 1 - p]);
-
-#pragma unroll 2
-  for (int n = n0; n < nend; n += 2) {
-    m.template step<true>(n);
-    m.template step<false>(n + 1);
-  }
+  double acc_r2;
+  if (PUSH && (xf.gather || ib < xf.zone || ie > g.nx - xf.zone))   // uniform over the CTA
+    acc_r2 = march_run<NSW, PROLONG, RES, PF, SOR, PUSH>(g, mcy, xin, b, xout, xf, s_c, ib, ie, n0, nend, r0, lane, wj);
+  else
+    acc_r2 = march_run<NSW, PROLONG, RES, PF, SOR, false>(g, mcy, xin, b, xout, xf, s_c, ib, ie, n0, nend, r0, lane, wj);
   if (PUSH) {
     __syncthreads();          // every store of this CTA happens before thread 0's fence (cumulativity)
     if (threadIdx.x == 0) {
@@ -361,7 +382,7 @@ k_march(LevelGeom g, const double* __restrict__ mcx, const double* __restrict__ 
     }
   }
   if (RES == 2) {
-    double acc[1] = {m.acc};
+    double acc[1] = {acc_r2};
     grid_reduce<1, OpSum>(acc, xf.red, xf.out, CtlEpilogue{xf.ctl, xf.pt, xf.out});
   }
 }

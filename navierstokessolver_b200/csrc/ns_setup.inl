@@ -175,6 +175,7 @@ static int create_impl(nsgpu_ctx* ctx, const nsgpu_grid* G, const nsgpu_params* 
   // ---- several ranks: one arena for everything the marching passes write, opened by both neighbours (CUDA IPC)
   if (const char* e = getenv("NSGPU_P2P")) ctx->use_p2p = atoi(e);
   if (const char* e = getenv("NSGPU_TRACE")) ctx->trace = atoi(e);
+  ctx->march_rb = -1;   // several ranks: boundary chunks (pushing loop) sized automatically; NSGPU_RB=0: uniform chunks, > 0: that width
   if (const char* e = getenv("NSGPU_RB")) ctx->march_rb = atoi(e);
   if (const char* e = getenv("NSGPU_RHS_MARCH")) ctx->rhs_march = atoi(e);
   if (const char* e = getenv("NSGPU_PHYS_MARCH")) ctx->phys_march = atoi(e);
@@ -436,11 +437,34 @@ static int create_impl(nsgpu_ctx* ctx, const nsgpu_grid* G, const nsgpu_params* 
     for (int r = 0; r < ctx->world; r++) t.off[r] = r == ctx->rank ? 0 : (long long)((ctx->peers[r] - ctx->arena) / (ptrdiff_t)sizeof(double));
     t.hdr = (unsigned long long*)ctx->arena;
     t.err = ctx->d_errflag;
+    t.nowait = getenv("NSGPU_XRED_NOWAIT") ? atoi(getenv("NSGPU_XRED_NOWAIT")) : 0;
+    if (getenv("NSGPU_NOWAIT")) { const int one = atoi(getenv("NSGPU_NOWAIT")); t.nowait = one; NS_CUDA(cudaMemcpyToSymbol(g_ns_nowait, &one, sizeof one)); }
     void* p = nullptr;
     NS_CUDA(cudaMalloc(&p, sizeof(PeerTable)));
     ctx->owned.push_back(p);
     NS_CUDA(cudaMemcpy(p, &t, sizeof t, cudaMemcpyHostToDevice));
     ctx->d_pt = (PeerTable*)p;
+  }
+  if (ctx->world == 1 && getenv("NSGPU_SELFPUSH") && atoi(getenv("NSGPU_SELFPUSH")) && ctx->rect) {
+    // profiling aid: the PUSH variants of k_march on ONE GPU (ncu cannot follow several ranks): the rank is its own left and right
+    // neighbour, pushes land in its own halo columns (results are wrong), waits are disabled
+    PeerTable t{};
+    t.world = 1; t.rank = 0; t.nowait = 1;
+    void* h = nullptr;
+    NS_CUDA(cudaMalloc(&h, HDR_WORDS * sizeof(unsigned long long)));
+    NS_CUDA(cudaMemset(h, 0, HDR_WORDS * sizeof(unsigned long long)));
+    ctx->owned.push_back(h);
+    t.hdr = (unsigned long long*)h;
+    ctx->selfpush_hdr = t.hdr;
+    t.err = ctx->d_errflag;
+    void* p = nullptr;
+    NS_CUDA(cudaMalloc(&p, sizeof(PeerTable)));
+    ctx->owned.push_back(p);
+    NS_CUDA(cudaMemcpy(p, &t, sizeof t, cudaMemcpyHostToDevice));
+    ctx->d_pt = (PeerTable*)p;
+    const int one = 1;
+    NS_CUDA(cudaMemcpyToSymbol(g_ns_nowait, &one, sizeof one));
+    ctx->selfpush = 1;
   }
   NS_CUDA(cudaDeviceSynchronize());
   if (ctx->world > 1) {   // nobody pushes into an arena that is still being zeroed

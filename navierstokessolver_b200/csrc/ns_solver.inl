@@ -166,9 +166,10 @@ static int march_pass(nsgpu_ctx* ctx, const Level& L, OpCoef c, int nsw, double*
   static const bool nopush = getenv("NSGPU_NOPUSH") != nullptr;   // debugging: arena mapped, halo columns through NCCL
   // (a buffer outside the arena has no image on the neighbour: `xout + offset` would be a wild peer pointer -- NCCL then)
   auto in_arena = [&](const double* q) { return (const char*)q >= ctx->arena && (const char*)q < ctx->arena + ctx->arena_bytes; };
-  const bool push = ctx->world > 1 && ctx->use_p2p && ctx->arena && !L.replicated && (ctx->peerL || ctx->peerR) && !nopush &&
-                    in_arena(xout) && (!Cr || in_arena(Cr->b));
-  const bool push_b = push && Cr && !Cr->replicated;
+  const bool selfpush = ctx->selfpush && L.g.nx >= 2 * HX;
+  const bool push = selfpush || (ctx->world > 1 && ctx->use_p2p && ctx->arena && !L.replicated && (ctx->peerL || ctx->peerR) && !nopush &&
+                                 in_arena(xout) && (!Cr || in_arena(Cr->b)));
+  const bool push_b = push && Cr && (selfpush ? Cr->g.nx >= 2 * HX : !Cr->replicated);
   MarchKernel kern = nullptr;
 #define NS_MARCH(NSW, PRO, RES, PF) do { if (push) kern = k_march<NSW, PRO, RES, PF, false, true>; else kern = k_march<NSW, PRO, RES, PF, false, false>; } while (0)
 #define NS_MARCH_RES(NSW, PRO) do { if (res == 0) NS_MARCH(NSW, PRO, 0, MARCH_PF); else if (res == 1) NS_MARCH(NSW, PRO, 1, MARCH_PF); else NS_MARCH(NSW, PRO, 2, MARCH_PF); } while (0)
@@ -188,32 +189,48 @@ static int march_pass(nsgpu_ctx* ctx, const Level& L, OpCoef c, int nsw, double*
   else { if (Cp) NS_MARCH_RES(2, true); else NS_MARCH_RES(2, false); }
 #undef NS_MARCH_RES
 #undef NS_MARCH
-  // several ranks: short boundary chunks (even width >= the push zone), see k_march
-  int rb = 0;
-  if (push && ctx->march_rb > 0 && L.g.nx >= ctx->march_rb_min_nx) {
-    rb = std::max(ctx->march_rb, 2 * (HX - 1));
-    rb += rb & 1;
-    if (L.g.nx < 2 * rb + 4 || (L.g.nx & 1)) rb = 0;
+  // Several ranks: the first and the last chunk of the slab run the pushing loop (march_run<..., true>), which costs about 1.5 x the
+  // plain loop per column; every other chunk runs the plain one.  The two boundary chunks are therefore made SHORTER, so that all CTAs
+  // of the launch take the same time: rb columns with 1.5 (rb + ovh) = ri + ovh, the interior shared evenly between the other rows.
+  const int ovh = 2 * lead + 2 * nsw + 2, wave = march_wave(kern);
+  int rb = 0, ri = march_chunk(ctx, L, uj, ovh, wave, 0);
+  if (push && ctx->march_rb != 0 && !(L.g.nx & 1) && L.g.nx >= ctx->march_rb_min_nx && !(Cr && Cr->replicated && !selfpush)) {
+    const int rows = (L.g.nx + ri - 1) / ri, rb_min = 2 * (HX - 1);   // >= the push zone of a restricting pass
+    if (ctx->march_rb > 0) { rb = std::max(ctx->march_rb, rb_min); rb += rb & 1; }
+    else if (rows >= 3) {
+      double best = 1e300;
+      for (int r = rb_min; 2 * r + 4 <= L.g.nx; r += 2) {
+        int rin = (L.g.nx - 2 * r + rows - 3) / (rows - 2);
+        rin += rin & 1;
+        const double cost = std::max(1.5 * (r + ovh), (double)(rin + ovh));
+        if (cost < best) { best = cost; rb = r; }
+        if (1.5 * (r + ovh) > rin + ovh) break;
+      }
+      if (rb) { ri = (L.g.nx - 2 * rb + rows - 3) / (rows - 2); ri += ri & 1; ri = std::max(ri, 2); }
+    }
+    if (rb && (L.g.nx < 2 * rb + 4)) rb = 0;
+    if (!rb) ri = march_chunk(ctx, L, uj, ovh, wave, 0);
+    else if (ctx->march_rb > 0) ri = march_chunk(ctx, L, uj, ovh, wave, rb);
   }
-  const int ri = march_chunk(ctx, L, uj, 2 * lead + 2 * nsw + 2, march_wave(kern), rb);
   dim3 grid(((L.g.ny + uj - 1) / uj + MARCH_WARPS - 1) / MARCH_WARPS, (L.g.nx + ri - 1) / ri);
   if (rb) grid.y = 2 + (unsigned)((L.g.nx - 2 * rb + ri - 1) / ri);
   const size_t sh = (size_t)3 * (std::max(ri, rb) + 2 * lead + 2 * nsw + 8) * sizeof(double);   // >= nrows of k_march
-  const bool gather = push && Cr && Cr->replicated;   // the slab of the replicated coarse right-hand side goes to every rank
+  const bool gather = push && !selfpush && Cr && Cr->replicated;   // the slab of the replicated coarse right-hand side goes to every rank
   if (push) {
     const long long offL = ctx->peerL ? (long long)((ctx->peerL - ctx->arena) / (ptrdiff_t)sizeof(double)) : 0;
     const long long offR = ctx->peerR ? (long long)((ctx->peerR - ctx->arena) / (ptrdiff_t)sizeof(double)) : 0;
     xf.pushw = std::min(HX - 1, L.g.nx);
-    xf.dL = ctx->peerL ? offL + (long long)L.g.nx * L.g.ld : 0;
-    xf.dR = ctx->peerR ? offR - (long long)L.g.nx * L.g.ld : 0;
+    xf.dL = (ctx->peerL || selfpush) ? offL + (long long)L.g.nx * L.g.ld : 0;
+    xf.dR = (ctx->peerR || selfpush) ? offR - (long long)L.g.nx * L.g.ld : 0;
     if (push_b) {
       xf.nxc = Cr->g.nx;
-      xf.dbL = ctx->peerL ? offL + (long long)Cr->g.nx * Cr->g.ld : 0;
-      xf.dbR = ctx->peerR ? offR - (long long)Cr->g.nx * Cr->g.ld : 0;
+      xf.dbL = (ctx->peerL || selfpush) ? offL + (long long)Cr->g.nx * Cr->g.ld : 0;
+      xf.dbR = (ctx->peerR || selfpush) ? offR - (long long)Cr->g.nx * Cr->g.ld : 0;
     }
     xf.zone = xf.pushw * (push_b ? L.cx : 1);
     xf.pt = ctx->d_pt;
     xf.hdr = (unsigned long long*)ctx->arena; xf.offL = offL; xf.offR = offR;
+    if (selfpush) { xf.hdr = ctx->selfpush_hdr; xf.offL = xf.offR = 0; }
     xf.gather = gather ? 1 : 0;
     // chunks that start inside the left zone / end inside the right zone signal once per CTA
     const int gy = (int)grid.y, zone = std::min(xf.zone, L.g.nx);
