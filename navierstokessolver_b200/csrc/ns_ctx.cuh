@@ -133,6 +133,7 @@ struct nsgpu_ctx {
   int selfpush = 0;                              // PROFILING ONLY (NSGPU_SELFPUSH=1, one rank): run the pushing kernel variants with this rank as its own neighbour
   int* d_errflag = nullptr;
   int use_p2p = 1;
+  int hx_push = 0;                               // halo exchanges outside the solves through peer stores (k_halo_push) instead of NCCL send / recv
   std::unordered_map<const double*, int> halo_w; // valid halo width of a buffer since its last write
   // coarse tail (ns_tail.cuh): levels >= tail_start run in one single-CTA kernel; 0 = no tail
   int tail_start = 0, use_tail = 1;

@@ -118,7 +118,8 @@ static_assert(sizeof(SolveCtl) == 64, "SolveCtl is one 64-byte block");
 // arena to rank r's, so `local_pointer + off[r]` is the same object on rank r.
 constexpr int MAX_RANKS = 8;
 enum : int { HDR_ARR_L = 0, HDR_ARR_R = 1, HDR_TAIL_ARR = 2, HDR_SENT_L = 3, HDR_SENT_R = 4, HDR_TICKET = 5, HDR_TAIL_NEED = 6,
-             HDR_XSEQ = 7, HDR_XSLOTS = 16 /* 4 buffers x MAX_RANKS x 3 words */, HDR_WORDS = 512 };
+             HDR_XSEQ = 7, /* 8: HDR_XVSEQ */ HDR_HX_ARR_L = 9, HDR_HX_ARR_R = 10, HDR_HX_NEED = 11, HDR_HX_TICKET = 12,
+             HDR_XSLOTS = 16 /* 4 buffers x MAX_RANKS x 3 words */, HDR_WORDS = 512 };
 struct PeerTable {
   int world, rank;
   long long off[MAX_RANKS];
@@ -223,6 +224,71 @@ struct SumEpilogue {   // out[0] <- sum over ranks
   double* out_w;
   __device__ void operator()(const double* out) const { if (pt) out_w[0] = xreduce_sum(pt, out[0]); }
 };
+
+// out[0..N) <- sums over the ranks (rank order: the same bits everywhere); no-op on one rank
+template <int N>
+struct XSumEpilogue {
+  const PeerTable* pt;
+  __device__ void operator()(const double* out_c) const {
+    if (!pt) return;
+    double* out = const_cast<double*>(out_c);
+    double mine[N], all[MAX_RANKS * N];
+#pragma unroll
+    for (int k = 0; k < N; k++) mine[k] = out[k];
+    xexchange<N>(pt, mine, all);
+#pragma unroll
+    for (int k = 0; k < N; k++) {
+      double t = 0.0;
+      for (int r = 0; r < pt->world; r++) t += all[r * N + k];
+      out[k] = t;
+    }
+  }
+};
+
+// Halo exchange of up to HXP_MAX fields outside the solves, without a library call: every rank stores the `width` first / last columns of
+// each field straight into its neighbours' halo columns (peer memory over NVLink), the last block to finish tells both neighbours
+// (system-scope fence, one arrival counter per side) and then waits for THEIR arrival -- all ranks run the same sequence of exchanges,
+// so "the k-th exchange has arrived" is a count, kept on the device (graph-safe).  When the kernel ends, this rank's halo columns are in
+// place.  Why a neighbour's early push cannot overwrite halo columns still being read: ns_solver.inl, halo_exchange_push.
+constexpr int HXP_MAX = 4;
+struct HaloPushArgs {
+  double* f[HXP_MAX];
+  int width[HXP_MAX];
+  int nf, ld, nx;
+  long long offL, offR;        // arena offsets (doubles) of the neighbours; 0 = none
+  unsigned long long* hdr;
+  int* err;
+};
+__global__ void __launch_bounds__(256) k_halo_push(HaloPushArgs a) {
+  const int k = blockIdx.y;
+  if (k < a.nf) {
+    const size_t n2 = (size_t)a.width[k] * a.ld / 2;                 // double2 per side (ld is a multiple of 4)
+    const double2* sL = reinterpret_cast<const double2*>(a.f[k] + (size_t)HX * a.ld);
+    const double2* sR = reinterpret_cast<const double2*>(a.f[k] + (size_t)(HX + a.nx - a.width[k]) * a.ld);
+    // my column c (0 .. w) is the left neighbour's halo column nx + c; my column nx - w + c the right neighbour's column -w + c
+    double2* dL = reinterpret_cast<double2*>(a.f[k] + (size_t)HX * a.ld + a.offL + (long long)a.nx * a.ld);
+    double2* dR = reinterpret_cast<double2*>(a.f[k] + (size_t)(HX + a.nx - a.width[k]) * a.ld + a.offR - (long long)a.nx * a.ld);
+    for (size_t q = blockIdx.x * (size_t)blockDim.x + threadIdx.x; q < n2; q += (size_t)gridDim.x * blockDim.x) {
+      if (a.offL) dL[q] = sL[q];
+      if (a.offR) dR[q] = sR[q];
+    }
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    __threadfence_system();                                           // this block's peer stores are visible before its ticket
+    const unsigned total = gridDim.x * gridDim.y;
+    if (atomicAdd(a.hdr + HDR_HX_TICKET, 1ull) == total - 1) {
+      a.hdr[HDR_HX_TICKET] = 0;
+      __threadfence_system();
+      if (a.offL) atomicAdd_system(a.hdr + a.offL + HDR_HX_ARR_R, 1ull);
+      if (a.offR) atomicAdd_system(a.hdr + a.offR + HDR_HX_ARR_L, 1ull);
+      const unsigned long long need = a.hdr[HDR_HX_NEED] + 1;
+      a.hdr[HDR_HX_NEED] = need;
+      if (a.offL) wait_word(a.hdr + HDR_HX_ARR_L, need, false, a.err);
+      if (a.offR) wait_word(a.hdr + HDR_HX_ARR_R, need, false, a.err);
+    }
+  }
+}
 
 // projection kernel: out[0..3] = the four maxima, out[4] = sum(phi) of this rank; over all ranks when pt != nullptr
 struct CorrectEpilogue {

@@ -146,7 +146,7 @@ __device__ __forceinline__ void st_interior(double* p, const double2& v, bool sa
 // b = Div_V(u*, v*) / dt ; out = {sum b, sum b^2}
 __global__ void __launch_bounds__(PH_THREADS, PH_MIN_CTAS)
 k_div_march(LevelGeom g, const EdgeDev* __restrict__ edges, StepConst sc, const double* __restrict__ u, const double* __restrict__ v,
-            double* __restrict__ b, int RI, Reducer red, double* __restrict__ out) {
+            double* __restrict__ b, int RI, Reducer red, double* __restrict__ out, const PeerTable* pt) {
   extern __shared__ __align__(128) unsigned char s_raw[];
   double* s_x = reinterpret_cast<double*>(s_raw);
   const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5, wj = blockIdx.x * PH_WARPS + wid;
@@ -231,7 +231,7 @@ k_div_march(LevelGeom g, const EdgeDev* __restrict__ edges, StepConst sc, const 
     });
     if (sink == 0x7fc0ffee && RI < 0) acc[0] += 1.0;               // never true (RI > 0): keeps `sink` and with it the consumption of every slot load
   }
-  grid_reduce<2, OpSum>(acc, red, out);
+  grid_reduce<2, OpSum>(acc, red, out, XSumEpilogue<2>{pt});   // summed over the ranks in the epilogue (peer map)
 }
 
 // ---------------------------------------------------------------------------------------------------------

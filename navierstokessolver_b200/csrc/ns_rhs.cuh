@@ -51,7 +51,7 @@ __global__ void __launch_bounds__(RHS_THREADS, 3)
 k_rhs_march(LevelGeom g, const EdgeDev* __restrict__ edges, StepConst sc, const double* __restrict__ u,
             const double* __restrict__ v, double* __restrict__ nu0, double* __restrict__ nv0,
             const double* __restrict__ gpx, const double* __restrict__ gpy, double* __restrict__ rhs_u,
-            double* __restrict__ rhs_v, int RI, Reducer red, double* __restrict__ norms, int i_begin, int i_end) {
+            double* __restrict__ rhs_v, int RI, Reducer red, double* __restrict__ norms, int i_begin, int i_end, const PeerTable* pt) {
   extern __shared__ __align__(128) unsigned char s_raw[];
   double* s_x = reinterpret_cast<double*>(s_raw);
   const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5, wj = blockIdx.x * RHS_WARPS + wid;
@@ -231,7 +231,7 @@ k_rhs_march(LevelGeom g, const EdgeDev* __restrict__ edges, StepConst sc, const 
     });
     if (sink == 0x7fc0ffee && RI < 0) nrm[0] += 1.0;                 // never true: keeps `sink` alive (ring_refill_point)
   }
-  if (norms) grid_reduce<2, OpSum>(nrm, red, norms);   // the velocity solves' |b|^2 (uniform branch)
+  if (norms) grid_reduce<2, OpSum>(nrm, red, norms, XSumEpilogue<2>{pt});   // the velocity solves' |b|^2 (uniform branch), summed over the ranks
 }
 
 }  // namespace nsgpu

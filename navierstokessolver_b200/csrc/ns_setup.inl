@@ -444,6 +444,10 @@ static int create_impl(nsgpu_ctx* ctx, const nsgpu_grid* G, const nsgpu_params* 
     ctx->owned.push_back(p);
     NS_CUDA(cudaMemcpy(p, &t, sizeof t, cudaMemcpyHostToDevice));
     ctx->d_pt = (PeerTable*)p;
+    // The exchanges around the solves go through peer stores too on the all-multigrid route (uniform rectangles): there the order of
+    // kernels and exchanges is fixed and audited (halo_exchange_push); the Krylov routes keep NCCL's rendezvous.
+    ctx->hx_push = ctx->rect && ctx->solver == 0 && !ctx->krylov_phi;
+    if (const char* e = getenv("NSGPU_HX_PUSH")) ctx->hx_push = ctx->hx_push && atoi(e);
   }
   if (ctx->world == 1 && getenv("NSGPU_SELFPUSH") && atoi(getenv("NSGPU_SELFPUSH")) && ctx->rect) {
     // profiling aid: the PUSH variants of k_march on ONE GPU (ncu cannot follow several ranks): the rank is its own left and right

@@ -36,16 +36,64 @@ static inline dim3 grid_cols(const LevelGeom& g, int threads, int max_blocks = 1
   return dim3(gx, gy, 1);
 }
 
+// Halo exchange of up to HXP_MAX fields in ONE kernel, through peer memory (k_halo_push): no NCCL call, capturable in a graph.
+// Safety of the one-sided stores.  A neighbour may be ahead of this rank: its stores of exchange k can land here while this rank is still
+// between its own exchanges k - 1 and k (not earlier: the neighbour finishes exchange k - 1 only after this rank has signalled it).  So no
+// kernel that runs between two consecutive exchanges may read the halo columns of a field of the LATER exchange.  The sequence of one
+// time step on this route is
+//   X(u, v, divPhi_y) K_rhs  X(rhs_u, rhs_v) X(u) solve_u X(v) solve_v  X(u*, v*) K_div  X(rhs_phi) X(phi) solve_phi  X(phi) K_correct
+// and every kernel between two exchanges reads only halos exchanged BEFORE it and none of the next exchange's fields' halos (the solves'
+// own passes exchange through the separate march protocol; the X(phi) behind solve_phi rewrites values its last pass has pushed already).
+static int halo_exchange_push(nsgpu_ctx* ctx, const Level& L, double* const* f, const int* width, int nf) {
+  HaloPushArgs a{};
+  a.nf = 0; a.ld = L.g.ld; a.nx = L.g.nx;
+  size_t nmax = 0;
+  for (int k = 0; k < nf; k++) {
+    const int w = std::min(width[k], std::min(HX, L.g.nx));
+    if (w <= 0) continue;
+    a.f[a.nf] = f[k]; a.width[a.nf] = w; a.nf++;
+    nmax = std::max(nmax, (size_t)w * L.g.ld / 2);
+    ctx->halo_w[f[k]] = w;
+  }
+  if (!a.nf) return 0;
+  a.offL = ctx->peerL ? (long long)((ctx->peerL - ctx->arena) / (ptrdiff_t)sizeof(double)) : 0;
+  a.offR = ctx->peerR ? (long long)((ctx->peerR - ctx->arena) / (ptrdiff_t)sizeof(double)) : 0;
+  a.hdr = (unsigned long long*)ctx->arena;
+  a.err = ctx->d_errflag;
+  const dim3 grid((unsigned)std::max<size_t>(1, std::min<size_t>(16, (nmax + 255) / 256)), (unsigned)a.nf);
+  k_halo_push<<<grid, 256, 0, ctx->stream>>>(a);
+  NS_LAUNCH_CHECK();
+  return 0;
+}
+static inline bool hx_push_ok(const nsgpu_ctx* ctx, const Level& L, const double* f) {
+  return ctx->hx_push && &L == &ctx->levels[0] && !L.replicated && ctx->arena && (const char*)f >= ctx->arena && (const char*)f < ctx->arena + ctx->arena_bytes;
+}
+// several fields at once (one kernel on the peer-store route, one NCCL group per field otherwise)
+static int halo_exchange(nsgpu_ctx* ctx, const Level& L, double* f, int width, bool march_consumer = false);
+static int halo_exchange_n(nsgpu_ctx* ctx, const Level& L, std::initializer_list<std::pair<double*, int>> fw) {
+  if (ctx->world == 1 || L.replicated) return 0;
+  bool all = fw.size() <= (size_t)HXP_MAX;
+  for (auto& e : fw) all = all && hx_push_ok(ctx, L, e.first);
+  if (all) {
+    double* f[HXP_MAX]; int w[HXP_MAX]; int n = 0;
+    for (auto& e : fw) { f[n] = e.first; w[n] = e.second; n++; }
+    return halo_exchange_push(ctx, L, f, w, n);
+  }
+  for (auto& e : fw) { int rc = halo_exchange(ctx, L, e.first, e.second, false); if (rc) return rc; }
+  return 0;
+}
+
 // One-column-block halo exchange with the x-neighbours: `width` columns, contiguous (width * ld doubles).
 // march_consumer: the reader is a marching pass, which waits for the neighbours' pushes itself -- if the buffer's halo
 // was filled by a pushing pass (ctx->halo_w) there is nothing to send.
-static int halo_exchange(nsgpu_ctx* ctx, const Level& L, double* f, int width, bool march_consumer = false) {
+static int halo_exchange(nsgpu_ctx* ctx, const Level& L, double* f, int width, bool march_consumer) {
   if (ctx->world == 1 || L.replicated) return 0;
   width = std::min(width, std::min(HX, L.g.nx));
   if (march_consumer) {
     auto it = ctx->halo_w.find(f);
     if (it != ctx->halo_w.end() && it->second >= width) return 0;
   }
+  if (hx_push_ok(ctx, L, f)) return halo_exchange_push(ctx, L, &f, &width, 1);
   if (ctx->capturing) ctx->capture_nccl = true;   // solve graphs hold this library's kernels only
   const size_t n = (size_t)width * L.g.ld;
   const int nx = L.g.nx;
@@ -976,18 +1024,16 @@ static int phase_rhs(nsgpu_ctx* ctx) {   // ConstructRHS_V, FS.cpp:546
   ctx->halo_w.clear();   // every field may have been rewritten by a non-marching kernel since
   const Level& L = ctx->levels[0];
   int rc;
-  if ((rc = halo_exchange(ctx, L, ctx->u, 2))) return rc;
-  if ((rc = halo_exchange(ctx, L, ctx->v, 2))) return rc;
-  if ((rc = halo_exchange(ctx, L, ctx->gpy, 1))) return rc;
+  if ((rc = halo_exchange_n(ctx, L, {{ctx->u, 2}, {ctx->v, 2}, {ctx->gpy, 1}}))) return rc;
   const StepConst sc{ctx->dt, ctx->re};
   if (ctx->rect && ctx->rhs_march && L.g.nx >= 2) {   // rectangles: marching kernel, every slope and face flux once
     int ri; size_t sh;
     const dim3 grid = rhs_grid(L, L.g.nx, &ri, &sh);
     k_rhs_march<<<grid, RHS_THREADS, sh, ctx->stream>>>(L.g, ctx->d_edges, sc, ctx->u, ctx->v, ctx->conv_u, ctx->conv_v, ctx->gpx, ctx->gpy,
-                                                        ctx->rhs_u, ctx->rhs_v, ri, ctx->red, ctx->fuse_bn2 ? ctx->d_scal + 30 : nullptr, 0, L.g.nx);
+                                                        ctx->rhs_u, ctx->rhs_v, ri, ctx->red, ctx->fuse_bn2 ? ctx->d_scal + 30 : nullptr, 0, L.g.nx, ctx->d_pt);
     NS_LAUNCH_CHECK();
     if (ctx->fuse_bn2) {
-      if ((rc = allreduce(ctx, ctx->d_scal + 30, 2, ncclSum))) return rc;
+      if (!ctx->d_pt && (rc = allreduce(ctx, ctx->d_scal + 30, 2, ncclSum))) return rc;
       ctx->bn2_ready[0] = ctx->bn2_ready[1] = true;
     }
     return 0;
@@ -1008,7 +1054,7 @@ static int phase_rhs_cols(nsgpu_ctx* ctx, int c0, int c1) {
   int ri; size_t sh;
   const dim3 grid = rhs_grid(L, c1 - c0, &ri, &sh);
   k_rhs_march<<<grid, RHS_THREADS, sh, ctx->stream>>>(L.g, ctx->d_edges, sc, ctx->u, ctx->v, ctx->conv_u, ctx->conv_v, ctx->gpx, ctx->gpy,
-                                                      ctx->rhs_u, ctx->rhs_v, ri, ctx->red, nullptr, c0, c1);
+                                                      ctx->rhs_u, ctx->rhs_v, ri, ctx->red, nullptr, c0, c1, nullptr);
   NS_LAUNCH_CHECK();
   return 0;
 }
@@ -1018,8 +1064,7 @@ static int phase_velocity(nsgpu_ctx* ctx, SolveResult* ru, SolveResult* rv) {   
   const Level& L = ctx->levels[0];
   // initial guess u^n (the reference starts from zero; the converged u* is the same to tolerance)
   int rc;
-  if ((rc = halo_exchange(ctx, L, ctx->rhs_u, HX - 1))) return rc;   // the fused passes recompute up to 4 halo columns
-  if ((rc = halo_exchange(ctx, L, ctx->rhs_v, HX - 1))) return rc;
+  if ((rc = halo_exchange_n(ctx, L, {{ctx->rhs_u, HX - 1}, {ctx->rhs_v, HX - 1}}))) return rc;   // the fused passes recompute up to 4 halo columns
   double *gu = ctx->vel_guess_rhs ? ctx->rhs_u : ctx->u, *gv = ctx->vel_guess_rhs ? ctx->rhs_v : ctx->v;
   if ((rc = solve(ctx, 0, coef_v(ctx), &ctx->ustar, ctx->rhs_u, ctx->rtol_u, ru, gu))) return rc;
   if ((rc = solve(ctx, 1, coef_v(ctx), &ctx->vstar, ctx->rhs_v, ctx->rtol_u, rv, gv))) return rc;
@@ -1030,21 +1075,20 @@ static int phase_div(nsgpu_ctx* ctx, bool remove_mean) {   // FS.cpp:549-550
   ctx->halo_w.clear();   // every field may have been rewritten by a non-marching kernel since
   const Level& L = ctx->levels[0];
   int rc;
-  if ((rc = halo_exchange(ctx, L, ctx->ustar, 1))) return rc;
-  if ((rc = halo_exchange(ctx, L, ctx->vstar, 1))) return rc;
+  if ((rc = halo_exchange_n(ctx, L, {{ctx->ustar, 1}, {ctx->vstar, 1}}))) return rc;
   const StepConst sc{ctx->dt, ctx->re};
   const dim3 grid = grid_cols(L.g, 256);
   if (ctx->rect && ctx->phys_march) {
     int ri; size_t sh;
     const dim3 pg = phys_grid((const void*)k_div_march, 2, L, &ri, &sh);
-    k_div_march<<<pg, PH_THREADS, sh, ctx->stream>>>(L.g, ctx->d_edges, sc, ctx->ustar, ctx->vstar, ctx->rhs_phi, ri, ctx->red, ctx->d_scal + 28);
+    k_div_march<<<pg, PH_THREADS, sh, ctx->stream>>>(L.g, ctx->d_edges, sc, ctx->ustar, ctx->vstar, ctx->rhs_phi, ri, ctx->red, ctx->d_scal + 28, ctx->d_pt);
   } else {
 #define CALL(RECT) k_div_rhs<RECT><<<grid, 256, 0, ctx->stream>>>(L.g, ctx->d_edges, sc, ctx->ustar, ctx->vstar, ctx->rhs_phi, ctx->red, ctx->d_scal + 28)
     NS_DISPATCH_RECT(ctx->rect, CALL);
 #undef CALL
   }
   NS_LAUNCH_CHECK();
-  if ((rc = allreduce(ctx, ctx->d_scal + 28, 2, ncclSum))) return rc;
+  if (!(ctx->rect && ctx->phys_march && ctx->d_pt) && (rc = allreduce(ctx, ctx->d_scal + 28, 2, ncclSum))) return rc;   // (k_div_march sums over the ranks itself)
   k_bn2_from_sums<<<1, 1, 0, ctx->stream>>>(ctx->d_scal + 32, ctx->d_scal + 28, remove_mean ? 1.0 / (double)ctx->n_cells_global : 0.0);
   NS_LAUNCH_CHECK();
   ctx->bn2_ready[2] = ctx->fuse_bn2 != 0;
