@@ -16,7 +16,7 @@ HOST_DEPS = $(wildcard $(HOST)/*.cpp $(HOST)/*.h)
 all: $(PKG)/libnsgpu.so bin/main
 
 $(PKG)/libnsgpu.so: $(CU_DEPS) $(HOST_DEPS)
-	$(NVCC) $(NVFLAGS) -shared $(CSRC)/nsgpu.cu $(HOST_SRC) -Iinclude -I$(HOST) -o $@ -lnccl
+	$(NVCC) $(NVFLAGS) -shared $(CSRC)/nsgpu.cu $(HOST_SRC) -Iinclude -I$(HOST) -o $@ -lnccl -ldl
 
 bin/main: $(PKG)/libnsgpu.so $(HOST)/main/ns_main.cpp
 	@mkdir -p bin

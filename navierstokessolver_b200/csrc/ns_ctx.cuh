@@ -2,6 +2,7 @@
 #pragma once
 #include <cuda_runtime.h>
 #include <nccl.h>
+#include <nvtx3/nvToolsExt.h>   // header-only: ranges per phase of the time step (visible in nsys / ncu --nvtx; no-ops without a tool attached)
 #include <string>
 #include <vector>
 #include <unordered_map>

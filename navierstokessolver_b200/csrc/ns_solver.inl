@@ -964,6 +964,11 @@ static void finish_results(nsgpu_ctx* ctx, SolveResult* ru, SolveResult* rv, Sol
 // ---------------------------------------------------------------------------------------------------------
 // Phases of one time step
 
+struct NvtxRange {   // host-side range around the launches of one phase (the kernels inherit it in nsys / ncu --nvtx views)
+  explicit NvtxRange(const char* name) { nvtxRangePushA(name); }
+  ~NvtxRange() { nvtxRangePop(); }
+};
+
 // Launch shape of the projection kernels of ns_phys.cuh: gx CTAs of 4 warps cover the rows, the columns are cut into chunks of *ri
 // so that the CTAs fill whole waves (same estimate as march_chunk: waves x (columns per chunk + start-up)).
 static dim3 phys_grid(const void* kern, int fields, const Level& L, int* ri, size_t* smem) {
@@ -1021,6 +1026,7 @@ static dim3 rhs_grid(const Level& L, int ncols, int* ri, size_t* smem) {
 }
 
 static int phase_rhs(nsgpu_ctx* ctx) {   // ConstructRHS_V, FS.cpp:546
+  NvtxRange nvtx_("nsgpu:ConstructRHS_V");
   ctx->halo_w.clear();   // every field may have been rewritten by a non-marching kernel since
   const Level& L = ctx->levels[0];
   int rc;
@@ -1060,6 +1066,7 @@ static int phase_rhs_cols(nsgpu_ctx* ctx, int c0, int c1) {
 }
 
 static int phase_velocity(nsgpu_ctx* ctx, SolveResult* ru, SolveResult* rv) {   // FS.cpp:547-548
+  NvtxRange nvtx_("nsgpu:KSPSolve_u_v");
   ctx->halo_w.clear();   // every field may have been rewritten by a non-marching kernel since
   const Level& L = ctx->levels[0];
   // initial guess u^n (the reference starts from zero; the converged u* is the same to tolerance)
@@ -1072,6 +1079,7 @@ static int phase_velocity(nsgpu_ctx* ctx, SolveResult* ru, SolveResult* rv) {   
 }
 
 static int phase_div(nsgpu_ctx* ctx, bool remove_mean) {   // FS.cpp:549-550
+  NvtxRange nvtx_("nsgpu:ConstructRHS_phi");
   ctx->halo_w.clear();   // every field may have been rewritten by a non-marching kernel since
   const Level& L = ctx->levels[0];
   int rc;
@@ -1103,6 +1111,7 @@ static int phase_div(nsgpu_ctx* ctx, bool remove_mean) {   // FS.cpp:549-550
 }
 
 static int phase_phi(nsgpu_ctx* ctx, SolveResult* rp) {   // FS.cpp:551, warm start from phi^n (FS.cpp:54)
+  NvtxRange nvtx_("nsgpu:KSPSolve_phi");
   if (ctx->phi_shift && !ctx->phi_sum_known) { int rcn = phi_normalize(ctx); if (rcn) return rcn; }   // two phi solves without a projection in between
   ctx->halo_w.clear();   // every field may have been rewritten by a non-marching kernel since
   const Level& L = ctx->levels[0];
@@ -1151,6 +1160,7 @@ static int phase_phi(nsgpu_ctx* ctx, SolveResult* rp) {   // FS.cpp:551, warm st
 }
 
 static int phase_correct(nsgpu_ctx* ctx, double mm[4]) {   // FS.cpp:552-557
+  NvtxRange nvtx_("nsgpu:CorrectVelocities");
   ctx->halo_w.clear();   // every field may have been rewritten by a non-marching kernel since
   const Level& L = ctx->levels[0];
   int rc;
