@@ -266,6 +266,26 @@ def parity_vs_one_rank(ns, capi, torch, dist, rank, world, local_rank, nccl_id, 
     return out
 
 
+def main_on_n_gpus(n):
+    """The drop-in driver on n GPUs of this box: `bin/main <grid> <sim>` with NSGPU_GPUS=n against the same command on one GPU --
+    stdout and FlowData CSVs compared (tests/test_gpu_parity.py holds the comparison; the driver's test box has one GPU)."""
+    import pathlib
+    import tempfile
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    try:
+        import test_gpu_parity as tp
+        wd = pathlib.Path(tempfile.mkdtemp())
+        t0 = time.perf_counter()
+        one = tp.run_main_on_gpus(1, wd, steps=20)
+        t1 = time.perf_counter()
+        many = tp.run_main_on_gpus(n, wd, steps=20)
+        t2 = time.perf_counter()
+        worst = tp.compare_main_runs(one, many)
+        return {"gpus": n, "case": "cavity 128x128, 20 steps, exports every 5", "worst_difference": worst,
+                "ok": bool(worst <= 2e-6), "wall_s": {"1": t1 - t0, str(n): t2 - t1}}
+    except Exception as e:   # reported, never fatal for the bench line
+        return {"gpus": n, "ok": False, "error": repr(e)[:400]}
+
 def ours(args, rank, world, local_rank):
     import numpy as np
     import navierstokessolver_b200 as ns
@@ -410,6 +430,12 @@ def ours(args, rank, world, local_rank):
             extras["size_1024"] = timed_case(ns, torch, dist, rank, world, local_rank, nccl_id, 1024, 1024, args, steps=args.steps, warmup=args.warmup)
             # ---- (d) fixed work: exactly 4 phi V-cycles and 4 x 4 SOR sweeps per velocity solve every step, whatever the residuals
             extras["fixed_work_4096"] = timed_case(ns, torch, dist, rank, world, local_rank, nccl_id, ny, nxl, args, steps=args.steps, warmup=3, fixed_cycles=4)
+
+        # ---- (e) several GPUs behind the unchanged command line: bin/main with NSGPU_GPUS=N against NSGPU_GPUS=1 (rank 0 runs both)
+        if world > 1:
+            if rank == 0:
+                extras["main_multi_gpu"] = main_on_n_gpus(world)
+            dist.barrier()
 
     cpu = cpu_baseline_sample() if (rank == 0 and world == 1 and not args.no_cpu_baseline) else None
 

@@ -9,6 +9,7 @@
 #include <cstdio>
 #include <cstring>
 #include <cmath>
+#include <unistd.h>
 #include "../../include/nsgpu.h"
 #include "ns_kernels.cuh"
 #include "ns_phys.cuh"
@@ -108,6 +109,7 @@ struct nsgpu_ctx {
   char* arena = nullptr;                 // device allocation (owned)
   size_t arena_bytes = 0, arena_used = 0;
   char* peers[nsgpu::MAX_RANKS] = {};                   // every other rank's arena in this process' address space (CUDA IPC)
+  bool peer_inproc[nsgpu::MAX_RANKS] = {};              // that rank lives in this process: its arena is reached by peer access, not IPC
   char *peerL = nullptr, *peerR = nullptr;       // the neighbours' (aliases into peers[])
   nsgpu::PeerTable* d_pt = nullptr;                     // device copy of the peer map (nullptr: one rank, or NCCL-only exchange)
   bool capturing = false, capture_nccl = false;  // a solve graph is being captured / an NCCL call was issued meanwhile

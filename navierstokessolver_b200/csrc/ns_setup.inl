@@ -101,7 +101,7 @@ static void destroy_ctx(nsgpu_ctx* ctx) {
   if (!ctx) return;
   cudaSetDevice(ctx->device);
   if (ctx->stream) cudaStreamSynchronize(ctx->stream);
-  for (int r = 0; r < MAX_RANKS; r++) if (ctx->peers[r]) cudaIpcCloseMemHandle(ctx->peers[r]);
+  for (int r = 0; r < MAX_RANKS; r++) if (ctx->peers[r] && !ctx->peer_inproc[r]) cudaIpcCloseMemHandle(ctx->peers[r]);
   if (ctx->comm) ncclCommDestroy(ctx->comm);
   if (ctx->arena) cudaFree(ctx->arena);
   for (auto& L : ctx->levels)
@@ -204,21 +204,35 @@ static int create_impl(nsgpu_ctx* ctx, const nsgpu_grid* G, const nsgpu_params* 
     NS_CUDA(cudaMalloc((void**)&ctx->arena, ctx->arena_bytes));
     NS_CUDA(cudaMemset(ctx->arena, 0, ctx->arena_bytes));
     ctx->arena_used = HDR_WORDS * sizeof(unsigned long long);   // control header: arrival / sent counters, reduction slots
-    // exchange the IPC handles through the communicator that exists anyway
-    cudaIpcMemHandle_t mine;
-    NS_CUDA(cudaIpcGetMemHandle(&mine, ctx->arena));
-    static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle size");
+    // exchange the IPC handles through the communicator that exists anyway.  Ranks of ONE process (FluidSolver with NSGPU_GPUS=N: one
+    // host thread per GPU) cannot open each other's IPC handles; they pass the arena's address itself and enable peer access.
+    struct PeerInfo { cudaIpcMemHandle_t h; long long pid; unsigned long long ptr; int dev, pad; };
+    static_assert(sizeof(cudaIpcMemHandle_t) == 64 && sizeof(PeerInfo) == 88, "peer record size");
+    PeerInfo mine{};
+    NS_CUDA(cudaIpcGetMemHandle(&mine.h, ctx->arena));
+    mine.pid = (long long)getpid(); mine.ptr = (unsigned long long)(uintptr_t)ctx->arena; mine.dev = ctx->device;
     char* d_h = nullptr;
-    NS_CUDA(cudaMalloc((void**)&d_h, 64 * (size_t)ctx->world));
-    NS_CUDA(cudaMemcpy(d_h + 64 * (size_t)ctx->rank, &mine, 64, cudaMemcpyHostToDevice));
-    NS_NCCL(ncclAllGather(d_h + 64 * (size_t)ctx->rank, d_h, 64, ncclChar, ctx->comm, ctx->stream));
+    NS_CUDA(cudaMalloc((void**)&d_h, sizeof(PeerInfo) * (size_t)ctx->world));
+    NS_CUDA(cudaMemcpy(d_h + sizeof(PeerInfo) * (size_t)ctx->rank, &mine, sizeof mine, cudaMemcpyHostToDevice));
+    NS_NCCL(ncclAllGather(d_h + sizeof(PeerInfo) * (size_t)ctx->rank, d_h, sizeof(PeerInfo), ncclChar, ctx->comm, ctx->stream));
     NS_CUDA(cudaStreamSynchronize(ctx->stream));
-    std::vector<cudaIpcMemHandle_t> all(ctx->world);
-    NS_CUDA(cudaMemcpy(all.data(), d_h, 64 * (size_t)ctx->world, cudaMemcpyDeviceToHost));
+    std::vector<PeerInfo> all(ctx->world);
+    NS_CUDA(cudaMemcpy(all.data(), d_h, sizeof(PeerInfo) * (size_t)ctx->world, cudaMemcpyDeviceToHost));
     cudaFree(d_h);
     bool ok = true;
-    for (int r = 0; r < ctx->world; r++)
-      if (r != ctx->rank && cudaIpcOpenMemHandle((void**)&ctx->peers[r], all[r], cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) { ctx->peers[r] = nullptr; ok = false; }
+    for (int r = 0; r < ctx->world; r++) {
+      if (r == ctx->rank) continue;
+      if (all[r].pid == mine.pid) {   // same process: direct peer access
+        int can = 0;
+        cudaError_t e = all[r].dev == ctx->device ? cudaSuccess : cudaDeviceCanAccessPeer(&can, ctx->device, all[r].dev);
+        if (e == cudaSuccess && all[r].dev != ctx->device && can) {
+          e = cudaDeviceEnablePeerAccess(all[r].dev, 0);
+          if (e == cudaErrorPeerAccessAlreadyEnabled) { e = cudaSuccess; cudaGetLastError(); }
+        } else if (all[r].dev != ctx->device) e = cudaErrorInvalidDevice;
+        if (e == cudaSuccess) { ctx->peers[r] = (char*)(uintptr_t)all[r].ptr; ctx->peer_inproc[r] = true; }
+        else { cudaGetLastError(); ok = false; }
+      } else if (cudaIpcOpenMemHandle((void**)&ctx->peers[r], all[r].h, cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) { ctx->peers[r] = nullptr; ok = false; }
+    }
     if (ok) { ctx->peerL = ctx->rank > 0 ? ctx->peers[ctx->rank - 1] : nullptr; ctx->peerR = ctx->rank < ctx->world - 1 ? ctx->peers[ctx->rank + 1] : nullptr; }
     // every rank must agree, or the halo protocols would differ: all-reduce the outcome
     int* d_ok = nullptr;
@@ -233,7 +247,7 @@ static int create_impl(nsgpu_ctx* ctx, const nsgpu_grid* G, const nsgpu_params* 
     cudaGetLastError();
     if (!all_ok) {
       fprintf(stderr, "nsgpu: CUDA IPC mapping of the neighbour slabs failed; halo columns go through NCCL\n");
-      for (int r = 0; r < MAX_RANKS; r++) if (ctx->peers[r]) { cudaIpcCloseMemHandle(ctx->peers[r]); ctx->peers[r] = nullptr; }
+      for (int r = 0; r < MAX_RANKS; r++) if (ctx->peers[r]) { if (!ctx->peer_inproc[r]) cudaIpcCloseMemHandle(ctx->peers[r]); ctx->peers[r] = nullptr; }
       ctx->peerL = ctx->peerR = nullptr;
       ctx->use_p2p = 0;
     }

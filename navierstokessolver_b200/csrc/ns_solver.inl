@@ -156,7 +156,7 @@ typedef void (*MarchKernel)(LevelGeom, const double*, const double*, const doubl
 
 // CTAs of `kern` that fit on the GPU at once (one wave), cached per kernel
 static int march_wave(MarchKernel kern) {
-  static std::vector<std::pair<MarchKernel, int>> cache;
+  static thread_local std::vector<std::pair<MarchKernel, int>> cache;   // (per host thread: one thread drives one GPU)
   for (auto& e : cache) if (e.first == kern) return e.second;
   int per_sm = 0, dev = 0, sms = 148;
   cudaGetDevice(&dev);
@@ -972,7 +972,7 @@ struct NvtxRange {   // host-side range around the launches of one phase (the ke
 // Launch shape of the projection kernels of ns_phys.cuh: gx CTAs of 4 warps cover the rows, the columns are cut into chunks of *ri
 // so that the CTAs fill whole waves (same estimate as march_chunk: waves x (columns per chunk + start-up)).
 static dim3 phys_grid(const void* kern, int fields, const Level& L, int* ri, size_t* smem) {
-  static std::vector<std::pair<const void*, int>> cache;
+  static thread_local std::vector<std::pair<const void*, int>> cache;
   int wave = 0;
   for (auto& e : cache) if (e.first == kern) wave = e.second;
   if (!wave) {
@@ -1001,7 +1001,7 @@ static dim3 phys_grid(const void* kern, int fields, const Level& L, int* ri, siz
 
 // launch shape of k_rhs_march over `ncols` columns: whole waves of CTAs, like phys_grid
 static dim3 rhs_grid(const Level& L, int ncols, int* ri, size_t* smem) {
-  static int wave = 0;
+  static thread_local int wave = 0;
   if (!wave) {
     int per_sm = 0, dev = 0, sms = 148;
     cudaGetDevice(&dev);

@@ -11,6 +11,45 @@
 #include <iostream>
 #include <sstream>
 
+GpuTeam::GpuTeam(int n) {
+  for (int r = 0; r < n; r++) workers.emplace_back([this, r] { loop(r); });
+}
+GpuTeam::~GpuTeam() {
+  { std::lock_guard<std::mutex> l(m); stop = true; }
+  cv_go.notify_all();
+  for (auto& t : workers) t.join();
+}
+void GpuTeam::loop(int r) {
+  long seen = 0;
+  for (;;) {
+    std::function<void(int)> f;
+    {
+      std::unique_lock<std::mutex> l(m);
+      cv_go.wait(l, [&] { return stop || gen != seen; });
+      if (stop) return;
+      seen = gen;
+      f = job;
+    }
+    f(r);
+    { std::lock_guard<std::mutex> l(m); done++; }
+    cv_done.notify_one();
+  }
+}
+void GpuTeam::run(const std::function<void(int)>& f) {
+  std::unique_lock<std::mutex> l(m);
+  job = f; done = 0; gen++;
+  cv_go.notify_all();
+  cv_done.wait(l, [&] { return done == (int)workers.size(); });
+}
+
+template <class F> int FluidSolver::onAll(F f) {
+  if (!team) return f(0);
+  std::vector<int> rc(gpus.size(), 0);
+  team->run([&](int r) { rc[r] = f(r); });
+  for (int c : rc) if (c) return c;
+  return 0;
+}
+
 double minmode(double a, double b) {   // FS.cpp:671-674 (kept as a free function of the public surface)
   if (a * b > 0) return a * std::min(1.0, std::abs(b / a));
   return 0;
@@ -30,7 +69,10 @@ FluidSolver::FluidSolver(char* fname, Grid* g) : grid(g) {
 
 FluidSolver::~FluidSolver() {
   if (writer.joinable()) writer.join();
-  if (gpu) nsgpu_destroy(gpu);
+  if (team) {
+    onAll([&](int r) { if (gpus[r]) nsgpu_destroy(gpus[r]); return 0; });
+    delete team;
+  } else if (gpu) nsgpu_destroy(gpu);
 }
 
 // Keywords: BC { one "<type> [info]" line per edge }, dt, final_time, re, saveIter.  As in the reference every
@@ -134,24 +176,56 @@ bool FluidSolver::createDeviceSolver() {
   p.rtol_phi = env_double("NSGPU_RTOL_PHI", 1e-8);
   p.solver = env_int("NSGPU_SOLVER", grid->N == nx * ny ? 0 : 1);
   p.max_cycles = env_int("NSGPU_MAX_CYCLES", 0);
+  const int ngpu = env_int("NSGPU_GPUS", 1);
+  if (ngpu > 1) {   // one process, ngpu x-slabs: one context per GPU, created concurrently (the communicator needs every rank)
+    unsigned char id[128];
+    if (nsgpu_nccl_unique_id(id) != 0) { cout << "GPU solver setup failed: no NCCL id\n"; return false; }
+    team = new GpuTeam(ngpu);
+    gpus.assign(ngpu, nullptr);
+    std::vector<std::string> msg(ngpu);
+    std::vector<int> rcs(ngpu, 0);
+    const int dev0 = p.device;
+    team->run([&](int r) {
+      nsgpu_params q = p;
+      q.rank = r; q.world = ngpu; q.device = dev0 + r; q.nccl_id = id;
+      rcs[r] = nsgpu_create(&g, &q, &gpus[r]);
+      if (rcs[r]) { msg[r] = nsgpu_last_error(nullptr); gpus[r] = nullptr; }
+    });
+    for (int r = 0; r < ngpu; r++)
+      if (rcs[r]) {
+        cout << "GPU solver setup failed (" << rcs[r] << ") on GPU " << dev0 + r << ": " << msg[r] << "\n";
+        onAll([&](int q) { if (gpus[q]) nsgpu_destroy(gpus[q]); gpus[q] = nullptr; return 0; });
+        delete team; team = nullptr; gpus.clear();
+        return false;
+      }
+    gpu = gpus[0];
+    slab_id0.assign(ngpu, 0); slab_n.assign(ngpu, 0);
+    for (int r = 0; r < ngpu; r++) nsgpu_local_range(gpus[r], nullptr, nullptr, &slab_id0[r], &slab_n[r]);
+    return true;
+  }
   int rc = nsgpu_create(&g, &p, &gpu);
   if (rc != 0) {
     cout << "GPU solver setup failed (" << rc << "): " << nsgpu_last_error(nullptr) << "\n";
     gpu = nullptr;
     return false;
   }
+  gpus.assign(1, gpu);
+  slab_id0.assign(1, 0); slab_n.assign(1, (int64_t)grid->N);
   return true;
 }
 
 // Same loop control as FS.cpp:536-567: iter starts at 1, the first step always runs, stop when dt*iter > finalTime.
 bool FluidSolver::SaveCheckpoint(const char* path) {
-  if (!gpu || nsgpu_checkpoint_save(gpu, path, lastIter) != 0) { cout << "Checkpoint not written: " << nsgpu_last_error(gpu) << "\n"; return false; }
+  if (!gpu || onAll([&](int r) { return nsgpu_checkpoint_save(gpus[r], path, lastIter); }) != 0) { cout << "Checkpoint not written: " << nsgpu_last_error(gpu) << "\n"; return false; }
   return true;
 }
 
 bool FluidSolver::LoadCheckpoint(const char* path) {
   int64_t step = 0;
-  if (!gpu || nsgpu_checkpoint_load(gpu, path, &step) != 0) { cout << "Checkpoint not loaded: " << nsgpu_last_error(gpu) << "\n"; return false; }
+  std::vector<int64_t> steps(gpus.size(), 0);
+  const int rcl = gpu ? onAll([&](int r) { return nsgpu_checkpoint_load(gpus[r], path, &steps[r]); }) : -1;
+  if (!steps.empty()) step = steps[0];
+  if (rcl != 0) { cout << "Checkpoint not loaded: " << nsgpu_last_error(gpu) << "\n"; return false; }
   lastIter = (int)step;
   firstIter = lastIter + 1;
   return true;
@@ -166,7 +240,9 @@ void FluidSolver::Solve() {
   }
   do {
     nsgpu_step_info info;
-    int rc = nsgpu_step(gpu, 1, &info);
+    std::vector<nsgpu_step_info> infos(gpus.size());
+    int rc = onAll([&](int r) { return nsgpu_step(gpus[r], 1, &infos[r]); });   // min / max are combined over the ranks on the device: every rank reports the same four
+    info = infos[0];
     if (rc != 0 && rc != NSGPU_ERR_NOT_CONVERGED && rc != NSGPU_ERR_NAN) {
       cout << "GPU time step failed (" << rc << "): " << nsgpu_last_error(gpu) << "\n";
       return;
@@ -202,7 +278,7 @@ double FluidSolver::ghostPhi(const double* P, int i, int j, int e) {            
 // time steps run (nsgpu_export_begin / nsgpu_export_wait); NSGPU_EXPORT_SYNC=1 writes the file before the loop goes on.
 void FluidSolver::ExportData(int iter) {
   if (writer.joinable()) writer.join();   // one file at a time; its pinned buffer is free again for the snapshot after this one
-  if (nsgpu_export_begin(gpu, iter) != 0) {
+  if (onAll([&](int r) { return nsgpu_export_begin(gpus[r], iter); }) != 0) {
     cout << "GPU export failed: " << nsgpu_last_error(gpu) << "\n";
     return;
   }
@@ -213,7 +289,20 @@ void FluidSolver::ExportData(int iter) {
 void FluidSolver::writeSnapshot() {
   const double *u, *v, *phi, *pr, *lap;
   int64_t iter = 0;
-  if (nsgpu_export_wait(gpu, &u, &v, &phi, &pr, &lap, &iter) != 0) {
+  std::vector<double> all;   // several GPUs: the slabs' snapshots side by side in compact-id order
+  if (gpus.size() > 1) {
+    const size_t n = (size_t)grid->N;
+    all.resize(5 * n);
+    for (size_t r = 0; r < gpus.size(); r++) {
+      const double* q[5];
+      if (nsgpu_export_wait(gpus[r], &q[0], &q[1], &q[2], &q[3], &q[4], &iter) != 0) {
+        cout << "GPU export failed: " << nsgpu_last_error(gpus[r]) << "\n";
+        return;
+      }
+      for (int k = 0; k < 5; k++) std::copy(q[k], q[k] + slab_n[r], all.begin() + k * n + slab_id0[r]);
+    }
+    u = all.data(); v = u + n; phi = v + n; pr = phi + n; lap = pr + n;
+  } else if (nsgpu_export_wait(gpu, &u, &v, &phi, &pr, &lap, &iter) != 0) {
     cout << "GPU export failed: " << nsgpu_last_error(gpu) << "\n";
     return;
   }

@@ -9,12 +9,39 @@
 #include "compat/petsc.h"   // the reference header pulls in petsc.h (FS.h:3); MAIN_Solver.cpp relies on it
 #include "Grid.h"
 #include "nsgpu.h"
+#include <condition_variable>
+#include <functional>
+#include <mutex>
 #include <thread>
+#include <vector>
+
+// NSGPU_GPUS=N (N > 1): one process drives N GPUs -- the domain is cut into N x-slabs (rank r on device NSGPU_DEVICE + r), one
+// persistent host thread per GPU runs that rank's C-ABI calls; the calls of one time step must run concurrently (the kernels exchange
+// halo columns with each other over NVLink), which is what run() does: the same job on every worker, return when all are done.
+class GpuTeam {
+  std::vector<std::thread> workers;
+  std::mutex m;
+  std::condition_variable cv_go, cv_done;
+  std::function<void(int)> job;
+  long gen = 0;
+  int done = 0;
+  bool stop = false;
+  void loop(int r);
+ public:
+  explicit GpuTeam(int n);
+  ~GpuTeam();
+  int size() const { return (int)workers.size(); }
+  void run(const std::function<void(int)>& f);
+};
 
 class FluidSolver {
  private:
   Grid* grid;                 // borrowed; its edges receive bcType / bcInfo / ghost stencils like in the reference
-  nsgpu_ctx* gpu = nullptr;   // device-resident prevField, RHS vectors, operators (FS.h:22-33)
+  nsgpu_ctx* gpu = nullptr;   // device-resident prevField, RHS vectors, operators (FS.h:22-33); rank 0 of gpus when there are several
+  std::vector<nsgpu_ctx*> gpus;        // NSGPU_GPUS > 1: one context per GPU (gpus[0] == gpu)
+  std::vector<int64_t> slab_id0, slab_n;   // compact-id range of every rank's x-slab
+  GpuTeam* team = nullptr;
+  template <class F> int onAll(F f);   // f(rank) on every GPU concurrently; first non-zero return code
   double dt;                  // deliberately uninitialised when the file omits them, like FS.h:24-26
   double finalTime;
   double re;

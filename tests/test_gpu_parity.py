@@ -409,6 +409,54 @@ def test_two_gpus_equal_one_gpu(workdir):
     assert out.returncode == 0, out.stdout[-2000:] + out.stderr[-2000:]
 
 
+def run_main_on_gpus(ngpu, workdir, grid=None, steps=10):
+    """bin/main <grid> <sim> with NSGPU_GPUS=ngpu in a fresh directory: (stdout, {csv name: text})."""
+    import os
+    import subprocess
+    d = workdir / ("main_%d_gpus" % ngpu)
+    d.mkdir()
+    sim = d / "case.sim"
+    sim.write_text("BC {\n2 0\n2 1\n2 0\n2 0\n}\ndt 0.002\nfinal_time %g\nre 400\nsaveIter 5\n" % (0.002 * steps + 1e-9))
+    env = dict(os.environ, NSGPU_GPUS=str(ngpu))
+    out = subprocess.run([f"{refapi.ROOT}/bin/main", grid or f"{CASES}/cavity_128.grid", str(sim)], cwd=d, capture_output=True, text=True, timeout=600, env=env)
+    assert out.returncode == 0, out.stderr[-2000:]
+    return out.stdout, {f: open(d / f).read() for f in sorted(os.listdir(d)) if f.endswith(".csv")}
+
+
+def compare_main_runs(a, b):
+    """Two runs of bin/main: same messages, same step table and CSV numbers to 1e-9 (the printed digits: 6 decimals / 6 significant)."""
+    (oa, ca), (ob, cb) = a, b
+    ma, ta = _split_stdout(oa)
+    mb, tb = _split_stdout(ob)
+    drop = lambda m: [l for l in m if not l.startswith("NCCL version")]   # NCCL's own banner (printed when NCCL_DEBUG is set)
+    assert drop(ma) == drop(mb) and ta.shape == tb.shape and len(ta) >= 5
+    worst = float(np.abs(ta - tb).max())
+    assert sorted(ca) == sorted(cb) and len(ca) >= 3
+    for f in ca:
+        if f == "CellCenters.csv":
+            assert ca[f] == cb[f]
+            continue
+        xa = np.array([[float(v) for v in l.split(",")] for l in ca[f].splitlines()[1:]])
+        xb = np.array([[float(v) for v in l.split(",")] for l in cb[f].splitlines()[1:]])
+        assert xa.shape == xb.shape
+        worst = max(worst, float(np.abs(xa - xb).max() / max(np.abs(xa).max(), 1e-300)))
+    return worst
+
+
+def test_drop_in_main_on_two_gpus(workdir):
+    """The unchanged command line on several GPUs: NSGPU_GPUS=2 makes FluidSolver drive two x-slabs from one process (one host thread per
+    GPU, peer access instead of IPC); stdout and the exported CSV files equal the one-GPU run's."""
+    import os
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    if not os.path.exists(f"{refapi.ROOT}/bin/main"):
+        pytest.skip("bin/main not built")
+    worst = compare_main_runs(run_main_on_gpus(1, workdir), run_main_on_gpus(2, workdir))
+    print("bin/main, 2 GPUs against 1: worst difference", worst)
+    assert worst <= 2e-6
+
+
 def test_whole_steps_stretched_cavity(workdir):
     """Wall-refined lid-driven cavity (geometric stretching, h_max / h_min = 3.4): LHS_phi x = b is inconsistent at 2.4e-4 there and
     the reference returns A x + c w = b with c = (vol, b) / (vol, w); the GPU solves that bordered system (BiCGStab on the augmented
