@@ -7,7 +7,7 @@ CXX = /usr/bin/g++
 PKG = navierstokessolver_b200
 CSRC = $(PKG)/csrc
 HOST = $(PKG)/host
-NVFLAGS = -std=c++17 -O3 -lineinfo -gencode arch=compute_100a,code=sm_100a -Xcompiler -fPIC
+NVFLAGS = -std=c++17 -O3 -lineinfo -gencode arch=compute_100a,code=sm_100a -Xcompiler -fPIC $(if $(NSGPU_BUILD_STAMPS),-DNSGPU_STAMPS=1)
 CU_DEPS = $(wildcard $(CSRC)/*.cu $(CSRC)/*.cuh $(CSRC)/*.inl $(CSRC)/*.h) include/nsgpu.h
 HOST_SRC = $(wildcard $(HOST)/*.cpp)
 HOST_DEPS = $(wildcard $(HOST)/*.cpp $(HOST)/*.h)

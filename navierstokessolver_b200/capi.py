@@ -8,7 +8,7 @@ import numpy as np
 U, V, PHI, RHS_U, RHS_V, RHS_PHI, CONV_U0, CONV_V0, GRADPHI_X, GRADPHI_Y, USTAR, VSTAR = range(12)
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-lib_path = os.path.join(_HERE, "libnsgpu.so")
+lib_path = os.environ.get("NSGPU_LIB") or os.path.join(_HERE, "libnsgpu.so")   # NSGPU_LIB: another build of the same library (kernel experiments)
 
 
 class NsGpuError(RuntimeError):

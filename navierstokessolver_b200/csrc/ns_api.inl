@@ -120,6 +120,35 @@ int nsgpu_create(const nsgpu_grid* grid, const nsgpu_params* params, nsgpu_ctx**
 }
 
 void nsgpu_destroy(nsgpu_ctx* ctx) {
+  if (ctx && getenv("NSGPU_XRED_DBG")) {
+    long long h[8];
+    cudaSetDevice(ctx->device);
+    if (cudaMemcpyFromSymbol(h, g_ns_xdbg_acc, sizeof h) == cudaSuccess && h[0] > 0) {
+      const double us = 1.0 / 1965.0;   // cycles -> microseconds at the B200's 1965 MHz
+      fprintf(stderr, "nsgpu xred rank %d: %lld reductions: last block's sum %.2f us, epilogue %.2f us", ctx->rank, h[0], us * h[1] / h[0], us * h[2] / h[0]);
+      if (h[7] > 0) fprintf(stderr, "; %lld cross-rank sums: stores %.2f, fence %.2f, flags %.2f, wait %.2f us", h[7], us * h[3] / h[7], us * h[4] / h[7], us * h[5] / h[7], us * h[6] / h[7]);
+      fprintf(stderr, "\n");
+    }
+    unsigned gd[2] = {0, 0};
+    if ((atoi(getenv("NSGPU_XRED_DBG")) & 2) && cudaMemcpyFromSymbol(gd, g_ns_cta_grid, sizeof gd) == cudaSuccess && gd[0] * gd[1] > 0 && gd[0] * gd[1] <= NS_DBG_CTAS) {
+      std::vector<unsigned long long> t(4 * NS_DBG_CTAS);
+      if (cudaMemcpyFromSymbol(t.data(), g_ns_cta_t, t.size() * sizeof t[0]) == cudaSuccess) {
+        unsigned long long t0 = ~0ull;
+        for (unsigned c = 0; c < gd[0] * gd[1]; c++) t0 = std::min(t0, t[4 * c]);
+        fprintf(stderr, "nsgpu cta stamps rank %d, last k_march launch, grid %u x %u; per chunk row y: start / after wait / after march / end (us after the first CTA's start; min..max over x)\n", ctx->rank, gd[0], gd[1]);
+        // rows 0 and 1 are the boundary chunks of a pushing pass (when it has them); the other rows together
+        for (int part = 0; part < 3; part++) {
+          double lo[4] = {1e30, 1e30, 1e30, 1e30}, hi[4] = {0, 0, 0, 0};
+          const unsigned y0 = part < 2 ? part : 2, y1 = part < 2 ? part + 1 : gd[1];
+          for (unsigned y = y0; y < y1 && y < gd[1]; y++)
+            for (unsigned x = 0; x < gd[0]; x++)
+              for (int k = 0; k < 4; k++) { const double v = 1e-3 * (double)(t[4 * (x + gd[0] * y) + k] - t0); lo[k] = std::min(lo[k], v); hi[k] = std::max(hi[k], v); }
+          if (y0 < gd[1])
+            fprintf(stderr, "nsgpu cta rank %d rows %u..%u  start %6.1f..%6.1f  waited %6.1f..%6.1f  marched %6.1f..%6.1f  end %6.1f..%6.1f\n", ctx->rank, y0, std::min(y1, gd[1]) - 1, lo[0], hi[0], lo[1], hi[1], lo[2], hi[2], lo[3], hi[3]);
+        }
+      }
+    }
+  }
   if (ctx && ctx->tail_dbg) {
     long long h[64];
     if (cudaMemcpy(h, ctx->tail_dbg, sizeof h, cudaMemcpyDeviceToHost) == cudaSuccess)

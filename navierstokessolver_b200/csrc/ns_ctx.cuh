@@ -103,6 +103,7 @@ struct nsgpu_ctx {
   nsgpu::SolveCtl* h_ctl = nullptr;       // pinned mirror
   int seen_cycles[3] = {0, 0, 0}, seen_fails[3] = {0, 0, 0};
   nsgpu::SolveGraph sgraph[3];
+  nsgpu::SolveGraph kgraph[3];            // Krylov solves (BiCGStab): begin -> WHILE { iteration } -> true residual; x0 holds the operator / aug key
   int graph_cycles_pending[3] = {0, 0, 0};
   // several ranks: every buffer a marching pass writes lives in one arena, mapped by the two neighbours through CUDA IPC,
   // so that the pass can store its boundary columns straight into their halo columns (ns_march.cuh)
@@ -130,6 +131,9 @@ struct nsgpu_ctx {
   int rhs_march = 1;                             // ConstructRHS_V on rectangles through k_rhs_march (NSGPU_RHS_MARCH=0: cell kernel)
   int vel_guess_rhs = 0;                         // initial guess of the u*, v* solves: 0 = u^n, v^n; 1 = the right-hand side (LHS_V = I - dt/(2Re) L is close to I)
   int march_rb_min_nx = 0;                       // levels with fewer columns keep uniform chunks (NSGPU_RB_MINNX)
+  int stamp_key = -1;                            // stamps builds: trace key of the marching pass whose CTA stamps are kept (NSGPU_STAMP_KEY; -2: every pass)
+  int field_skew = 0, alloc_k = 0;               // dev_zeros: the k-th large array starts k x field_skew bytes later (NSGPU_FIELD_SKEW)
+  double rb_cost = 1.5, rb_cost_up = 1.5;        // pushing loop / plain loop, per column (NSGPU_RB_COST, NSGPU_RB_COST_UP: passes that prolong and reduce)
   int march_rb = 0;                              // width of the short boundary chunks of pushing passes (NSGPU_RB, 0 = off)
   unsigned last_gather_ctas = 0;                 // CTAs of the last restriction pass that gathered onto the replicated level
   unsigned long long* selfpush_hdr = nullptr;
@@ -165,6 +169,7 @@ struct nsgpu_ctx {
   bool phi_shift = false;                        // phi in memory still contains its mean
   bool phi_sum_known = false;                    // ... and SolveCtl::xsum of the phi slot holds sum(phi) (written by k_correct_march)
   const double* next_pass_shift = nullptr;       // consumed by the next march_pass (set by the head of the phi solve)
+  bool kry_graph_off = false;                    // a Krylov solve could not be captured (several ranks over NCCL, or the driver refused): direct launches from then on
   bool graph_fallback = false;                   // graphs were asked for but a solve had to fall back to direct launches
   int krylov_restarts = 0;                       // BiCGStab restarts from the true residual during the last call
   int64_t launches = 0;

@@ -45,6 +45,21 @@ __device__ __forceinline__ double warp_red(int k, double v) {
   return v;
 }
 
+// NSGPU_XRED_DBG=1: clock stamps of the reduction tails (cycles, summed; printed by nsgpu_destroy): [0] calls, [1] last block's sum of the
+// partials, [2] whole epilogue, [3] xreduce value stores, [4] system fence, [5] flag stores, [6] waiting for the other ranks, [7] xreduce calls
+// Compiled in only with -DNSGPU_STAMPS=1 (NSGPU_BUILD_STAMPS=1 python -c "import __graft_entry__ as g; g.build()"): even switched off at run time the
+// stamps change the register allocation of the fused passes (4096^2: last pass of a cycle 96 -> 117 us), so the product is built without them.
+#ifndef NSGPU_STAMPS
+#define NSGPU_STAMPS 0
+#endif
+constexpr bool NS_STAMPS = NSGPU_STAMPS != 0;
+static __device__ int g_ns_xdbg = 0;
+static __device__ long long g_ns_xdbg_acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+constexpr unsigned NS_DBG_CTAS = 2048;
+static __device__ unsigned long long g_ns_cta_t[4 * NS_DBG_CTAS];
+static __device__ unsigned g_ns_cta_grid[2];
+__device__ __forceinline__ unsigned long long globaltimer_ns() { unsigned long long t; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t)); return t; }
+
 // Block-level then grid-level reduction of NV values held by every thread.  All threads of the block must call.
 struct NoEpilogue { __device__ void operator()(const double*) const {} };
 
@@ -79,6 +94,7 @@ __device__ void grid_reduce(double (&v)[NV], Reducer red, double* out, EPI epi =
   }
   __syncthreads();
   if (!is_last) return;
+  const long long dbg_t0 = (NS_STAMPS && g_ns_xdbg) ? clock64() : 0;
   __threadfence();
 #pragma unroll
   for (int k = 0; k < NV; k++) {
@@ -94,7 +110,15 @@ __device__ void grid_reduce(double (&v)[NV], Reducer red, double* out, EPI epi =
       if (lane == 0) out[k] = z;
     }
   }
-  if (tid == 0) { *red.counter = 0u; epi(out); }
+  if (tid == 0) {
+    *red.counter = 0u;
+    if (NS_STAMPS && g_ns_xdbg) {
+      const long long t1 = clock64();
+      epi(out);
+      const long long t2 = clock64();
+      g_ns_xdbg_acc[0] += 1; g_ns_xdbg_acc[1] += t1 - dbg_t0; g_ns_xdbg_acc[2] += t2 - t1;
+    } else epi(out);
+  }
 }
 
 // Convergence control block of one linear solve, resident on the device (one per solve slot).
@@ -151,6 +175,8 @@ __device__ __forceinline__ void wait_word(const unsigned long long* p, unsigned 
 // Slot of (buffer, rank): three words {value a, value b, sequence}.
 __device__ inline void xreduce_sum2(const PeerTable* pt, double a, double b, double* ra, double* rb) {
   if (pt->nowait) { *ra = a * pt->world; *rb = b * pt->world; return; }
+  const bool dbg = NS_STAMPS && g_ns_xdbg != 0;
+  const long long t0 = dbg ? clock64() : 0;
   unsigned long long* hdr = pt->hdr;
   const unsigned long long s = hdr[HDR_XSEQ] + 1;
   hdr[HDR_XSEQ] = s;
@@ -160,17 +186,24 @@ __device__ inline void xreduce_sum2(const PeerTable* pt, double a, double b, dou
     reinterpret_cast<double*>(my_slot + pt->off[r])[0] = a;
     reinterpret_cast<double*>(my_slot + pt->off[r])[1] = b;
   }
+  const long long t1 = dbg ? clock64() : 0;
   __threadfence_system();
+  const long long t2 = dbg ? clock64() : 0;
   for (int r = 0; r < pt->world; r++) {
     unsigned long long* q = my_slot + pt->off[r] + 2;
     asm volatile("st.relaxed.sys.global.u64 [%0], %1;" :: "l"(q), "l"(s) : "memory");   // ordered after the values by the fence
   }
+  const long long t3 = dbg ? clock64() : 0;
   double sa = 0.0, sb = 0.0;
   for (int r = 0; r < pt->world; r++) {
     const unsigned long long* q = hdr + HDR_XSLOTS + 3 * (buf * MAX_RANKS + r);
     wait_word(q + 2, s, true, pt->err);
     sa += reinterpret_cast<const volatile double*>(q)[0];
     sb += reinterpret_cast<const volatile double*>(q)[1];
+  }
+  if (dbg) {
+    const long long t4 = clock64();
+    g_ns_xdbg_acc[3] += t1 - t0; g_ns_xdbg_acc[4] += t2 - t1; g_ns_xdbg_acc[5] += t3 - t2; g_ns_xdbg_acc[6] += t4 - t3; g_ns_xdbg_acc[7] += 1;
   }
   *ra = sa; *rb = sb;
 }
@@ -760,6 +793,29 @@ __global__ void k_publish_ctl(SolveCtl* host_mapped, const SolveCtl* src) { *hos
 __global__ void k_scalar_div(double* dst, const double* num, const double* den) { *dst = *num / *den; }
 __global__ void k_scalar_copy(double* dst, const double* src) { *dst = *src; }
 __global__ void k_scalar_set(double* dst, double v) { *dst = v; }
+// Device-side control of the Krylov solves (BiCGStab, solve_bicgstab): the recurrence scalars live in d_scal (S), the loop condition in
+// the solve's control block, and the iteration is the body of a CUDA-graph WHILE node -- the host looks at a residual once per solve.
+//   k_kry_first: start of a solve (|b|^2 = S[11], iteration counter);  k_kry_begin: start of a (re)start from the TRUE residual in S[9];
+//   k_kry_ctl: end of an iteration (S[9] = (r, r) of the recurrence);  k_kry_end: the true residual after the loop.
+__global__ void k_kry_first(const double* S, SolveCtl* c, double tol2, int max_cycles) {
+  c->bn2 = S[11]; c->tol2 = tol2; c->max_cycles = max_cycles; c->cycles = 0; c->zero_rhs = !(S[11] > 0.0) ? 1 : 0;
+}
+__global__ void k_kry_begin(double* S, SolveCtl* c, unsigned long long handle) {
+  const double rn2 = S[9];
+  S[0] = rn2; S[1] = 1.0; S[2] = 1.0; S[3] = 1.0;   // rho_new = (r0, r) = (r, r); rho_old = alpha = omega = 1
+  c->rn2 = rn2; c->handle = handle;
+  const bool go = !c->zero_rhs && (rn2 > c->tol2 * c->bn2) && (c->cycles < c->max_cycles) && (rn2 == rn2);
+  c->go = go ? 1 : 0;
+  if (handle) cudaGraphSetConditional((cudaGraphConditionalHandle)handle, go ? 1u : 0u);
+}
+__global__ void k_kry_ctl(const double* S, SolveCtl* c) {
+  const double rn2 = S[9];
+  c->rn2 = rn2; c->cycles += 1;
+  const bool go = (rn2 > c->tol2 * c->bn2) && (c->cycles < c->max_cycles) && (rn2 == rn2);
+  c->go = go ? 1 : 0;
+  if (c->handle) cudaGraphSetConditional((cudaGraphConditionalHandle)c->handle, go ? 1u : 0u);
+}
+__global__ void k_kry_end(const double* S, SolveCtl* c, SolveCtl* pub) { c->rn2 = S[9]; c->go = 0; *pub = *c; }
 // |b - mean|^2 from s = {sum b, sum b^2} over n cells (inv_n = 1 / n; 0: the mean stays in)
 __global__ void k_bn2_from_sums(double* dst, const double* s, double inv_n) { *dst = fmax(s[1] - s[0] * s[0] * inv_n, 0.0); }
 

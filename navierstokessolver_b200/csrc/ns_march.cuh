@@ -117,6 +117,7 @@ struct MarchXfer {
   int gather;                                // RES == 1 onto a replicated coarse level: store the slab on every rank
   const double* shift;                       // != nullptr: xin - *shift * shift_scale is what the pass smooths (phi's lazily removed mean)
   double shift_scale;
+  int stamp;                                 // -DNSGPU_STAMPS=1 builds: this launch writes its per-CTA time stamps (NSGPU_STAMP_KEY)
 };
 
 // Per-thread state of the march: one ring of columns (PF prefetched ones ahead of the K being worked on) and
@@ -260,50 +261,7 @@ template <int NSW, bool PROLONG, int RES, int PF, bool SOR, bool P>
 __device__ __forceinline__ double march_run(const LevelGeom& g, const double* __restrict__ mcy, const double* __restrict__ xin,
                                             const double* __restrict__ b, double* __restrict__ xout, const MarchXfer& xf, const double* s_c,
                                             int ib, int ie, int n0, int nend, int r0, int lane, int wj) {
-  using M = Marcher<NSW, PROLONG, RES, PF, SOR, P>;
-  constexpr int L = M::L;
-  constexpr int HJ = march_halo(NSW, RES);
-  constexpr int UJ = 64 - 2 * HJ;
-  constexpr int HL = HJ / 2;
-  // warps past the last strip run with every predicate false (no divergent exit: the shuffles stay convergent)
-  M m;
-  m.xf = xf;
-  m.ld = g.ld; m.ny = g.ny; m.ib = ib; m.ie = ie; m.nxl = g.nx;
-  m.pfo = (size_t)MARCH_PFD * g.ld;
-  m.pushL = P && xf.dL != 0 && ib < xf.zone;
-  m.pushR = P && xf.dR != 0 && ie > g.nx - xf.zone;
-  m.j0 = wj * UJ - HJ + 2 * lane;                            // even, >= -HJ >= -PJ
-  const int jl = min(m.j0, (g.ny + PJ - 2) & ~1);            // lanes past the column end: an even (16-byte aligned) zero pair
-  {
-    const int a = jl + PJ;                                   // entries outside the domain have cs = cn = 0
-    m.k.csa = mcy[3 * a]; m.k.cna = mcy[3 * a + 1]; m.k.dya = mcy[3 * a + 2];
-    m.k.csb = mcy[3 * a + 3]; m.k.cnb = mcy[3 * a + 4]; m.k.dyb = mcy[3 * a + 5];
-  }
-  const size_t joff = (size_t)(jl + PJ);
-  m.useful = lane >= HL && lane < 32 - HL;
-  m.jstore2 = m.useful && (m.j0 + 1 < g.ny);
-  m.jstore1 = m.useful && (m.j0 < g.ny) && !m.jstore2;
-  m.cc = s_c + 3 * (n0 - r0);
-  m.px = xin ? xin + (size_t)(n0 + HX) * g.ld + joff : nullptr;
-  m.pb = b + (size_t)(n0 + HX) * g.ld + joff;
-  m.po = xout + (size_t)(n0 - L + HX) * g.ld + joff;        // only dereferenced inside [ib, ie)
-  m.pbc = nullptr;
-  if (RES == 1) m.pbc = xf.bc + (size_t)((xf.rcx == 2 ? (ib >> 1) : ib) + HX) * xf.ldbc + (xf.rcy == 2 ? (size_t)((m.j0 >> 1) + PJ) : joff);
-  m.pxc = nullptr;
-  if (PROLONG) m.pxc = xf.xc + (size_t)((xf.pcy == 2 ? ((jl + 2 * PJ) >> 1) - PJ : jl) + PJ);
-  m.racc = make_double2(0.0, 0.0);
-  m.acc = 0.0;
-  m.xshift = xf.shift ? *xf.shift * xf.shift_scale : 0.0;
-#pragma unroll
-  for (int q = 0; q < M::RL; q++) { m.X[q] = make_double2(0.0, 0.0); m.Bq[q] = make_double2(0.0, 0.0); }
-#pragma unroll
-  for (int p = 0; p < PF; p++) m.load_col(n0 + p, m.X[PF - 1 - p], m.Bq[PF - 1 - p]);
-
-#pragma unroll 2
-  for (int n = n0; n < nend; n += 2) {
-    m.template step<true>(n);
-    m.template step<false>(n + 1);
-  }
+#include "ns_march_body.inl"
   return m.acc;
 }
 
@@ -319,6 +277,10 @@ k_march(LevelGeom g, const double* __restrict__ mcx, const double* __restrict__ 
   extern __shared__ double s_c[];            // (cw, ce, dx) of columns [r0, r0 + nrows)
   const int lane = threadIdx.x & 31;
   const int wj = blockIdx.x * MARCH_WARPS + (threadIdx.x >> 5);
+  // NSGPU_XRED_DBG=2|3: per-CTA time stamps of the last k_march launch (start, after the halo wait, after the march, end)
+  const unsigned dbg_cta = blockIdx.x + gridDim.x * blockIdx.y;
+  const bool dbg = NS_STAMPS && xf.stamp && threadIdx.x == 0 && dbg_cta < NS_DBG_CTAS;
+  if (dbg) { g_ns_cta_t[4 * dbg_cta] = globaltimer_ns(); if (dbg_cta == 0) { g_ns_cta_grid[0] = gridDim.x; g_ns_cta_grid[1] = gridDim.y; } }
   // Several ranks: the columns a neighbour needs come out of two SHORT chunks that are scheduled first, so that they
   // are pushed and signalled long before the neighbour's next pass asks for them (and a late start costs little).
   int ib = blockIdx.y * RI, ie = min(ib + RI, g.nx);
@@ -351,13 +313,24 @@ k_march(LevelGeom g, const double* __restrict__ mcx, const double* __restrict__ 
     }
   }
   __syncthreads();
+  if (dbg) g_ns_cta_t[4 * dbg_cta + 1] = globaltimer_ns();
 
   // warps past the last strip run with every predicate false (no divergent exit: the shuffles stay convergent)
+  // Kernels without peer stores hold the march DIRECTLY (included, not called): the same statements reached through march_run compile to a
+  // plain sweep of 81 us instead of 70 us at 4096^2 (100 against 96 registers, another schedule).  The pushing family calls march_run
+  // for both of its loops (one per CTA, uniform branch); the plain loop as a __noinline__ function of its own, or the pushing one, were
+  // measured too and are slower (per-kind times of all eight arrangements: DESIGN section 7).
   double acc_r2;
   if (PUSH && (xf.gather || ib < xf.zone || ie > g.nx - xf.zone))   // uniform over the CTA
     acc_r2 = march_run<NSW, PROLONG, RES, PF, SOR, PUSH>(g, mcy, xin, b, xout, xf, s_c, ib, ie, n0, nend, r0, lane, wj);
-  else
+  else if (PUSH)
     acc_r2 = march_run<NSW, PROLONG, RES, PF, SOR, false>(g, mcy, xin, b, xout, xf, s_c, ib, ie, n0, nend, r0, lane, wj);
+  else {
+    constexpr bool P = false;
+#include "ns_march_body.inl"
+    acc_r2 = m.acc;
+  }
+  if (dbg) g_ns_cta_t[4 * dbg_cta + 2] = globaltimer_ns();
   if (PUSH) {
     __syncthreads();          // every store of this CTA happens before thread 0's fence (cumulativity)
     if (threadIdx.x == 0) {
@@ -381,6 +354,7 @@ k_march(LevelGeom g, const double* __restrict__ mcx, const double* __restrict__ 
       }
     }
   }
+  if (dbg) g_ns_cta_t[4 * dbg_cta + 3] = globaltimer_ns();
   if (RES == 2) {
     double acc[1] = {acc_r2};
     grid_reduce<1, OpSum>(acc, xf.red, xf.out, CtlEpilogue{xf.ctl, xf.pt, xf.out});

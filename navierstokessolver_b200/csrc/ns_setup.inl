@@ -39,16 +39,20 @@ static int dev_upload(nsgpu_ctx* ctx, std::vector<void*>& owned, const std::vect
 
 static int dev_zeros(nsgpu_ctx* ctx, std::vector<void*>& owned, size_t n_doubles, double** out) {
   const size_t bytes = (n_doubles * sizeof(double) + 255) & ~(size_t)255;
-  if (ctx->arena && ctx->arena_used + bytes <= ctx->arena_bytes) {   // peer-visible arena (already zeroed)
+  // Large arrays do not all start on the same 2 MB boundary (cudaMalloc's granularity) / at multiples of a column: the k-th one is shifted by
+  // k x field_skew bytes, so that the streams a pass reads and writes at the same column do not meet in the same memory channels
+  const size_t skew = (ctx->field_skew && bytes >= ((size_t)1 << 20)) ? ((size_t)ctx->field_skew * (size_t)(ctx->alloc_k++)) % ((size_t)1 << 21) : 0;
+  if (ctx->arena && ctx->arena_used + skew + bytes <= ctx->arena_bytes) {   // peer-visible arena (already zeroed)
+    ctx->arena_used += skew;
     *out = (double*)(ctx->arena + ctx->arena_used);
     ctx->arena_used += bytes;
     return 0;
   }
   void* p = nullptr;
-  NS_CUDA(cudaMalloc(&p, n_doubles * sizeof(double)));
+  NS_CUDA(cudaMalloc(&p, n_doubles * sizeof(double) + skew));
   owned.push_back(p);
-  NS_CUDA(cudaMemset(p, 0, n_doubles * sizeof(double)));
-  *out = (double*)p;
+  NS_CUDA(cudaMemset(p, 0, n_doubles * sizeof(double) + skew));
+  *out = (double*)((char*)p + skew);
   return 0;
 }
 
@@ -108,6 +112,7 @@ static void destroy_ctx(nsgpu_ctx* ctx) {
     for (void* p : L.owned) cudaFree(p);
   for (void* p : ctx->owned) cudaFree(p);
   for (auto& sg : ctx->sgraph) { if (sg.exec) cudaGraphExecDestroy(sg.exec); if (sg.graph) cudaGraphDestroy(sg.graph); }
+  for (auto& sg : ctx->kgraph) { if (sg.exec) cudaGraphExecDestroy(sg.exec); if (sg.graph) cudaGraphDestroy(sg.graph); }
   if (ctx->s_in) { cudaStreamDestroy(ctx->s_in); cudaStreamDestroy(ctx->s_out); for (auto& e : ctx->ev_io) if (e) cudaEventDestroy(e); }
   for (auto& e : ctx->ev_chunk) if (e) cudaEventDestroy(e);
   for (auto& q : ctx->exp_host) if (q) cudaFreeHost(q);
@@ -177,6 +182,12 @@ static int create_impl(nsgpu_ctx* ctx, const nsgpu_grid* G, const nsgpu_params* 
   if (const char* e = getenv("NSGPU_TRACE")) ctx->trace = atoi(e);
   ctx->march_rb = -1;   // several ranks: boundary chunks (pushing loop) sized automatically; NSGPU_RB=0: uniform chunks, > 0: that width
   if (const char* e = getenv("NSGPU_RB")) ctx->march_rb = atoi(e);
+  if (const char* e = getenv("NSGPU_XRED_DBG")) { const int v = atoi(e); cudaMemcpyToSymbol(g_ns_xdbg, &v, sizeof v); }   // 1: reduction tails, 2: CTA stamps
+  if (const char* e = getenv("NSGPU_STAMP_KEY")) ctx->stamp_key = atoi(e);
+  else if (getenv("NSGPU_XRED_DBG") && (atoi(getenv("NSGPU_XRED_DBG")) & 2)) ctx->stamp_key = -2;
+  if (const char* e = getenv("NSGPU_FIELD_SKEW")) ctx->field_skew = (atoi(e) + 255) & ~255;
+  if (const char* e = getenv("NSGPU_RB_COST")) ctx->rb_cost = ctx->rb_cost_up = std::max(1.0, atof(e));
+  if (const char* e = getenv("NSGPU_RB_COST_UP")) ctx->rb_cost_up = std::max(1.0, atof(e));
   if (const char* e = getenv("NSGPU_RHS_MARCH")) ctx->rhs_march = atoi(e);
   if (const char* e = getenv("NSGPU_PHYS_MARCH")) ctx->phys_march = atoi(e);
   if (const char* e = getenv("NSGPU_LAZY_MEAN")) ctx->lazy_mean = atoi(e);

@@ -246,13 +246,14 @@ static int march_pass(nsgpu_ctx* ctx, const Level& L, OpCoef c, int nsw, double*
     const int rows = (L.g.nx + ri - 1) / ri, rb_min = 2 * (HX - 1);   // >= the push zone of a restricting pass
     if (ctx->march_rb > 0) { rb = std::max(ctx->march_rb, rb_min); rb += rb & 1; }
     else if (rows >= 3) {
+      const double pc = (Cp && res == 2) ? ctx->rb_cost_up : ctx->rb_cost;   // cost of a column in the pushing loop / in the plain loop
       double best = 1e300;
       for (int r = rb_min; 2 * r + 4 <= L.g.nx; r += 2) {
         int rin = (L.g.nx - 2 * r + rows - 3) / (rows - 2);
         rin += rin & 1;
-        const double cost = std::max(1.5 * (r + ovh), (double)(rin + ovh));
+        const double cost = std::max(pc * (r + ovh), (double)(rin + ovh));
         if (cost < best) { best = cost; rb = r; }
-        if (1.5 * (r + ovh) > rin + ovh) break;
+        if (pc * (r + ovh) > rin + ovh) break;
       }
       if (rb) { ri = (L.g.nx - 2 * rb + rows - 3) / (rows - 2); ri += ri & 1; ri = std::max(ri, 2); }
     }
@@ -290,7 +291,9 @@ static int march_pass(nsgpu_ctx* ctx, const Level& L, OpCoef c, int nsw, double*
     }
     if (gather) ctx->last_gather_ctas = grid.x * grid.y;
   } else if (res == 2 && ctx->d_pt) xf.pt = ctx->d_pt;   // the residual norm is summed over the ranks in the epilogue
-  trace_begin(ctx, (int)(&L - ctx->levels.data()) * 1000 + nsw * 100 + res * 10 + (Cp ? 2 : 0) + (push ? 1 : 0) + (omega > 0 ? 50000 : 0));
+  const int trace_key = (int)(&L - ctx->levels.data()) * 1000 + nsw * 100 + res * 10 + (Cp ? 2 : 0) + (push ? 1 : 0) + (omega > 0 ? 50000 : 0);
+  xf.stamp = ctx->stamp_key == -2 || ctx->stamp_key == trace_key;
+  trace_begin(ctx, trace_key);
   kern<<<grid, MARCH_THREADS, sh, ctx->stream>>>(L.g, L.mcx[op_tab(c)], L.mcy[op_tab(c)], xin, b, xout, ri, xf);
   trace_end(ctx);
   if (push) {
@@ -619,91 +622,237 @@ static int aug_precond(nsgpu_ctx* ctx, const Level& L, const double* v, double**
 // on the device, one 8-byte readback per iteration for the stopping test.
 //   d_scal layout: [0] rho_new [1] rho_old [2] alpha [3] omega [4..5] (r0,v),(v,v) [6..7] (t,s),(t,t)
 //                  [8] (s,s) [9..10] (r,r),(r0,r) [11] (b,b)
-static int solve_bicgstab(nsgpu_ctx* ctx, OpCoef c, double** xp, double** xtp, const double* b, double rtol, SolveResult* out) {
+// The pieces of a solve are launches only (no readback), so that they can be captured: bicg_begin -> WHILE { bicg_iteration } -> bicg_end.
+struct BicgVecs { double *r, *r0, *p, *v, *s, *t; };
+static inline BicgVecs bicg_vecs(nsgpu_ctx* ctx) { return {ctx->kry[0], ctx->kry[1], ctx->kry[2], ctx->kry[3], ctx->kry[4], ctx->kry[5]}; }
+
+// r <- b - A x (the TRUE residual; on augmented systems minus mean(x) w), S[9] = (r, r)
+static int bicg_true_residual(nsgpu_ctx* ctx, OpCoef c, double* x, const double* b, bool aug) {
+  const Level& L = ctx->levels[0];
+  double* S = ctx->d_scal;
+  const BicgVecs V = bicg_vecs(ctx);
+  int rc;
+  if ((rc = residual_vec(ctx, L, c, x, b, V.r, S + 9))) return rc;
+  if (aug) {
+    if ((rc = aug_rank_one(ctx, L, x, V.r, -1.0, nullptr, S + 44))) return rc;
+    k_scalar_copy<<<1, 1, 0, ctx->stream>>>(S + 9, S + 45);
+    NS_LAUNCH_CHECK();
+  }
+  return 0;
+}
+
+// (re)start from the true residual in r: r0 = r, p = v = 0, recurrence scalars, loop condition
+static int bicg_begin(nsgpu_ctx* ctx, SolveCtl* ctl, unsigned long long handle) {
+  const Level& L = ctx->levels[0];
+  const BicgVecs V = bicg_vecs(ctx);
+  cudaError_t e = cudaMemcpyAsync(V.r0, V.r, L.stride * sizeof(double), cudaMemcpyDeviceToDevice, ctx->stream);
+  if (e == cudaSuccess) e = cudaMemsetAsync(V.p, 0, L.stride * sizeof(double), ctx->stream);
+  if (e == cudaSuccess) e = cudaMemsetAsync(V.v, 0, L.stride * sizeof(double), ctx->stream);
+  if (e != cudaSuccess) { ctx->err = cudaGetErrorString(e); return NSGPU_ERR_CUDA; }
+  k_kry_begin<<<1, 1, 0, ctx->stream>>>(ctx->d_scal, ctl, handle);
+  NS_LAUNCH_CHECK();
+  return 0;
+}
+
+// One iteration.  ph, sh and the preconditioner's ping-pong partner carry nothing from one iteration to the next, so every iteration starts
+// from the same three arrays: the launch sequence is the same each time, which is what lets it be the body of a graph's WHILE node.
+static int bicg_iteration(nsgpu_ctx* ctx, OpCoef c, double* x, bool aug, SolveCtl* ctl) {
   const Level& L = ctx->levels[0];
   const size_t n = (size_t)L.g.nx * L.g.ld, off = (size_t)HX * L.g.ld;
   const int blocks = (int)std::min<size_t>((n + 255) / 256, 148 * 8);
-  double *x = *xp;
-  double *r = ctx->kry[0], *r0 = ctx->kry[1], *p = ctx->kry[2], *v = ctx->kry[3], *s = ctx->kry[4], *t = ctx->kry[5],
-         *ph = ctx->kry[6], *sh = ctx->kry[7];
+  const BicgVecs V = bicg_vecs(ctx);
+  double *r = V.r, *r0 = V.r0, *p = V.p, *v = V.v, *s = V.s, *t = V.t;
+  double *ph = ctx->kry[6], *sh = ctx->kry[7], *tmpA = ctx->tmp;
   double* S = ctx->d_scal;
-  double h[4];
+  int rc;
+  k_bicg_p<<<blocks, 256, 0, ctx->stream>>>(n, r + off, p + off, v + off, S);
+  NS_LAUNCH_CHECK();
+  // ph = M^-1 p
+  { double *a = ph, *bq = tmpA; if ((rc = aug ? aug_precond(ctx, L, p, &a, &bq) : vcycle_any(ctx, c, &a, &bq, p, true))) return rc; ph = a; tmpA = bq; }
+  if (aug) {
+    if ((rc = apply_op(ctx, L, c, ph, v, nullptr, nullptr))) return rc;
+    if ((rc = aug_rank_one(ctx, L, ph, v, 1.0, r0, S + 4))) return rc;
+  } else if ((rc = apply_op(ctx, L, c, ph, v, r0, S + 4))) return rc;
+  k_scalar_div<<<1, 1, 0, ctx->stream>>>(S + 2, S + 0, S + 4);   // alpha = rho / (r0, v)
+  NS_LAUNCH_CHECK();
+  k_bicg_s<<<blocks, 256, 0, ctx->stream>>>(n, r + off, v + off, s + off, S + 2, ctx->red, S + 8);
+  NS_LAUNCH_CHECK();
+  if ((rc = allreduce(ctx, S + 8, 1, ncclSum))) return rc;
+  // sh = M^-1 s
+  { double *a = sh, *bq = tmpA; if ((rc = aug ? aug_precond(ctx, L, s, &a, &bq) : vcycle_any(ctx, c, &a, &bq, s, true))) return rc; sh = a; tmpA = bq; }
+  if (aug) {
+    if ((rc = apply_op(ctx, L, c, sh, t, nullptr, nullptr))) return rc;
+    if ((rc = aug_rank_one(ctx, L, sh, t, 1.0, s, S + 6))) return rc;
+  } else if ((rc = apply_op(ctx, L, c, sh, t, s, S + 6))) return rc;
+  k_scalar_div<<<1, 1, 0, ctx->stream>>>(S + 3, S + 6, S + 7);   // omega = (t,s)/(t,t)
+  NS_LAUNCH_CHECK();
+  k_scalar_copy<<<1, 1, 0, ctx->stream>>>(S + 1, S + 0);         // rho_old = rho_new
+  NS_LAUNCH_CHECK();
+  k_bicg_xr<<<blocks, 256, 0, ctx->stream>>>(n, x + off, ph + off, sh + off, r + off, s + off, t + off, r0 + off, S + 2, S + 3,
+                                             ctx->red, S + 9);
+  NS_LAUNCH_CHECK();
+  if ((rc = allreduce(ctx, S + 9, 2, ncclSum))) return rc;
+  k_scalar_copy<<<1, 1, 0, ctx->stream>>>(S + 0, S + 10);        // rho_new = (r0, r)
+  NS_LAUNCH_CHECK();
+  k_kry_ctl<<<1, 1, 0, ctx->stream>>>(S, ctl);                   // stopping test of the recurrence residual, on the device
+  NS_LAUNCH_CHECK();
+  return 0;
+}
+
+static int bicg_end(nsgpu_ctx* ctx, int slot, OpCoef c, double* x, const double* b, bool aug) {
+  int rc = bicg_true_residual(ctx, c, x, b, aug);
+  if (rc) return rc;
+  k_kry_end<<<1, 1, 0, ctx->stream>>>(ctx->d_scal, ctx->d_ctl + slot, ctx->h_ctl + slot);   // h_ctl: mapped host memory
+  NS_LAUNCH_CHECK();
+  return 0;
+}
+
+#define NS_GRAPH_TRY(call)                                                                          \
+  do {                                                                                              \
+    cudaError_t e_ = (call);                                                                        \
+    if (e_ != cudaSuccess) {                                                                        \
+      fprintf(stderr, "nsgpu: %s -> %s; falling back to direct launches\n", #call, cudaGetErrorString(e_)); \
+      cudaGetLastError();                                                                           \
+      return 1;                                                                                     \
+    }                                                                                               \
+  } while (0)
+
+// begin -> WHILE (go) { iteration } -> true residual + publish, as one graph.  0 ok, 1 unsupported, < 0 error.
+static int build_kry_graph_(nsgpu_ctx* ctx, int slot, OpCoef c, double* x, const double* b, bool aug) {
+  SolveGraph& G = ctx->kgraph[slot];
+  if (G.exec) { cudaGraphExecDestroy(G.exec); G.exec = nullptr; }
+  if (G.graph) { cudaGraphDestroy(G.graph); G.graph = nullptr; }
+  const cudaStreamCaptureMode mode = cudaStreamCaptureModeThreadLocal;
+  SolveCtl* ctl = ctx->d_ctl + slot;
+  NS_GRAPH_TRY(cudaGraphCreate(&G.graph, 0));
+  cudaGraphConditionalHandle handle;
+  NS_GRAPH_TRY(cudaGraphConditionalHandleCreate(&handle, G.graph, 0, cudaGraphCondAssignDefault));
+  const int64_t l0 = ctx->launches;
+  NS_GRAPH_TRY(cudaStreamBeginCaptureToGraph(ctx->stream, G.graph, nullptr, nullptr, 0, mode));
+  int rc = bicg_begin(ctx, ctl, (unsigned long long)handle);
+  cudaStreamCaptureStatus st;
+  const cudaGraphNode_t* deps = nullptr;
+  size_t ndeps = 0;
+  cudaGraph_t gcap = nullptr;
+  cudaError_t e = cudaStreamGetCaptureInfo(ctx->stream, &st, nullptr, &gcap, &deps, &ndeps);
+  std::vector<cudaGraphNode_t> leaf(deps, deps + (e == cudaSuccess ? ndeps : 0));
+  cudaGraph_t gout = nullptr;
+  cudaError_t e2 = cudaStreamEndCapture(ctx->stream, &gout);
+  if (rc) return rc;
+  NS_GRAPH_TRY(e);
+  NS_GRAPH_TRY(e2);
+  const int64_t l1 = ctx->launches;
+  cudaGraphNodeParams p = {cudaGraphNodeTypeConditional};
+  p.type = cudaGraphNodeTypeConditional;
+  p.conditional.handle = handle;
+  p.conditional.type = cudaGraphCondTypeWhile;
+  p.conditional.size = 1;
+  cudaGraphNode_t loop;
+  NS_GRAPH_TRY(cudaGraphAddNode(&loop, G.graph, leaf.data(), leaf.size(), &p));
+  cudaGraph_t body = p.conditional.phGraph_out[0];
+  NS_GRAPH_TRY(cudaStreamBeginCaptureToGraph(ctx->stream, body, nullptr, nullptr, 0, mode));
+  rc = bicg_iteration(ctx, c, x, aug, ctl);
+  e2 = cudaStreamEndCapture(ctx->stream, &gout);
+  if (rc) return rc;
+  NS_GRAPH_TRY(e2);
+  const int64_t l2 = ctx->launches;
+  NS_GRAPH_TRY(cudaStreamBeginCaptureToGraph(ctx->stream, G.graph, &loop, nullptr, 1, mode));
+  rc = bicg_end(ctx, slot, c, x, b, aug);
+  e2 = cudaStreamEndCapture(ctx->stream, &gout);
+  if (rc) return rc;
+  NS_GRAPH_TRY(e2);
+  const int64_t l3 = ctx->launches;
+  NS_GRAPH_TRY(cudaGraphInstantiate(&G.exec, G.graph, 0));
+  ctx->launches = l0;   // capture is not execution
+  G.launches_fixed = (int)((l1 - l0) + (l3 - l2));
+  G.launches_body = (int)(l2 - l1);
+  G.x = x; G.b = b; G.xt = ctx->tmp; G.x0 = nullptr; G.rtol = (double)(c.op * 2 + (aug ? 1 : 0));   // (operator, augmented) the graph was built for
+  return 0;
+}
+static int build_kry_graph(nsgpu_ctx* ctx, int slot, OpCoef c, double* x, const double* b, bool aug) {
+  ctx->capturing = true; ctx->capture_nccl = false;
+  int rc = build_kry_graph_(ctx, slot, c, x, b, aug);
+  ctx->capturing = false;
+  if (rc == 0 && ctx->capture_nccl) rc = 1;   // several ranks without the peer map: NCCL all-reduces inside the iteration
+  if (rc > 0) {
+    cudaStreamCaptureStatus st = cudaStreamCaptureStatusNone;
+    cudaStreamIsCapturing(ctx->stream, &st);
+    if (st != cudaStreamCaptureStatusNone) { cudaGraph_t g = nullptr; cudaStreamEndCapture(ctx->stream, &g); }
+    cudaGetLastError();
+    SolveGraph& G = ctx->kgraph[slot];
+    if (G.exec) { cudaGraphExecDestroy(G.exec); G.exec = nullptr; }
+  }
+  return rc;
+}
+
+// BiCGStab with the stopping test on the device.  With graphs: one graph launch and one readback per (re)start; without (NSGPU_GRAPH=0,
+// several ranks, or a capture the driver refuses): the same kernels launched directly, the loop condition read back once per iteration.
+static int solve_bicgstab(nsgpu_ctx* ctx, int slot, OpCoef c, double** xp, double** xtp, const double* b, double rtol, SolveResult* out) {
+  (void)xtp;
+  const Level& L = ctx->levels[0];
+  double* x = *xp;
+  double* S = ctx->d_scal;
+  SolveCtl* ctl = ctx->d_ctl + slot;
   int rc;
   const bool aug = ctx->aug && c.op == 1;
   if ((rc = norm2_vec(ctx, L, b, S + 11))) return rc;
   if (aug && (rc = add_scaled_const(ctx, L, x, S + 46, 1.0 / (double)ctx->n_cells_global))) return rc;   // warm start: phi^n + the last mean(x)
-  if ((rc = residual_vec(ctx, L, c, x, b, r, S + 9))) return rc;
-  if (aug) {
-    if ((rc = aug_rank_one(ctx, L, x, r, -1.0, nullptr, S + 44))) return rc;
-    k_scalar_copy<<<1, 1, 0, ctx->stream>>>(S + 9, S + 45);
-    NS_LAUNCH_CHECK();
-  }
-  if ((rc = read_scalars(ctx, S + 9, 3, h))) return rc;
-  const double bn = std::sqrt(h[2]);
-  double rn = std::sqrt(h[0]);
-  out->cycles = 0;
-  if (bn == 0.0) { cudaMemsetAsync(x, 0, L.stride * sizeof(double), ctx->stream); out->rel = 0; out->converged = true; return 0; }
-  if (rn <= rtol * bn) { out->rel = rn / bn; out->converged = true; return 0; }
-  double* tmpA = ctx->tmp;   // ping-pong partner for the preconditioner's fine level
-  // The recurrence residual can drift from the true one.  After the recurrence says "converged" the true residual is recomputed; if
-  // it misses rtol the iteration restarts from the current x (r0 = r = true residual) -- at most MAX_RESTARTS times; a solve is
-  // reported as converged only when the TRUE residual meets rtol (the stopping rule stated in include/nsgpu.h).
+  if ((rc = bicg_true_residual(ctx, c, x, b, aug))) return rc;
+  k_kry_first<<<1, 1, 0, ctx->stream>>>(S, ctl, rtol * rtol, ctx->max_cycles);
+  NS_LAUNCH_CHECK();
+  // The recurrence residual can drift from the true one.  After the recurrence says "converged" the true residual is recomputed (into
+  // r: it is the restart vector if one is needed); if it misses rtol the iteration restarts from the current x (r0 = r = true residual)
+  // -- at most MAX_RESTARTS times; a solve is reported as converged only when the TRUE residual meets rtol (include/nsgpu.h).
   constexpr int MAX_RESTARTS = 3;
+  bool use_graph = ctx->use_graph != 0 && !ctx->kry_graph_off;
+  double bn = 0.0, rn = 0.0;
+  out->cycles = 0;
   for (int restart = 0;; restart++) {
-    cudaMemcpyAsync(r0, r, L.stride * sizeof(double), cudaMemcpyDeviceToDevice, ctx->stream);
-    cudaMemsetAsync(p, 0, L.stride * sizeof(double), ctx->stream);
-    cudaMemsetAsync(v, 0, L.stride * sizeof(double), ctx->stream);
-    const double init[4] = {rn * rn, 1.0, 1.0, 1.0};   // rho_new = (r0, r) = (r, r); rho_old = alpha = omega = 1
-    cudaMemcpyAsync(S, init, sizeof init, cudaMemcpyHostToDevice, ctx->stream);
-    cudaStreamSynchronize(ctx->stream);
-    while (out->cycles < ctx->max_cycles) {
-      k_bicg_p<<<blocks, 256, 0, ctx->stream>>>(n, r + off, p + off, v + off, S);
-      NS_LAUNCH_CHECK();
-      // ph = M^-1 p
-      { double *a = ph, *bq = tmpA; if ((rc = aug ? aug_precond(ctx, L, p, &a, &bq) : vcycle_any(ctx, c, &a, &bq, p, true))) return rc; ph = a; tmpA = bq; }
-      if (aug) {
-        if ((rc = apply_op(ctx, L, c, ph, v, nullptr, nullptr))) return rc;
-        if ((rc = aug_rank_one(ctx, L, ph, v, 1.0, r0, S + 4))) return rc;
-      } else if ((rc = apply_op(ctx, L, c, ph, v, r0, S + 4))) return rc;
-      k_scalar_div<<<1, 1, 0, ctx->stream>>>(S + 2, S + 0, S + 4);   // alpha = rho / (r0, v)
-      NS_LAUNCH_CHECK();
-      k_bicg_s<<<blocks, 256, 0, ctx->stream>>>(n, r + off, v + off, s + off, S + 2, ctx->red, S + 8);
-      NS_LAUNCH_CHECK();
-      if ((rc = allreduce(ctx, S + 8, 1, ncclSum))) return rc;
-      // sh = M^-1 s
-      { double *a = sh, *bq = tmpA; if ((rc = aug ? aug_precond(ctx, L, s, &a, &bq) : vcycle_any(ctx, c, &a, &bq, s, true))) return rc; sh = a; tmpA = bq; }
-      if (aug) {
-        if ((rc = apply_op(ctx, L, c, sh, t, nullptr, nullptr))) return rc;
-        if ((rc = aug_rank_one(ctx, L, sh, t, 1.0, s, S + 6))) return rc;
-      } else if ((rc = apply_op(ctx, L, c, sh, t, s, S + 6))) return rc;
-      k_scalar_div<<<1, 1, 0, ctx->stream>>>(S + 3, S + 6, S + 7);   // omega = (t,s)/(t,t)
-      NS_LAUNCH_CHECK();
-      k_scalar_copy<<<1, 1, 0, ctx->stream>>>(S + 1, S + 0);         // rho_old = rho_new
-      NS_LAUNCH_CHECK();
-      k_bicg_xr<<<blocks, 256, 0, ctx->stream>>>(n, x + off, ph + off, sh + off, r + off, s + off, t + off, r0 + off, S + 2, S + 3,
-                                                 ctx->red, S + 9);
-      NS_LAUNCH_CHECK();
-      if ((rc = allreduce(ctx, S + 9, 2, ncclSum))) return rc;
-      k_scalar_copy<<<1, 1, 0, ctx->stream>>>(S + 0, S + 10);        // rho_new = (r0, r)
-      NS_LAUNCH_CHECK();
-      out->cycles++;
-      if ((rc = read_scalars(ctx, S + 9, 1, h))) return rc;
-      rn = std::sqrt(h[0]);
-      if (!(rn == rn) || rn <= rtol * bn) break;
+    if (use_graph) {
+      SolveGraph& G = ctx->kgraph[slot];
+      const double key = (double)(c.op * 2 + (aug ? 1 : 0));
+      if (!G.exec || G.x != x || G.b != b || G.xt != ctx->tmp || G.rtol != key) {
+        rc = build_kry_graph(ctx, slot, c, x, b, aug);
+        if (rc < 0) return rc;
+        if (rc > 0) { use_graph = false; ctx->kry_graph_off = true; if (ctx->world == 1) ctx->graph_fallback = true; }
+      }
     }
-    // the true residual (into r: it is the restart vector if one is needed)
-    if ((rc = residual_vec(ctx, L, c, x, b, r, S + 9))) return rc;
-    if (aug) {
-      if ((rc = aug_rank_one(ctx, L, x, r, -1.0, nullptr, S + 44))) return rc;
-      k_scalar_copy<<<1, 1, 0, ctx->stream>>>(S + 9, S + 45);
-      NS_LAUNCH_CHECK();
+    const int cycles_before = out->cycles;
+    if (use_graph) {
+      SolveGraph& G = ctx->kgraph[slot];
+      cudaError_t e = cudaGraphLaunch(G.exec, ctx->stream);
+      if (e != cudaSuccess) { ctx->err = std::string("cudaGraphLaunch (Krylov solve): ") + cudaGetErrorString(e); return NSGPU_ERR_CUDA; }
+      ctx->launches += G.launches_fixed;
+    } else {
+      if ((rc = bicg_begin(ctx, ctl, 0ull))) return rc;
+      for (;;) {
+        k_publish_ctl<<<1, 1, 0, ctx->stream>>>(ctx->h_ctl + slot, ctl);
+        cudaError_t e = cudaGetLastError();
+        if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+        if (e != cudaSuccess) { ctx->err = std::string("ctl readback: ") + cudaGetErrorString(e); return NSGPU_ERR_CUDA; }
+        if (!ctx->h_ctl[slot].go) break;
+        if ((rc = bicg_iteration(ctx, c, x, aug, ctl))) return rc;
+      }
+      if ((rc = bicg_end(ctx, slot, c, x, b, aug))) return rc;
     }
-    if ((rc = read_scalars(ctx, S + 9, 1, h))) return rc;
-    rn = std::sqrt(h[0]);
+    {
+      cudaError_t e = cudaStreamSynchronize(ctx->stream);
+      if (e != cudaSuccess) { ctx->err = std::string("Krylov solve: ") + cudaGetErrorString(e); return NSGPU_ERR_CUDA; }
+    }
+    const SolveCtl& h = ctx->h_ctl[slot];
+    out->cycles = h.cycles;
+    if (use_graph) ctx->launches += (int64_t)(out->cycles - cycles_before) * ctx->kgraph[slot].launches_body;
+    bn = std::sqrt(h.bn2);
+    rn = std::sqrt(h.rn2);
+    if (!(h.bn2 > 0.0)) {   // KSPSolve returns x = 0 for b = 0
+      cudaMemsetAsync(x, 0, L.stride * sizeof(double), ctx->stream);
+      out->rel = 0; out->converged = true;
+      return 0;
+    }
+    if (restart == 0 && out->cycles == 0 && rn <= rtol * bn) { out->rel = rn / bn; out->converged = true; return 0; }   // the guess was the answer
     if (!(rn == rn) || rn <= rtol * bn || out->cycles >= ctx->max_cycles || restart >= MAX_RESTARTS) break;
     ctx->krylov_restarts++;
   }
-  ctx->kry[6] = ph; ctx->kry[7] = sh; ctx->tmp = tmpA;
   if (aug && (rc = vec_sum(ctx, L, x, S + 46))) return rc;   // mean(x) * n: next step's warm start (phase_phi removes it from phi)
   out->rel = rn / bn;
   out->converged = rn <= rtol * bn;
@@ -765,16 +914,6 @@ static int solve_tail(nsgpu_ctx* ctx, int slot, double* x) {
   NS_LAUNCH_CHECK();
   return 0;
 }
-
-#define NS_GRAPH_TRY(call)                                                                          \
-  do {                                                                                              \
-    cudaError_t e_ = (call);                                                                        \
-    if (e_ != cudaSuccess) {                                                                        \
-      fprintf(stderr, "nsgpu: %s -> %s; falling back to direct launches\n", #call, cudaGetErrorString(e_)); \
-      cudaGetLastError();                                                                           \
-      return 1;                                                                                     \
-    }                                                                                               \
-  } while (0)
 
 // Builds head -> WHILE(go){ V-cycle + residual norm } -> tail for (x, xt, b).  Returns 0 ok, 1 unsupported, < 0 error.
 static int build_solve_graph_(nsgpu_ctx* ctx, int slot, OpCoef c, double* x, double* xt, double* x0, const double* b, double rtol, bool bn2_pre);
@@ -951,7 +1090,7 @@ static int solve(nsgpu_ctx* ctx, int slot, OpCoef c, double** x, const double* b
     cudaError_t e = cudaMemcpyAsync(*x, x0, ctx->levels[0].stride * sizeof(double), cudaMemcpyDeviceToDevice, ctx->stream);
     if (e != cudaSuccess) { ctx->err = cudaGetErrorString(e); return NSGPU_ERR_CUDA; }
   }
-  if (krylov) return solve_bicgstab(ctx, c, x, &ctx->tmp, b, rtol, out);
+  if (krylov) return solve_bicgstab(ctx, slot, c, x, &ctx->tmp, b, rtol, out);
   return solve_mg(ctx, c, x, &ctx->tmp, b, rtol, out);
 }
 

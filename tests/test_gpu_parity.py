@@ -409,6 +409,20 @@ def test_two_gpus_equal_one_gpu(workdir):
     assert out.returncode == 0, out.stdout[-2000:] + out.stderr[-2000:]
 
 
+def test_two_gpus_equal_one_gpu_on_an_outflow_channel(workdir):
+    """The Krylov route on two x-slabs (inlet / walls / outflow channel 128 x 64: generic kernels, the bordered phi system, device-side
+    stopping test with the loop condition read back per iteration -- NCCL all-reduces keep it out of a graph) against one GPU: same
+    iteration counts, fields to 1e-6 (tools/mgpu_check.py ... channel)."""
+    import subprocess
+    import sys
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    out = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr", "127.0.0.1",
+                          "--master-port", "29534", f"{refapi.ROOT}/tools/mgpu_check.py", "64", "64", "4", "channel"], capture_output=True, text=True, timeout=600)
+    assert out.returncode == 0, out.stdout[-2000:] + out.stderr[-2000:]
+
+
 def run_main_on_gpus(ngpu, workdir, grid=None, steps=10):
     """bin/main <grid> <sim> with NSGPU_GPUS=ngpu in a fresh directory: (stdout, {csv name: text})."""
     import os

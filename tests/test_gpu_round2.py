@@ -227,6 +227,35 @@ def test_checkpoint_restart_on_krylov_routes(case, workdir, tmp_path):
         other.checkpoint_load(ck)
 
 
+@pytest.mark.parametrize("case", ["channel", "step", "cavity_stretched_64", "cavity_33"])
+def test_krylov_solves_as_graphs_equal_direct_launches(case, workdir):
+    """The Krylov route (outflow, masked, stretched, uncoarsenable grids) with its stopping test on the device: as one CUDA graph per
+    (re)start (begin -> WHILE { BiCGStab iteration } -> true residual) and with the same kernels launched directly, the loop condition read
+    back every iteration.  Same kernels in the same order: identical fields and iteration counts; the graph run must not have fallen back."""
+    if case == "cavity_33":
+        import navierstokessolver_b200 as ns
+        mk = lambda **kw: ns.GpuFluidSolver(ns.GridDesc.cavity(33), 0.25 / 33, 100.0, **kw)
+    else:
+        ref = refapi.RefSolver(f"{CASES}/{case}.grid", f"{CASES}/{case}.sim")
+        mk = lambda **kw: _gpu(ref, **kw)
+    a, b = mk(use_graph=0), mk(use_graph=-1)
+    t = {}
+    for name, s in (("graph", a), ("direct", b)):
+        s.step(2)
+        t0 = time.perf_counter()
+        info = s.step(4)
+        t[name] = (time.perf_counter() - t0) / 4 * 1e3
+        assert info.status == 0, (name, info.status)
+        t[name + "_it"] = (info.it_u, info.it_v, info.it_phi)
+        t[name + "_flags"] = info.flags
+    print(f"\n{case}: ms/step graph {t['graph']:.2f}, direct {t['direct']:.2f}; iterations {t['graph_it']}; flags {t['graph_flags']}")
+    assert t["graph_it"] == t["direct_it"]
+    assert t["graph_flags"] & 2, "phi is expected on the Krylov route here"
+    assert not (t["graph_flags"] & 1), "the graph run fell back to direct launches"
+    for k in (U, V, PHI):
+        assert np.array_equal(a.get(k), b.get(k)), k
+
+
 def test_export_snapshot_matches_synchronous_downloads(workdir):
     """nsgpu_export_begin / _wait (pressure recovery on the device, FS.cpp:577-581): the snapshot equals the fields downloaded at the same
     step even though the time loop has moved on, Pr = phi - dt/(2Re) lapPhi exactly, lapPhi = LHS_phi phi (operator rows, Tier A), two
