@@ -804,7 +804,8 @@ static int solve_bicgstab(nsgpu_ctx* ctx, int slot, OpCoef c, double** xp, doubl
   // r: it is the restart vector if one is needed); if it misses rtol the iteration restarts from the current x (r0 = r = true residual)
   // -- at most MAX_RESTARTS times; a solve is reported as converged only when the TRUE residual meets rtol (include/nsgpu.h).
   constexpr int MAX_RESTARTS = 3;
-  bool use_graph = ctx->use_graph != 0 && !ctx->kry_graph_off;
+  // (several ranks: the all-reduces and halo exchanges of this route are NCCL calls -- no capture is attempted, the loop condition is read back)
+  bool use_graph = ctx->use_graph != 0 && ctx->world == 1 && !ctx->kry_graph_off;
   double bn = 0.0, rn = 0.0;
   out->cycles = 0;
   for (int restart = 0;; restart++) {
