@@ -155,13 +155,14 @@ static inline bool march_level_ok(const nsgpu_ctx* ctx, const Level& L, OpCoef c
 typedef void (*MarchKernel)(LevelGeom, const double*, const double*, const double*, const double*, double*, int, MarchXfer);
 
 // CTAs of `kern` that fit on the GPU at once (one wave), cached per kernel
-static int march_wave(MarchKernel kern) {
+static int march_wave(MarchKernel kern, size_t smem = 4096) {
   static thread_local std::vector<std::pair<MarchKernel, int>> cache;   // (per host thread: one thread drives one GPU)
   for (auto& e : cache) if (e.first == kern) return e.second;
   int per_sm = 0, dev = 0, sms = 148;
   cudaGetDevice(&dev);
   cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, MARCH_THREADS, 4096) != cudaSuccess || per_sm < 1) per_sm = 2;
+  if (smem > 48 * 1024) cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024);   // ring kernels (ns_march_ring.cuh)
+  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, MARCH_THREADS, smem) != cudaSuccess || per_sm < 1) per_sm = 2;
   cache.push_back({kern, per_sm * sms});
   return per_sm * sms;
 }
@@ -237,10 +238,20 @@ static int march_pass(nsgpu_ctx* ctx, const Level& L, OpCoef c, int nsw, double*
   else { if (Cp) NS_MARCH_RES(2, true); else NS_MARCH_RES(2, false); }
 #undef NS_MARCH_RES
 #undef NS_MARCH
+  // one rank, no transfer from below: the columns of x and b through the shared-memory ring (bulk copies) instead of the register ring
+  bool ring = false;
+  if (ctx->march_ring && !push && nsw == 2 && !Cp && L.g.nx >= 64) {
+    ring = true;
+    if (omega > 0.0 && res == 2) kern = k_march_ring<2, false, 2, true>;
+    else if (omega > 0.0) ring = false;                                   // the plain SOR double sweep is at its roofline already
+    else if (res == 1) kern = k_march_ring<2, false, 1, false>;
+    else if (res == 2) kern = k_march_ring<2, false, 2, false>;
+    else ring = false;
+  }
   // Several ranks: the first and the last chunk of the slab run the pushing loop (march_run<..., true>), which costs about 1.5 x the
   // plain loop per column; every other chunk runs the plain one.  The two boundary chunks are therefore made SHORTER, so that all CTAs
   // of the launch take the same time: rb columns with 1.5 (rb + ovh) = ri + ovh, the interior shared evenly between the other rows.
-  const int ovh = 2 * lead + 2 * nsw + 2, wave = march_wave(kern);
+  const int ovh = 2 * lead + 2 * nsw + 2, wave = march_wave(kern, ring ? march_ring_smem(256, nsw, res) : 4096);
   int rb = 0, ri = march_chunk(ctx, L, uj, ovh, wave, 0);
   if (push && ctx->march_rb != 0 && !(L.g.nx & 1) && L.g.nx >= ctx->march_rb_min_nx && !(Cr && Cr->replicated && !selfpush)) {
     const int rows = (L.g.nx + ri - 1) / ri, rb_min = 2 * (HX - 1);   // >= the push zone of a restricting pass
@@ -263,7 +274,7 @@ static int march_pass(nsgpu_ctx* ctx, const Level& L, OpCoef c, int nsw, double*
   }
   dim3 grid(((L.g.ny + uj - 1) / uj + MARCH_WARPS - 1) / MARCH_WARPS, (L.g.nx + ri - 1) / ri);
   if (rb) grid.y = 2 + (unsigned)((L.g.nx - 2 * rb + ri - 1) / ri);
-  const size_t sh = (size_t)3 * (std::max(ri, rb) + 2 * lead + 2 * nsw + 8) * sizeof(double);   // >= nrows of k_march
+  const size_t sh = ring ? march_ring_smem(ri, nsw, res) : (size_t)3 * (std::max(ri, rb) + 2 * lead + 2 * nsw + 8) * sizeof(double);   // >= nrows of k_march
   const bool gather = push && !selfpush && Cr && Cr->replicated;   // the slab of the replicated coarse right-hand side goes to every rank
   if (push) {
     const long long offL = ctx->peerL ? (long long)((ctx->peerL - ctx->arena) / (ptrdiff_t)sizeof(double)) : 0;

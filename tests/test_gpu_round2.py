@@ -376,3 +376,22 @@ def test_projection_kernels_random_fields_repeatable(ny, nx, workdir, monkeypatc
     for a, b in zip(out["1"][:5], out["0"][:5]):
         assert np.abs(a - b).max() <= 1e-13 * np.abs(b).max()
     assert out["1"][5] == out["0"][5]
+
+
+@pytest.mark.parametrize("ny,nx", [(256, 256), (200, 130), (1000, 1024), (2048, 2048)])
+def test_ring_march_equals_register_march(ny, nx, workdir, monkeypatch):
+    """ns_march_ring.cuh (columns of x and b through a per-warp shared-memory ring filled by bulk copies) against ns_march.cuh (register
+    ring): same arithmetic in the same order -- identical fields and iteration counts after whole time steps, on even, odd and ragged sizes
+    (strips that end inside a warp, warps wholly past the last row)."""
+    import navierstokessolver_b200 as ns
+    out = {}
+    for mode in ("0", "1"):
+        monkeypatch.setenv("NSGPU_MARCH_RING", mode)
+        s = ns.GpuFluidSolver(ns.GridDesc.cavity(ny, nx=nx, lx=nx / float(ny)), 0.25 / ny, 1000.0)
+        info = s.step(4)
+        assert info.status == 0
+        out[mode] = ((info.it_u, info.it_v, info.it_phi), {k: s.get(k) for k in (U, V, PHI)})
+        s.close()
+    assert out["0"][0] == out["1"][0]
+    for k in (U, V, PHI):
+        assert np.array_equal(out["0"][1][k], out["1"][1][k]), k
