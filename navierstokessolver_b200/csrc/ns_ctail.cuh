@@ -22,7 +22,7 @@ namespace nsgpu {
 
 namespace cg = cooperative_groups;
 
-constexpr int CT_C = 8;                  // CTAs per cluster (the portable maximum)
+constexpr int CT_C = 8;                  // CTAs per cluster: the portable maximum (NSGPU_CTAIL_C=16: non-portable size, with NSGPU_CTAIL_CELLS=65536 the tail starts at 256 x 256)
 constexpr int CT_THREADS = 512;
 constexpr int CT_MAX_LEVELS = 12;
 constexpr int CT_KC = 4;                 // cells of one colour per thread, at most
@@ -67,7 +67,7 @@ __device__ void ct_smooth(cg::cluster_group& cl, const CtLevel& L, double* sm, i
   const int hny = (L.ny + 1) >> 1, n = nc * hny, p = L.ny + 2;
   // neighbours' copies of x (distributed shared memory): my first column is the left neighbour's right halo and vice versa
   double* xl = (L.dist && r > 0) ? cl.map_shared_rank(x, r - 1) : nullptr;
-  double* xr = (L.dist && r < CT_C - 1) ? cl.map_shared_rank(x, r + 1) : nullptr;
+  double* xr = (L.dist && r < (int)cl.num_blocks() - 1) ? cl.map_shared_rank(x, r + 1) : nullptr;
   int ci[CT_KC], cjj[CT_KC];
 #pragma unroll
   for (int k = 0; k < CT_KC; k++) {

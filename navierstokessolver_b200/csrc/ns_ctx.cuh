@@ -132,6 +132,7 @@ struct nsgpu_ctx {
   int rhs_march = 1;                             // ConstructRHS_V on rectangles through k_rhs_march (NSGPU_RHS_MARCH=0: cell kernel)
   int vel_guess_rhs = 0;                         // initial guess of the u*, v* solves: 0 = u^n, v^n; 1 = the right-hand side (LHS_V = I - dt/(2Re) L is close to I)
   int march_rb_min_nx = 0;                       // levels with fewer columns keep uniform chunks (NSGPU_RB_MINNX)
+  int ctail_c = 8;                               // CTAs of the cluster that runs the coarse tail (NSGPU_CTAIL_C)
   int march_ring = 0;                            // fused passes without peer stores through the shared-memory ring kernels (NSGPU_MARCH_RING)
   int stamp_key = -1;                            // stamps builds: trace key of the marching pass whose CTA stamps are kept (NSGPU_STAMP_KEY; -2: every pass)
   int field_skew = 0, alloc_k = 0;               // dev_zeros: the k-th large array starts k x field_skew bytes later (NSGPU_FIELD_SKEW)

@@ -356,6 +356,9 @@ static int create_impl(nsgpu_ctx* ctx, const nsgpu_grid* G, const nsgpu_params* 
   if (ctx->use_ctail && ctx->rect && (ctx->world == 1 || plan.rep_start > 0)) {
     long long first_cells = CT_FIRST_CELLS;
     if (const char* e = getenv("NSGPU_CTAIL_CELLS")) first_cells = atoll(e);
+    int C = CT_C;
+    if (const char* e = getenv("NSGPU_CTAIL_C")) C = atoi(e) == 16 ? 16 : CT_C;
+    ctx->ctail_c = C;
     const int nl = (int)ctx->levels.size();
     int ts = 0;
     for (int l = 1; l < nl; l++)
@@ -380,9 +383,9 @@ static int create_impl(nsgpu_ctx* ctx, const nsgpu_grid* G, const nsgpu_params* 
         t.mcx = L.mcx[op]; t.mcy = L.mcy[op];
         // a level stays distributed while its columns split evenly and every coarse column has both children in one CTA
         const bool last = k == T.nlev - 1;
-        dist = dist && t.nx % CT_C == 0 && (last || t.cx == 1 || (t.nx / CT_C) % 2 == 0);
+        dist = dist && t.nx % C == 0 && (last || t.cx == 1 || (t.nx / C) % 2 == 0);
         t.dist = dist ? 1 : 0;
-        t.nc = dist ? t.nx / CT_C : t.nx;
+        t.nc = dist ? t.nx / C : t.nx;
         if ((long long)t.nc * ((t.ny + 1) / 2) > (long long)CT_KC * CT_THREADS) ok = false;
         t.xoff = off; off += (t.nc + 2) * (t.ny + 2);
         t.boff = off; off += t.nc * t.ny;
@@ -397,12 +400,27 @@ static int create_impl(nsgpu_ctx* ctx, const nsgpu_grid* G, const nsgpu_params* 
     if (ok) {
       const size_t bytes = (size_t)ctx->ctail[0].smem_doubles * sizeof(double);
       ok = cudaFuncSetAttribute(k_cluster_tail, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes) == cudaSuccess;
+      if (ok && C > 8) {   // a cluster of 16 CTAs is a non-portable size: allowed explicitly, and checked against what the GPU can co-schedule
+        ok = cudaFuncSetAttribute(k_cluster_tail, cudaFuncAttributeNonPortableClusterSizeAllowed, 1) == cudaSuccess;
+        if (ok) {
+          cudaLaunchConfig_t cfg = {};
+          cfg.gridDim = dim3(C); cfg.blockDim = dim3(CT_THREADS); cfg.dynamicSmemBytes = bytes;
+          cudaLaunchAttribute at[1];
+          at[0].id = cudaLaunchAttributeClusterDimension;
+          at[0].val.clusterDim.x = C; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+          cfg.attrs = at; cfg.numAttrs = 1;
+          int nclusters = 0;
+          ok = cudaOccupancyMaxActiveClusters(&nclusters, k_cluster_tail, &cfg) == cudaSuccess && nclusters >= 1;
+        }
+        if (!ok) fprintf(stderr, "nsgpu: a 16-CTA cluster cannot be scheduled here; coarse tail without clusters\n");
+        cudaGetLastError();
+      }
       for (int op = 0; op < 2 && ok; op++) {
         void* q = nullptr;
-        NS_CUDA(cudaMalloc(&q, bytes * CT_C));
+        NS_CUDA(cudaMalloc(&q, bytes * C));
         ctx->owned.push_back(q);
         ctx->ctail_img[op] = (double*)q;
-        k_ctail_image<<<CT_C, CT_THREADS, 0, ctx->stream>>>(ctx->ctail[op], ctx->ctail_img[op]);
+        k_ctail_image<<<C, CT_THREADS, 0, ctx->stream>>>(ctx->ctail[op], ctx->ctail_img[op]);
         NS_CUDA(cudaGetLastError());
       }
       cudaGetLastError();

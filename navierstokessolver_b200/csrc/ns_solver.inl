@@ -351,12 +351,12 @@ static int vcycle_fused(nsgpu_ctx* ctx, int l, OpCoef c, double** x, double** xt
   if (ctx->ctail_start > 0 && l == ctx->ctail_start && march_tab_ok(L, c)) {   // the rest of the cycle in one kernel on a cluster of CT_C CTAs
     const CtDesc& T = ctx->ctail[op_tab(c)];
     cudaLaunchConfig_t cfg = {};
-    cfg.gridDim = dim3(CT_C); cfg.blockDim = dim3(CT_THREADS);
+    cfg.gridDim = dim3(ctx->ctail_c); cfg.blockDim = dim3(CT_THREADS);
     cfg.dynamicSmemBytes = (size_t)T.smem_doubles * sizeof(double);
     cfg.stream = ctx->stream;
     cudaLaunchAttribute at[1];
     at[0].id = cudaLaunchAttributeClusterDimension;
-    at[0].val.clusterDim.x = CT_C; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+    at[0].val.clusterDim.x = ctx->ctail_c; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
     cfg.attrs = at; cfg.numAttrs = 1;
     trace_begin(ctx, 99998);
     cudaError_t e = cudaLaunchKernelEx(&cfg, k_cluster_tail, T, (const double*)ctx->ctail_img[op_tab(c)], b, *x, ctx->tail_dbg);

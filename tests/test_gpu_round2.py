@@ -395,3 +395,24 @@ def test_ring_march_equals_register_march(ny, nx, workdir, monkeypatch):
     assert out["0"][0] == out["1"][0]
     for k in (U, V, PHI):
         assert np.array_equal(out["0"][1][k], out["1"][1][k]), k
+
+
+def test_cluster_tail_of_16_ctas(workdir, monkeypatch):
+    """NSGPU_CTAIL_C=16 + NSGPU_CTAIL_CELLS=65536: the coarse tail starts at 256 x 256 on a (non-portable) cluster of 16 CTAs instead of at
+    128 x 128 on 8.  Same algorithm, another order of the same sums nowhere: the levels a cluster holds are smoothed in shared memory instead of
+    by marching passes -- the fields agree to rounding and the iteration counts are equal.  Skips when the GPU cannot schedule 16-CTA clusters."""
+    import navierstokessolver_b200 as ns
+    out = {}
+    for mode in ("8", "16"):
+        if mode == "16":
+            monkeypatch.setenv("NSGPU_CTAIL_C", "16")
+            monkeypatch.setenv("NSGPU_CTAIL_CELLS", "65536")
+        s = ns.GpuFluidSolver(ns.GridDesc.cavity(1024), 0.25 / 1024, 1000.0)
+        info = s.step(4)
+        assert info.status == 0
+        out[mode] = ((info.it_u, info.it_v, info.it_phi), {k: s.get(k) for k in (U, V, PHI)}, info.ms_total / 4)
+        s.close()
+    print("\nms/step: 8-CTA tail from 128^2", round(out["8"][2], 3), " 16-CTA tail from 256^2", round(out["16"][2], 3))
+    assert out["8"][0] == out["16"][0]
+    for k in (U, V, PHI):
+        assert _rel(out["16"][1][k], out["8"][1][k]) <= 1e-9, k
