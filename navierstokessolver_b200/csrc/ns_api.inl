@@ -568,6 +568,11 @@ int nsgpu_time_passes(nsgpu_ctx* ctx, int32_t kind, int32_t n, float* ms) {
   if ((rc = halo_exchange(ctx, L, const_cast<double*>(b), HX - 1))) return rc;
   if ((rc = halo_exchange(ctx, L, *x, HX - 1))) return rc;
   ctx->halo_w[*x] = std::min(HX - 1, L.g.nx);
+  if (kind == 2) {   // inside a cycle the level-1 pass has pushed the halo of the coarse correction: exchange it once, outside the timed launches
+    const Level& C = ctx->levels[1];
+    if ((rc = halo_exchange(ctx, C, C.x, HX - 1))) return rc;
+    ctx->halo_w[C.x] = std::min(HX - 1, C.g.nx);
+  }
   NS_CUDA(cudaEventRecord(ctx->ev0, ctx->stream));
   for (int k = 0; k < n; k++) {
     if (kind == 1) rc = march_pass(ctx, L, c, 2, *x, b, ctx->tmp, nullptr, nullptr, &ctx->levels[1], nullptr, nullptr);
