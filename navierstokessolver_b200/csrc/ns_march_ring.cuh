@@ -1,10 +1,12 @@
-// ns_march_ring.cuh -- the fused marching passes of ns_march.cuh with the columns of x and b arriving through a ring of column
-// slots in SHARED memory (one ring per CTA, shared by its four warps), filled by bulk asynchronous copies (TMA engine, cp.async.bulk + mbarrier: ns_tma.cuh) instead of a register
-// prefetch ring.
+// ns_march_ring.cuh -- the fused marching passes of ns_march.cuh with the columns of x and b arriving through a ring of column slots in
+// SHARED memory (one ring per CTA, shared by its four warps), filled by bulk asynchronous copies (TMA engine, cp.async.bulk + mbarrier:
+// ns_tma.cuh) instead of a register prefetch ring.  AN EXPERIMENT, off by default (NSGPU_MARCH_RING=1): it gives the same bits as k_march
+// and is slower -- 126 us against 91 us for the first pass of a cycle at 4096^2, because it executes 83 M warp instructions instead of
+// 49 M (slot arithmetic, six LDS per step, barriers, the producer's turn) and the pass is issue-bound, not bandwidth-bound.
 //
 // Why.  k_march<2, *, 1|2> carries x AND b of ten columns in registers (three of them only to cover the load latency, b through all five
 // stages that use it): 80 of its 156-168 registers, three CTAs of four warps per SM, 12 warps -- ncu: issue slots 50 % busy, 2.9 warps per
-// scheduler, stalls `wait` 1.95 and `long_scoreboard` 1.17 per issue, 71 % of the HBM peak (profiles/r2_down_key.txt).  Here a column of b
+// scheduler, stalls `wait` 1.95 and `long_scoreboard` 1.17 per issue, 71 % of the HBM peak (profiles/r2_zz_down_ncu_key.txt).  Here a column of b
 // is read from its slot by each of the five stages that need it (one LDS.128 each), x is read once when the column enters the working
 // set; a slot is free again once all four warps have left it (an `empty` mbarrier per slot, one arrival per warp) and is refilled, two steps
 // later, with the column AHEAD steps in front, so the prefetch distance is a shared-memory budget (MR_D slots of 3.5 KB per CTA), not a
