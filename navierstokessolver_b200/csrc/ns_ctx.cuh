@@ -49,6 +49,7 @@ struct SolveGraph {
   double rtol = 0;
   int launches_fixed = 0, launches_body = 0;                 // kernels outside / inside the loop body
   int head_iterations = 0;                                   // iterations the head runs itself (counted in launches_fixed)
+  int k0 = 1;                                                // ... of which the first k0 - 1 carry no stopping test
 };
 
 }  // namespace nsgpu
@@ -106,6 +107,9 @@ struct nsgpu_ctx {
   nsgpu::SolveGraph sgraph[3];
   nsgpu::SolveGraph kgraph[3];            // Krylov solves (BiCGStab): begin -> WHILE { iteration } -> true residual; x0 holds the operator / aug key
   int graph_cycles_pending[3] = {0, 0, 0};
+  // Stopping tests that cannot succeed are not run: a velocity solve that took n iterations in the last time step runs its first n - 1
+  // without the residual reduction (the iterate does not depend on the test; NSGPU_SKIP_CHECKS=0: test after every iteration)
+  int skip_checks = 1, solve_k0[3] = {1, 1, 1}, solve_hist[3][4] = {}, solve_hist_n[3] = {0, 0, 0};
   // several ranks: every buffer a marching pass writes lives in one arena, mapped by the two neighbours through CUDA IPC,
   // so that the pass can store its boundary columns straight into their halo columns (ns_march.cuh)
   char* arena = nullptr;                 // device allocation (owned)

@@ -368,9 +368,11 @@ struct CtlEpilogue {
 
 // ctl <- start of a solve: cycles0 = -1 when the first residual reduction is the initial guess' (it brings it to 0),
 // 0 when it already closes the first iteration
-__global__ void k_ctl_init(SolveCtl* c, double tol2, int max_cycles, unsigned long long handle, int cycles0, const double* bn2_src) {
+// skipped: iterations the head runs without a stopping test before the first tested one (they count as cycles)
+__global__ void k_ctl_init(SolveCtl* c, double tol2, int max_cycles, unsigned long long handle, int cycles0, const double* bn2_src, int skipped) {
   if (bn2_src) c->bn2 = *bn2_src;   // |b|^2 came out of the kernel that wrote b
   c->tol2 = tol2; c->max_cycles = max_cycles; c->cycles = cycles0; c->go = 0; c->zero_rhs = 0; c->handle = handle; c->rn2 = 0.0;
+  c->total_cycles += skipped;
 }
 // x <- 0 when the right-hand side was identically zero (KSPSolve returns x = 0 for b = 0)
 // Also publishes the control block to the host: `pub` is page-locked host memory mapped into the device's address space, written by

@@ -184,6 +184,7 @@ static int create_impl(nsgpu_ctx* ctx, const nsgpu_grid* G, const nsgpu_params* 
   if (const char* e = getenv("NSGPU_RB")) ctx->march_rb = atoi(e);
   if (const char* e = getenv("NSGPU_XRED_DBG")) { const int v = atoi(e); cudaMemcpyToSymbol(g_ns_xdbg, &v, sizeof v); }   // 1: reduction tails, 2: CTA stamps
   if (const char* e = getenv("NSGPU_MARCH_RING")) ctx->march_ring = atoi(e);
+  if (const char* e = getenv("NSGPU_SKIP_CHECKS")) ctx->skip_checks = atoi(e);
   if (const char* e = getenv("NSGPU_STAMP_KEY")) ctx->stamp_key = atoi(e);
   else if (getenv("NSGPU_XRED_DBG") && (atoi(getenv("NSGPU_XRED_DBG")) & 2)) ctx->stamp_key = -2;
   if (const char* e = getenv("NSGPU_FIELD_SKEW")) ctx->field_skew = (atoi(e) + 255) & ~255;
